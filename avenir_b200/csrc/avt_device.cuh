@@ -1,0 +1,64 @@
+// Device-side building blocks shared by the kernels of libavenir_tree.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/avenir_tree.h"
+#include "fdlibm_log.cuh"
+
+namespace avt {
+
+constexpr int kMaxC = AVT_MAX_CLASSES;
+constexpr int kMaxSeg = AVT_MAX_SEG;
+
+// 128-bit streaming load that does not allocate in L1 (each column byte is used once per pass).
+__device__ __forceinline__ uint4 ld_stream(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ uint32_t u4_word(const uint4& v, int i) {
+    return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w;
+}
+// j-th byte (0..15) of a 16-byte vector
+__device__ __forceinline__ uint32_t u4_byte(const uint4& v, int j) {
+    return (u4_word(v, j >> 2) >> ((j & 3) * 8)) & 0xFFu;
+}
+// j-th halfword (0..7)
+__device__ __forceinline__ uint32_t u4_half(const uint4& v, int j) {
+    return (u4_word(v, j >> 1) >> ((j & 1) * 16)) & 0xFFFFu;
+}
+
+// Impurity of one class-count vector, evaluated exactly as InfoContentStat.processStat
+// (util/InfoContentStat.java:71-101): classes with zero count do not exist,
+// terms are accumulated in `order`, every operation is a single IEEE rounding (no FMA).
+__device__ __forceinline__ double impurity(const uint32_t* cnt, int C, const uint8_t* order,
+                                           int criterion, uint32_t total) {
+    if (total == 0) return 0.0;
+    const double tot = (double)total;
+    if (criterion == AVT_CRIT_ENTROPY) {
+        const double log2v = 0.6931471805599453;  // StrictMath.log(2)
+        double stat = 0.0;
+        for (int i = 0; i < C; ++i) {
+            uint32_t c = cnt[order[i]];
+            if (c == 0) continue;
+            double pr = __ddiv_rn((double)c, tot);
+            double t = __ddiv_rn(__dmul_rn(pr, strict_log(pr)), log2v);
+            stat = __dsub_rn(stat, t);
+        }
+        return stat;
+    }
+    double prsq = 0.0;
+    for (int i = 0; i < C; ++i) {
+        uint32_t c = cnt[order[i]];
+        if (c == 0) continue;
+        double pr = __ddiv_rn((double)c, tot);
+        prsq = __dadd_rn(prsq, __dmul_rn(pr, pr));
+    }
+    return __dsub_rn(1.0, prsq);
+}
+
+}  // namespace avt

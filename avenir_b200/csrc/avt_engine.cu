@@ -1,0 +1,739 @@
+// libavenir_tree.so -- kernel-level C-ABI (include/avenir_tree.h) on top of the sm_100a kernels.
+// Plain CUDA runtime + NCCL; no torch types anywhere.  There is no CPU path: every entry point needs
+// a CUDA device and fails with AVT_E_CUDA when there is none.
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "avt_kernels.cuh"
+
+using namespace avt;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+constexpr int kSmCountFallback = 148;
+constexpr size_t kMaxDynSmem = 227 * 1024;        // B200: 227 KB of shared memory per CTA
+constexpr int kHistWordsBudget = 220 * 1024 / 4;  // shared-memory words one histogram block may use
+
+struct TimerSlot {
+    cudaEvent_t a, b;
+    double* acc;
+};
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = n + n / 4 + 64;
+        cudaError_t e = cudaMalloc((void**)&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+}  // namespace
+
+struct avt_engine {
+    int device = 0;
+    int sm_count = kSmCountFallback;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    // data set
+    long long N = 0, Npad = 0;
+    int A = 0, C = 0, TB = 0;
+    std::vector<int> n_bins, bin_off, wide;
+    std::vector<void*> cols;
+    DevBuf<void*> d_colptrs;
+    DevBuf<uint8_t> d_cls;
+    DevBuf<int32_t> d_bin_off, d_wide;
+    // forest
+    int T = 0;
+    bool any_w = false;
+    DevBuf<uint16_t> d_nid;
+    DevBuf<uint8_t> d_w, d_has_w;
+    // frontier
+    std::vector<int> node_base;
+    int NF = 0;
+    bool hist_valid = false, scan_valid = false;
+    DevBuf<int32_t> d_node_base;
+    DevBuf<uint32_t> d_H;
+    // histogram group tables
+    DevBuf<int32_t> d_grp;  // packed int tables
+    // splits
+    int S = 0;
+    std::vector<avt_split> splits;
+    DevBuf<avt_split> d_splits;
+    DevBuf<int32_t> d_bounds, d_attr_first;
+    DevBuf<uint8_t> d_seg_lut;
+    // scan
+    DevBuf<double> d_av;
+    DevBuf<avt_node_best> d_best;
+    DevBuf<uint32_t> d_mask;
+    DevBuf<uint8_t> d_order;
+    DevBuf<int32_t> d_pairs;
+    DevBuf<avt_split_eval> d_eval;
+    DevBuf<avt_cpg_stat> d_cpg;
+    DevBuf<uint32_t> d_ccnt;
+    DevBuf<int32_t> d_node_attr;
+    DevBuf<uint16_t> d_lut;
+    // timing
+    std::vector<TimerSlot> pending;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> free_events;
+    cudaEvent_t tev0 = nullptr, tev1 = nullptr;
+    avt_stats stats{};
+    int force_variant = -1;
+    // comm
+    ncclComm_t comm = nullptr;
+    int n_ranks = 1, rank = 0;
+};
+
+namespace {
+
+int fail(avt_engine* e, int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (e) e->err = buf;
+    else g_create_error = buf;
+    return code;
+}
+
+#define CUDA_TRY(e, call)                                                                      \
+    do {                                                                                       \
+        cudaError_t _st = (call);                                                              \
+        if (_st != cudaSuccess)                                                                \
+            return fail((e), AVT_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_st), \
+                        __FILE__, __LINE__);                                                   \
+    } while (0)
+
+#define NCCL_TRY(e, call)                                                                      \
+    do {                                                                                       \
+        ncclResult_t _st = (call);                                                             \
+        if (_st != ncclSuccess)                                                                \
+            return fail((e), AVT_E_COMM, "%s failed: %s (%s:%d)", #call, ncclGetErrorString(_st), \
+                        __FILE__, __LINE__);                                                   \
+    } while (0)
+
+int use_device(avt_engine* e) {
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    return AVT_OK;
+}
+
+// device timing: events around a launch, resolved at the next synchronisation point
+int timer_open(avt_engine* e, double* acc, TimerSlot* slot) {
+    if (e->free_events.empty()) {
+        cudaEvent_t a, b;
+        CUDA_TRY(e, cudaEventCreate(&a));
+        CUDA_TRY(e, cudaEventCreate(&b));
+        e->free_events.push_back({a, b});
+    }
+    auto ev = e->free_events.back();
+    e->free_events.pop_back();
+    slot->a = ev.first;
+    slot->b = ev.second;
+    slot->acc = acc;
+    CUDA_TRY(e, cudaEventRecord(slot->a, e->stream));
+    return AVT_OK;
+}
+int timer_close(avt_engine* e, const TimerSlot& slot) {
+    CUDA_TRY(e, cudaEventRecord(slot.b, e->stream));
+    e->pending.push_back(slot);
+    return AVT_OK;
+}
+int sync_and_resolve(avt_engine* e) {
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    for (auto& s : e->pending) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess) *s.acc += ms;
+        e->free_events.push_back({s.a, s.b});
+    }
+    e->pending.clear();
+    return AVT_OK;
+}
+
+template <class T>
+int upload(avt_engine* e, DevBuf<T>& buf, const T* host, size_t n) {
+    CUDA_TRY(e, buf.ensure(n ? n : 1));
+    if (n) CUDA_TRY(e, cudaMemcpyAsync(buf.p, host, n * sizeof(T), cudaMemcpyHostToDevice, e->stream));
+    return AVT_OK;
+}
+
+SplitTable make_table(avt_engine* e) {
+    SplitTable st;
+    st.splits = e->d_splits.p;
+    st.bounds = e->d_bounds.p;
+    st.seg_lut = e->d_seg_lut.p;
+    st.attr_first = e->d_attr_first.p;
+    st.bin_off = e->d_bin_off.p;
+    st.S = e->S;
+    st.A = e->A;
+    st.TB = e->TB;
+    st.C = e->C;
+    return st;
+}
+
+int upload_order(avt_engine* e, const uint8_t* class_order) {
+    uint8_t ord[AVT_MAX_CLASSES];
+    bool seen[AVT_MAX_CLASSES] = {false};
+    for (int i = 0; i < e->C; ++i) {
+        ord[i] = class_order ? class_order[i] : (uint8_t)i;
+        if (ord[i] >= e->C || seen[ord[i]]) return fail(e, AVT_E_INVALID, "class_order is not a permutation of 0..%d", e->C - 1);
+        seen[ord[i]] = true;
+    }
+    return upload(e, e->d_order, ord, (size_t)e->C);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* avt_last_error(const avt_engine* e) { return e ? e->err.c_str() : g_create_error.c_str(); }
+
+int avt_create(int device, avt_engine** out) {
+    if (!out) return fail(nullptr, AVT_E_INVALID, "avt_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t st = cudaGetDeviceCount(&count);
+    if (st != cudaSuccess || count == 0)
+        return fail(nullptr, AVT_E_CUDA, "avt_create: no CUDA device (%s); libavenir_tree has no CPU path",
+                    st == cudaSuccess ? "device count is 0" : cudaGetErrorString(st));
+    if (device < 0 || device >= count) return fail(nullptr, AVT_E_INVALID, "avt_create: device %d out of range [0,%d)", device, count);
+    avt_engine* e = new avt_engine();
+    e->device = device;
+    st = cudaSetDevice(device);
+    if (st == cudaSuccess) st = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    if (st == cudaSuccess) st = cudaEventCreate(&e->tev0);
+    if (st == cudaSuccess) st = cudaEventCreate(&e->tev1);
+    cudaDeviceProp prop;
+    if (st == cudaSuccess) st = cudaGetDeviceProperties(&prop, device);
+    if (st == cudaSuccess) {
+        e->sm_count = prop.multiProcessorCount;
+        if (prop.major < 10) {
+            delete e;
+            return fail(nullptr, AVT_E_CUDA, "avt_create: device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
+        }
+    }
+    if (st == cudaSuccess) st = cudaFuncSetAttribute(hist_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    if (st == cudaSuccess) st = cudaFuncSetAttribute(hist_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    if (st != cudaSuccess) {
+        int rc = fail(nullptr, AVT_E_CUDA, "avt_create: %s", cudaGetErrorString(st));
+        delete e;
+        return rc;
+    }
+    *out = e;
+    return AVT_OK;
+}
+
+void avt_destroy(avt_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->comm) ncclCommDestroy(e->comm);
+    for (void* c : e->cols)
+        if (c) cudaFree(c);
+    e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
+    e->d_nid.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
+    e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
+    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_av.release(); e->d_best.release();
+    e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
+    e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release();
+    for (auto& s : e->pending) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
+    for (auto& p : e->free_events) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+    if (e->tev0) cudaEventDestroy(e->tev0);
+    if (e->tev1) cudaEventDestroy(e->tev1);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins,
+                     const void* const* columns, const uint8_t* class_codes, int32_t n_classes) {
+    if (!e) return AVT_E_INVALID;
+    if (n_rows <= 0 || n_attrs <= 0 || !n_bins || !columns || !class_codes)
+        return fail(e, AVT_E_INVALID, "avt_dataset_load: empty data set or NULL argument");
+    if (n_classes < 1 || n_classes > AVT_MAX_CLASSES)
+        return fail(e, AVT_E_INVALID, "avt_dataset_load: n_classes %d outside 1..%d", n_classes, AVT_MAX_CLASSES);
+    if (int rc = use_device(e)) return rc;
+    for (void* c : e->cols)
+        if (c) cudaFree(c);
+    e->cols.assign(n_attrs, nullptr);
+    e->N = n_rows;
+    e->Npad = (n_rows + 15) & ~15LL;
+    e->A = n_attrs;
+    e->C = n_classes;
+    e->n_bins.assign(n_bins, n_bins + n_attrs);
+    e->bin_off.assign(n_attrs + 1, 0);
+    e->wide.assign(n_attrs, 0);
+    for (int a = 0; a < n_attrs; ++a) {
+        if (n_bins[a] < 1 || n_bins[a] > 65535) return fail(e, AVT_E_INVALID, "avt_dataset_load: n_bins[%d]=%d outside 1..65535", a, n_bins[a]);
+        e->bin_off[a + 1] = e->bin_off[a] + n_bins[a];
+        e->wide[a] = n_bins[a] > 256;
+    }
+    e->TB = e->bin_off[n_attrs];
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.h2d_ms, &ts)) return rc;
+    for (int a = 0; a < n_attrs; ++a) {
+        const size_t w = e->wide[a] ? 2 : 1;
+        CUDA_TRY(e, cudaMalloc(&e->cols[a], (size_t)e->Npad * w));
+        CUDA_TRY(e, cudaMemsetAsync((char*)e->cols[a] + (size_t)n_rows * w, 0, (size_t)(e->Npad - n_rows) * w, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(e->cols[a], columns[a], (size_t)n_rows * w, cudaMemcpyHostToDevice, e->stream));
+    }
+    CUDA_TRY(e, e->d_cls.ensure((size_t)e->Npad));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_cls.p, 0, (size_t)e->Npad, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_cls.p, class_codes, (size_t)n_rows, cudaMemcpyHostToDevice, e->stream));
+    if (int rc = upload(e, e->d_colptrs, e->cols.data(), (size_t)n_attrs)) return rc;
+    if (int rc = upload(e, e->d_bin_off, e->bin_off.data(), (size_t)n_attrs + 1)) return rc;
+    if (int rc = upload(e, e->d_wide, e->wide.data(), (size_t)n_attrs)) return rc;
+    if (int rc = timer_close(e, ts)) return rc;
+    e->T = 0;
+    e->S = 0;
+    e->hist_valid = e->scan_valid = false;
+    return sync_and_resolve(e);
+}
+
+int avt_forest_init(avt_engine* e, int32_t n_trees, const uint8_t* const* weights,
+                    const uint16_t* const* node_ids) {
+    if (!e) return AVT_E_INVALID;
+    if (e->N == 0) return fail(e, AVT_E_STATE, "avt_forest_init: no data set loaded");
+    if (n_trees < 1) return fail(e, AVT_E_INVALID, "avt_forest_init: n_trees %d < 1", n_trees);
+    if (int rc = use_device(e)) return rc;
+    e->T = n_trees;
+    e->any_w = false;
+    std::vector<uint8_t> has_w(n_trees, 0);
+    if (weights)
+        for (int t = 0; t < n_trees; ++t)
+            if (weights[t]) { has_w[t] = 1; e->any_w = true; }
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.h2d_ms, &ts)) return rc;
+    CUDA_TRY(e, e->d_nid.ensure((size_t)n_trees * e->Npad));
+    // 0xFFFF everywhere (covers the padding), then node 0 / caller ids for the real rows
+    CUDA_TRY(e, cudaMemsetAsync(e->d_nid.p, 0xFF, (size_t)n_trees * e->Npad * 2, e->stream));
+    for (int t = 0; t < n_trees; ++t) {
+        uint16_t* dst = e->d_nid.p + (size_t)t * e->Npad;
+        if (node_ids && node_ids[t]) CUDA_TRY(e, cudaMemcpyAsync(dst, node_ids[t], (size_t)e->N * 2, cudaMemcpyHostToDevice, e->stream));
+        else CUDA_TRY(e, cudaMemsetAsync(dst, 0, (size_t)e->N * 2, e->stream));
+    }
+    if (e->any_w) {
+        CUDA_TRY(e, e->d_w.ensure((size_t)n_trees * e->Npad));
+        CUDA_TRY(e, cudaMemsetAsync(e->d_w.p, 0, (size_t)n_trees * e->Npad, e->stream));
+        for (int t = 0; t < n_trees; ++t)
+            if (has_w[t]) CUDA_TRY(e, cudaMemcpyAsync(e->d_w.p + (size_t)t * e->Npad, weights[t], (size_t)e->N, cudaMemcpyHostToDevice, e->stream));
+    }
+    if (int rc = upload(e, e->d_has_w, has_w.data(), (size_t)n_trees)) return rc;
+    if (int rc = timer_close(e, ts)) return rc;
+    e->hist_valid = e->scan_valid = false;
+    return sync_and_resolve(e);
+}
+
+int avt_split_table_set(avt_engine* e, int32_t n_splits, const avt_split* splits, const int32_t* bounds,
+                        int32_t n_bounds, const uint8_t* seg_lut, int64_t n_lut) {
+    if (!e) return AVT_E_INVALID;
+    if (e->N == 0) return fail(e, AVT_E_STATE, "avt_split_table_set: no data set loaded");
+    if (n_splits < 0 || (n_splits && !splits)) return fail(e, AVT_E_INVALID, "avt_split_table_set: bad split table");
+    if (int rc = use_device(e)) return rc;
+    std::vector<int32_t> attr_first(e->A + 1, 0);
+    int prev = 0;
+    for (int s = 0; s < n_splits; ++s) {
+        const avt_split& sp = splits[s];
+        if (sp.attr < 0 || sp.attr >= e->A) return fail(e, AVT_E_INVALID, "split %d: attribute %d out of range", s, sp.attr);
+        if (sp.attr < prev) return fail(e, AVT_E_INVALID, "split %d: splits must be grouped by non-decreasing attribute", s);
+        if (sp.n_seg < 2 || sp.n_seg > AVT_MAX_SEG) return fail(e, AVT_E_INVALID, "split %d: n_seg %d outside 2..%d", s, sp.n_seg, AVT_MAX_SEG);
+        if (sp.kind == AVT_SPLIT_NUMERIC) {
+            if (sp.off < 0 || sp.off + sp.n_seg - 1 > n_bounds) return fail(e, AVT_E_INVALID, "split %d: bounds out of range", s);
+            for (int j = 0; j < sp.n_seg - 1; ++j) {
+                int b = bounds[sp.off + j];
+                if (b < -1 || b >= e->n_bins[sp.attr]) return fail(e, AVT_E_INVALID, "split %d: bound %d outside the attribute's bins", s, b);
+            }
+        } else if (sp.kind == AVT_SPLIT_LUT) {
+            if (sp.off < 0 || (int64_t)sp.off + e->n_bins[sp.attr] > n_lut) return fail(e, AVT_E_INVALID, "split %d: segment table out of range", s);
+        } else {
+            return fail(e, AVT_E_INVALID, "split %d: unknown kind %d", s, sp.kind);
+        }
+        for (int a = prev + 1; a <= sp.attr; ++a) attr_first[a] = s;
+        prev = sp.attr;
+    }
+    for (int a = prev + 1; a <= e->A; ++a) attr_first[a] = n_splits;
+    e->S = n_splits;
+    e->splits.assign(splits, splits + n_splits);
+    if (int rc = upload(e, e->d_splits, splits, (size_t)n_splits)) return rc;
+    if (int rc = upload(e, e->d_bounds, bounds, (size_t)std::max(n_bounds, 0))) return rc;
+    if (int rc = upload(e, e->d_seg_lut, seg_lut, (size_t)std::max<int64_t>(n_lut, 0))) return rc;
+    if (int rc = upload(e, e->d_attr_first, attr_first.data(), attr_first.size())) return rc;
+    e->scan_valid = false;
+    return sync_and_resolve(e);
+}
+
+int avt_level_histogram(avt_engine* e, const int32_t* nodes_per_tree, uint32_t* hist_out) {
+    if (!e) return AVT_E_INVALID;
+    if (e->T == 0) return fail(e, AVT_E_STATE, "avt_level_histogram: avt_forest_init has not been called");
+    if (!nodes_per_tree) return fail(e, AVT_E_INVALID, "avt_level_histogram: nodes_per_tree is NULL");
+    if (int rc = use_device(e)) return rc;
+    e->node_base.assign(e->T + 1, 0);
+    int n_max = 0;
+    for (int t = 0; t < e->T; ++t) {
+        if (nodes_per_tree[t] < 0 || nodes_per_tree[t] >= (int)AVT_NODE_NONE)
+            return fail(e, AVT_E_INVALID, "avt_level_histogram: tree %d has %d frontier nodes (limit %d)", t, nodes_per_tree[t], AVT_NODE_NONE - 1);
+        e->node_base[t + 1] = e->node_base[t] + nodes_per_tree[t];
+        n_max = std::max(n_max, nodes_per_tree[t]);
+    }
+    e->NF = e->node_base[e->T];
+    e->hist_valid = e->scan_valid = false;
+    if (e->NF == 0) return fail(e, AVT_E_INVALID, "avt_level_histogram: empty frontier");
+    const size_t hwords = (size_t)e->NF * e->TB * e->C;
+    CUDA_TRY(e, e->d_H.ensure(hwords));
+    if (int rc = upload(e, e->d_node_base, e->node_base.data(), e->node_base.size())) return rc;
+
+    // ---- plan: attribute groups whose per-tree histogram fits the shared-memory budget
+    const long long per_bin = (long long)n_max * e->C;  // words per bin (all nodes of a tree)
+    int max_bins = 0;
+    for (int a = 0; a < e->A; ++a) max_bins = std::max(max_bins, e->n_bins[a]);
+    int variant = (per_bin * max_bins <= kHistWordsBudget) ? 0 : 1;
+    if (e->force_variant >= 0) {
+        if (e->force_variant == 0 && variant == 1)
+            return fail(e, AVT_E_INVALID, "avt_level_histogram: shared-memory variant forced but the frontier needs %lld words", per_bin * max_bins);
+        variant = e->force_variant;
+    }
+    HistArgs ha{};
+    ha.cols = (const void* const*)e->d_colptrs.p;
+    ha.cls = e->d_cls.p;
+    ha.nid = e->d_nid.p;
+    ha.wts = e->any_w ? e->d_w.p : nullptr;
+    ha.has_w = e->d_has_w.p;
+    ha.H = e->d_H.p;
+    ha.node_base = e->d_node_base.p;
+    ha.N = e->N;
+    ha.Npad = e->Npad;
+    ha.C = e->C;
+    ha.TB = e->TB;
+    ha.T = e->T;
+
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.hist_ms, &ts)) return rc;
+    CUDA_TRY(e, cudaMemsetAsync(e->d_H.p, 0, hwords * sizeof(uint32_t), e->stream));
+    if (variant == 0) {
+        const int bins_budget = (int)(kHistWordsBudget / per_bin);
+        std::vector<int32_t> ent_attr, ent_loc, ent_glob, ent_wide, grp_start{0}, grp_bins, grp_rlog, l2g, l2g_off;
+        int cur = 0;
+        for (int a = 0; a < e->A; ++a) {
+            if (cur && cur + e->n_bins[a] > bins_budget) {
+                grp_bins.push_back(cur);
+                grp_start.push_back((int)ent_attr.size());
+                cur = 0;
+            }
+            if (cur == 0) l2g_off.push_back((int)l2g.size());
+            ent_attr.push_back(a);
+            ent_loc.push_back(cur);
+            ent_glob.push_back(e->bin_off[a]);
+            ent_wide.push_back(e->wide[a]);
+            for (int b = 0; b < e->n_bins[a]; ++b) l2g.push_back(e->bin_off[a] + b);
+            cur += e->n_bins[a];
+        }
+        grp_bins.push_back(cur);
+        grp_start.push_back((int)ent_attr.size());
+        const int G = (int)grp_bins.size();
+        size_t smem_words = 0;
+        int rlog_min = 5;
+        for (int g = 0; g < G; ++g) {
+            const long long keys = per_bin * grp_bins[g];
+            int rlog = 0;
+            while (rlog < 5 && (keys << (rlog + 1)) <= kHistWordsBudget) ++rlog;
+            grp_rlog.push_back(rlog);
+            rlog_min = std::min(rlog_min, rlog);
+            smem_words = std::max(smem_words, (size_t)(keys << rlog));
+        }
+        // pack the int tables into one upload
+        std::vector<int32_t> pack;
+        auto put = [&](const std::vector<int32_t>& v) {
+            size_t o = pack.size();
+            pack.insert(pack.end(), v.begin(), v.end());
+            return o;
+        };
+        const size_t o_attr = put(ent_attr), o_loc = put(ent_loc), o_glob = put(ent_glob), o_wide = put(ent_wide),
+                     o_gs = put(grp_start), o_gb = put(grp_bins), o_gr = put(grp_rlog), o_l2g = put(l2g), o_lo = put(l2g_off);
+        if (int rc = upload(e, e->d_grp, pack.data(), pack.size())) return rc;
+        const int32_t* base = e->d_grp.p;
+        ha.ent_attr = base + o_attr; ha.ent_locoff = base + o_loc; ha.ent_globoff = base + o_glob; ha.ent_wide = base + o_wide;
+        ha.grp_start = base + o_gs; ha.grp_bins = base + o_gb; ha.grp_rlog = base + o_gr; ha.grp_l2g = base + o_l2g; ha.grp_l2g_off = base + o_lo;
+        const size_t smem = smem_words * sizeof(uint32_t);
+        int bpsm = (int)std::min<size_t>(4, std::max<size_t>(1, kMaxDynSmem / std::max<size_t>(smem, 1)));
+        long long resident = (long long)e->sm_count * bpsm;
+        long long chunks = std::max<long long>(1, resident / ((long long)e->T * G));
+        const long long tiles = (e->N + (long long)kHistThreads * kRowsPerThread - 1) / ((long long)kHistThreads * kRowsPerThread);
+        chunks = std::min(chunks, tiles);
+        chunks = std::min<long long>(chunks, 65535);
+        dim3 grid((unsigned)e->T, (unsigned)chunks, (unsigned)G);
+        if (e->any_w) hist_smem_kernel<true><<<grid, kHistThreads, smem, e->stream>>>(ha);
+        else hist_smem_kernel<false><<<grid, kHistThreads, smem, e->stream>>>(ha);
+        e->stats.last_hist_replicas = 1 << rlog_min;
+        e->stats.last_hist_grid = (int)(grid.x * grid.y * grid.z);
+        e->stats.last_hist_block = kHistThreads;
+        e->stats.last_hist_smem = (int)smem;
+    } else {
+        long long blocks = std::min<long long>((e->N + 255) / 256, (long long)e->sm_count * 8);
+        dim3 grid((unsigned)blocks, (unsigned)e->T);
+        hist_global_kernel<<<grid, 256, 0, e->stream>>>(ha, e->A, e->d_bin_off.p, e->d_wide.p);
+        e->stats.last_hist_replicas = 1;
+        e->stats.last_hist_grid = (int)(grid.x * grid.y);
+        e->stats.last_hist_block = 256;
+        e->stats.last_hist_smem = 0;
+    }
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = timer_close(e, ts)) return rc;
+    e->stats.last_hist_variant = variant;
+    e->stats.hist_launches += 1;
+    {
+        long long code_bytes = 0;
+        for (int a = 0; a < e->A; ++a) code_bytes += e->wide[a] ? 2 : 1;
+        long long per_row = code_bytes + 1;
+        for (int t = 0; t < e->T; ++t) per_row += 2 + ((e->any_w) ? 1 : 0);
+        e->stats.hist_alg_bytes += per_row * e->N;
+    }
+    if (e->comm) {
+        TimerSlot tc;
+        if (int rc = timer_open(e, &e->stats.comm_ms, &tc)) return rc;
+        NCCL_TRY(e, ncclAllReduce(e->d_H.p, e->d_H.p, hwords, ncclUint32, ncclSum, e->comm, e->stream));
+        if (int rc = timer_close(e, tc)) return rc;
+        e->stats.comm_calls += 1;
+    }
+    e->hist_valid = true;
+    if (hist_out) {
+        CUDA_TRY(e, cudaMemcpyAsync(hist_out, e->d_H.p, hwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+        return sync_and_resolve(e);
+    }
+    return AVT_OK;
+}
+
+int avt_level_scan(avt_engine* e, int32_t criterion, const uint32_t* cand_mask, const uint8_t* class_order,
+                   avt_node_best* out) {
+    if (!e) return AVT_E_INVALID;
+    if (!e->hist_valid) return fail(e, AVT_E_STATE, "avt_level_scan: no histogram for the current frontier");
+    if (e->S == 0) return fail(e, AVT_E_STATE, "avt_level_scan: no split table installed");
+    if (criterion != AVT_CRIT_GINI && criterion != AVT_CRIT_ENTROPY) return fail(e, AVT_E_INVALID, "avt_level_scan: criterion %d", criterion);
+    if (!out) return fail(e, AVT_E_INVALID, "avt_level_scan: out is NULL");
+    if (int rc = use_device(e)) return rc;
+    if (int rc = upload_order(e, class_order)) return rc;
+    const int mw = (e->A + 31) / 32;
+    const uint32_t* dmask = nullptr;
+    if (cand_mask) {
+        if (int rc = upload(e, e->d_mask, cand_mask, (size_t)e->NF * mw)) return rc;
+        dmask = e->d_mask.p;
+    }
+    CUDA_TRY(e, e->d_av.ensure((size_t)e->NF * e->S));
+    CUDA_TRY(e, e->d_best.ensure((size_t)e->NF));
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
+    scan_kernel<<<e->NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), dmask, e->d_order.p, criterion, e->d_av.p, e->d_best.p);
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = timer_close(e, ts)) return rc;
+    e->stats.scan_launches += 1;
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->d_best.p, (size_t)e->NF * sizeof(avt_node_best), cudaMemcpyDeviceToHost, e->stream));
+    e->scan_valid = true;
+    return sync_and_resolve(e);
+}
+
+int avt_level_fetch_av(avt_engine* e, int32_t node, double* av_out) {
+    if (!e) return AVT_E_INVALID;
+    if (!e->scan_valid) return fail(e, AVT_E_STATE, "avt_level_fetch_av: no scan for the current frontier");
+    if (node < 0 || node >= e->NF || !av_out) return fail(e, AVT_E_INVALID, "avt_level_fetch_av: node %d out of range", node);
+    if (int rc = use_device(e)) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(av_out, e->d_av.p + (size_t)node * e->S, (size_t)e->S * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    return sync_and_resolve(e);
+}
+
+int avt_level_fetch_hist(avt_engine* e, int32_t node, uint32_t* hist_out) {
+    if (!e) return AVT_E_INVALID;
+    if (!e->hist_valid) return fail(e, AVT_E_STATE, "avt_level_fetch_hist: no histogram for the current frontier");
+    if (node < 0 || node >= e->NF || !hist_out) return fail(e, AVT_E_INVALID, "avt_level_fetch_hist: node %d out of range", node);
+    if (int rc = use_device(e)) return rc;
+    const size_t words = (size_t)e->TB * e->C;
+    CUDA_TRY(e, cudaMemcpyAsync(hist_out, e->d_H.p + (size_t)node * words, words * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    return sync_and_resolve(e);
+}
+
+int avt_level_eval(avt_engine* e, int32_t criterion, const uint8_t* class_order, int32_t n, const int32_t* nodes,
+                   const int32_t* splits, avt_split_eval* out) {
+    if (!e) return AVT_E_INVALID;
+    if (!e->hist_valid) return fail(e, AVT_E_STATE, "avt_level_eval: no histogram for the current frontier");
+    if (criterion != AVT_CRIT_GINI && criterion != AVT_CRIT_ENTROPY) return fail(e, AVT_E_INVALID, "avt_level_eval: criterion %d", criterion);
+    if (n < 0 || (n && (!nodes || !splits || !out))) return fail(e, AVT_E_INVALID, "avt_level_eval: NULL argument");
+    if (n == 0) return AVT_OK;
+    for (int i = 0; i < n; ++i)
+        if (nodes[i] < 0 || nodes[i] >= e->NF || splits[i] < 0 || splits[i] >= e->S)
+            return fail(e, AVT_E_INVALID, "avt_level_eval: pair %d (node %d, split %d) out of range", i, nodes[i], splits[i]);
+    if (int rc = use_device(e)) return rc;
+    if (int rc = upload_order(e, class_order)) return rc;
+    std::vector<int32_t> pairs(2 * (size_t)n);
+    std::copy(nodes, nodes + n, pairs.begin());
+    std::copy(splits, splits + n, pairs.begin() + n);
+    if (int rc = upload(e, e->d_pairs, pairs.data(), pairs.size())) return rc;
+    CUDA_TRY(e, e->d_eval.ensure((size_t)n));
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.eval_ms, &ts)) return rc;
+    eval_kernel<<<(n + 63) / 64, 64, 0, e->stream>>>(e->d_H.p, make_table(e), e->d_order.p, criterion, n, e->d_pairs.p, e->d_pairs.p + n, e->d_eval.p);
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = timer_close(e, ts)) return rc;
+    e->stats.eval_launches += 1;
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->d_eval.p, (size_t)n * sizeof(avt_split_eval), cudaMemcpyDeviceToHost, e->stream));
+    return sync_and_resolve(e);
+}
+
+int avt_level_repartition(avt_engine* e, const int32_t* node_attr, const uint16_t* child_lut, int32_t lut_width) {
+    if (!e) return AVT_E_INVALID;
+    if (e->NF == 0) return fail(e, AVT_E_STATE, "avt_level_repartition: no frontier (call avt_level_histogram first)");
+    if (!node_attr || !child_lut || lut_width < 1) return fail(e, AVT_E_INVALID, "avt_level_repartition: NULL argument");
+    for (int g = 0; g < e->NF; ++g) {
+        if (node_attr[g] >= e->A) return fail(e, AVT_E_INVALID, "avt_level_repartition: node %d attribute %d out of range", g, node_attr[g]);
+        if (node_attr[g] >= 0 && e->n_bins[node_attr[g]] > lut_width)
+            return fail(e, AVT_E_INVALID, "avt_level_repartition: lut_width %d < bins of attribute %d", lut_width, node_attr[g]);
+    }
+    if (int rc = use_device(e)) return rc;
+    if (int rc = upload(e, e->d_node_attr, node_attr, (size_t)e->NF)) return rc;
+    if (int rc = upload(e, e->d_lut, child_lut, (size_t)e->NF * lut_width)) return rc;
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.repart_ms, &ts)) return rc;
+    long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
+    dim3 grid((unsigned)blocks, (unsigned)e->T);
+    repartition_kernel<<<grid, 256, 0, e->stream>>>(e->d_nid.p, (const void* const*)e->d_colptrs.p, e->d_wide.p, e->d_node_base.p,
+                                                    e->d_node_attr.p, e->d_lut.p, lut_width, e->N, e->Npad);
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = timer_close(e, ts)) return rc;
+    e->stats.repart_launches += 1;
+    e->stats.repart_alg_bytes += (long long)e->N * e->T * 5;
+    e->hist_valid = e->scan_valid = false;
+    e->NF = 0;
+    return AVT_OK;
+}
+
+int avt_cpg_sweep(avt_engine* e, int32_t node, int32_t criterion, const uint8_t* class_order, avt_cpg_stat* out) {
+    if (!e) return AVT_E_INVALID;
+    if (!e->hist_valid) return fail(e, AVT_E_STATE, "avt_cpg_sweep: no histogram for the current frontier");
+    if (e->S == 0) return fail(e, AVT_E_STATE, "avt_cpg_sweep: no split table installed");
+    if (node < 0 || node >= e->NF || !out) return fail(e, AVT_E_INVALID, "avt_cpg_sweep: node %d out of range", node);
+    if (criterion < AVT_CRIT_GINI || criterion > AVT_CRIT_CLASS_CONF) return fail(e, AVT_E_INVALID, "avt_cpg_sweep: criterion %d", criterion);
+    if (criterion == AVT_CRIT_HELLINGER && e->C != 2)
+        return fail(e, AVT_E_REFERENCE, "Hellinger distance algorithm is only valid for binary valued class attributes");
+    if (int rc = use_device(e)) return rc;
+    if (int rc = upload_order(e, class_order)) return rc;
+    CUDA_TRY(e, e->d_cpg.ensure((size_t)e->S));
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
+    cpg_kernel<<<(e->S + 63) / 64, 64, 0, e->stream>>>(e->d_H.p, make_table(e), node, e->d_order.p, criterion, e->d_cpg.p);
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = timer_close(e, ts)) return rc;
+    e->stats.scan_launches += 1;
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->d_cpg.p, (size_t)e->S * sizeof(avt_cpg_stat), cudaMemcpyDeviceToHost, e->stream));
+    return sync_and_resolve(e);
+}
+
+int avt_forest_node_ids(avt_engine* e, int32_t tree, uint16_t* out) {
+    if (!e) return AVT_E_INVALID;
+    if (tree < 0 || tree >= e->T || !out) return fail(e, AVT_E_INVALID, "avt_forest_node_ids: tree %d out of range", tree);
+    if (int rc = use_device(e)) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->d_nid.p + (size_t)tree * e->Npad, (size_t)e->N * 2, cudaMemcpyDeviceToHost, e->stream));
+    return sync_and_resolve(e);
+}
+
+int avt_level_class_counts(avt_engine* e, uint32_t* out) {
+    if (!e) return AVT_E_INVALID;
+    if (!e->hist_valid || !out) return fail(e, AVT_E_STATE, "avt_level_class_counts: no histogram for the current frontier");
+    if (int rc = use_device(e)) return rc;
+    const int n = e->NF * e->C;
+    CUDA_TRY(e, e->d_ccnt.ensure((size_t)n));
+    class_counts_kernel<<<(n + 127) / 128, 128, 0, e->stream>>>(e->d_H.p, e->NF, e->TB, e->C, e->n_bins[0], e->d_ccnt.p);
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->d_ccnt.p, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
+    return sync_and_resolve(e);
+}
+
+int avt_timer_begin(avt_engine* e) {
+    if (!e) return AVT_E_INVALID;
+    if (int rc = use_device(e)) return rc;
+    CUDA_TRY(e, cudaEventRecord(e->tev0, e->stream));
+    return AVT_OK;
+}
+
+int avt_timer_end(avt_engine* e, float* ms) {
+    if (!e || !ms) return AVT_E_INVALID;
+    if (int rc = use_device(e)) return rc;
+    CUDA_TRY(e, cudaEventRecord(e->tev1, e->stream));
+    if (int rc = sync_and_resolve(e)) return rc;
+    CUDA_TRY(e, cudaEventElapsedTime(ms, e->tev0, e->tev1));
+    return AVT_OK;
+}
+
+int avt_synchronize(avt_engine* e) {
+    if (!e) return AVT_E_INVALID;
+    if (int rc = use_device(e)) return rc;
+    return sync_and_resolve(e);
+}
+
+int avt_get_stats(avt_engine* e, avt_stats* out) {
+    if (!e || !out) return AVT_E_INVALID;
+    if (int rc = use_device(e)) return rc;
+    if (int rc = sync_and_resolve(e)) return rc;
+    *out = e->stats;
+    return AVT_OK;
+}
+
+int avt_reset_stats(avt_engine* e) {
+    if (!e) return AVT_E_INVALID;
+    if (int rc = use_device(e)) return rc;
+    if (int rc = sync_and_resolve(e)) return rc;
+    avt_stats z{};
+    z.last_hist_variant = e->stats.last_hist_variant;
+    e->stats = z;
+    return AVT_OK;
+}
+
+int avt_set_hist_variant(avt_engine* e, int32_t variant) {
+    if (!e) return AVT_E_INVALID;
+    if (variant < -1 || variant > 1) return fail(e, AVT_E_INVALID, "avt_set_hist_variant: %d", variant);
+    e->force_variant = variant;
+    return AVT_OK;
+}
+
+int avt_comm_unique_id(void* id128) {
+    if (!id128) return AVT_E_INVALID;
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    ncclResult_t st = ncclGetUniqueId(&id);
+    if (st != ncclSuccess) return fail(nullptr, AVT_E_COMM, "ncclGetUniqueId: %s", ncclGetErrorString(st));
+    memcpy(id128, &id, 128);
+    return AVT_OK;
+}
+
+int avt_comm_init_rank(avt_engine* e, int32_t n_ranks, int32_t rank, const void* id128) {
+    if (!e || !id128 || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(e, AVT_E_INVALID, "avt_comm_init_rank: bad argument");
+    if (int rc = use_device(e)) return rc;
+    if (e->comm) {
+        ncclCommDestroy(e->comm);
+        e->comm = nullptr;
+    }
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    NCCL_TRY(e, ncclCommInitRank(&e->comm, n_ranks, id, rank));
+    e->n_ranks = n_ranks;
+    e->rank = rank;
+    return AVT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,931 @@
+// DecisionTreeBuilder re-hosted above the kernel-level C-ABI.
+//
+// Keeps the reference job's surface (tree/DecisionTreeBuilder.java): same dtb.* knobs, the JSON
+// feature schema, CSV rows (path-tagged after the first pass), the DecisionPathList JSON written to
+// dtb.decision.file.path.out and the path-tagged data file <outPath>/part-r-00000.  What changes is
+// who does the work: rows are binned once into columns, kernel (a) builds the per-(node, attribute,
+// bin, class) counts that BuilderMapper.pathMapHelper + the shuffle + BuilderReducer.reduce produce
+// as N x S text records, kernel (b) computes what BuilderReducer.expandTree computes, kernel (c)
+// re-keys the rows.  The host keeps the string world: split ids, predicate strings, HashMap
+// iteration orders, stopping flags, JSON.
+//
+// Extensions (absent from the reference, default = reference behaviour):
+//   avt.dtb.num.levels   (1)  levels run inside this one invocation (root pass counts as one when
+//                             dtb.decision.file.path.in is absent); the reference needs one job and
+//                             a manual file shuffle (resource/detr.sh:34-54) per level
+//   avt.forest.num.trees (1)  bagged trees built together, one launch per level for all of them
+//   avt.random.seed      (0)  seed of the java.util.Random stream that replaces Math.random()
+//   avt.device           (0)  CUDA device ordinal
+#include <dirent.h>
+#include <sys/stat.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+
+#include "tool.hpp"
+
+namespace avt_host {
+
+static const char* kRoot = "$root";
+
+// ---- shared helpers ---------------------------------------------------------------------------
+
+Engine::Engine(int device) {
+    int rc = avt_create(device, &e_);
+    if (rc != AVT_OK) throw EngineError(rc, avt_last_error(nullptr));
+}
+Engine::~Engine() { avt_destroy(e_); }
+void Engine::check(int rc) const {
+    if (rc != AVT_OK) throw EngineError(rc, avt_last_error(e_));
+}
+
+int ClassTable::code_of(const std::string& s) {
+    for (size_t i = 0; i < names.size(); ++i)
+        if (names[i] == s) return (int)i;
+    names.push_back(s);
+    if (names.size() > 12)
+        throw Unsupported("more than 12 class values: HashMap<String,Integer> resizes and its iteration order becomes node-dependent (SURVEY App. B-7); not implemented");
+    return (int)names.size() - 1;
+}
+void ClassTable::finish() {
+    order.clear();
+    for (auto& k : hashmap_key_order(names))
+        for (size_t i = 0; i < names.size(); ++i)
+            if (names[i] == k) order.push_back((uint8_t)i);
+}
+
+std::vector<std::string> read_input_lines(const std::string& path) {
+    struct stat st;
+    if (stat(path.c_str(), &st) != 0) throw std::runtime_error("input path does not exist: " + path);
+    std::vector<std::string> files;
+    if (S_ISDIR(st.st_mode)) {
+        DIR* d = opendir(path.c_str());
+        if (!d) throw std::runtime_error("cannot list " + path);
+        while (dirent* de = readdir(d)) {
+            std::string n = de->d_name;
+            if (n.empty() || n[0] == '.' || n[0] == '_') continue;
+            std::string p = path + "/" + n;
+            struct stat s2;
+            if (stat(p.c_str(), &s2) == 0 && S_ISREG(s2.st_mode)) files.push_back(p);
+        }
+        closedir(d);
+        std::sort(files.begin(), files.end());
+    } else {
+        files.push_back(path);
+    }
+    std::vector<std::string> lines;
+    for (auto& f : files) {
+        std::string data = read_file(f);
+        size_t pos = 0;
+        while (pos < data.size()) {
+            size_t q = data.find('\n', pos);
+            if (q == std::string::npos) q = data.size();
+            size_t end = q;
+            if (end > pos && data[end - 1] == '\r') --end;
+            lines.emplace_back(data, pos, end - pos);
+            pos = q + 1;
+        }
+    }
+    return lines;
+}
+
+static void mkdirs(const std::string& dir) {
+    std::string cur;
+    for (size_t i = 0; i <= dir.size(); ++i) {
+        if (i == dir.size() || dir[i] == '/') {
+            if (!cur.empty()) mkdir(cur.c_str(), 0777);
+        }
+        if (i < dir.size()) cur.push_back(dir[i]);
+    }
+}
+
+static void write_text(const std::string& path, const std::string& text) {
+    size_t slash = path.rfind('/');
+    if (slash != std::string::npos && slash > 0) mkdirs(path.substr(0, slash));
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    fwrite(text.data(), 1, text.size(), f);
+    fclose(f);
+}
+
+void write_output_lines(const std::string& out_dir, const std::vector<std::string>& lines) {
+    mkdirs(out_dir);
+    std::string path = out_dir + "/part-r-00000";
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    for (auto& l : lines) {
+        fwrite(l.data(), 1, l.size(), f);
+        fputc('\n', f);
+    }
+    fclose(f);
+}
+
+// ---- DecisionPathList beans (tree/DecisionPathList.java) ----------------------------------------
+
+struct PathPred {
+    int attribute = 0;
+    std::string predicate_str, op;
+    bool has_op = false;
+    int value_int = 0;
+    double value_dbl = 0.0;
+    bool has_cat = false;
+    std::vector<std::string> cat;
+    bool has_other_int = false, has_other_dbl = false;
+    int other_int = 0;
+    double other_dbl = 0;
+};
+
+struct DecPath {
+    bool has_preds = false;
+    std::vector<PathPred> preds;
+    long long population = 0;
+    double info_content = 0;
+    bool stopped = false;
+    std::vector<std::pair<std::string, double>> class_val_pr;  // HashMap iteration order
+    std::string output_class_val;
+    double confidence = 0, support = 0;
+};
+
+static PathPred root_pred() {
+    PathPred p;
+    p.predicate_str = kRoot;
+    return p;
+}
+
+// DecisionPathPredicate.create{Int,Double,Categorical}Predicate (tree/DecisionPathList.java:402-447)
+static PathPred make_pred(const std::string& s, const Field& f) {
+    std::vector<std::string> it;
+    {
+        std::istringstream is(s);
+        std::string w;
+        while (is >> w) it.push_back(w);
+    }
+    if (it.size() < 3) throw ReferenceError("ArrayIndexOutOfBoundsException: predicate '" + s + "'");
+    PathPred p;
+    p.attribute = std::stoi(it[0]);
+    p.op = it[1];
+    p.has_op = true;
+    p.predicate_str = s;
+    if (f.is_int()) {
+        p.value_int = std::stoi(it[2]);
+        if (it.size() == 4) { p.has_other_int = true; p.other_int = std::stoi(it[3]); }
+    } else if (f.is_double()) {
+        p.value_dbl = std::stod(it[2]);
+        if (it.size() == 4) { p.has_other_dbl = true; p.other_dbl = std::stod(it[3]); }
+    } else if (f.is_categorical()) {
+        p.has_cat = true;
+        p.cat = split_str(it[2], ":", false);
+    } else {
+        throw ReferenceError("invalid data type for predicates");
+    }
+    return p;
+}
+
+static std::string dbl(double x) { return java_double_to_string(x); }
+
+static std::string pred_json(const PathPred& p) {
+    std::string o = "{";
+    o += "\"attribute\":" + std::to_string(p.attribute);
+    o += ",\"predicateStr\":" + json_escape(p.predicate_str);
+    o += ",\"operator\":" + (p.has_op ? json_escape(p.op) : std::string("null"));
+    o += ",\"valueInt\":" + std::to_string(p.value_int);
+    o += ",\"valueDbl\":" + dbl(p.value_dbl);
+    if (p.has_cat) {
+        o += ",\"categoricalValues\":[";
+        for (size_t i = 0; i < p.cat.size(); ++i) o += (i ? "," : "") + json_escape(p.cat[i]);
+        o += "]";
+    } else {
+        o += ",\"categoricalValues\":null";
+    }
+    o += ",\"otherBoundInt\":" + (p.has_other_int ? std::to_string(p.other_int) : std::string("null"));
+    o += ",\"otherBoundDbl\":" + (p.has_other_dbl ? dbl(p.other_dbl) : std::string("null"));
+    return o + "}";
+}
+
+// Field order of the sample model resource/dec_tree_rules.json, then the three newer bean fields.
+static std::string path_json(const DecPath& d) {
+    std::string o = "{\"stopped\":";
+    o += d.stopped ? "true" : "false";
+    o += ",\"classValPr\":{";
+    for (size_t i = 0; i < d.class_val_pr.size(); ++i)
+        o += (i ? "," : "") + json_escape(d.class_val_pr[i].first) + ":" + dbl(d.class_val_pr[i].second);
+    o += "},\"infoContent\":" + dbl(d.info_content);
+    if (d.has_preds) {
+        o += ",\"predicates\":[";
+        for (size_t i = 0; i < d.preds.size(); ++i) o += (i ? "," : "") + pred_json(d.preds[i]);
+        o += "]";
+    } else {
+        o += ",\"predicates\":null";
+    }
+    o += ",\"population\":" + std::to_string(d.population);
+    o += ",\"outputClassVal\":" + json_escape(d.output_class_val);
+    o += ",\"confidence\":" + dbl(d.confidence);
+    o += ",\"support\":" + dbl(d.support);
+    return o + "}";
+}
+
+static std::string path_list_json(const std::vector<DecPath>* paths) {
+    if (!paths) return "{\"decisionPaths\":null}";
+    std::string o = "{\"decisionPaths\":[";
+    for (size_t i = 0; i < paths->size(); ++i) o += (i ? "," : "") + path_json((*paths)[i]);
+    return o + "]}";
+}
+
+static DecPath path_from_json(const Json& j) {
+    DecPath d;
+    if (auto* v = j.get("population")) d.population = (long long)v->num;
+    if (auto* v = j.get("infoContent")) d.info_content = v->num;
+    if (auto* v = j.get("stopped")) d.stopped = v->b;
+    if (auto* v = j.get("classValPr"))
+        for (auto& kv : v->obj) d.class_val_pr.emplace_back(kv.first, kv.second.num);
+    if (auto* v = j.get("outputClassVal")) d.output_class_val = v->str;
+    if (auto* v = j.get("confidence")) d.confidence = v->num;
+    if (auto* v = j.get("support")) d.support = v->num;
+    if (auto* v = j.get("predicates"); v && v->kind == Json::Arr) {
+        d.has_preds = true;
+        for (auto& pj : v->arr) {
+            PathPred p;
+            if (auto* x = pj.get("attribute")) p.attribute = (int)x->num;
+            if (auto* x = pj.get("predicateStr")) p.predicate_str = x->str;
+            if (auto* x = pj.get("operator"); x && x->kind == Json::Str) { p.has_op = true; p.op = x->str; }
+            if (auto* x = pj.get("valueInt")) p.value_int = (int)x->num;
+            if (auto* x = pj.get("valueDbl")) p.value_dbl = x->num;
+            if (auto* x = pj.get("categoricalValues"); x && x->kind == Json::Arr) {
+                p.has_cat = true;
+                for (auto& c : x->arr) p.cat.push_back(c.str);
+            }
+            if (auto* x = pj.get("otherBoundInt"); x && x->kind == Json::Num) { p.has_other_int = true; p.other_int = (int)x->num; }
+            if (auto* x = pj.get("otherBoundDbl"); x && x->kind == Json::Num) { p.has_other_dbl = true; p.other_dbl = x->num; }
+            d.preds.push_back(p);
+        }
+    }
+    return d;
+}
+
+// DecisionPathList.stripSplitId (tree/DecisionPathList.java:97-107)
+static std::string strip_id(const std::string& item) {
+    if (item == kRoot) return item;
+    size_t p = item.find(':');
+    if (p == std::string::npos) throw ReferenceError("split id delimiter not found in path element '" + item + "'");
+    return item.substr(p + 1);
+}
+
+// DecisionPath.findMajorityClass (tree/DecisionPathList.java:175-192)
+static void majority(DecPath& d) {
+    double maj = -1.0;
+    for (auto& kv : d.class_val_pr)
+        if (kv.second > maj) { maj = kv.second; d.output_class_val = kv.first; }
+    double mn = 1.0 - maj;
+    if (mn > 0) {
+        d.confidence = maj / mn;
+        if (d.confidence > 100) d.confidence = 100;
+    } else {
+        d.confidence = 100;
+    }
+}
+
+// ---- the job ------------------------------------------------------------------------------------
+
+namespace {
+
+struct Node {
+    std::vector<std::string> tagged;  // key items as the reducer sees them: "$root", "3:2 le 20", ...
+    DecPath path;                     // its entry in the current decision-path list
+    std::vector<int> cand;            // candidate attribute columns (indices into attrs_)
+};
+
+struct Tree {
+    std::vector<Node> frontier;
+    std::vector<uint8_t> weights;  // empty = all ones
+};
+
+class DtbJob {
+    const Props& conf_;
+    std::string in_path_, out_path_;
+    // knobs (tree/DecisionTreeBuilder.java:137-193, 414-463)
+    std::string delim_regex_, delim_out_, path_delim_, attr_strategy_, sampling_, algorithm_, split_sel_, stop_strategy_;
+    int sampling_rate_ = 0, sampling_buffer_ = 10000, total_population_ = -1, top_split_count_ = 3;
+    int max_depth_ = -1, min_population_ = -1;
+    double min_info_gain_ = -1;
+    int num_levels_ = 1, num_trees_ = 1, device_ = 0;
+    long long seed_ = 0;
+    bool debug_ = false;
+    // model
+    Schema schema_;
+    std::vector<AttrSplits> attrs_;  // base attributes in getBaseAttributeOrdinals() order = device columns
+    DeviceSplitTable table_;
+    int class_ord_ = 0;
+    ClassTable classes_;
+    // data
+    std::vector<std::string> rows_;  // row text without the path prefix
+    std::vector<std::vector<uint8_t>> col8_;
+    std::vector<std::vector<uint16_t>> col16_;
+    std::vector<uint8_t> cls_;
+    std::vector<Tree> trees_;
+    std::unique_ptr<Engine> eng_;
+    JavaRandom rng_{0};
+    int pass_ = 0;  // passes written so far (0 = root pass)
+
+public:
+    DtbJob(const Props& conf, std::string in, std::string out) : conf_(conf), in_path_(std::move(in)), out_path_(std::move(out)) {}
+
+    int run() {
+        read_conf();
+        const bool tree_available = conf_.nonblank("dtb.decision.file.path.in") && file_exists(conf_.get("dtb.decision.file.path.in"));
+        std::vector<std::string> lines = read_input_lines(in_path_);
+        std::vector<std::vector<std::string>> row_tagged;  // per row: tagged path items (tree available)
+        std::vector<DecPath> dec_in;
+        if (tree_available) {
+            Json j = JsonParser(read_file(conf_.get("dtb.decision.file.path.in"))).parse();
+            const Json* arr = j.get("decisionPaths");
+            if (!arr || arr->kind != Json::Arr) throw ReferenceError("NullPointerException: decision path list has no decisionPaths");
+            for (auto& pj : arr->arr) dec_in.push_back(path_from_json(pj));
+        }
+        encode(lines, tree_available, row_tagged);
+        eng_.reset(new Engine(device_));
+        upload();
+        int levels_left = num_levels_;
+        if (!tree_available) {
+            init_root_pass();
+            std::vector<std::vector<DecPath>> lists = root_pass();
+            --levels_left;
+            if (levels_left == 0) {
+                write_lists(lists);
+                write_root_data();
+                return 0;
+            }
+            write_lists(lists);
+        } else {
+            init_from_paths(dec_in, row_tagged);
+        }
+        std::vector<std::vector<DecPath>> lists;
+        std::vector<bool> list_null;
+        for (; levels_left > 0; --levels_left) {
+            bool any = expand_level(lists, list_null);
+            write_lists(lists, &list_null);
+            if (!any) break;
+        }
+        write_level_data();
+        return 0;
+    }
+
+private:
+    static bool file_exists(const std::string& p) {
+        struct stat st;
+        return stat(p.c_str(), &st) == 0;
+    }
+
+    void read_conf() {
+        debug_ = conf_.get_bool("debug.on", false);
+        delim_regex_ = conf_.get("field.delim.regex", ",");
+        delim_out_ = conf_.get("field.delim.out", ",");
+        path_delim_ = conf_.get("dtb.dec.path.delim", ";");
+        for (const std::string* d : {&delim_regex_, &path_delim_})
+            for (char c : *d)
+                if (strchr(".*+?()[]{}|^$\\", c)) throw Unsupported("delimiter '" + *d + "' contains regex metacharacters; only literal delimiters are implemented");
+        if (!conf_.nonblank("dtb.feature.schema.file.path")) throw ReferenceError("NullPointerException: dtb.feature.schema.file.path not set");
+        schema_ = Schema::load(conf_.get("dtb.feature.schema.file.path"));
+        attr_strategy_ = conf_.get("dtb.split.attribute.selection.strategy", "notUsedYet");
+        if (attr_strategy_ == "randomAll" || attr_strategy_ == "randomNotUsedYet")
+            throw ReferenceError("NullPointerException: dtb.split.attribute.selection.strategy=" + attr_strategy_ +
+                                 " never assigns splitAttrs in the reference (tree/DecisionTreeBuilder.java:372-378)");
+        if (attr_strategy_ != "all" && attr_strategy_ != "notUsedYet") throw ReferenceError("invalid splitting attribute selection strategy");
+        sampling_ = conf_.get("dtb.sub.sampling.strategy", "withReplace");
+        if (sampling_ == "withoutReplace") {
+            if (!conf_.nonblank("dtb.sub.sampling.rate")) throw ReferenceError("samling rate should be provided for sampling without replacement");
+            sampling_rate_ = conf_.get_int("dtb.sub.sampling.rate", 0);
+        }
+        sampling_buffer_ = conf_.get_int("dtb.sub.sampling.buffer.size", 10000);
+        algorithm_ = conf_.get("dtb.split.algorithm", "giniIndex");
+        total_population_ = conf_.get_int("dtb.total.population", -1);
+        split_sel_ = conf_.get("dtb.split.select.strategy", "best");
+        if (split_sel_ == "randomAmongTop") throw Unsupported("dtb.split.select.strategy=randomAmongTop is not implemented yet");
+        if (split_sel_ != "best") throw ReferenceError("ivalid split slection strategy");
+        top_split_count_ = conf_.get_int("dtb.top.split.count", 3);
+        stop_strategy_ = conf_.get("dtb.path.stopping.strategy", "minInfoGain");
+        if (stop_strategy_ == "maxDepth") {
+            if (!conf_.nonblank("dtb.max.depth.limit")) throw ReferenceError("missing max depth limit for tree");
+            max_depth_ = conf_.get_int("dtb.max.depth.limit", -1);
+        } else if (stop_strategy_ == "minInfoGain") {
+            if (!conf_.nonblank("dtb.min.info.gain.limit")) throw ReferenceError("missing min info gain limit");
+            min_info_gain_ = conf_.get_double("dtb.min.info.gain.limit", -1);
+        } else if (stop_strategy_ == "minPopulation") {
+            if (!conf_.nonblank("dtb.min.population.limit")) throw ReferenceError("missing min population limit");
+            min_population_ = conf_.get_int("dtb.min.population.limit", -1);
+        } else {
+            throw ReferenceError("invalid stopping strategy " + stop_strategy_);
+        }
+        if (!conf_.nonblank("dtb.decision.file.path.out")) throw ReferenceError("NullPointerException: dtb.decision.file.path.out not set");
+        num_levels_ = std::max(1, conf_.get_int("avt.dtb.num.levels", 1));
+        num_trees_ = std::max(1, conf_.get_int("avt.forest.num.trees", 1));
+        seed_ = conf_.get_int("avt.random.seed", 0);
+        device_ = conf_.get_int("avt.device", 0);
+        rng_ = JavaRandom(seed_);
+        // base attributes (tree/SplitManager.java:141-157)
+        std::vector<int> base;
+        if (conf_.nonblank("dtb.custom.base.attributes")) {
+            for (auto& s : split_str(conf_.get("dtb.custom.base.attributes"), ",", false)) base.push_back(std::stoi(trim(s)));
+        } else {
+            base = schema_.feature_ordinals();
+        }
+        for (int o : base) attrs_.push_back(dtb_attr_splits(schema_.by_ordinal(o)));
+        if (attrs_.empty()) throw ReferenceError("no candidate attributes in the schema");
+        table_ = flatten_splits(attrs_);
+        class_ord_ = schema_.class_field().ordinal;
+        int rec_len = conf_.get_int("dtb.rec.len", -1);
+        if (rec_len > 0)
+            for (auto& f : schema_.fields)
+                if (f.ordinal >= rec_len) throw ReferenceError("field ordinal " + std::to_string(f.ordinal) + " beyond record length");
+    }
+
+    // CSV rows -> columnar bin codes + class codes; with a tree available also the tagged path of
+    // every row (tree/DecisionTreeBuilder.java:268-320).
+    void encode(const std::vector<std::string>& lines, bool tagged, std::vector<std::vector<std::string>>& row_tagged) {
+        const size_t n = lines.size();
+        if (n == 0) throw ReferenceError("NullPointerException: no input rows (the reducer never sees a key)");
+        col8_.assign(attrs_.size(), {});
+        col16_.assign(attrs_.size(), {});
+        for (size_t a = 0; a < attrs_.size(); ++a) {
+            if (attrs_[a].n_bins > 256) col16_[a].resize(n);
+            else col8_[a].resize(n);
+        }
+        cls_.resize(n);
+        rows_.resize(n);
+        if (tagged) row_tagged.resize(n);
+        const int shift = tagged ? 1 : 0;
+        for (size_t r = 0; r < n; ++r) {
+            std::vector<std::string> items = split_str(lines[r], delim_regex_, true);
+            if (tagged) {
+                row_tagged[r] = split_str(items[0], path_delim_, false);
+                size_t pos = lines[r].find(delim_regex_);
+                if (pos == std::string::npos) throw ReferenceError("StringIndexOutOfBoundsException: row without a path field: " + lines[r]);
+                rows_[r] = lines[r].substr(pos + delim_regex_.size());
+            } else {
+                rows_[r] = lines[r];
+            }
+            for (size_t a = 0; a < attrs_.size(); ++a) {
+                const int ord = attrs_[a].ordinal;
+                if (ord + shift >= (int)items.size() || (tagged && ord > (int)items.size() - 2))
+                    throw ReferenceError("attrbite index out of bound attr:" + std::to_string(ord) + " rec length:" + std::to_string(items.size() - 1));
+                int b = encode_value(attrs_[a], items[(size_t)(ord + shift)]);
+                if (attrs_[a].n_bins > 256) col16_[a][r] = (uint16_t)b;
+                else col8_[a][r] = (uint8_t)b;
+            }
+            if (class_ord_ + shift >= (int)items.size()) throw ReferenceError("ArrayIndexOutOfBoundsException: class attribute missing in row: " + lines[r]);
+            cls_[r] = (uint8_t)classes_.code_of(items[(size_t)(class_ord_ + shift)]);
+        }
+        classes_.finish();
+    }
+
+    void upload() {
+        std::vector<int32_t> nb;
+        std::vector<const void*> cols;
+        for (size_t a = 0; a < attrs_.size(); ++a) {
+            nb.push_back(attrs_[a].n_bins);
+            cols.push_back(attrs_[a].n_bins > 256 ? (const void*)col16_[a].data() : (const void*)col8_[a].data());
+        }
+        eng_->check(avt_dataset_load(eng_->raw(), (int64_t)rows_.size(), (int32_t)attrs_.size(), nb.data(), cols.data(), cls_.data(), (int32_t)classes_.names.size()));
+        eng_->check(avt_split_table_set(eng_->raw(), (int32_t)table_.splits.size(), table_.splits.data(), table_.bounds.data(), (int32_t)table_.bounds.size(),
+                                        table_.lut.data(), (int64_t)table_.lut.size()));
+    }
+
+    // First pass: sampling (tree/DecisionTreeBuilder.java:209-243; `withReplace` = the intended
+    // buffer bootstrap, identical to explore/BaggingSampler.java:101-122).
+    void init_root_pass() {
+        const size_t n = rows_.size();
+        trees_.assign((size_t)num_trees_, Tree());
+        std::vector<const uint8_t*> wptr((size_t)num_trees_, nullptr);
+        for (int t = 0; t < num_trees_; ++t) {
+            Tree& tr = trees_[(size_t)t];
+            JavaRandom rng(seed_ + t);
+            if (sampling_ == "withReplace") {
+                tr.weights.assign(n, 0);
+                const size_t B = (size_t)std::max(1, sampling_buffer_);
+                for (size_t s = 0; s < n; s += B) {
+                    const size_t m = std::min(B, n - s);
+                    for (size_t i = 0; i < m; ++i) {
+                        size_t sel = (size_t)java_int_cast(rng.next_double() * (double)m);
+                        if (sel == m) sel = m - 1;
+                        if (tr.weights[s + sel] == 255) throw Unsupported("bootstrap multiplicity above 255");
+                        ++tr.weights[s + sel];
+                    }
+                }
+            } else if (sampling_ == "withoutReplace") {
+                tr.weights.assign(n, 0);
+                for (size_t r = 0; r < n; ++r)
+                    if (java_int_cast(rng.next_double() * 100) < sampling_rate_) tr.weights[r] = 1;
+            }
+            if (!tr.weights.empty()) wptr[(size_t)t] = tr.weights.data();
+            Node root;
+            root.tagged = {kRoot};
+            tr.frontier.push_back(root);
+        }
+        eng_->check(avt_forest_init(eng_->raw(), num_trees_, wptr.data(), nullptr));
+    }
+
+    // Tree available: node of a row = first decision path matched by its id-stripped path
+    // (tree/DecisionTreeBuilder.java:268-292; tree/DecisionPathList.java:71-81,198-214).
+    void init_from_paths(const std::vector<DecPath>& dec_in, const std::vector<std::vector<std::string>>& row_tagged) {
+        if (num_trees_ != 1) throw Unsupported("avt.forest.num.trees > 1 needs the in-process level loop (no dtb.decision.file.path.in)");
+        trees_.assign(1, Tree());
+        Tree& tr = trees_[0];
+        tr.frontier.resize(dec_in.size());
+        for (size_t i = 0; i < dec_in.size(); ++i) tr.frontier[i].path = dec_in[i];
+        if (dec_in.size() >= AVT_NODE_NONE) throw Unsupported("more than 65534 frontier nodes");
+        std::vector<uint16_t> nid(rows_.size(), (uint16_t)AVT_NODE_NONE);
+        JStrMap<int> cache;  // validDecPaths
+        for (size_t r = 0; r < rows_.size(); ++r) {
+            std::vector<std::string> stripped;
+            for (auto& it : row_tagged[r]) stripped.push_back(strip_id(it));
+            const std::string key = join_str(stripped, path_delim_);
+            int* hit = cache.find(key);
+            int node;
+            if (hit) {
+                node = *hit;
+            } else {
+                node = -1;
+                for (size_t i = 0; i < dec_in.size() && node < 0; ++i) {
+                    const DecPath& d = dec_in[i];
+                    if (!d.has_preds) {
+                        if (stripped[0] == kRoot) node = (int)i;
+                        continue;
+                    }
+                    bool ok = true;
+                    for (size_t k = 0; k < d.preds.size(); ++k) {
+                        if (k >= stripped.size()) throw ReferenceError("ArrayIndexOutOfBoundsException: row path shorter than decision path");
+                        if (d.preds[k].predicate_str != stripped[k]) { ok = false; break; }
+                    }
+                    if (ok) node = (int)i;
+                }
+                cache.put(key, node);
+            }
+            if (node >= 0) {
+                nid[r] = (uint16_t)node;
+                if (tr.frontier[(size_t)node].tagged.empty()) tr.frontier[(size_t)node].tagged = row_tagged[r];
+            }
+        }
+        const uint16_t* np = nid.data();
+        eng_->check(avt_forest_init(eng_->raw(), 1, nullptr, &np));
+    }
+
+    std::vector<int32_t> nodes_per_tree() const {
+        std::vector<int32_t> v;
+        for (auto& t : trees_) v.push_back((int32_t)t.frontier.size());
+        return v;
+    }
+
+    std::vector<std::pair<std::string, double>> class_pr(const uint32_t* cnt, long long total) const {
+        std::vector<std::pair<std::string, double>> pr;
+        for (uint8_t c : classes_.order)
+            if (cnt[c]) pr.emplace_back(classes_.names[c], (double)cnt[c] / (double)total);
+        return pr;
+    }
+
+    int criterion() const { return algorithm_ == "entropy" ? AVT_CRIT_ENTROPY : AVT_CRIT_GINI; }
+
+    // BuilderReducer.generateRoot (tree/DecisionTreeBuilder.java:478-493)
+    std::vector<std::vector<DecPath>> root_pass() {
+        auto npt = nodes_per_tree();
+        eng_->check(avt_level_histogram(eng_->raw(), npt.data(), nullptr));
+        std::vector<avt_node_best> best((size_t)num_trees_);
+        eng_->check(avt_level_scan(eng_->raw(), criterion(), nullptr, classes_.order.data(), best.data()));
+        std::vector<uint32_t> cc((size_t)num_trees_ * classes_.names.size());
+        eng_->check(avt_level_class_counts(eng_->raw(), cc.data()));
+        std::vector<std::vector<DecPath>> lists;
+        for (int t = 0; t < num_trees_; ++t) {
+            DecPath d;
+            d.population = best[(size_t)t].population;
+            if (d.population == 0) throw ReferenceError("NullPointerException: no rows reach the reducer in the root pass");
+            d.info_content = best[(size_t)t].node_stat;
+            d.class_val_pr = class_pr(&cc[(size_t)t * classes_.names.size()], d.population);
+            if (total_population_ > 0) d.support = (double)d.population / (double)total_population_;
+            trees_[(size_t)t].frontier[0].path = d;
+            lists.push_back({d});
+        }
+        return lists;
+    }
+
+    // candidate attribute columns of a node (tree/DecisionTreeBuilder.java:365-381;
+    // tree/SplitManager.java:195-232)
+    std::vector<int> candidates(const Node& nd) const {
+        std::vector<int> out;
+        if (attr_strategy_ == "all") {
+            for (size_t a = 0; a < attrs_.size(); ++a) out.push_back((int)a);
+            return out;
+        }
+        std::vector<int> used;
+        for (auto& it : nd.tagged) {
+            if (it == kRoot) continue;
+            std::string s = strip_id(it);
+            used.push_back(std::stoi(s.substr(0, s.find(' '))));
+        }
+        for (size_t a = 0; a < attrs_.size(); ++a)
+            if (std::find(used.begin(), used.end(), attrs_[a].ordinal) == used.end()) out.push_back((int)a);
+        return out;
+    }
+
+    struct NodeOrder {
+        std::vector<int> split_order;                       // table indices in splitInfoContent.keySet() order
+        std::vector<std::vector<int>> seg_order_by_split;   // per table index: segments in predInfoContent.keySet() order
+    };
+
+    // Replays the insertion chain that fixes the reference's iteration orders for one parent:
+    // reducer keys arrive sorted -> childStats (HashMap<"id:pred">) -> infoContentBySplit regroups
+    // into splitInfoContent (HashMap<id>) and predInfoContent (HashMap<pred>)
+    // (tree/DecisionTreeBuilder.java:730-767, 636-668).  `hist` = the node's [TB][C] counts.
+    NodeOrder java_order(const Node& nd, const std::vector<uint32_t>& hist) const {
+        const int C = (int)classes_.names.size();
+        struct Key { std::string s; int table_idx; int seg; };
+        std::vector<Key> keys;
+        int split_id = 0;
+        std::vector<int> bin_off(attrs_.size() + 1, 0);
+        for (size_t a = 0; a < attrs_.size(); ++a) bin_off[a + 1] = bin_off[a] + attrs_[a].n_bins;
+        for (int a : nd.cand) {
+            const AttrSplits& as = attrs_[(size_t)a];
+            for (size_t k = 0; k < as.splits.size(); ++k) {
+                ++split_id;
+                const HostSplit& h = as.splits[k];
+                std::vector<char> present((size_t)h.n_seg, 0);
+                for (int b = 0; b < as.n_bins; ++b) {
+                    bool any = false;
+                    for (int c = 0; c < C; ++c) any = any || hist[(size_t)(bin_off[(size_t)a] + b) * C + c] != 0;
+                    if (!any) continue;
+                    int sg = split_segment_of_bin(as, h, b);
+                    if (sg >= 0) present[(size_t)sg] = 1;
+                }
+                for (int sg = 0; sg < h.n_seg; ++sg)
+                    if (present[(size_t)sg]) keys.push_back({std::to_string(split_id) + ":" + h.pred_str[(size_t)sg], table_.attr_first[(size_t)a] + (int)k, sg});
+            }
+        }
+        std::sort(keys.begin(), keys.end(), [](const Key& x, const Key& y) { return x.s < y.s; });
+        JStrMap<int> child_stats;
+        for (size_t i = 0; i < keys.size(); ++i) child_stats.put(keys[i].s, (int)i);
+        JStrMap<int> split_map;                    // split id string -> slot
+        std::vector<JStrMap<int>> pred_maps;       // per slot: predicate -> key index
+        std::vector<int> slot_table_idx;
+        child_stats.for_each([&](const std::string& k, int& ki) {
+            size_t p = k.find(':');
+            std::string sid = k.substr(0, p), pred = k.substr(p + 1);
+            int* slot = split_map.find(sid);
+            if (!slot) {
+                pred_maps.emplace_back();
+                slot_table_idx.push_back(keys[(size_t)ki].table_idx);
+                slot = &split_map.put(sid, (int)pred_maps.size() - 1);
+            }
+            pred_maps[(size_t)*slot].put(pred, ki);
+        });
+        NodeOrder o;
+        o.seg_order_by_split.resize(table_.splits.size());
+        split_map.for_each([&](const std::string&, int& slot) {
+            const int ti = slot_table_idx[(size_t)slot];
+            o.split_order.push_back(ti);
+            pred_maps[(size_t)slot].for_each([&](const std::string&, int& ki) { o.seg_order_by_split[(size_t)ti].push_back(keys[(size_t)ki].seg); });
+        });
+        return o;
+    }
+
+    // Parent iteration order of decPathsInfoContentBySplit.keySet() (tree/DecisionTreeBuilder.java:
+    // 512, 640-650): parents enter `decPaths` in reducer key order (Tuple order, element-wise),
+    // are re-inserted id-stripped in decPaths.keySet() order, then iterated.
+    std::vector<int> parent_order(const Tree& tr, const std::vector<int>& live) const {
+        std::vector<int> sorted = live;
+        std::sort(sorted.begin(), sorted.end(), [&](int x, int y) { return tr.frontier[(size_t)x].tagged < tr.frontier[(size_t)y].tagged; });
+        JStrMap<int> dec_paths;
+        for (int i : sorted) dec_paths.put(join_str(tr.frontier[(size_t)i].tagged, path_delim_), i);
+        JStrMap<int> by_split;
+        dec_paths.for_each([&](const std::string&, int& i) {
+            std::vector<std::string> st;
+            for (auto& it : tr.frontier[(size_t)i].tagged) st.push_back(strip_id(it));
+            std::string k = join_str(st, path_delim_);
+            if (!by_split.find(k)) by_split.put(k, i);
+        });
+        std::vector<int> out;
+        by_split.for_each([&](const std::string&, int& i) { out.push_back(i); });
+        return out;
+    }
+
+    // DecisionPathStoppingStrategy.shouldStop (tree/DecisionPathStoppingStrategy.java:57-70)
+    bool should_stop(long long population, double stat, double parent_stat, int depth) const {
+        if (stop_strategy_ == "minPopulation") return population < min_population_;
+        if (stop_strategy_ == "minInfoGain") return (parent_stat - stat) < min_info_gain_;
+        return depth >= max_depth_;
+    }
+
+    // One level for every tree: BuilderReducer.expandTree (tree/DecisionTreeBuilder.java:499-616).
+    bool expand_level(std::vector<std::vector<DecPath>>& lists, std::vector<bool>& list_null) {
+        const int C = (int)classes_.names.size();
+        const int A = (int)attrs_.size();
+        const int mw = (A + 31) / 32;
+        auto npt = nodes_per_tree();
+        std::vector<int> base((size_t)num_trees_ + 1, 0);
+        for (int t = 0; t < num_trees_; ++t) base[(size_t)t + 1] = base[(size_t)t] + npt[(size_t)t];
+        const int NF = base[(size_t)num_trees_];
+        lists.assign((size_t)num_trees_, {});
+        list_null.assign((size_t)num_trees_, true);
+        if (NF == 0) return false;
+        eng_->check(avt_level_histogram(eng_->raw(), npt.data(), nullptr));
+        std::vector<uint32_t> mask((size_t)NF * mw, 0);
+        for (int t = 0; t < num_trees_; ++t)
+            for (size_t i = 0; i < trees_[(size_t)t].frontier.size(); ++i) {
+                Node& nd = trees_[(size_t)t].frontier[i];
+                nd.cand = candidates(nd);
+                for (int a : nd.cand) mask[(size_t)(base[(size_t)t] + (int)i) * mw + (a >> 5)] |= 1u << (a & 31);
+            }
+        std::vector<avt_node_best> best((size_t)NF);
+        eng_->check(avt_level_scan(eng_->raw(), criterion(), mask.data(), classes_.order.data(), best.data()));
+
+        // choose the split of every live node; ties go through the HashMap-order replay
+        std::vector<int> chosen((size_t)NF, -1);
+        std::vector<NodeOrder> orders((size_t)NF);
+        std::vector<char> have_order((size_t)NF, 0);
+        std::vector<uint32_t> hist((size_t)table_bins() * C);
+        std::vector<double> av(table_.splits.size());
+        auto need_order = [&](int g, const Node& nd) {
+            if (have_order[(size_t)g]) return;
+            eng_->check(avt_level_fetch_hist(eng_->raw(), g, hist.data()));
+            orders[(size_t)g] = java_order(nd, hist);
+            have_order[(size_t)g] = 1;
+        };
+        for (int t = 0; t < num_trees_; ++t)
+            for (size_t i = 0; i < trees_[(size_t)t].frontier.size(); ++i) {
+                const int g = base[(size_t)t] + (int)i;
+                const Node& nd = trees_[(size_t)t].frontier[i];
+                const avt_node_best& b = best[(size_t)g];
+                if (b.population == 0 || b.best_split < 0) continue;  // no rows or no candidate split: nothing is emitted for this parent
+                chosen[(size_t)g] = b.best_split;
+                if (b.n_ties > 1) {
+                    need_order(g, nd);
+                    eng_->check(avt_level_fetch_av(eng_->raw(), g, av.data()));
+                    for (int ti : orders[(size_t)g].split_order)
+                        if (av[(size_t)ti] == b.min_av) { chosen[(size_t)g] = ti; break; }
+                }
+            }
+        std::vector<int32_t> ev_nodes, ev_splits;
+        for (int g = 0; g < NF; ++g)
+            if (chosen[(size_t)g] >= 0) { ev_nodes.push_back(g); ev_splits.push_back(chosen[(size_t)g]); }
+        std::vector<avt_split_eval> evals(ev_nodes.size());
+        eng_->check(avt_level_eval(eng_->raw(), criterion(), classes_.order.data(), (int32_t)ev_nodes.size(), ev_nodes.data(), ev_splits.data(), evals.data()));
+        std::vector<int> eval_of((size_t)NF, -1);
+        for (size_t k = 0; k < ev_nodes.size(); ++k) eval_of[(size_t)ev_nodes[k]] = (int)k;
+
+        int lut_w = 1;
+        for (auto& as : attrs_) lut_w = std::max(lut_w, as.n_bins);
+        std::vector<int32_t> node_attr((size_t)NF, -1);
+        std::vector<uint16_t> child_lut((size_t)NF * lut_w, (uint16_t)AVT_NODE_NONE);
+        bool any = false;
+        for (int t = 0; t < num_trees_; ++t) {
+            Tree& tr = trees_[(size_t)t];
+            std::vector<int> live;
+            for (size_t i = 0; i < tr.frontier.size(); ++i)
+                if (chosen[(size_t)(base[(size_t)t] + (int)i)] >= 0) live.push_back((int)i);
+            std::vector<Node> next;
+            std::vector<DecPath>& out_list = lists[(size_t)t];
+            for (int i : parent_order(tr, live)) {
+                const int g = base[(size_t)t] + i;
+                const Node& nd = tr.frontier[(size_t)i];
+                const int ti = chosen[(size_t)g];
+                const avt_split& ds = table_.splits[(size_t)ti];
+                const AttrSplits& as = attrs_[(size_t)ds.attr];
+                const HostSplit& hs = as.splits[(size_t)(ti - table_.attr_first[(size_t)ds.attr])];
+                const avt_split_eval& ev = evals[(size_t)eval_of[(size_t)g]];
+                // running split id of the chosen split among this node's candidates (:299,325)
+                int split_id = 0;
+                for (int a : nd.cand) {
+                    if (a == ds.attr) { split_id += ti - table_.attr_first[(size_t)a] + 1; break; }
+                    split_id += (int)attrs_[(size_t)a].splits.size();
+                }
+                // children in predInfoContent.keySet() order
+                std::vector<int> segs;
+                std::vector<long long> seg_n((size_t)hs.n_seg, 0);
+                for (int sg = 0; sg < hs.n_seg; ++sg) {
+                    for (int c = 0; c < C; ++c) seg_n[(size_t)sg] += ev.seg_count[sg][c];
+                    if (seg_n[(size_t)sg]) segs.push_back(sg);
+                }
+                if (segs.size() == 2) {
+                    uint32_t b0 = StrHasher()(hs.pred_str[(size_t)segs[0]]) & 15u, b1 = StrHasher()(hs.pred_str[(size_t)segs[1]]) & 15u;
+                    if (b0 == b1) {
+                        need_order(g, nd);
+                        segs = orders[(size_t)g].seg_order_by_split[(size_t)ti];
+                    } else if (b1 < b0) {
+                        std::swap(segs[0], segs[1]);
+                    }
+                } else if (segs.size() > 2) {
+                    need_order(g, nd);
+                    segs = orders[(size_t)g].seg_order_by_split[(size_t)ti];
+                }
+                // parent predicates (tree/DecisionPathList.java:454-472)
+                std::vector<PathPred> parent_preds;
+                for (auto& it : nd.tagged) {
+                    if (it == kRoot) { parent_preds.push_back(root_pred()); continue; }
+                    std::string s = strip_id(it);
+                    parent_preds.push_back(make_pred(s, schema_.by_ordinal(std::stoi(s.substr(0, s.find(' '))))));
+                }
+                const double parent_stat = nd.path.info_content;
+                node_attr[(size_t)g] = ds.attr;
+                for (int sg : segs) {
+                    DecPath d;
+                    d.has_preds = true;
+                    d.preds = parent_preds;
+                    d.preds.push_back(make_pred(hs.pred_str[(size_t)sg], *as.field));
+                    d.population = seg_n[(size_t)sg];
+                    d.info_content = ev.seg_stat[sg];
+                    d.stopped = should_stop(d.population, d.info_content, parent_stat, (int)parent_preds.size() + 1);
+                    d.class_val_pr = class_pr(ev.seg_count[sg], d.population);
+                    majority(d);
+                    if (total_population_ > 0) d.support = (double)d.population / (double)total_population_;
+                    Node ch;
+                    ch.tagged = nd.tagged;
+                    ch.tagged.push_back(std::to_string(split_id) + ":" + hs.pred_str[(size_t)sg]);
+                    ch.path = d;
+                    if (next.size() >= AVT_NODE_NONE - 1) throw Unsupported("more than 65534 frontier nodes in one tree");
+                    const uint16_t child_id = (uint16_t)next.size();
+                    for (int b = 0; b < as.n_bins; ++b)
+                        if (split_segment_of_bin(as, hs, b) == sg) child_lut[(size_t)g * lut_w + b] = child_id;
+                    next.push_back(ch);
+                    out_list.push_back(d);
+                }
+            }
+            list_null[(size_t)t] = live.empty();
+            any = any || !next.empty();
+            tr.frontier.swap(next);
+        }
+        eng_->check(avt_level_repartition(eng_->raw(), node_attr.data(), child_lut.data(), lut_w));
+        return any;
+    }
+
+    int table_bins() const {
+        int tb = 0;
+        for (auto& a : attrs_) tb += a.n_bins;
+        return tb;
+    }
+
+    std::string list_path(int t) const {
+        std::string p = conf_.get("dtb.decision.file.path.out");
+        return num_trees_ == 1 ? p : p + ".tree" + std::to_string(t);
+    }
+
+    // writeDecisioList (tree/DecisionTreeBuilder.java:713-725)
+    void write_lists(const std::vector<std::vector<DecPath>>& lists, const std::vector<bool>* is_null = nullptr) {
+        for (int t = 0; t < num_trees_; ++t) {
+            const bool null_list = is_null && (*is_null)[(size_t)t];
+            if (null_list && total_population_ > 0) throw ReferenceError("NullPointerException in DecisionPathList.withTotalPopulation: no decision path was generated");
+            const std::string text = path_list_json(null_list ? nullptr : &lists[(size_t)t]) + "\n";
+            write_text(list_path(t), text);
+            // with the in-process level loop every pass is also kept (the reference overwrites one file per job)
+            if (num_levels_ > 1) write_text(list_path(t) + ".level" + std::to_string(pass_), text);
+        }
+        ++pass_;
+    }
+
+    std::string data_dir(int t) const { return num_trees_ == 1 ? out_path_ : out_path_ + "/tree" + std::to_string(t); }
+
+    // "$root,<row>" for every sampled row (tree/DecisionTreeBuilder.java:248-258, 761-766)
+    void write_root_data() {
+        for (int t = 0; t < num_trees_; ++t) {
+            std::vector<std::string> out;
+            const Tree& tr = trees_[(size_t)t];
+            for (size_t r = 0; r < rows_.size(); ++r) {
+                int w = tr.weights.empty() ? 1 : tr.weights[r];
+                for (int k = 0; k < w; ++k) out.push_back(std::string(kRoot) + delim_out_ + rows_[r]);
+            }
+            write_output_lines(data_dir(t), out);
+        }
+    }
+
+    // After expansions: every row under its new path, selected split only (the records the next
+    // pass's mapper would keep, tree/DecisionTreeBuilder.java:279-292), in
+    // reducer key order.
+    void write_level_data() {
+        std::vector<uint16_t> nid(rows_.size());
+        for (int t = 0; t < num_trees_; ++t) {
+            const Tree& tr = trees_[(size_t)t];
+            eng_->check(avt_forest_node_ids(eng_->raw(), t, nid.data()));
+            std::vector<int> order(tr.frontier.size());
+            for (size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
+            std::sort(order.begin(), order.end(), [&](int x, int y) { return tr.frontier[(size_t)x].tagged < tr.frontier[(size_t)y].tagged; });
+            std::vector<std::vector<size_t>> rows_of(tr.frontier.size());
+            for (size_t r = 0; r < rows_.size(); ++r)
+                if (nid[r] != AVT_NODE_NONE && nid[r] < tr.frontier.size()) rows_of[nid[r]].push_back(r);
+            std::vector<std::string> out;
+            for (int i : order) {
+                const std::string key = join_str(tr.frontier[(size_t)i].tagged, path_delim_);
+                for (size_t r : rows_of[(size_t)i]) {
+                    int w = tr.weights.empty() ? 1 : tr.weights[r];
+                    for (int k = 0; k < w; ++k) out.push_back(key + delim_out_ + rows_[r]);
+                }
+            }
+            write_output_lines(data_dir(t), out);
+        }
+    }
+};
+
+}  // namespace
+
+int run_decision_tree_builder(const Props& conf, const std::string& in_path, const std::string& out_path) {
+    DtbJob job(conf, in_path, out_path);
+    return job.run();
+}
+
+}  // namespace avt_host

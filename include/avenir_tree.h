@@ -1,0 +1,214 @@
+/*
+ * avenir_tree.h -- C-ABI of libavenir_tree.so, the B200-native split-evaluation engine that sits
+ * behind avenir's tree-building path (DecisionTreeBuilder / ClassPartitionGenerator / bagged
+ * forests).
+ *
+ * The reference (kutieme/avenir) is pure JVM code and has NO native/FFI interface; the seams this
+ * ABI replaces are Java object seams.  Each entry point below cites the reference code whose work
+ * it takes over (paths relative to src/main/java/org/avenir/).  INTEGRATION.md shows the Panama
+ * FFM / JNI binding a maintainer would add on the Java side.
+ *
+ * Conventions
+ *   - plain C types, caller-owned host buffers, library-owned device memory behind an opaque handle;
+ *   - every function returns 0 on success, a negative AVT_E_* code on failure; the message is
+ *     available through avt_last_error();  no exception crosses the boundary;
+ *   - one engine = one CUDA device + one stream; an engine is single-threaded, distinct engines are
+ *     independent;  multi-GPU = one process (engine) per GPU joined by avt_comm_init_rank();
+ *   - there is NO CPU fallback: without a CUDA device avt_create() fails.
+ *
+ * Data layout handed over by the host (encoded ONCE from the CSV rows, Appendix F of SURVEY.md):
+ *   - columnar bin codes: for attribute a, column[a][r] = bin of row r (uint8 if n_bins[a] <= 256,
+ *     else uint16).  Numeric: bin = #{grid points p_k < value}; categorical: index in `cardinality`;
+ *   - class codes uint8[n_rows];
+ *   - per tree: node id uint16[n_rows] (AVT_NODE_NONE = row not in any frontier node) and an
+ *     optional bootstrap multiplicity uint8[n_rows].
+ */
+#ifndef AVENIR_TREE_H
+#define AVENIR_TREE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AVT_OK 0
+#define AVT_E_INVALID (-1)   /* bad argument / unsupported configuration */
+#define AVT_E_CUDA (-2)      /* CUDA runtime error (message has the CUDA error string) */
+#define AVT_E_STATE (-3)     /* call out of order (e.g. scan before histogram) */
+#define AVT_E_NOMEM (-4)
+#define AVT_E_COMM (-5)      /* NCCL error */
+#define AVT_E_IO (-6)        /* tool level: file / parse error */
+#define AVT_E_REFERENCE (-7) /* tool level: a configuration on which the reference itself fails */
+
+#define AVT_NODE_NONE 0xFFFFu
+#define AVT_MAX_CLASSES 16
+#define AVT_MAX_SEG 8
+
+#define AVT_CRIT_GINI 0
+#define AVT_CRIT_ENTROPY 1
+#define AVT_CRIT_HELLINGER 2
+#define AVT_CRIT_CLASS_CONF 3
+
+#define AVT_SPLIT_NUMERIC 0 /* segments are contiguous bin ranges given by upper bounds */
+#define AVT_SPLIT_LUT 1     /* segments given by a per-bin uint8 segment table */
+
+typedef struct avt_engine avt_engine;
+
+/* One candidate split.  Splits of one attribute must be contiguous in the table; the table order
+ * is the reference's enumeration order (tree/SplitManager.java:256-330,405-569;
+ * explore/ClassPartitionGenerator.java:235-443), so index+1 within a node's candidate list is the
+ * reference's running splitId (tree/DecisionTreeBuilder.java:299,325). */
+typedef struct avt_split {
+    int32_t attr;  /* attribute (column) index in the loaded dataset */
+    int32_t kind;  /* AVT_SPLIT_NUMERIC | AVT_SPLIT_LUT */
+    int32_t n_seg; /* number of segments, 2..AVT_MAX_SEG */
+    int32_t off;   /* NUMERIC: index into `bounds` of n_seg-1 inclusive upper bin bounds;
+                      LUT:     index into `seg_lut` of n_bins[attr] segment ids */
+} avt_split;
+
+/* Result of the fused impurity scan for one frontier node. */
+typedef struct avt_node_best {
+    double min_av;      /* minimum weighted-average impurity over the node's candidate splits */
+    double node_stat;   /* impurity of the node itself (InfoContentStat.processStat on its rows) */
+    int64_t population; /* rows (weighted) in the node */
+    int32_t best_split; /* lowest table index attaining min_av, -1 if the node has no candidate */
+    int32_t n_ties;     /* number of candidate splits whose av compares == to min_av */
+} avt_node_best;
+
+/* Statistics of the children one (node, split) pair would create. */
+typedef struct avt_split_eval {
+    double av;                                        /* weighted average impurity of the split */
+    double seg_stat[AVT_MAX_SEG];                     /* impurity per segment (0 if empty) */
+    uint32_t seg_count[AVT_MAX_SEG][AVT_MAX_CLASSES]; /* class counts per segment */
+} avt_split_eval;
+
+/* Statistics of one ClassPartitionGenerator split (explore/ClassPartitionGenerator.java:514-553). */
+typedef struct avt_cpg_stat {
+    double stat;       /* SplitStat.processStat: weighted impurity / Hellinger / class-conf ratio */
+    double split_info; /* SplitStat.getInfoContent: intrinsic information of the segment sizes */
+    uint32_t seg_count[AVT_MAX_SEG][AVT_MAX_CLASSES];
+} avt_cpg_stat;
+
+typedef struct avt_stats {
+    double hist_ms, scan_ms, eval_ms, repart_ms, comm_ms, h2d_ms; /* accumulated device time */
+    int64_t hist_launches, scan_launches, eval_launches, repart_launches, comm_calls;
+    int64_t hist_alg_bytes; /* algorithmic bytes of all histogram passes so far */
+    int64_t repart_alg_bytes;
+    int32_t last_hist_variant; /* 0 shared-memory privatised, 1 global atomics (match_any) */
+    int32_t last_hist_replicas;
+    int32_t last_hist_grid, last_hist_block, last_hist_smem;
+} avt_stats;
+
+/* ---- engine ------------------------------------------------------------------------------- */
+
+/* Creates an engine on CUDA device `device`.  Replaces nothing in the reference (which has no
+ * device notion); it is the per-task state a BuilderMapper/BuilderReducer pair keeps in fields
+ * (tree/DecisionTreeBuilder.java:102-131, 388-412). */
+int avt_create(int device, avt_engine** out);
+void avt_destroy(avt_engine* e);
+/* Message of the last failure on `e` (or of the last failed avt_create when e == NULL). */
+const char* avt_last_error(const avt_engine* e);
+
+/* Uploads the once-encoded columnar data set.  Replaces the per-level re-read and re-parse of the
+ * text rows in BuilderMapper.pathMapHelper (tree/DecisionTreeBuilder.java:266-320).
+ * columns[a] is uint8[n_rows] when n_bins[a] <= 256, else uint16[n_rows]. */
+int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins,
+                     const void* const* columns, const uint8_t* class_codes, int32_t n_classes);
+
+/* Starts `n_trees` trees over the loaded rows.  weights == NULL or weights[t] == NULL means
+ * multiplicity 1 for every row (dtb.sub.sampling.strategy=none); otherwise weights[t][r] is the
+ * number of times row r was drawn for tree t (explore/BaggingSampler.java:101-122 semantics).
+ * node_ids == NULL or node_ids[t] == NULL puts every row in node 0 (the $root pass,
+ * tree/DecisionTreeBuilder.java:248-258); otherwise node_ids[t][r] is the frontier node of row r
+ * (AVT_NODE_NONE = dropped), as recovered from a path-tagged input file (:268-292). */
+int avt_forest_init(avt_engine* e, int32_t n_trees, const uint8_t* const* weights,
+                    const uint16_t* const* node_ids);
+
+/* Installs the candidate-split table shared by all nodes. */
+int avt_split_table_set(avt_engine* e, int32_t n_splits, const avt_split* splits,
+                        const int32_t* bounds, int32_t n_bounds, const uint8_t* seg_lut,
+                        int64_t n_lut);
+
+/* Kernel (a): count histograms H[tree][node][attr][bin][class] for the current frontier, all
+ * trees in one launch.  Replaces the mapper-side emission of one record per (row, split, true
+ * predicate) plus the shuffle and the reducer-side counting (tree/DecisionTreeBuilder.java:
+ * 323-352, 730-767; util/InfoContentStat.java:50-64).  nodes_per_tree[t] = frontier size of tree t.
+ * With a communicator attached the histogram is all-reduced (sum) over the ranks.
+ * hist_out (nullable) receives the [sum nodes][total_bins][n_classes] uint32 counts. */
+int avt_level_histogram(avt_engine* e, const int32_t* nodes_per_tree, uint32_t* hist_out);
+
+/* Kernel (b): fused gini/entropy scan + per-node arg-min.  Replaces BuilderReducer.expandTree's
+ * per-parent split loop (tree/DecisionTreeBuilder.java:512-565) and InfoContentStat.processStat
+ * (util/InfoContentStat.java:71-101).  cand_mask (nullable = every attribute) holds, per frontier
+ * node, ceil(n_attrs/32) words with bit a set when attribute a is a candidate
+ * (getSplitAttributes, :365-381).  class_order (nullable = 0..C-1) is the order in which class
+ * terms are summed (HashMap order of the class strings).  out[node] is filled for
+ * every frontier node. */
+int avt_level_scan(avt_engine* e, int32_t criterion, const uint32_t* cand_mask,
+                   const uint8_t* class_order, avt_node_best* out);
+
+/* Per-split av values of one node from the last scan (NaN where the split's attribute is not a
+ * candidate); the host needs them only to resolve ties in the reference's HashMap order. */
+int avt_level_fetch_av(avt_engine* e, int32_t node, double* av_out);
+
+/* Raw counts [total_bins][n_classes] of one frontier node of the last histogram; the host needs them
+ * only to know which (split, segment) pairs received rows when it replays the reference's HashMap
+ * insertion orders. */
+int avt_level_fetch_hist(avt_engine* e, int32_t node, uint32_t* hist_out);
+
+/* Children statistics for chosen (node, split) pairs (tree/DecisionTreeBuilder.java:575-611). */
+int avt_level_eval(avt_engine* e, int32_t criterion, const uint8_t* class_order, int32_t n,
+                   const int32_t* nodes, const int32_t* splits, avt_split_eval* out);
+
+/* Kernel (c): row -> child node.  Replaces the re-keying of every row with its new path and the
+ * next mapper's path filter (tree/DecisionTreeBuilder.java:333-349, 279-292).  For frontier node g
+ * (global index over trees), node_attr[g] is the attribute of its selected split (-1: the node is
+ * not expanded, its rows leave the frontier) and child_lut[g*lut_width + bin] the tree-local id of
+ * the child that bin falls in (AVT_NODE_NONE: none). */
+int avt_level_repartition(avt_engine* e, const int32_t* node_attr, const uint16_t* child_lut,
+                          int32_t lut_width);
+
+/* ClassPartitionGenerator sweep over every split of the installed table for the rows of frontier
+ * node `node` (use 0 after avt_forest_init(1, NULL, NULL) for "all rows") of the last histogram.
+ * Replaces PartitionGeneratorMapper.map + Combiner + Reducer (explore/ClassPartitionGenerator.java:
+ * 200-230, 450-463, 514-592) and util/AttributeSplitStat.java:153-170,191-218,240-282,298-336.
+ * class_order2 (Hellinger) = the two class codes in HashSet order. */
+int avt_cpg_sweep(avt_engine* e, int32_t node, int32_t criterion, const uint8_t* class_order,
+                  avt_cpg_stat* out);
+
+/* Copies back tree t's node ids (uint16[n_rows]). */
+int avt_forest_node_ids(avt_engine* e, int32_t tree, uint16_t* out);
+/* Copies back the class counts of every frontier node of the last histogram ([nodes][n_classes]). */
+int avt_level_class_counts(avt_engine* e, uint32_t* out);
+
+/* Device timer on the engine's stream (CUDA events): begin .. end -> elapsed milliseconds. */
+int avt_timer_begin(avt_engine* e);
+int avt_timer_end(avt_engine* e, float* ms);
+int avt_synchronize(avt_engine* e);
+int avt_get_stats(avt_engine* e, avt_stats* out);
+int avt_reset_stats(avt_engine* e);
+/* Forces a histogram variant (-1 auto, 0 shared-memory, 1 global atomics) -- for tests/profiling. */
+int avt_set_hist_variant(avt_engine* e, int32_t variant);
+
+/* ---- multi-GPU: one process per GPU, rows sharded, histograms summed over NVLink ------------- */
+/* Fills 128 bytes with an NCCL unique id (rank 0 calls it, the host broadcasts it). */
+int avt_comm_unique_id(void* id128);
+/* Joins the communicator.  From then on avt_level_histogram all-reduces H over the ranks: the one
+ * exchange step of the path (the role of Hadoop's shuffle between BuilderMapper and
+ * BuilderReducer, tree/DecisionTreeBuilder.java:80-93). */
+int avt_comm_init_rank(avt_engine* e, int32_t n_ranks, int32_t rank, const void* id128);
+
+/* ---- tool level: the reference's own entry points -------------------------------------------- */
+/* ToolRunner.run(new <tool>(), args): tool is "org.avenir.tree.DecisionTreeBuilder" or
+ * "org.avenir.explore.ClassPartitionGenerator" (short names accepted); args are the Hadoop-style
+ * arguments `-Dconf.path=<file.properties> [-Dkey=value ...] <inPath> <outPath>`
+ * (tree/DecisionTreeBuilder.java:70-95,773-776; explore/ClassPartitionGenerator.java:64-91,611-614).
+ * Returns 0 (success) or 1 (failure, message in errbuf) like the reference's exit status. */
+int avt_tool_run(const char* tool, int argc, const char* const* argv, char* errbuf, size_t errlen);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AVENIR_TREE_H */
