@@ -80,6 +80,8 @@ struct avt_engine {
     // splits
     int S = 0;
     std::vector<avt_split> splits;
+    std::vector<int32_t> h_bounds;
+    std::vector<uint8_t> h_seg_lut;
     DevBuf<avt_split> d_splits;
     DevBuf<int32_t> d_bounds, d_attr_first;
     DevBuf<uint8_t> d_seg_lut;
@@ -374,6 +376,8 @@ int avt_split_table_set(avt_engine* e, int32_t n_splits, const avt_split* splits
     for (int a = prev + 1; a <= e->A; ++a) attr_first[a] = n_splits;
     e->S = n_splits;
     e->splits.assign(splits, splits + n_splits);
+    e->h_bounds.assign(bounds, bounds + std::max(n_bounds, 0));
+    e->h_seg_lut.assign(seg_lut, seg_lut + std::max<int64_t>(n_lut, 0));
     if (int rc = upload(e, e->d_splits, splits, (size_t)n_splits)) return rc;
     if (int rc = upload(e, e->d_bounds, bounds, (size_t)std::max(n_bounds, 0))) return rc;
     if (int rc = upload(e, e->d_seg_lut, seg_lut, (size_t)std::max<int64_t>(n_lut, 0))) return rc;
@@ -621,6 +625,87 @@ int avt_level_repartition(avt_engine* e, const int32_t* node_attr, const uint16_
     e->hist_valid = e->scan_valid = false;
     e->NF = 0;
     return AVT_OK;
+}
+
+int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
+                    avt_grow_record* records, int64_t max_records, int64_t* n_records) {
+    if (!e) return AVT_E_INVALID;
+    if (!nodes_per_tree) return fail(e, AVT_E_INVALID, "avt_grow_levels: nodes_per_tree is NULL");
+    if (e->T == 0 || e->S == 0) return fail(e, AVT_E_STATE, "avt_grow_levels: needs avt_forest_init and avt_split_table_set first");
+    int64_t nrec = 0;
+    int lut_w = 1;
+    for (int a = 0; a < e->A; ++a) lut_w = std::max(lut_w, e->n_bins[a]);
+    std::vector<avt_node_best> best;
+    std::vector<avt_split_eval> evals;
+    std::vector<int32_t> ev_nodes, ev_splits, node_attr;
+    std::vector<uint16_t> child_lut;
+    for (int level = 0; level < n_levels; ++level) {
+        int NF = 0;
+        for (int t = 0; t < e->T; ++t) NF += nodes_per_tree[t];
+        if (NF == 0) break;
+        if (int rc = avt_level_histogram(e, nodes_per_tree, nullptr)) return rc;
+        best.resize((size_t)NF);
+        if (int rc = avt_level_scan(e, criterion, nullptr, class_order, best.data())) return rc;
+        ev_nodes.clear();
+        ev_splits.clear();
+        for (int g = 0; g < NF; ++g)
+            if (best[(size_t)g].population > 0 && best[(size_t)g].best_split >= 0) {
+                ev_nodes.push_back(g);
+                ev_splits.push_back(best[(size_t)g].best_split);
+            }
+        evals.resize(ev_nodes.size() ? ev_nodes.size() : 1);
+        if (int rc = avt_level_eval(e, criterion, class_order, (int32_t)ev_nodes.size(), ev_nodes.data(), ev_splits.data(), evals.data())) return rc;
+        node_attr.assign((size_t)NF, -1);
+        child_lut.assign((size_t)NF * lut_w, (uint16_t)AVT_NODE_NONE);
+        size_t k = 0;
+        int base = 0;
+        for (int t = 0; t < e->T; ++t) {
+            int next = 0;
+            for (int i = 0; i < nodes_per_tree[t]; ++i) {
+                const int g = base + i;
+                if (k >= ev_nodes.size() || ev_nodes[k] != g) continue;
+                const int s = ev_splits[k];
+                const avt_split_eval& ev = evals[k];
+                ++k;
+                const avt_split& sp = e->splits[(size_t)s];
+                node_attr[(size_t)g] = sp.attr;
+                avt_grow_record rec{};
+                rec.level = level; rec.tree = t; rec.node = i; rec.split = s;
+                rec.n_ties = best[(size_t)g].n_ties;
+                rec.min_av = best[(size_t)g].min_av;
+                for (int sg = 0; sg < AVT_MAX_SEG; ++sg) rec.child[sg] = -1;
+                for (int sg = 0; sg < sp.n_seg; ++sg) {
+                    int64_t pop = 0;
+                    for (int c = 0; c < e->C; ++c) pop += ev.seg_count[sg][c];
+                    rec.child_pop[sg] = pop;
+                    rec.child_stat[sg] = ev.seg_stat[sg];
+                    if (pop) {
+                        if (next >= (int)AVT_NODE_NONE - 1) return fail(e, AVT_E_INVALID, "avt_grow_levels: more than %d frontier nodes in tree %d", AVT_NODE_NONE - 1, t);
+                        rec.child[sg] = next++;
+                    }
+                }
+                const int B = e->n_bins[sp.attr];
+                for (int b = 0; b < B; ++b) {
+                    int sg;
+                    if (sp.kind == AVT_SPLIT_NUMERIC) {
+                        sg = 0;
+                        while (sg < sp.n_seg - 1 && b > e->h_bounds[(size_t)(sp.off + sg)]) ++sg;
+                    } else {
+                        sg = e->h_seg_lut[(size_t)(sp.off + b)];
+                        if (sg >= sp.n_seg) continue;
+                    }
+                    if (rec.child[sg] >= 0) child_lut[(size_t)g * lut_w + b] = (uint16_t)rec.child[sg];
+                }
+                if (records && nrec < max_records) records[nrec] = rec;
+                ++nrec;
+            }
+            base += nodes_per_tree[t];
+            nodes_per_tree[t] = next;
+        }
+        if (int rc = avt_level_repartition(e, node_attr.data(), child_lut.data(), lut_w)) return rc;
+    }
+    if (n_records) *n_records = nrec;
+    return sync_and_resolve(e);
 }
 
 int avt_cpg_sweep(avt_engine* e, int32_t node, int32_t criterion, const uint8_t* class_order, avt_cpg_stat* out) {

