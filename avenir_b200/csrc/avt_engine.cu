@@ -67,7 +67,8 @@ struct avt_engine {
     // forest
     int T = 0;
     bool any_w = false;
-    DevBuf<uint16_t> d_nid;
+    DevBuf<uint16_t> d_nid, d_nid2;
+    uint16_t* nid_cur = nullptr;  // buffer holding the current node ids (d_nid or d_nid2)
     DevBuf<uint8_t> d_w, d_has_w;
     // frontier
     std::vector<int> node_base;
@@ -96,12 +97,18 @@ struct avt_engine {
     DevBuf<uint32_t> d_ccnt;
     DevBuf<int32_t> d_node_attr;
     DevBuf<uint16_t> d_lut;
+    // device-driven level loop
+    DevBuf<int32_t> d_prev_node_base, d_next_count, d_err;
+    DevBuf<avt_split_eval> d_best_eval;
+    DevBuf<avt_grow_record> d_records;
     // timing
     std::vector<TimerSlot> pending;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> free_events;
     cudaEvent_t tev0 = nullptr, tev1 = nullptr;
     avt_stats stats{};
     int force_variant = -1;
+    long long hist_target_addrs = 4096;  // AVT_HIST_TARGET_ADDRS
+    int grow_host_loop = 0;              // AVT_GROW_HOST=1: host-driven level loop (3 round trips per level)
     // comm
     ncclComm_t comm = nullptr;
     int n_ranks = 1, rank = 0;
@@ -235,13 +242,21 @@ int avt_create(int device, avt_engine** out) {
             return fail(nullptr, AVT_E_CUDA, "avt_create: device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
         }
     }
-    if (st == cudaSuccess) st = cudaFuncSetAttribute(hist_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
-    if (st == cudaSuccess) st = cudaFuncSetAttribute(hist_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    {
+        const void* kernels[] = {(const void*)hist_smem_kernel<false, false, false>, (const void*)hist_smem_kernel<false, false, true>,
+                                 (const void*)hist_smem_kernel<false, true, false>,  (const void*)hist_smem_kernel<false, true, true>,
+                                 (const void*)hist_smem_kernel<true, false, false>,  (const void*)hist_smem_kernel<true, false, true>,
+                                 (const void*)hist_smem_kernel<true, true, false>,   (const void*)hist_smem_kernel<true, true, true>};
+        for (const void* k : kernels)
+            if (st == cudaSuccess) st = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    }
     if (st != cudaSuccess) {
         int rc = fail(nullptr, AVT_E_CUDA, "avt_create: %s", cudaGetErrorString(st));
         delete e;
         return rc;
     }
+    if (const char* v = getenv("AVT_HIST_TARGET_ADDRS")) e->hist_target_addrs = std::max(1LL, atoll(v));
+    if (const char* v = getenv("AVT_GROW_HOST")) e->grow_host_loop = atoi(v);
     *out = e;
     return AVT_OK;
 }
@@ -254,7 +269,7 @@ void avt_destroy(avt_engine* e) {
     for (void* c : e->cols)
         if (c) cudaFree(c);
     e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
-    e->d_nid.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
+    e->d_nid.release(); e->d_nid2.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
     e->d_attr_first.release(); e->d_seg_lut.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
@@ -331,6 +346,7 @@ int avt_forest_init(avt_engine* e, int32_t n_trees, const uint8_t* const* weight
     CUDA_TRY(e, cudaMemsetAsync(e->d_nid.p, 0xFF, (size_t)n_trees * e->Npad * 2, e->stream));
     for (int t = 0; t < n_trees; ++t) {
         uint16_t* dst = e->d_nid.p + (size_t)t * e->Npad;
+        e->nid_cur = e->d_nid.p;
         if (node_ids && node_ids[t]) CUDA_TRY(e, cudaMemcpyAsync(dst, node_ids[t], (size_t)e->N * 2, cudaMemcpyHostToDevice, e->stream));
         else CUDA_TRY(e, cudaMemsetAsync(dst, 0, (size_t)e->N * 2, e->stream));
     }
@@ -386,40 +402,59 @@ int avt_split_table_set(avt_engine* e, int32_t n_splits, const avt_split* splits
     return sync_and_resolve(e);
 }
 
-int avt_level_histogram(avt_engine* e, const int32_t* nodes_per_tree, uint32_t* hist_out) {
-    if (!e) return AVT_E_INVALID;
-    if (e->T == 0) return fail(e, AVT_E_STATE, "avt_level_histogram: avt_forest_init has not been called");
-    if (!nodes_per_tree) return fail(e, AVT_E_INVALID, "avt_level_histogram: nodes_per_tree is NULL");
-    if (int rc = use_device(e)) return rc;
-    e->node_base.assign(e->T + 1, 0);
-    int n_max = 0;
-    for (int t = 0; t < e->T; ++t) {
-        if (nodes_per_tree[t] < 0 || nodes_per_tree[t] >= (int)AVT_NODE_NONE)
-            return fail(e, AVT_E_INVALID, "avt_level_histogram: tree %d has %d frontier nodes (limit %d)", t, nodes_per_tree[t], AVT_NODE_NONE - 1);
-        e->node_base[t + 1] = e->node_base[t] + nodes_per_tree[t];
-        n_max = std::max(n_max, nodes_per_tree[t]);
-    }
-    e->NF = e->node_base[e->T];
-    e->hist_valid = e->scan_valid = false;
-    if (e->NF == 0) return fail(e, AVT_E_INVALID, "avt_level_histogram: empty frontier");
+// Repartition state folded into a histogram pass (device-driven level loop).
+struct FusedRepart {
+    const int32_t* prev_node_base;
+    const int32_t* node_attr;
+    const uint16_t* child_lut;
+    int lut_w;
+};
+
+// Plans and launches kernel (a) for the frontier in e->node_base (already uploaded to d_node_base).
+// With `fr` the previous level's repartition is applied on the fly (node ids ping-pong between the two
+// buffers); without it the node ids are read in place.
+static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr) {
     const size_t hwords = (size_t)e->NF * e->TB * e->C;
     CUDA_TRY(e, e->d_H.ensure(hwords));
-    if (int rc = upload(e, e->d_node_base, e->node_base.data(), e->node_base.size())) return rc;
-
     // ---- plan: attribute groups whose per-tree histogram fits the shared-memory budget
-    const long long per_bin = (long long)n_max * e->C;  // words per bin (all nodes of a tree)
+    const long long per_bin = (long long)std::max(n_max, 1) * e->C;  // words per bin (all nodes of a tree)
     int max_bins = 0;
-    for (int a = 0; a < e->A; ++a) max_bins = std::max(max_bins, e->n_bins[a]);
+    bool any_wide = false;
+    for (int a = 0; a < e->A; ++a) {
+        max_bins = std::max(max_bins, e->n_bins[a]);
+        any_wide = any_wide || e->wide[a];
+    }
     int variant = (per_bin * max_bins <= kHistWordsBudget) ? 0 : 1;
     if (e->force_variant >= 0) {
         if (e->force_variant == 0 && variant == 1)
             return fail(e, AVT_E_INVALID, "avt_level_histogram: shared-memory variant forced but the frontier needs %lld words", per_bin * max_bins);
         variant = e->force_variant;
     }
+    uint16_t* nid_in = e->nid_cur;
+    uint16_t* nid_out = nullptr;
+    if (fr) {
+        CUDA_TRY(e, e->d_nid2.ensure((size_t)e->T * e->Npad));
+        nid_out = (e->nid_cur == e->d_nid.p) ? e->d_nid2.p : e->d_nid.p;
+    }
+    if (fr && variant == 1) {
+        // the global-atomics fallback has no fused form: repartition in place first
+        TimerSlot tr;
+        if (int rc = timer_open(e, &e->stats.repart_ms, &tr)) return rc;
+        long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
+        dim3 grid((unsigned)blocks, (unsigned)e->T);
+        repartition_kernel<<<grid, 256, 0, e->stream>>>(e->nid_cur, (const void* const*)e->d_colptrs.p, e->d_wide.p, fr->prev_node_base,
+                                                        fr->node_attr, fr->child_lut, fr->lut_w, e->N, e->Npad);
+        CUDA_TRY(e, cudaGetLastError());
+        if (int rc = timer_close(e, tr)) return rc;
+        e->stats.repart_launches += 1;
+        e->stats.repart_alg_bytes += (long long)e->N * e->T * 5;
+        fr = nullptr;
+        nid_out = nullptr;
+    }
     HistArgs ha{};
     ha.cols = (const void* const*)e->d_colptrs.p;
     ha.cls = e->d_cls.p;
-    ha.nid = e->d_nid.p;
+    ha.nid = nid_in;
     ha.wts = e->any_w ? e->d_w.p : nullptr;
     ha.has_w = e->d_has_w.p;
     ha.H = e->d_H.p;
@@ -429,11 +464,21 @@ int avt_level_histogram(avt_engine* e, const int32_t* nodes_per_tree, uint32_t* 
     ha.C = e->C;
     ha.TB = e->TB;
     ha.T = e->T;
+    ha.wide = e->d_wide.p;
+    if (fr) {
+        ha.nid_out = nid_out;
+        ha.prev_node_base = fr->prev_node_base;
+        ha.node_attr = fr->node_attr;
+        ha.child_lut = fr->child_lut;
+        ha.lut_w = fr->lut_w;
+    }
 
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.hist_ms, &ts)) return rc;
     CUDA_TRY(e, cudaMemsetAsync(e->d_H.p, 0, hwords * sizeof(uint32_t), e->stream));
     if (variant == 0) {
+        // Replication policy: enough copies that a warp's 32 updates spread over >= kTargetAddrs distinct
+        // words, but no more -- smaller histograms mean more resident blocks per SM (latency hiding).
         const int bins_budget = (int)(kHistWordsBudget / per_bin);
         std::vector<int32_t> ent_attr, ent_loc, ent_glob, ent_wide, grp_start{0}, grp_bins, grp_rlog, l2g, l2g_off;
         int cur = 0;
@@ -459,12 +504,11 @@ int avt_level_histogram(avt_engine* e, const int32_t* nodes_per_tree, uint32_t* 
         for (int g = 0; g < G; ++g) {
             const long long keys = per_bin * grp_bins[g];
             int rlog = 0;
-            while (rlog < 5 && (keys << (rlog + 1)) <= kHistWordsBudget) ++rlog;
+            while (rlog < 5 && (keys << (rlog + 1)) <= kHistWordsBudget && (keys << rlog) < e->hist_target_addrs) ++rlog;
             grp_rlog.push_back(rlog);
             rlog_min = std::min(rlog_min, rlog);
             smem_words = std::max(smem_words, (size_t)(keys << rlog));
         }
-        // pack the int tables into one upload
         std::vector<int32_t> pack;
         auto put = [&](const std::vector<int32_t>& v) {
             size_t o = pack.size();
@@ -477,16 +521,26 @@ int avt_level_histogram(avt_engine* e, const int32_t* nodes_per_tree, uint32_t* 
         const int32_t* base = e->d_grp.p;
         ha.ent_attr = base + o_attr; ha.ent_locoff = base + o_loc; ha.ent_globoff = base + o_glob; ha.ent_wide = base + o_wide;
         ha.grp_start = base + o_gs; ha.grp_bins = base + o_gb; ha.grp_rlog = base + o_gr; ha.grp_l2g = base + o_l2g; ha.grp_l2g_off = base + o_lo;
+        ha.codes_in_regs = (G == 1 && !any_wide && e->A <= 4) ? 1 : 0;
         const size_t smem = smem_words * sizeof(uint32_t);
-        int bpsm = (int)std::min<size_t>(4, std::max<size_t>(1, kMaxDynSmem / std::max<size_t>(smem, 1)));
+        int bpsm = (int)std::min<size_t>(4, std::max<size_t>(1, (kMaxDynSmem + 1024) / (smem + 1024)));
         long long resident = (long long)e->sm_count * bpsm;
         long long chunks = std::max<long long>(1, resident / ((long long)e->T * G));
         const long long tiles = (e->N + (long long)kHistThreads * kRowsPerThread - 1) / ((long long)kHistThreads * kRowsPerThread);
         chunks = std::min(chunks, tiles);
         chunks = std::min<long long>(chunks, 65535);
         dim3 grid((unsigned)e->T, (unsigned)chunks, (unsigned)G);
-        if (e->any_w) hist_smem_kernel<true><<<grid, kHistThreads, smem, e->stream>>>(ha);
-        else hist_smem_kernel<false><<<grid, kHistThreads, smem, e->stream>>>(ha);
+        const int sel = (e->any_w ? 4 : 0) | (any_wide ? 2 : 0) | (fr ? 1 : 0);
+        switch (sel) {
+            case 0: hist_smem_kernel<false, false, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
+            case 1: hist_smem_kernel<false, false, true><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
+            case 2: hist_smem_kernel<false, true, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
+            case 3: hist_smem_kernel<false, true, true><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
+            case 4: hist_smem_kernel<true, false, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
+            case 5: hist_smem_kernel<true, false, true><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
+            case 6: hist_smem_kernel<true, true, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
+            default: hist_smem_kernel<true, true, true><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
+        }
         e->stats.last_hist_replicas = 1 << rlog_min;
         e->stats.last_hist_grid = (int)(grid.x * grid.y * grid.z);
         e->stats.last_hist_block = kHistThreads;
@@ -502,13 +556,14 @@ int avt_level_histogram(avt_engine* e, const int32_t* nodes_per_tree, uint32_t* 
     }
     CUDA_TRY(e, cudaGetLastError());
     if (int rc = timer_close(e, ts)) return rc;
+    if (fr) e->nid_cur = nid_out;
     e->stats.last_hist_variant = variant;
     e->stats.hist_launches += 1;
     {
         long long code_bytes = 0;
         for (int a = 0; a < e->A; ++a) code_bytes += e->wide[a] ? 2 : 1;
         long long per_row = code_bytes + 1;
-        for (int t = 0; t < e->T; ++t) per_row += 2 + ((e->any_w) ? 1 : 0);
+        for (int t = 0; t < e->T; ++t) per_row += 2 + ((e->any_w) ? 1 : 0) + (fr ? 2 : 0);  // fused: + the node-id write
         e->stats.hist_alg_bytes += per_row * e->N;
     }
     if (e->comm) {
@@ -519,7 +574,36 @@ int avt_level_histogram(avt_engine* e, const int32_t* nodes_per_tree, uint32_t* 
         e->stats.comm_calls += 1;
     }
     e->hist_valid = true;
+    return AVT_OK;
+}
+
+static int set_frontier(avt_engine* e, const int32_t* nodes_per_tree, int* n_max_out, const char* who) {
+    e->node_base.assign(e->T + 1, 0);
+    int n_max = 0;
+    for (int t = 0; t < e->T; ++t) {
+        if (nodes_per_tree[t] < 0 || nodes_per_tree[t] >= (int)AVT_NODE_NONE)
+            return fail(e, AVT_E_INVALID, "%s: tree %d has %d frontier nodes (limit %d)", who, t, nodes_per_tree[t], AVT_NODE_NONE - 1);
+        e->node_base[t + 1] = e->node_base[t] + nodes_per_tree[t];
+        n_max = std::max(n_max, nodes_per_tree[t]);
+    }
+    e->NF = e->node_base[e->T];
+    e->hist_valid = e->scan_valid = false;
+    *n_max_out = n_max;
+    return AVT_OK;
+}
+
+int avt_level_histogram(avt_engine* e, const int32_t* nodes_per_tree, uint32_t* hist_out) {
+    if (!e) return AVT_E_INVALID;
+    if (e->T == 0) return fail(e, AVT_E_STATE, "avt_level_histogram: avt_forest_init has not been called");
+    if (!nodes_per_tree) return fail(e, AVT_E_INVALID, "avt_level_histogram: nodes_per_tree is NULL");
+    if (int rc = use_device(e)) return rc;
+    int n_max = 0;
+    if (int rc = set_frontier(e, nodes_per_tree, &n_max, "avt_level_histogram")) return rc;
+    if (e->NF == 0) return fail(e, AVT_E_INVALID, "avt_level_histogram: empty frontier");
+    if (int rc = upload(e, e->d_node_base, e->node_base.data(), e->node_base.size())) return rc;
+    if (int rc = launch_histogram(e, n_max, nullptr)) return rc;
     if (hist_out) {
+        const size_t hwords = (size_t)e->NF * e->TB * e->C;
         CUDA_TRY(e, cudaMemcpyAsync(hist_out, e->d_H.p, hwords * sizeof(uint32_t), cudaMemcpyDeviceToHost, e->stream));
         return sync_and_resolve(e);
     }
@@ -545,7 +629,7 @@ int avt_level_scan(avt_engine* e, int32_t criterion, const uint32_t* cand_mask, 
     CUDA_TRY(e, e->d_best.ensure((size_t)e->NF));
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
-    scan_kernel<<<e->NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), dmask, e->d_order.p, criterion, e->d_av.p, e->d_best.p);
+    scan_kernel<<<e->NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), dmask, e->d_order.p, criterion, e->d_av.p, e->d_best.p, nullptr, nullptr);
     CUDA_TRY(e, cudaGetLastError());
     if (int rc = timer_close(e, ts)) return rc;
     e->stats.scan_launches += 1;
@@ -616,7 +700,7 @@ int avt_level_repartition(avt_engine* e, const int32_t* node_attr, const uint16_
     if (int rc = timer_open(e, &e->stats.repart_ms, &ts)) return rc;
     long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
     dim3 grid((unsigned)blocks, (unsigned)e->T);
-    repartition_kernel<<<grid, 256, 0, e->stream>>>(e->d_nid.p, (const void* const*)e->d_colptrs.p, e->d_wide.p, e->d_node_base.p,
+    repartition_kernel<<<grid, 256, 0, e->stream>>>(e->nid_cur, (const void* const*)e->d_colptrs.p, e->d_wide.p, e->d_node_base.p,
                                                     e->d_node_attr.p, e->d_lut.p, lut_width, e->N, e->Npad);
     CUDA_TRY(e, cudaGetLastError());
     if (int rc = timer_close(e, ts)) return rc;
@@ -627,11 +711,10 @@ int avt_level_repartition(avt_engine* e, const int32_t* node_attr, const uint16_
     return AVT_OK;
 }
 
-int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
-                    avt_grow_record* records, int64_t max_records, int64_t* n_records) {
-    if (!e) return AVT_E_INVALID;
-    if (!nodes_per_tree) return fail(e, AVT_E_INVALID, "avt_grow_levels: nodes_per_tree is NULL");
-    if (e->T == 0 || e->S == 0) return fail(e, AVT_E_STATE, "avt_grow_levels: needs avt_forest_init and avt_split_table_set first");
+// Host-driven form of the level loop (separate kernels, three device->host round trips per level);
+// kept for A/B checks against the device-driven loop below (AVT_GROW_HOST=1).
+static int grow_host_loop(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
+                          avt_grow_record* records, int64_t max_records, int64_t* n_records) {
     int64_t nrec = 0;
     int lut_w = 1;
     for (int a = 0; a < e->A; ++a) lut_w = std::max(lut_w, e->n_bins[a]);
@@ -708,6 +791,124 @@ int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const ui
     return sync_and_resolve(e);
 }
 
+// Device-driven level loop: per level ONE fused repartition+histogram pass, the scan (which also emits
+// the children of the best split) and a planning kernel that numbers the children and builds the next
+// pass's bin -> child tables on the device.  The host only reads back T frontier sizes per level.
+static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
+                            avt_grow_record* records, int64_t max_records, int64_t* n_records) {
+    int lut_w = 1;
+    for (int a = 0; a < e->A; ++a) lut_w = std::max(lut_w, e->n_bins[a]);
+    if (int rc = upload_order(e, class_order)) return rc;
+    CUDA_TRY(e, e->d_next_count.ensure((size_t)e->T));
+    CUDA_TRY(e, e->d_err.ensure(1));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_err.p, 0, sizeof(int32_t), e->stream));
+    std::vector<int32_t> next((size_t)e->T);
+    std::vector<avt_grow_record> all;  // every level's records, in (level, tree, node) order
+    const bool want_records = records != nullptr || n_records != nullptr;
+    bool pending = false;  // a planned split not yet applied to the node ids
+    FusedRepart fr{};
+    for (int level = 0; level < n_levels; ++level) {
+        int n_max = 0;
+        if (int rc = set_frontier(e, nodes_per_tree, &n_max, "avt_grow_levels")) return rc;
+        if (e->NF == 0) break;
+        const int NF = e->NF;
+        // the tables of the previous level are indexed with the previous frontier's node_base
+        if (pending) {
+            CUDA_TRY(e, e->d_prev_node_base.ensure((size_t)e->T + 1));
+            CUDA_TRY(e, cudaMemcpyAsync(e->d_prev_node_base.p, e->d_node_base.p, ((size_t)e->T + 1) * sizeof(int32_t), cudaMemcpyDeviceToDevice, e->stream));
+            fr.prev_node_base = e->d_prev_node_base.p;
+        }
+        if (int rc = upload(e, e->d_node_base, e->node_base.data(), e->node_base.size())) return rc;
+        if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr)) return rc;
+        pending = false;
+        // scan + children of the best split
+        CUDA_TRY(e, e->d_av.ensure((size_t)NF * e->S));
+        CUDA_TRY(e, e->d_best.ensure((size_t)NF));
+        CUDA_TRY(e, e->d_best_eval.ensure((size_t)NF));
+        TimerSlot ts;
+        if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
+        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), nullptr, e->d_order.p, criterion, e->d_av.p, e->d_best.p,
+                                                        e->d_best_eval.p, nullptr);
+        CUDA_TRY(e, cudaGetLastError());
+        if (int rc = timer_close(e, ts)) return rc;
+        e->stats.scan_launches += 1;
+        e->scan_valid = true;
+        // plan: child numbering, next tables, records
+        // (node_attr / child_lut double as inputs of the NEXT histogram pass, so they must not be
+        //  overwritten before that pass has run: sizes only grow, and the pass above already consumed them)
+        CUDA_TRY(e, e->d_node_attr.ensure((size_t)NF));
+        CUDA_TRY(e, e->d_lut.ensure((size_t)NF * lut_w));
+        CUDA_TRY(e, e->d_records.ensure((size_t)NF));
+        PlanArgs pa{};
+        pa.best = e->d_best.p;
+        pa.best_eval = e->d_best_eval.p;
+        pa.node_base = e->d_node_base.p;
+        pa.node_attr = e->d_node_attr.p;
+        pa.child_lut = e->d_lut.p;
+        pa.next_count = e->d_next_count.p;
+        pa.records = want_records ? e->d_records.p : nullptr;
+        pa.err = e->d_err.p;
+        pa.lut_w = lut_w;
+        pa.level = level;
+        TimerSlot tp;
+        if (int rc = timer_open(e, &e->stats.eval_ms, &tp)) return rc;
+        plan_kernel<<<e->T, 256, 0, e->stream>>>(pa, make_table(e));
+        CUDA_TRY(e, cudaGetLastError());
+        if (int rc = timer_close(e, tp)) return rc;
+        e->stats.eval_launches += 1;
+        if (want_records) {
+            const size_t at = all.size();
+            all.resize(at + (size_t)NF);
+            CUDA_TRY(e, cudaMemcpyAsync(all.data() + at, e->d_records.p, (size_t)NF * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
+        }
+        CUDA_TRY(e, cudaMemcpyAsync(next.data(), e->d_next_count.p, (size_t)e->T * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        if (int rc = sync_and_resolve(e)) return rc;
+        for (int t = 0; t < e->T; ++t) nodes_per_tree[t] = next[(size_t)t];
+        fr.node_attr = e->d_node_attr.p;
+        fr.child_lut = e->d_lut.p;
+        fr.lut_w = lut_w;
+        pending = true;
+    }
+    if (pending) {
+        // apply the last planned split so that the node ids match the returned frontier
+        TimerSlot tr;
+        if (int rc = timer_open(e, &e->stats.repart_ms, &tr)) return rc;
+        long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
+        dim3 grid((unsigned)blocks, (unsigned)e->T);
+        repartition_kernel<<<grid, 256, 0, e->stream>>>(e->nid_cur, (const void* const*)e->d_colptrs.p, e->d_wide.p, e->d_node_base.p,
+                                                        e->d_node_attr.p, e->d_lut.p, lut_w, e->N, e->Npad);
+        CUDA_TRY(e, cudaGetLastError());
+        if (int rc = timer_close(e, tr)) return rc;
+        e->stats.repart_launches += 1;
+        e->stats.repart_alg_bytes += (long long)e->N * e->T * 5;
+    }
+    e->hist_valid = e->scan_valid = false;
+    e->NF = 0;
+    int32_t err = 0;
+    CUDA_TRY(e, cudaMemcpyAsync(&err, e->d_err.p, sizeof err, cudaMemcpyDeviceToHost, e->stream));
+    if (int rc = sync_and_resolve(e)) return rc;
+    int64_t nrec = 0;
+    for (size_t i = 0; i < all.size(); ++i) {
+        if (all[i].split < 0) continue;
+        if (records && nrec < max_records) records[nrec] = all[i];
+        ++nrec;
+    }
+    if (err) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
+    if (n_records) *n_records = nrec;
+    return AVT_OK;
+}
+
+int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
+                    avt_grow_record* records, int64_t max_records, int64_t* n_records) {
+    if (!e) return AVT_E_INVALID;
+    if (!nodes_per_tree) return fail(e, AVT_E_INVALID, "avt_grow_levels: nodes_per_tree is NULL");
+    if (e->T == 0 || e->S == 0) return fail(e, AVT_E_STATE, "avt_grow_levels: needs avt_forest_init and avt_split_table_set first");
+    if (criterion != AVT_CRIT_GINI && criterion != AVT_CRIT_ENTROPY) return fail(e, AVT_E_INVALID, "avt_grow_levels: criterion %d", criterion);
+    if (int rc = use_device(e)) return rc;
+    if (e->grow_host_loop) return grow_host_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
+    return grow_device_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
+}
+
 int avt_cpg_sweep(avt_engine* e, int32_t node, int32_t criterion, const uint8_t* class_order, avt_cpg_stat* out) {
     if (!e) return AVT_E_INVALID;
     if (!e->hist_valid) return fail(e, AVT_E_STATE, "avt_cpg_sweep: no histogram for the current frontier");
@@ -733,7 +934,7 @@ int avt_forest_node_ids(avt_engine* e, int32_t tree, uint16_t* out) {
     if (!e) return AVT_E_INVALID;
     if (tree < 0 || tree >= e->T || !out) return fail(e, AVT_E_INVALID, "avt_forest_node_ids: tree %d out of range", tree);
     if (int rc = use_device(e)) return rc;
-    CUDA_TRY(e, cudaMemcpyAsync(out, e->d_nid.p + (size_t)tree * e->Npad, (size_t)e->N * 2, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->nid_cur + (size_t)tree * e->Npad, (size_t)e->N * 2, cudaMemcpyDeviceToHost, e->stream));
     return sync_and_resolve(e);
 }
 

@@ -20,11 +20,11 @@ constexpr int kScanWordsPerWarp = 1024;  // per-warp prefix staging (4 KB; stati
 struct HistArgs {
     const void* const* cols;   // [A] device column pointers (uint8 or uint16 codes, padded to 16 rows)
     const uint8_t* cls;        // [Npad]
-    const uint16_t* nid;       // [T][Npad]
+    const uint16_t* nid;       // [T][Npad] node ids read by this pass
     const uint8_t* wts;        // [T][Npad] or nullptr
     const uint8_t* has_w;      // [T] (nullptr when wts == nullptr)
     uint32_t* H;               // [NF][TB][C]
-    const int32_t* node_base;  // [T+1]
+    const int32_t* node_base;  // [T+1] frontier being counted
     // attribute groups (one block handles one group): entry e in [grp_start[g], grp_start[g+1])
     const int32_t* ent_attr;    // attribute index
     const int32_t* ent_locoff;  // first bin of the attribute inside its group
@@ -37,62 +37,119 @@ struct HistArgs {
     const int32_t* grp_l2g_off; // [G]
     long long N, Npad;
     int C, TB, T;
+    // fused repartition (kernel (c) folded into kernel (a)): with nid_out != nullptr every row is first
+    // moved from its node of the previous frontier to the child its bin selects, the new id is stored
+    // to nid_out and counted.  `nid` and `nid_out` are different buffers (blocks of different attribute
+    // groups redo the same move).
+    uint16_t* nid_out;
+    const int32_t* prev_node_base;  // [T+1]
+    const int32_t* node_attr;       // [NF_prev] split attribute of each previous node, -1 = not expanded
+    const uint16_t* child_lut;      // [NF_prev][lut_w]
+    const int32_t* wide;            // [A]
+    int lut_w;
+    int codes_in_regs;  // 1: one group, <= 4 uint8 attributes, entry q == attribute q (the split code is in registers)
 };
 
-template <bool HAS_W>
-__device__ __forceinline__ void hist_rows16(uint32_t* sh, const HistArgs& a, int e0, int e1,
-                                            long long base, const uint16_t* nid, const uint8_t* wt,
-                                            int GB, int rlog, uint32_t rep) {
-    const uint4 vn0 = ld_stream(nid + base);
-    const uint4 vn1 = ld_stream(nid + base + 8);
+// hist_rows16: 16 consecutive rows of one tree for one attribute group.
+//   rowkey[j] = ((node * GB * C + cls) << rlog) + replica   (word index of the row's class slot of bin 0)
+//   counter   = rowkey[j] + ((locoff * C) << rlog) + code * (C << rlog)
+template <bool HAS_W, bool WIDE, bool REPART>
+__device__ __forceinline__ void hist_rows16(uint32_t* sh, const HistArgs& a, int e0, int ne, long long base,
+                                            const uint16_t* nid, uint16_t* nid_out, const uint8_t* wt,
+                                            uint32_t node_stride, uint32_t cs, int rlog, uint32_t rep, int prev_nb) {
+    uint4 vn0 = ld_stream(nid + base);
+    uint4 vn1 = ld_stream(nid + base + 8);
     const uint4 vc = ld_stream(a.cls + base);
-    uint4 vw = make_uint4(0x01010101u, 0x01010101u, 0x01010101u, 0x01010101u);
+    uint4 vw = make_uint4(0, 0, 0, 0);
     if (HAS_W) vw = ld_stream(wt + base);
-    // per-row base key (node*GB)*C + cls ; rows outside the frontier get a negative marker
-    int rowkey[kRowsPerThread];
-    uint32_t roww[kRowsPerThread];
+    uint4 v[4];
+    const int n0 = ne < 4 ? ne : 4;
+    if (!WIDE) {
 #pragma unroll
-    for (int j = 0; j < kRowsPerThread; ++j) {
-        uint32_t node = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
-        uint32_t w = u4_byte(vw, j);
-        roww[j] = w;
-        rowkey[j] = (node == AVT_NODE_NONE || w == 0) ? -1 : (int)(node * GB * a.C + u4_byte(vc, j));
+        for (int q = 0; q < 4; ++q)
+            if (q < n0) v[q] = ld_stream((const char*)a.cols[a.ent_attr[e0 + q]] + base);
     }
-    for (int e = e0; e < e1; e += 2) {
-        // two columns in flight per iteration
-        const bool two = (e + 1 < e1);
-        const int wide0 = a.ent_wide[e], wide1 = two ? a.ent_wide[e + 1] : 0;
-        const char* c0 = (const char*)a.cols[a.ent_attr[e]];
-        const char* c1 = two ? (const char*)a.cols[a.ent_attr[e + 1]] : c0;
-        uint4 v0a, v0b, v1a, v1b;
-        if (wide0) { v0a = ld_stream(c0 + base * 2); v0b = ld_stream(c0 + base * 2 + 16); }
-        else { v0a = ld_stream(c0 + base); v0b = v0a; }
-        if (two) {
-            if (wide1) { v1a = ld_stream(c1 + base * 2); v1b = ld_stream(c1 + base * 2 + 16); }
-            else { v1a = ld_stream(c1 + base); v1b = v1a; }
-        } else { v1a = v0a; v1b = v0b; }
-        const int off0 = a.ent_locoff[e] * a.C;
-        const int off1 = two ? a.ent_locoff[e + 1] * a.C : 0;
+    if (REPART) {
+        uint32_t nw[8];
 #pragma unroll
         for (int j = 0; j < kRowsPerThread; ++j) {
-            if (rowkey[j] < 0) continue;
-            uint32_t code0 = wide0 ? (j < 8 ? u4_half(v0a, j) : u4_half(v0b, j - 8)) : u4_byte(v0a, j);
-            uint32_t k0 = (uint32_t)(rowkey[j] + off0 + code0 * a.C);
-            atomicAdd(&sh[(k0 << rlog) + rep], roww[j]);
-            if (two) {
-                uint32_t code1 = wide1 ? (j < 8 ? u4_half(v1a, j) : u4_half(v1b, j - 8)) : u4_byte(v1a, j);
-                uint32_t k1 = (uint32_t)(rowkey[j] + off1 + code1 * a.C);
-                atomicAdd(&sh[(k1 << rlog) + rep], roww[j]);
+            const uint32_t old = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
+            uint32_t nn = AVT_NODE_NONE;
+            if (old != AVT_NODE_NONE) {
+                const int gi = prev_nb + (int)old;
+                const int at = __ldg(a.node_attr + gi);
+                if (at >= 0) {
+                    uint32_t code;
+                    if (!WIDE && a.codes_in_regs) {
+                        const uint32_t c01 = at == 0 ? u4_byte(v[0], j) : u4_byte(v[1], j);
+                        const uint32_t c23 = at == 2 ? u4_byte(v[2], j) : u4_byte(v[3], j);
+                        code = at < 2 ? c01 : c23;
+                    } else {
+                        code = a.wide[at] ? ((const uint16_t*)a.cols[at])[base + j] : ((const uint8_t*)a.cols[at])[base + j];
+                    }
+                    nn = __ldg(a.child_lut + (long long)gi * a.lut_w + code);
+                }
+            }
+            if (j & 1) nw[j >> 1] |= nn << 16;
+            else nw[j >> 1] = nn;
+        }
+        vn0 = make_uint4(nw[0], nw[1], nw[2], nw[3]);
+        vn1 = make_uint4(nw[4], nw[5], nw[6], nw[7]);
+        *reinterpret_cast<uint4*>(nid_out + base) = vn0;
+        *reinterpret_cast<uint4*>(nid_out + base + 8) = vn1;
+    }
+    int rowkey[kRowsPerThread];
+#pragma unroll
+    for (int j = 0; j < kRowsPerThread; ++j) {
+        const uint32_t node = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
+        const bool dead = node == AVT_NODE_NONE || (HAS_W && u4_byte(vw, j) == 0);
+        rowkey[j] = dead ? -1 : (int)(node * node_stride + (u4_byte(vc, j) << rlog) + rep);
+    }
+    if (!WIDE) {
+        for (int c0 = 0; c0 < ne; c0 += 4) {
+            const int nq = ne - c0 < 4 ? ne - c0 : 4;
+            if (c0) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (q < nq) v[q] = ld_stream((const char*)a.cols[a.ent_attr[e0 + c0 + q]] + base);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (q < nq) {
+                    const uint32_t offs = (uint32_t)(a.ent_locoff[e0 + c0 + q] * a.C) << rlog;
+#pragma unroll
+                    for (int j = 0; j < kRowsPerThread; ++j) {
+                        if (rowkey[j] >= 0)
+                            atomicAdd(sh + ((uint32_t)rowkey[j] + offs + u4_byte(v[q], j) * cs), HAS_W ? u4_byte(vw, j) : 1u);
+                    }
+                }
+            }
+        }
+    } else {
+        for (int e = e0; e < e0 + ne; ++e) {
+            const char* col = (const char*)a.cols[a.ent_attr[e]];
+            const bool wd = a.ent_wide[e] != 0;
+            uint4 va, vb;
+            if (wd) { va = ld_stream(col + base * 2); vb = ld_stream(col + base * 2 + 16); }
+            else { va = ld_stream(col + base); vb = va; }
+            const uint32_t offs = (uint32_t)(a.ent_locoff[e] * a.C) << rlog;
+#pragma unroll
+            for (int j = 0; j < kRowsPerThread; ++j) {
+                if (rowkey[j] >= 0) {
+                    const uint32_t code = wd ? (j < 8 ? u4_half(va, j) : u4_half(vb, j - 8)) : u4_byte(va, j);
+                    atomicAdd(sh + ((uint32_t)rowkey[j] + offs + code * cs), HAS_W ? u4_byte(vw, j) : 1u);
+                }
             }
         }
     }
 }
 
-// Shared-memory privatised histogram.  grid = (T, chunks, G).  Block (t, chunk, g) counts the rows of
-// its grid-strided 16-row vectors into a private copy of H[t][*][bins of group g][*] kept in shared
-// memory, replicated 2^rlog times (copy = lane mod replicas) so that lanes of a warp that hit the
-// same counter land in different banks; the block then folds the copies and adds them to global H.
-template <bool HAS_W>
+// Shared-memory privatised histogram, optionally with the previous level's repartition folded in.
+// grid = (T, chunks, G).  Block (t, chunk, g) counts the rows of its grid-strided 16-row vectors into a
+// private copy of H[t][*][bins of group g][*] kept in shared memory, replicated 2^rlog times (copy =
+// lane mod replicas) so that lanes of a warp that hit the same counter land in different banks; the
+// block then folds the copies and adds them to global H.
+template <bool HAS_W, bool WIDE, bool REPART>
 __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs a) {
     extern __shared__ uint32_t sh[];
     const int t = blockIdx.x, g = blockIdx.z;
@@ -103,15 +160,19 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
     for (int i = threadIdx.x; i < words; i += blockDim.x) sh[i] = 0;
     __syncthreads();
     const uint16_t* nid = a.nid + (long long)t * a.Npad;
+    uint16_t* nid_out = REPART ? a.nid_out + (long long)t * a.Npad : nullptr;
     const bool tree_has_w = HAS_W && a.has_w[t];
     const uint8_t* wt = HAS_W ? a.wts + (long long)t * a.Npad : nullptr;
     const uint32_t rep = (threadIdx.x & 31) & ((1u << rlog) - 1);
-    const int e0 = a.grp_start[g], e1 = a.grp_start[g + 1];
+    const uint32_t cs = (uint32_t)a.C << rlog;
+    const uint32_t node_stride = (uint32_t)(GB * a.C) << rlog;
+    const int e0 = a.grp_start[g], ne = a.grp_start[g + 1] - e0;
+    const int prev_nb = REPART ? a.prev_node_base[t] : 0;
     const long long stride = (long long)gridDim.y * blockDim.x * kRowsPerThread;
     for (long long base = ((long long)blockIdx.y * blockDim.x + threadIdx.x) * kRowsPerThread;
          base < a.N; base += stride) {
-        if (tree_has_w) hist_rows16<true>(sh, a, e0, e1, base, nid, wt, GB, rlog, rep);
-        else hist_rows16<false>(sh, a, e0, e1, base, nid, wt, GB, rlog, rep);
+        if (tree_has_w) hist_rows16<true, WIDE, REPART>(sh, a, e0, ne, base, nid, nid_out, wt, node_stride, cs, rlog, rep, prev_nb);
+        else hist_rows16<false, WIDE, REPART>(sh, a, e0, ne, base, nid, nid_out, wt, node_stride, cs, rlog, rep, prev_nb);
     }
     __syncthreads();
     const int* l2g = a.grp_l2g + a.grp_l2g_off[g];
@@ -272,10 +333,12 @@ __device__ __forceinline__ void best_merge(ScanBest& a, const ScanBest& b) {
 __global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, SplitTable st,
                                                             const uint32_t* cand_mask,
                                                             const uint8_t* order, int criterion,
-                                                            double* av_buf, avt_node_best* out) {
+                                                            double* av_buf, avt_node_best* out,
+                                                            avt_split_eval* best_eval, const int32_t* n_nodes_dev) {
     __shared__ uint32_t Pbuf[kScanWarps][kScanWordsPerWarp];
     __shared__ ScanBest wbest[kScanWarps];
     const int node = blockIdx.x;
+    if (n_nodes_dev && node >= *n_nodes_dev) return;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int C = st.C;
     const uint32_t* Hnode = H + (long long)node * st.TB * C;
@@ -336,7 +399,120 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, S
         r.best_split = b.split;
         r.n_ties = b.ties;
         out[node] = r;
+        // children of the (lowest-index) best split, so that a tie-free level needs no second pass
+        if (best_eval) {
+            avt_split_eval ev;
+            for (int j = 0; j < kMaxSeg; ++j) {
+                ev.seg_stat[j] = 0.0;
+                for (int c = 0; c < kMaxC; ++c) ev.seg_count[j][c] = 0;
+            }
+            ev.av = nan;
+            if (b.split >= 0 && n > 0) {
+                const avt_split sp = st.splits[b.split];
+                const int Bs = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
+                ev.av = split_av(st, sp, Bs, nullptr, Hnode + (long long)st.bin_off[sp.attr] * C, order, criterion, &ev);
+            }
+            best_eval[node] = ev;
+        }
     }
+}
+
+// Device-side level planning: from the scan results derive, per tree, the numbering of the children,
+// the bin -> child table and split attribute of every frontier node (inputs of the next fused
+// repartition + histogram pass), the next frontier sizes, and one record per node.  grid = T blocks.
+struct PlanArgs {
+    const avt_node_best* best;
+    const avt_split_eval* best_eval;
+    const int32_t* node_base;  // [T+1] current frontier
+    int32_t* node_attr;        // [NF]
+    uint16_t* child_lut;       // [NF][lut_w]
+    int32_t* next_count;       // [T]
+    avt_grow_record* records;  // [NF] (nullable)
+    int32_t* err;              // set to 1 when a tree would exceed the node-id range
+    int lut_w, level;
+};
+
+__global__ void __launch_bounds__(256) plan_kernel(PlanArgs p, SplitTable st) {
+    __shared__ int warp_tot[8];
+    __shared__ int running;
+    const int t = blockIdx.x;
+    const int nb = p.node_base[t], n = p.node_base[t + 1] - nb;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) running = 0;
+    __syncthreads();
+    for (int i0 = 0; i0 < n; i0 += blockDim.x) {
+        const int i = i0 + threadIdx.x;
+        const int g = nb + i;
+        int nkids = 0;
+        bool live = false;
+        avt_split sp{};
+        if (i < n) {
+            const avt_node_best b = p.best[g];
+            live = b.population > 0 && b.best_split >= 0;
+            if (live) {
+                sp = st.splits[b.best_split];
+                for (int sg = 0; sg < sp.n_seg; ++sg) {
+                    uint32_t pop = 0;
+                    for (int c = 0; c < st.C; ++c) pop += p.best_eval[g].seg_count[sg][c];
+                    nkids += pop != 0;
+                }
+            }
+        }
+        // block exclusive scan of nkids
+        int v = nkids;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int u = __shfl_up_sync(0xffffffffu, v, d);
+            if (lane >= d) v += u;
+        }
+        if (lane == 31) warp_tot[warp] = v;
+        __syncthreads();
+        int woff = 0, tot = 0;
+        for (int w = 0; w < 8; ++w) {
+            if (w < warp) woff += warp_tot[w];
+            tot += warp_tot[w];
+        }
+        const int first = running + woff + v - nkids;
+        if (i < n) {
+            p.node_attr[g] = live ? sp.attr : -1;
+            uint16_t* lut = p.child_lut + (long long)g * p.lut_w;
+            for (int b = 0; b < p.lut_w; ++b) lut[b] = (uint16_t)AVT_NODE_NONE;
+            avt_grow_record rec;
+            rec.level = p.level; rec.tree = t; rec.node = i;
+            rec.split = live ? p.best[g].best_split : -1;
+            rec.n_ties = p.best[g].n_ties;
+            rec.min_av = p.best[g].min_av;
+            for (int sg = 0; sg < kMaxSeg; ++sg) { rec.child[sg] = -1; rec.child_pop[sg] = 0; rec.child_stat[sg] = 0.0; }
+            if (live) {
+                int k = 0;
+                for (int sg = 0; sg < sp.n_seg; ++sg) {
+                    long long pop = 0;
+                    for (int c = 0; c < st.C; ++c) pop += p.best_eval[g].seg_count[sg][c];
+                    rec.child_pop[sg] = pop;
+                    rec.child_stat[sg] = p.best_eval[g].seg_stat[sg];
+                    if (pop) rec.child[sg] = first + k++;
+                }
+                if (first + k > (int)AVT_NODE_NONE - 1) *p.err = 1;
+                const int B = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
+                for (int b = 0; b < B; ++b) {
+                    int sg;
+                    if (sp.kind == AVT_SPLIT_NUMERIC) {
+                        sg = 0;
+                        while (sg < sp.n_seg - 1 && b > st.bounds[sp.off + sg]) ++sg;
+                    } else {
+                        sg = st.seg_lut[sp.off + b];
+                        if (sg >= sp.n_seg) continue;
+                    }
+                    if (rec.child[sg] >= 0) lut[b] = (uint16_t)rec.child[sg];
+                }
+            }
+            if (p.records) p.records[g] = rec;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) running += tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) p.next_count[t] = running;
 }
 
 // Children statistics for chosen (node, split) pairs; one thread per pair (tiny).

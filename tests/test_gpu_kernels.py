@@ -204,3 +204,45 @@ def test_api_misuse_is_reported():
     t.add_numeric(0, [9])
     with pytest.raises(EngineError):
         g.set_splits(t)                                  # bound outside the attribute's bins
+
+
+@pytest.mark.parametrize("host_loop", [0, 1])
+@pytest.mark.parametrize("criterion", [CRIT_GINI, CRIT_ENTROPY])
+def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
+    """avt_grow_levels (device-driven: fused repartition+histogram, scan, on-device planning; and its
+    host-driven twin) against the oracle's level loop: every record and every final node id."""
+    monkeypatch.setenv("AVT_GROW_HOST", str(host_loop))
+    n = 150001
+    rng = np.random.default_rng(12)
+    cols, cls, n_bins, _ = synth.call_hangup_encoded(n)
+    table = binary_split_table(n_bins, [True, True, True, False])
+    weights = [None, rng.poisson(1.0, n).clip(0, 255).astype(np.uint8), None]
+    g, o = make_pair(cols, cls, n_bins, 2, table, 3, weights, None)
+    (rec, nrec), frontier = g.grow(7, criterion, [1, 1, 1], max_records=4096)
+    ho, fo = grow_levels(o, table, 7, criterion, n_trees=3)
+    want = [(lvl, t, nd, s, pops, av, ties) for lvl, level in enumerate(ho) for (t, nd, s, pops, av, ties) in level]
+    assert frontier == fo and nrec == len(want)
+    for i, (lvl, t, nd, s, pops, av, ties) in enumerate(want):
+        r = rec[i]
+        assert (r.level, r.tree, r.node, r.split, r.n_ties) == (lvl, t, nd, s, ties), i
+        assert [p for p in r.child_pop if p] == pops
+        assert helpers.bits(r.min_av) == helpers.bits(av)
+    for t in range(3):
+        assert np.array_equal(g.node_ids(t), o.node_ids(t))
+
+
+def test_level_loop_with_wide_codes_and_many_attrs():
+    """uint16 column + more than 4 attributes (generic gather path of the fused repartition), 3 classes."""
+    n = 90001
+    n_bins = [6, 300, 9, 4, 12, 3]
+    cols, cls = synth.binned_dataset(n, n_bins, 3, seed=4)
+    table = binary_split_table(n_bins, [False, False, False, True, False, True])
+    g, o = make_pair(cols, cls, n_bins, 3, table)
+    (rec, nrec), frontier = g.grow(5, CRIT_GINI, [1], class_order=[2, 0, 1], max_records=1024)
+    ho, fo = grow_levels(o, table, 5, CRIT_GINI, class_order=[2, 0, 1])
+    assert frontier == fo
+    want = [x for level in ho for x in level]
+    assert nrec == len(want)
+    for i, (t, nd, s, pops, av, ties) in enumerate(want):
+        assert (rec[i].node, rec[i].split) == (nd, s) and helpers.bits(rec[i].min_av) == helpers.bits(av)
+    assert np.array_equal(g.node_ids(0), o.node_ids(0))

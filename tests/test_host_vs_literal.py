@@ -35,7 +35,8 @@ def run_dtb_both(lib, tmp, lines, schema_dict, conf, expansions, tool_run=helper
     _props(pp, conf)
     rc, err = tool_run(lib, DTB, [f"-Dconf.path={pp}", f"-Davt.dtb.num.levels={expansions + 1}", data, os.path.join(tmp, "out")])
     try:
-        want = literal.dtb_build(lines, literal.load_properties(pp), literal.FeatureSchema(schema_dict), expansions)
+        want = literal.dtb_build(lines, literal.load_properties(pp), literal.FeatureSchema(schema_dict), expansions,
+                                 seed=int(conf.get("avt.random.seed", 0)))
     except TypeError as e:          # the reference itself dies (NullPointerException): the job must fail too
         assert "NullPointerException" in str(e)
         assert rc == 1 and "NullPointerException" in err, err
