@@ -20,6 +20,11 @@ __device__ __forceinline__ uint4 ld_stream(const void* p) {
     return r;
 }
 
+// shared-memory reduction on a 32-bit shared-window address (no generic-address conversion per update)
+__device__ __forceinline__ void red_shared_add(uint32_t addr, uint32_t v) {
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
 __device__ __forceinline__ uint32_t u4_word(const uint4& v, int i) {
     return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w;
 }

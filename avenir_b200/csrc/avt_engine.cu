@@ -417,7 +417,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr) {
     const size_t hwords = (size_t)e->NF * e->TB * e->C;
     CUDA_TRY(e, e->d_H.ensure(hwords));
     // ---- plan: attribute groups whose per-tree histogram fits the shared-memory budget
-    const long long per_bin = (long long)std::max(n_max, 1) * e->C;  // words per bin (all nodes of a tree)
+    const long long per_bin = (long long)(std::max(n_max, 1) + 1) * e->C;  // words per bin: all nodes of a tree + the phantom node
     int max_bins = 0;
     bool any_wide = false;
     for (int a = 0; a < e->A; ++a) {

@@ -52,11 +52,12 @@ struct HistArgs {
 
 // hist_rows16: 16 consecutive rows of one tree for one attribute group.
 //   rowkey[j] = ((node * GB * C + cls) << rlog) + replica   (word index of the row's class slot of bin 0)
-//   counter   = rowkey[j] + ((locoff * C) << rlog) + code * (C << rlog)
+//   counter   = rowkey[j] + ((locoff * C) << rlog) + code * (C << rlog)          (all kept as byte addresses)
 template <bool HAS_W, bool WIDE, bool REPART>
-__device__ __forceinline__ void hist_rows16(uint32_t* sh, const HistArgs& a, int e0, int ne, long long base,
+__device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a, int e0, int ne, long long base,
                                             const uint16_t* nid, uint16_t* nid_out, const uint8_t* wt,
-                                            uint32_t node_stride, uint32_t cs, int rlog, uint32_t rep, int prev_nb) {
+                                            uint32_t node_stride, uint32_t cs4, int rlog, uint32_t rep, int prev_nb,
+                                            uint32_t phantom) {
     uint4 vn0 = ld_stream(nid + base);
     uint4 vn1 = ld_stream(nid + base + 8);
     const uint4 vc = ld_stream(a.cls + base);
@@ -98,12 +99,16 @@ __device__ __forceinline__ void hist_rows16(uint32_t* sh, const HistArgs& a, int
         *reinterpret_cast<uint4*>(nid_out + base) = vn0;
         *reinterpret_cast<uint4*>(nid_out + base + 8) = vn1;
     }
-    int rowkey[kRowsPerThread];
+    // byte address (shared window) of the row's class slot of bin 0; rows outside the frontier (and rows
+    // with multiplicity 0) are sent to a phantom node behind the last real one, so the update loop has
+    // no branches; the phantom counters are never flushed.
+    uint32_t rowkey[kRowsPerThread];
 #pragma unroll
     for (int j = 0; j < kRowsPerThread; ++j) {
-        const uint32_t node = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
+        uint32_t node = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
         const bool dead = node == AVT_NODE_NONE || (HAS_W && u4_byte(vw, j) == 0);
-        rowkey[j] = dead ? -1 : (int)(node * node_stride + (u4_byte(vc, j) << rlog) + rep);
+        node = dead ? phantom : node;
+        rowkey[j] = sh_base + (node * node_stride + (u4_byte(vc, j) << rlog) + rep) * 4u;
     }
     if (!WIDE) {
         for (int c0 = 0; c0 < ne; c0 += 4) {
@@ -116,12 +121,10 @@ __device__ __forceinline__ void hist_rows16(uint32_t* sh, const HistArgs& a, int
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 if (q < nq) {
-                    const uint32_t offs = (uint32_t)(a.ent_locoff[e0 + c0 + q] * a.C) << rlog;
+                    const uint32_t offs = ((uint32_t)(a.ent_locoff[e0 + c0 + q] * a.C) << rlog) * 4u;
 #pragma unroll
-                    for (int j = 0; j < kRowsPerThread; ++j) {
-                        if (rowkey[j] >= 0)
-                            atomicAdd(sh + ((uint32_t)rowkey[j] + offs + u4_byte(v[q], j) * cs), HAS_W ? u4_byte(vw, j) : 1u);
-                    }
+                    for (int j = 0; j < kRowsPerThread; ++j)
+                        red_shared_add(rowkey[j] + offs + u4_byte(v[q], j) * cs4, HAS_W ? u4_byte(vw, j) : 1u);
                 }
             }
         }
@@ -132,13 +135,11 @@ __device__ __forceinline__ void hist_rows16(uint32_t* sh, const HistArgs& a, int
             uint4 va, vb;
             if (wd) { va = ld_stream(col + base * 2); vb = ld_stream(col + base * 2 + 16); }
             else { va = ld_stream(col + base); vb = va; }
-            const uint32_t offs = (uint32_t)(a.ent_locoff[e] * a.C) << rlog;
+            const uint32_t offs = ((uint32_t)(a.ent_locoff[e] * a.C) << rlog) * 4u;
 #pragma unroll
             for (int j = 0; j < kRowsPerThread; ++j) {
-                if (rowkey[j] >= 0) {
-                    const uint32_t code = wd ? (j < 8 ? u4_half(va, j) : u4_half(vb, j - 8)) : u4_byte(va, j);
-                    atomicAdd(sh + ((uint32_t)rowkey[j] + offs + code * cs), HAS_W ? u4_byte(vw, j) : 1u);
-                }
+                const uint32_t code = wd ? (j < 8 ? u4_half(va, j) : u4_half(vb, j - 8)) : u4_byte(va, j);
+                red_shared_add(rowkey[j] + offs + code * cs4, HAS_W ? u4_byte(vw, j) : 1u);
             }
         }
     }
@@ -156,23 +157,24 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
     const int nb = a.node_base[t], n_nodes = a.node_base[t + 1] - nb;
     const int GB = a.grp_bins[g], rlog = a.grp_rlog[g];
     const int keys = n_nodes * GB * a.C;
-    const int words = keys << rlog;
+    const int words = (keys + GB * a.C) << rlog;  // + one phantom node that swallows rows outside the frontier
     for (int i = threadIdx.x; i < words; i += blockDim.x) sh[i] = 0;
     __syncthreads();
+    const uint32_t sh_base = (uint32_t)__cvta_generic_to_shared(sh);
     const uint16_t* nid = a.nid + (long long)t * a.Npad;
     uint16_t* nid_out = REPART ? a.nid_out + (long long)t * a.Npad : nullptr;
     const bool tree_has_w = HAS_W && a.has_w[t];
     const uint8_t* wt = HAS_W ? a.wts + (long long)t * a.Npad : nullptr;
     const uint32_t rep = (threadIdx.x & 31) & ((1u << rlog) - 1);
-    const uint32_t cs = (uint32_t)a.C << rlog;
+    const uint32_t cs4 = ((uint32_t)a.C << rlog) * 4u;
     const uint32_t node_stride = (uint32_t)(GB * a.C) << rlog;
     const int e0 = a.grp_start[g], ne = a.grp_start[g + 1] - e0;
     const int prev_nb = REPART ? a.prev_node_base[t] : 0;
     const long long stride = (long long)gridDim.y * blockDim.x * kRowsPerThread;
     for (long long base = ((long long)blockIdx.y * blockDim.x + threadIdx.x) * kRowsPerThread;
          base < a.N; base += stride) {
-        if (tree_has_w) hist_rows16<true, WIDE, REPART>(sh, a, e0, ne, base, nid, nid_out, wt, node_stride, cs, rlog, rep, prev_nb);
-        else hist_rows16<false, WIDE, REPART>(sh, a, e0, ne, base, nid, nid_out, wt, node_stride, cs, rlog, rep, prev_nb);
+        if (tree_has_w) hist_rows16<true, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes);
+        else hist_rows16<false, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes);
     }
     __syncthreads();
     const int* l2g = a.grp_l2g + a.grp_l2g_off[g];

@@ -24,7 +24,6 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -50,39 +49,57 @@ def measured_peak():
 
 
 class ClockSampler(threading.Thread):
-    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock + throttle reasons DURING the timed region, through NVML (the library behind nvidia-smi's
+    clocks.sm / clocks_event_reasons.* query; in-process so that sampling does not stall CUDA calls)."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, gpu_index: int):
         super().__init__(daemon=True)
-        self.gpu = gpu_index
         self.samples = []
         self.stop_flag = False
+        self.handle = None
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML indexes physical GPUs; honour CUDA_VISIBLE_DEVICES when it lists indices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = gpu_index
+            if vis:
+                parts = [p for p in vis.split(",") if p.strip().isdigit()]
+                if gpu_index < len(parts):
+                    idx = int(parts[gpu_index])
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
 
     def run(self):
+        if self.nvml is None:
+            return
+        n = self.nvml
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
+                sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+                mx = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+                rs = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle) if hasattr(n, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                self.samples.append((sm, mx, rs))
             except Exception:
                 pass
-            time.sleep(0.1)
+            time.sleep(0.002)
 
     def summary(self):
-        sm, mx, reasons = [], [], set()
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": "nvml unavailable"}
+        sm = [s[0] for s in self.samples]
+        reasons = set()
         for s in self.samples:
-            try:
-                sm.append(float(s[1])); mx.append(float(s[2]))
-            except Exception:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[4:8]):
-                if v.lower().startswith("active"):
+            for bit, name in self.REASONS.items():
+                if s[2] & bit:
                     reasons.add(name)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(s[1] for s in self.samples)), "reasons": sorted(reasons),
+                "samples": len(sm), "source": "nvml"}
 
 
 def cpu_port_rows_per_sec(rows: int, levels: int, threads: int, repeats: int = 1):
@@ -212,7 +229,7 @@ def main():
     wall = time.perf_counter() - t0
     st = eng.stats()
     sampler.stop_flag = True
-    sampler.join(timeout=2)
+    sampler.join()
 
     # ---- e2e: host buffers -> tree, through the C-ABI
     def step_e2e():
