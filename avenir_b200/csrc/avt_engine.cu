@@ -98,7 +98,8 @@ struct avt_engine {
     DevBuf<int32_t> d_node_attr;
     DevBuf<uint16_t> d_lut;
     // device-driven level loop
-    DevBuf<int32_t> d_prev_node_base, d_next_count, d_err;
+    DevBuf<int32_t> d_prev_node_base, d_next_count, d_err, d_nb_all;
+    DevBuf<uint32_t> d_ticket;
     DevBuf<avt_split_eval> d_best_eval;
     DevBuf<avt_grow_record> d_records;
     // timing
@@ -269,7 +270,7 @@ void avt_destroy(avt_engine* e) {
     for (void* c : e->cols)
         if (c) cudaFree(c);
     e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
-    e->d_nid.release(); e->d_nid2.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
+    e->d_nid.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
     e->d_attr_first.release(); e->d_seg_lut.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
@@ -413,7 +414,7 @@ struct FusedRepart {
 // Plans and launches kernel (a) for the frontier in e->node_base (already uploaded to d_node_base).
 // With `fr` the previous level's repartition is applied on the fly (node ids ping-pong between the two
 // buffers); without it the node ids are read in place.
-static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr) {
+static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, const int32_t* d_node_base = nullptr) {
     const size_t hwords = (size_t)e->NF * e->TB * e->C;
     CUDA_TRY(e, e->d_H.ensure(hwords));
     // ---- plan: attribute groups whose per-tree histogram fits the shared-memory budget
@@ -458,7 +459,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr) {
     ha.wts = e->any_w ? e->d_w.p : nullptr;
     ha.has_w = e->d_has_w.p;
     ha.H = e->d_H.p;
-    ha.node_base = e->d_node_base.p;
+    ha.node_base = d_node_base ? d_node_base : e->d_node_base.p;
     ha.N = e->N;
     ha.Npad = e->Npad;
     ha.C = e->C;
@@ -794,7 +795,7 @@ static int grow_host_loop(avt_engine* e, int32_t n_levels, int32_t criterion, co
 // Device-driven level loop: per level ONE fused repartition+histogram pass, the scan (which also emits
 // the children of the best split) and a planning kernel that numbers the children and builds the next
 // pass's bin -> child tables on the device.  The host only reads back T frontier sizes per level.
-static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
+static int grow_device_loop_sync(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
                             avt_grow_record* records, int64_t max_records, int64_t* n_records) {
     int lut_w = 1;
     for (int a = 0; a < e->A; ++a) lut_w = std::max(lut_w, e->n_bins[a]);
@@ -850,6 +851,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         pa.err = e->d_err.p;
         pa.lut_w = lut_w;
         pa.level = level;
+        pa.n_trees = e->T;
         TimerSlot tp;
         if (int rc = timer_open(e, &e->stats.eval_ms, &tp)) return rc;
         plan_kernel<<<e->T, 256, 0, e->stream>>>(pa, make_table(e));
@@ -898,6 +900,185 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     return AVT_OK;
 }
 
+// Asynchronous form of the device-driven loop: nothing is read back until the last level.  The host
+// sizes every launch from an UPPER BOUND of the frontier (each node has at most max-n_seg children);
+// the kernels read the true frontier (node_base of every level lives on the device, written by the
+// planning kernel of the level before).  Levels whose bound exceeds kAsyncNodeLimit fall back to one
+// read-back so that buffers follow the real frontier.
+constexpr int kAsyncNodeLimit = 16384;
+
+static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
+                            avt_grow_record* records, int64_t max_records, int64_t* n_records) {
+    const int T = e->T;
+    int lut_w = 1, g_max = 2;
+    for (int a = 0; a < e->A; ++a) lut_w = std::max(lut_w, e->n_bins[a]);
+    for (auto& sp : e->splits) g_max = std::max(g_max, sp.n_seg);
+    if (n_levels <= 0) {
+        if (n_records) *n_records = 0;
+        return AVT_OK;
+    }
+    if (int rc = upload_order(e, class_order)) return rc;
+    const bool want_records = records != nullptr || n_records != nullptr;
+    CUDA_TRY(e, e->d_next_count.ensure((size_t)T));
+    CUDA_TRY(e, e->d_err.ensure(1));
+    CUDA_TRY(e, e->d_ticket.ensure(1));
+    CUDA_TRY(e, e->d_nb_all.ensure((size_t)(n_levels + 1) * (T + 1)));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_err.p, 0, sizeof(int32_t), e->stream));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_ticket.p, 0, sizeof(uint32_t), e->stream));
+    std::vector<avt_grow_record> all;
+    std::vector<int32_t> ub(nodes_per_tree, nodes_per_tree + T), nb_host((size_t)T + 1);
+    std::vector<std::pair<size_t, size_t>> rec_regions;  // (offset, count) of every level's record region
+    auto nb_level = [&](int level) { return e->d_nb_all.p + (size_t)level * (T + 1); };
+    // level 0: the caller's frontier is exact
+    nb_host[0] = 0;
+    for (int t = 0; t < T; ++t) nb_host[(size_t)t + 1] = nb_host[(size_t)t] + ub[(size_t)t];
+    CUDA_TRY(e, cudaMemcpyAsync(nb_level(0), nb_host.data(), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+    bool pending = false;
+    FusedRepart fr{};
+    size_t rec_off = 0;
+    int last_level = -1;
+    for (int level = 0; level < n_levels; ++level) {
+        long long nf_ub = 0;
+        int n_max = 0;
+        for (int t = 0; t < T; ++t) {
+            nf_ub += ub[(size_t)t];
+            n_max = std::max(n_max, ub[(size_t)t]);
+        }
+        if (level > 0 && nf_ub > kAsyncNodeLimit) {
+            // bound too loose to size buffers from: read the true frontier back once
+            CUDA_TRY(e, cudaMemcpyAsync(nb_host.data(), nb_level(level), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+            if (int rc = sync_and_resolve(e)) return rc;
+            nf_ub = 0;
+            n_max = 0;
+            for (int t = 0; t < T; ++t) {
+                ub[(size_t)t] = nb_host[(size_t)t + 1] - nb_host[(size_t)t];
+                nf_ub += ub[(size_t)t];
+                n_max = std::max(n_max, ub[(size_t)t]);
+            }
+        }
+        if (nf_ub == 0) break;
+        if (n_max >= (int)AVT_NODE_NONE) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
+        const int NF = (int)nf_ub;
+        e->NF = NF;
+        e->hist_valid = e->scan_valid = false;
+        // every buffer of this level is sized BEFORE anything is enqueued (a reallocation frees memory
+        // that earlier, still running launches may use)
+        if (e->d_av.cap < (size_t)NF * e->S || e->d_best.cap < (size_t)NF || e->d_best_eval.cap < (size_t)NF || e->d_node_attr.cap < (size_t)NF ||
+            e->d_lut.cap < (size_t)NF * lut_w || e->d_H.cap < (size_t)NF * e->TB * e->C || (want_records && e->d_records.cap < rec_off + (size_t)NF)) {
+            if (int rc = sync_and_resolve(e)) return rc;
+            // flush records gathered so far: the record buffer may move
+            if (want_records && rec_off) {
+                const size_t at = all.size();
+                all.resize(at + rec_off);
+                CUDA_TRY(e, cudaMemcpy(all.data() + at, e->d_records.p, rec_off * sizeof(avt_grow_record), cudaMemcpyDeviceToHost));
+                rec_off = 0;
+            }
+            // tables of the previous level are still needed by this level's fused pass: preserve them
+            std::vector<int32_t> keep_attr;
+            std::vector<uint16_t> keep_lut;
+            size_t prev_nf = 0;
+            if (pending) {
+                prev_nf = std::min(e->d_node_attr.cap, e->d_lut.cap / (size_t)lut_w);
+                keep_attr.resize(prev_nf);
+                keep_lut.resize(prev_nf * lut_w);
+                CUDA_TRY(e, cudaMemcpy(keep_attr.data(), e->d_node_attr.p, prev_nf * sizeof(int32_t), cudaMemcpyDeviceToHost));
+                CUDA_TRY(e, cudaMemcpy(keep_lut.data(), e->d_lut.p, prev_nf * lut_w * sizeof(uint16_t), cudaMemcpyDeviceToHost));
+            }
+            const size_t grow = (size_t)NF * (size_t)g_max * 2;  // room for the next levels as well
+            CUDA_TRY(e, e->d_av.ensure(grow * e->S));
+            CUDA_TRY(e, e->d_best.ensure(grow));
+            CUDA_TRY(e, e->d_best_eval.ensure(grow));
+            CUDA_TRY(e, e->d_node_attr.ensure(grow));
+            CUDA_TRY(e, e->d_lut.ensure(grow * lut_w));
+            CUDA_TRY(e, e->d_H.ensure(grow * e->TB * e->C));
+            if (want_records) CUDA_TRY(e, e->d_records.ensure(grow * 2));
+            if (pending) {
+                CUDA_TRY(e, cudaMemcpy(e->d_node_attr.p, keep_attr.data(), prev_nf * sizeof(int32_t), cudaMemcpyHostToDevice));
+                CUDA_TRY(e, cudaMemcpy(e->d_lut.p, keep_lut.data(), prev_nf * lut_w * sizeof(uint16_t), cudaMemcpyHostToDevice));
+                fr.node_attr = e->d_node_attr.p;
+                fr.child_lut = e->d_lut.p;
+            }
+        }
+        if (pending) fr.prev_node_base = nb_level(level - 1);
+        if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr, nb_level(level))) return rc;
+        pending = false;
+        TimerSlot ts;
+        if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
+        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), nullptr, e->d_order.p, criterion, e->d_av.p, e->d_best.p,
+                                                        e->d_best_eval.p, nb_level(level) + T);
+        CUDA_TRY(e, cudaGetLastError());
+        if (int rc = timer_close(e, ts)) return rc;
+        e->stats.scan_launches += 1;
+        PlanArgs pa{};
+        pa.best = e->d_best.p;
+        pa.best_eval = e->d_best_eval.p;
+        pa.node_base = nb_level(level);
+        pa.node_attr = e->d_node_attr.p;
+        pa.child_lut = e->d_lut.p;
+        pa.next_count = e->d_next_count.p;
+        pa.records = want_records ? e->d_records.p + rec_off : nullptr;
+        pa.err = e->d_err.p;
+        pa.next_node_base = nb_level(level + 1);
+        pa.ticket = e->d_ticket.p;
+        pa.lut_w = lut_w;
+        pa.level = level;
+        pa.n_trees = T;
+        TimerSlot tp;
+        if (int rc = timer_open(e, &e->stats.eval_ms, &tp)) return rc;
+        if (want_records) CUDA_TRY(e, cudaMemsetAsync(e->d_records.p + rec_off, 0xFF, (size_t)NF * sizeof(avt_grow_record), e->stream));
+        plan_kernel<<<T, 256, 0, e->stream>>>(pa, make_table(e));
+        CUDA_TRY(e, cudaGetLastError());
+        if (int rc = timer_close(e, tp)) return rc;
+        e->stats.eval_launches += 1;
+        if (want_records) {
+            rec_regions.push_back({rec_off, (size_t)NF});
+            rec_off += (size_t)NF;
+        }
+        fr.node_attr = e->d_node_attr.p;
+        fr.child_lut = e->d_lut.p;
+        fr.lut_w = lut_w;
+        pending = true;
+        last_level = level;
+        for (int t = 0; t < T; ++t) ub[(size_t)t] = (int)std::min<long long>((long long)ub[(size_t)t] * g_max, (long long)AVT_NODE_NONE - 1);
+    }
+    if (pending) {
+        // apply the last planned split so that the node ids match the returned frontier
+        TimerSlot tr;
+        if (int rc = timer_open(e, &e->stats.repart_ms, &tr)) return rc;
+        long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
+        dim3 grid((unsigned)blocks, (unsigned)T);
+        repartition_kernel<<<grid, 256, 0, e->stream>>>(e->nid_cur, (const void* const*)e->d_colptrs.p, e->d_wide.p, nb_level(last_level),
+                                                        e->d_node_attr.p, e->d_lut.p, lut_w, e->N, e->Npad);
+        CUDA_TRY(e, cudaGetLastError());
+        if (int rc = timer_close(e, tr)) return rc;
+        e->stats.repart_launches += 1;
+        e->stats.repart_alg_bytes += (long long)e->N * T * 5;
+    }
+    e->hist_valid = e->scan_valid = false;
+    e->NF = 0;
+    int32_t err = 0;
+    CUDA_TRY(e, cudaMemcpyAsync(&err, e->d_err.p, sizeof err, cudaMemcpyDeviceToHost, e->stream));
+    if (last_level >= 0)
+        CUDA_TRY(e, cudaMemcpyAsync(nb_host.data(), nb_level(last_level + 1), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+    if (want_records && rec_off) {
+        const size_t at = all.size();
+        all.resize(at + rec_off);
+        CUDA_TRY(e, cudaMemcpyAsync(all.data() + at, e->d_records.p, rec_off * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
+    }
+    if (int rc = sync_and_resolve(e)) return rc;
+    if (err) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
+    if (last_level >= 0)
+        for (int t = 0; t < T; ++t) nodes_per_tree[t] = nb_host[(size_t)t + 1] - nb_host[(size_t)t];
+    int64_t nrec = 0;
+    for (size_t i = 0; i < all.size(); ++i) {
+        if (all[i].level < 0 || all[i].split < 0) continue;  // unused slot of a level's bound, or a node that was not expanded
+        if (records && nrec < max_records) records[nrec] = all[i];
+        ++nrec;
+    }
+    if (n_records) *n_records = nrec;
+    return AVT_OK;
+}
+
 int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
                     avt_grow_record* records, int64_t max_records, int64_t* n_records) {
     if (!e) return AVT_E_INVALID;
@@ -905,6 +1086,7 @@ int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const ui
     if (e->T == 0 || e->S == 0) return fail(e, AVT_E_STATE, "avt_grow_levels: needs avt_forest_init and avt_split_table_set first");
     if (criterion != AVT_CRIT_GINI && criterion != AVT_CRIT_ENTROPY) return fail(e, AVT_E_INVALID, "avt_grow_levels: criterion %d", criterion);
     if (int rc = use_device(e)) return rc;
+    if (e->grow_host_loop == 2) return grow_device_loop_sync(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
     if (e->grow_host_loop) return grow_host_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
     return grow_device_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
 }

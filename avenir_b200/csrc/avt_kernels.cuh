@@ -431,7 +431,9 @@ struct PlanArgs {
     int32_t* next_count;       // [T]
     avt_grow_record* records;  // [NF] (nullable)
     int32_t* err;              // set to 1 when a tree would exceed the node-id range
-    int lut_w, level;
+    int32_t* next_node_base;   // [T+1] (nullable): written by the last block to finish
+    uint32_t* ticket;          // zero-initialised counter for the last-block election
+    int lut_w, level, n_trees;
 };
 
 __global__ void __launch_bounds__(256) plan_kernel(PlanArgs p, SplitTable st) {
@@ -514,7 +516,23 @@ __global__ void __launch_bounds__(256) plan_kernel(PlanArgs p, SplitTable st) {
         if (threadIdx.x == 0) running += tot;
         __syncthreads();
     }
-    if (threadIdx.x == 0) p.next_count[t] = running;
+    if (threadIdx.x == 0) {
+        p.next_count[t] = running;
+        if (p.next_node_base) {
+            __threadfence();
+            const uint32_t done = atomicAdd(p.ticket, 1u);
+            if (done == (uint32_t)p.n_trees - 1) {  // every tree's count is visible: prefix them
+                __threadfence();
+                int acc = 0;
+                for (int k = 0; k < p.n_trees; ++k) {
+                    p.next_node_base[k] = acc;
+                    acc += ((volatile int32_t*)p.next_count)[k];
+                }
+                p.next_node_base[p.n_trees] = acc;
+                *p.ticket = 0;
+            }
+        }
+    }
 }
 
 // Children statistics for chosen (node, split) pairs; one thread per pair (tiny).

@@ -206,7 +206,7 @@ def test_api_misuse_is_reported():
         g.set_splits(t)                                  # bound outside the attribute's bins
 
 
-@pytest.mark.parametrize("host_loop", [0, 1])
+@pytest.mark.parametrize("host_loop", [0, 1, 2])
 @pytest.mark.parametrize("criterion", [CRIT_GINI, CRIT_ENTROPY])
 def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
     """avt_grow_levels (device-driven: fused repartition+histogram, scan, on-device planning; and its
