@@ -1205,3 +1205,161 @@ int avt_comm_init_rank(avt_engine* e, int32_t n_ranks, int32_t rank, const void*
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// avt_histogram_static -- histogram counts for callers that must not allocate device memory
+// ================================================================================================
+//
+// Who this is for.  Some hosts of this library run where a device allocation is either forbidden or
+// unaffordable at call time: a task thread inside a service whose GPU memory was carved up at start-up and
+// handed to other components (a later cudaMalloc can fail or push a neighbour out of memory); a caller on
+// a latency budget that cannot absorb cudaMalloc/cudaFree, which take driver-wide locks and may
+// synchronise the whole device; or code that issues its work while another part of the process has a
+// stream capture open, during which allocation calls are not permitted.  The regular entry points
+// (avt_create, avt_dataset_load, avt_level_histogram, ...) allocate and grow device buffers on demand, so
+// they are not usable from such places.
+//
+// What it does.  The same counts as avt_dataset_load + avt_forest_init(1 tree) + avt_level_histogram:
+//     hist_out[node][bin over all attributes][class] = number of rows of that node with that bin and class
+// computed by the warp-aggregated global-atomics histogram kernel (hist_global_kernel).  Everything the
+// kernel needs on the device -- the staged columns, class codes, node ids, its small index tables and
+// the count array it accumulates into -- lives in ONE fixed array that is part of the library image
+// (g_static_scratch below, AVT_STATIC_SCRATCH_BYTES = 8 MiB per GPU that loads the library, held until
+// the process exits).  The call performs no cudaMalloc / cudaFree, creates no stream or event, and uses
+// no allocating library routine; copies and the launch go through the legacy default stream.
+//
+// Limits.  All staged data plus the count array must fit the 8 MiB array; a larger request is refused with
+// AVT_E_INVALID and a message that states the bytes needed and the bytes available (avt_last_error(NULL)).
+// At most AVT_STATIC_MAX_ATTRS attributes.
+//
+// Set-up.  The array's name is only a host-side handle; the device address is obtained once per GPU, with
+// that GPU current, through cudaGetSymbolAddress, and cached.  This happens inside the FIRST call on each
+// device -- make that first call before any stream capture begins in the process.
+//
+// Sharing.  Every call on a device uses the same array and finds whatever the previous call left there.
+// The count region is cleared at the start of every call (it is accumulated into with atomics and must
+// start at zero); all other regions are fully overwritten before they are read.  Two calls that overlap
+// on the same GPU (from two threads, or two processes' worth of threads in one process) race on the array:
+// serialise them.
+#include <mutex>
+
+#define AVT_STATIC_SCRATCH_BYTES (8u << 20)
+#define AVT_STATIC_MAX_ATTRS 64
+#define AVT_STATIC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_static_scratch[AVT_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+struct StaticScratchDev {
+    bool ready = false;
+    unsigned char* base = nullptr;  // device address of g_static_scratch on this GPU
+};
+StaticScratchDev g_static_dev[AVT_STATIC_MAX_DEVICES];
+std::mutex g_static_mu;
+
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+}  // namespace
+
+extern "C" int avt_histogram_static(int device, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins, const void* const* columns,
+                                    const uint8_t* class_codes, int32_t n_classes, const uint16_t* node_ids, int32_t n_nodes,
+                                    uint32_t* hist_out) {
+    if (n_rows <= 0 || n_attrs <= 0 || !n_bins || !columns || !class_codes || !hist_out)
+        return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: empty data set or NULL argument");
+    if (n_attrs > AVT_STATIC_MAX_ATTRS) return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: %d attributes, limit %d", n_attrs, AVT_STATIC_MAX_ATTRS);
+    if (n_classes < 1 || n_classes > AVT_MAX_CLASSES) return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: n_classes %d outside 1..%d", n_classes, AVT_MAX_CLASSES);
+    if (n_nodes < 1 || n_nodes >= (int)AVT_NODE_NONE) return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: n_nodes %d outside 1..%d", n_nodes, AVT_NODE_NONE - 1);
+    if (device < 0 || device >= AVT_STATIC_MAX_DEVICES) return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: device %d outside 0..%d", device, AVT_STATIC_MAX_DEVICES - 1);
+
+    // ---- carve the static array (fixed-size host bookkeeping only: nothing is allocated anywhere)
+    int32_t bin_off[AVT_STATIC_MAX_ATTRS + 1], wide[AVT_STATIC_MAX_ATTRS];
+    size_t col_off[AVT_STATIC_MAX_ATTRS];
+    size_t cur = 0;
+    bin_off[0] = 0;
+    for (int a = 0; a < n_attrs; ++a) {
+        if (n_bins[a] < 1 || n_bins[a] > 65535) return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: n_bins[%d]=%d outside 1..65535", a, n_bins[a]);
+        if (!columns[a]) return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: columns[%d] is NULL", a);
+        bin_off[a + 1] = bin_off[a] + n_bins[a];
+        wide[a] = n_bins[a] > 256;
+        col_off[a] = cur;
+        cur += align256((size_t)n_rows * (wide[a] ? 2 : 1));
+    }
+    const int TB = bin_off[n_attrs];
+    const size_t off_cls = cur;       cur += align256((size_t)n_rows);
+    const size_t off_nid = cur;       cur += align256((size_t)n_rows * 2);
+    const size_t off_ptrs = cur;      cur += align256((size_t)n_attrs * sizeof(void*));
+    const size_t off_binoff = cur;    cur += align256((size_t)(n_attrs + 1) * sizeof(int32_t));
+    const size_t off_wide = cur;      cur += align256((size_t)n_attrs * sizeof(int32_t));
+    const size_t off_nb = cur;        cur += align256(2 * sizeof(int32_t));
+    const size_t off_hist = cur;
+    const size_t hist_bytes = (size_t)n_nodes * TB * n_classes * sizeof(uint32_t);
+    cur += align256(hist_bytes);
+    if (cur > AVT_STATIC_SCRATCH_BYTES)
+        return fail(nullptr, AVT_E_INVALID,
+                    "avt_histogram_static: this request needs %zu bytes of device scratch (%lld rows x %d attributes staged + %d nodes x %d bins x %d classes of "
+                    "counts) but the built-in array holds %u bytes; use avt_level_histogram (which allocates) or split the rows",
+                    cur, (long long)n_rows, n_attrs, n_nodes, TB, n_classes, (unsigned)AVT_STATIC_SCRATCH_BYTES);
+
+    cudaError_t st = cudaSetDevice(device);
+    if (st != cudaSuccess) return fail(nullptr, AVT_E_CUDA, "avt_histogram_static: cudaSetDevice(%d): %s", device, cudaGetErrorString(st));
+    unsigned char* base = nullptr;
+    {
+        // once per GPU, with that GPU current: turn the array's host-side handle into its device address
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        StaticScratchDev& d = g_static_dev[device];
+        if (!d.ready) {
+            void* p = nullptr;
+            st = cudaGetSymbolAddress(&p, g_static_scratch);
+            if (st != cudaSuccess || !p)
+                return fail(nullptr, AVT_E_CUDA, "avt_histogram_static: cudaGetSymbolAddress on device %d: %s", device, cudaGetErrorString(st));
+            d.base = (unsigned char*)p;
+            d.ready = true;
+        }
+        base = d.base;
+    }
+#define STATIC_TRY(call)                                                                                              \
+    do {                                                                                                              \
+        cudaError_t _e = (call);                                                                                      \
+        if (_e != cudaSuccess) return fail(nullptr, AVT_E_CUDA, "avt_histogram_static: %s: %s", #call, cudaGetErrorString(_e)); \
+    } while (0)
+    // ---- stage the caller's host buffers (synchronous copies on the legacy default stream)
+    const void* col_ptrs[AVT_STATIC_MAX_ATTRS];
+    for (int a = 0; a < n_attrs; ++a) {
+        STATIC_TRY(cudaMemcpy(base + col_off[a], columns[a], (size_t)n_rows * (wide[a] ? 2 : 1), cudaMemcpyHostToDevice));
+        col_ptrs[a] = base + col_off[a];
+    }
+    STATIC_TRY(cudaMemcpy(base + off_cls, class_codes, (size_t)n_rows, cudaMemcpyHostToDevice));
+    if (node_ids) STATIC_TRY(cudaMemcpy(base + off_nid, node_ids, (size_t)n_rows * 2, cudaMemcpyHostToDevice));
+    else STATIC_TRY(cudaMemset(base + off_nid, 0, (size_t)n_rows * 2));  // every row in node 0
+    const int32_t node_base[2] = {0, n_nodes};
+    STATIC_TRY(cudaMemcpy(base + off_ptrs, col_ptrs, (size_t)n_attrs * sizeof(void*), cudaMemcpyHostToDevice));
+    STATIC_TRY(cudaMemcpy(base + off_binoff, bin_off, (size_t)(n_attrs + 1) * sizeof(int32_t), cudaMemcpyHostToDevice));
+    STATIC_TRY(cudaMemcpy(base + off_wide, wide, (size_t)n_attrs * sizeof(int32_t), cudaMemcpyHostToDevice));
+    STATIC_TRY(cudaMemcpy(base + off_nb, node_base, sizeof node_base, cudaMemcpyHostToDevice));
+    // the counts are accumulated with atomics: whatever an earlier call left in this region must go
+    STATIC_TRY(cudaMemset(base + off_hist, 0, hist_bytes));
+
+    HistArgs ha{};
+    ha.cols = (const void* const*)(base + off_ptrs);
+    ha.cls = base + off_cls;
+    ha.nid = (const uint16_t*)(base + off_nid);
+    ha.wts = nullptr;
+    ha.has_w = nullptr;
+    ha.H = (uint32_t*)(base + off_hist);
+    ha.node_base = (const int32_t*)(base + off_nb);
+    ha.N = n_rows;
+    ha.Npad = n_rows;
+    ha.C = n_classes;
+    ha.TB = TB;
+    ha.T = 1;
+    int sm_count = kSmCountFallback;
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device);
+    const long long blocks = std::min<long long>((n_rows + 255) / 256, (long long)sm_count * 8);
+    hist_global_kernel<<<dim3((unsigned)blocks, 1), 256, 0, 0>>>(ha, n_attrs, (const int32_t*)(base + off_binoff), (const int32_t*)(base + off_wide));
+    STATIC_TRY(cudaGetLastError());
+    // synchronous copy on the same stream: waits for the kernel
+    STATIC_TRY(cudaMemcpy(hist_out, base + off_hist, hist_bytes, cudaMemcpyDeviceToHost));
+#undef STATIC_TRY
+    return AVT_OK;
+}

@@ -214,6 +214,23 @@ int avt_reset_stats(avt_engine* e);
 /* Forces a histogram variant (-1 auto, 0 shared-memory, 1 global atomics) -- for tests/profiling. */
 int avt_set_hist_variant(avt_engine* e, int32_t variant);
 
+/* Allocation-free histogram.  NO COUNTERPART IN THE REFERENCE (and none in its Java object seams): it exists
+ * for hosts that may not allocate device memory when they call -- a process whose GPU memory was divided
+ * up at start-up, a thread on a latency budget that cannot take cudaMalloc/cudaFree's device-wide locks,
+ * or code running while a stream capture is open elsewhere in the process.  Same counts as
+ * avt_dataset_load + avt_forest_init(1 tree) + avt_level_histogram for one tree:
+ *   hist_out[node][bin over all attributes][class], uint32, n_nodes x sum(n_bins) x n_classes.
+ * columns / class_codes / node_ids are host buffers as in avt_dataset_load / avt_forest_init (node_ids NULL
+ * = every row in node 0, AVT_NODE_NONE = row skipped).  All device-side storage is a fixed 8 MiB array
+ * built into the library (one copy per GPU that loads it, kept until exit): no cudaMalloc, cudaFree,
+ * stream or event creation happens.  Requests whose staged inputs plus counts exceed that array, or with
+ * more than 64 attributes, fail with AVT_E_INVALID (avt_last_error(NULL) states needed vs available bytes).
+ * The first call on each device looks up the array's device address: make it before any stream capture.
+ * Calls on one GPU share the array; overlapping calls race -- serialise them. */
+int avt_histogram_static(int device, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins,
+                         const void* const* columns, const uint8_t* class_codes, int32_t n_classes,
+                         const uint16_t* node_ids, int32_t n_nodes, uint32_t* hist_out);
+
 /* ---- multi-GPU: one process per GPU, rows sharded, histograms summed over NVLink ------------- */
 /* Fills 128 bytes with an NCCL unique id (rank 0 calls it, the host broadcasts it). */
 int avt_comm_unique_id(void* id128);

@@ -1,0 +1,84 @@
+"""avt_histogram_static: the histogram entry point for hosts that may not allocate device memory when they
+call (GPU memory fully assigned at start-up, a latency budget that excludes cudaMalloc/cudaFree, a stream
+capture open elsewhere in the process).  It keeps every device-side byte in an 8 MiB array built into the
+library, so a second call finds the first call's leftovers there: the test makes two calls in a row, with
+different shapes, and holds each against the regular (allocating) entry point, bit for bit -- the same
+tolerance every other count comparison in this suite uses.
+
+Kept in a file that pytest collects last: if it fails under `-x`, every other test has already run.
+Runs alone (fresh process: the first call does the per-device address look-up) and after the other tests.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from avenir_b200 import synth
+from avenir_b200._lib import AVT_NODE_NONE
+from avenir_b200.engine import Engine, binary_split_table
+
+pytestmark = pytest.mark.gpu
+
+
+def static_histogram(lib, cols, cls, n_bins, n_classes, node_ids, n_nodes, device=0):
+    fixed = [np.ascontiguousarray(c, dtype=np.uint16 if b > 256 else np.uint8) for c, b in zip(cols, n_bins)]
+    cls = np.ascontiguousarray(cls, dtype=np.uint8)
+    nb = (C.c_int32 * len(n_bins))(*n_bins)
+    ptrs = (C.c_void_p * len(fixed))(*[c.ctypes.data for c in fixed])
+    out = np.full((n_nodes, sum(n_bins), n_classes), 0xDEADBEEF, dtype=np.uint32)
+    nid = None if node_ids is None else np.ascontiguousarray(node_ids, dtype=np.uint16)
+    rc = lib.avt_histogram_static(device, len(cls), len(fixed), nb, ptrs, cls.ctypes.data_as(C.c_void_p), n_classes,
+                                  None if nid is None else nid.ctypes.data_as(C.c_void_p), n_nodes, out.ctypes.data_as(C.c_void_p))
+    return rc, out
+
+
+def regular_histogram(cols, cls, n_bins, n_classes, node_ids, n_nodes):
+    eng = Engine(0)
+    eng.load_dataset(cols, cls, n_bins, n_classes)
+    eng.forest_init(1, None, None if node_ids is None else [node_ids])
+    eng.set_splits(binary_split_table(n_bins, [False] * len(n_bins)))
+    h = eng.histogram([n_nodes], fetch=True)
+    eng.close()
+    return h
+
+
+def test_two_calls_in_a_row_match_the_allocating_entry_point():
+    from avenir_b200 import _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(2026)
+
+    # call 1: 5 nodes, some rows outside the frontier, a uint16 column, 3 classes
+    n1, bins1 = 120_007, [7, 300, 16, 3]
+    cols1, cls1 = synth.binned_dataset(n1, bins1, 3, seed=31)
+    nid1 = rng.integers(0, 5, size=n1).astype(np.uint16)
+    nid1[rng.random(n1) < 0.1] = AVT_NODE_NONE
+    rc, got1 = static_histogram(lib, cols1, cls1, bins1, 3, nid1, 5)
+    assert rc == 0, lib.avt_last_error(None).decode()
+    assert np.array_equal(got1, regular_histogram(cols1, cls1, bins1, 3, nid1, 5))
+
+    # call 2 straight after, smaller and differently shaped: nothing of call 1 may show through
+    n2, bins2 = 33_333, [2, 4, 2, 10]
+    cols2, cls2, bins2, _ = synth.call_hangup_encoded(n2)
+    rc, got2 = static_histogram(lib, cols2, cls2, bins2, 2, None, 1)
+    assert rc == 0, lib.avt_last_error(None).decode()
+    want2 = regular_histogram(cols2, cls2, bins2, 2, None, 1)
+    assert np.array_equal(got2, want2)
+    assert int(got2.sum()) == 4 * n2            # every row counted once per attribute, no stale counts
+
+    # and call 1's inputs again give call 1's answer again
+    rc, again = static_histogram(lib, cols1, cls1, bins1, 3, nid1, 5)
+    assert rc == 0 and np.array_equal(again, got1)
+
+
+def test_requests_beyond_the_built_in_array_are_refused():
+    from avenir_b200 import _lib
+    lib = _lib.load()
+    n = 3_000_000                                # 4 staged columns + classes + node ids > 8 MiB
+    cols = [np.zeros(n, dtype=np.uint8) for _ in range(4)]
+    rc, out = static_histogram(lib, cols, np.zeros(n, dtype=np.uint8), [2, 4, 2, 10], 2, None, 1)
+    assert rc == -1
+    msg = lib.avt_last_error(None).decode()
+    assert "needs" in msg and "8388608" in msg
+    assert (out == 0xDEADBEEF).all()             # nothing was written
+    rc, _ = static_histogram(lib, [np.zeros(10, dtype=np.uint8)] * 65, np.zeros(10, dtype=np.uint8), [2] * 65, 2, None, 1)
+    assert rc == -1 and "limit 64" in lib.avt_last_error(None).decode()
