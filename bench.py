@@ -191,11 +191,8 @@ def main():
 
     eng = Engine(local)
     if world > 1:
-        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            uid.copy_(torch.frombuffer(bytearray(comm_unique_id()), dtype=torch.uint8))
-        dist.broadcast(uid, 0)
-        eng.comm_init(world, rank, bytes(uid.cpu().numpy().tobytes()))
+        from avenir_b200.sharding import share_unique_id
+        eng.comm_init(world, rank, share_unique_id(dist, comm_unique_id, device="cuda"))
     eng.load_dataset(cols_p, cls_p, n_bins, 2)
     eng.set_splits(table)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
