@@ -74,6 +74,7 @@ SIGNATURES = {
     "avt_synchronize": (C.c_int, [_P]),
     "avt_get_stats": (C.c_int, [_P, C.POINTER(Stats)]),
     "avt_reset_stats": (C.c_int, [_P]),
+    "avt_set_profiling": (C.c_int, [_P, C.c_int32]),
     "avt_set_hist_variant": (C.c_int, [_P, C.c_int32]),
     "avt_comm_unique_id": (C.c_int, [_P]),
     "avt_comm_init_rank": (C.c_int, [_P, C.c_int32, C.c_int32, _P]),

@@ -108,6 +108,8 @@ struct avt_engine {
     cudaEvent_t tev0 = nullptr, tev1 = nullptr;
     avt_stats stats{};
     int force_variant = -1;
+    bool skip_h_memset = false;
+    bool profiling = true;  // CUDA-event timing of every launch (avt_set_profiling)
     long long hist_target_addrs = 4096;  // AVT_HIST_TARGET_ADDRS
     int grow_host_loop = 0;              // AVT_GROW_HOST=1: host-driven level loop (3 round trips per level)
     // comm
@@ -151,6 +153,8 @@ int use_device(avt_engine* e) {
 
 // device timing: events around a launch, resolved at the next synchronisation point
 int timer_open(avt_engine* e, double* acc, TimerSlot* slot) {
+    slot->acc = nullptr;
+    if (!e->profiling) return AVT_OK;
     if (e->free_events.empty()) {
         cudaEvent_t a, b;
         CUDA_TRY(e, cudaEventCreate(&a));
@@ -166,6 +170,7 @@ int timer_open(avt_engine* e, double* acc, TimerSlot* slot) {
     return AVT_OK;
 }
 int timer_close(avt_engine* e, const TimerSlot& slot) {
+    if (!slot.acc) return AVT_OK;
     CUDA_TRY(e, cudaEventRecord(slot.b, e->stream));
     e->pending.push_back(slot);
     return AVT_OK;
@@ -476,7 +481,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
 
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.hist_ms, &ts)) return rc;
-    CUDA_TRY(e, cudaMemsetAsync(e->d_H.p, 0, hwords * sizeof(uint32_t), e->stream));
+    if (!e->skip_h_memset) CUDA_TRY(e, cudaMemsetAsync(e->d_H.p, 0, hwords * sizeof(uint32_t), e->stream));
     if (variant == 0) {
         // Replication policy: enough copies that a warp's 32 updates spread over >= kTargetAddrs distinct
         // words, but no more -- smaller histograms mean more resident blocks per SM (latency hiding).
@@ -630,7 +635,7 @@ int avt_level_scan(avt_engine* e, int32_t criterion, const uint32_t* cand_mask, 
     CUDA_TRY(e, e->d_best.ensure((size_t)e->NF));
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
-    scan_kernel<<<e->NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), dmask, e->d_order.p, criterion, e->d_av.p, e->d_best.p, nullptr, nullptr);
+    scan_kernel<<<e->NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), dmask, e->d_order.p, criterion, e->d_av.p, e->d_best.p, nullptr, nullptr, PlanArgs{});
     CUDA_TRY(e, cudaGetLastError());
     if (int rc = timer_close(e, ts)) return rc;
     e->stats.scan_launches += 1;
@@ -829,7 +834,7 @@ static int grow_device_loop_sync(avt_engine* e, int32_t n_levels, int32_t criter
         TimerSlot ts;
         if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
         scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), nullptr, e->d_order.p, criterion, e->d_av.p, e->d_best.p,
-                                                        e->d_best_eval.p, nullptr);
+                                                        e->d_best_eval.p, nullptr, PlanArgs{});
         CUDA_TRY(e, cudaGetLastError());
         if (int rc = timer_close(e, ts)) return rc;
         e->stats.scan_launches += 1;
@@ -854,7 +859,7 @@ static int grow_device_loop_sync(avt_engine* e, int32_t n_levels, int32_t criter
         pa.n_trees = e->T;
         TimerSlot tp;
         if (int rc = timer_open(e, &e->stats.eval_ms, &tp)) return rc;
-        plan_kernel<<<e->T, 256, 0, e->stream>>>(pa, make_table(e));
+        plan_kernel<<<1, kScanThreads, 0, e->stream>>>(pa, make_table(e));
         CUDA_TRY(e, cudaGetLastError());
         if (int rc = timer_close(e, tp)) return rc;
         e->stats.eval_launches += 1;
@@ -927,13 +932,16 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     CUDA_TRY(e, cudaMemsetAsync(e->d_ticket.p, 0, sizeof(uint32_t), e->stream));
     std::vector<avt_grow_record> all;
     std::vector<int32_t> ub(nodes_per_tree, nodes_per_tree + T), nb_host((size_t)T + 1);
-    std::vector<std::pair<size_t, size_t>> rec_regions;  // (offset, count) of every level's record region
+    struct RecRegion { int level; size_t host_at, count; };
+    std::vector<RecRegion> rec_regions;  // where each level's record slots end up in `all`
+    size_t flushed = 0;                  // records already copied to `all` by a mid-loop flush
     auto nb_level = [&](int level) { return e->d_nb_all.p + (size_t)level * (T + 1); };
     // level 0: the caller's frontier is exact
     nb_host[0] = 0;
     for (int t = 0; t < T; ++t) nb_host[(size_t)t + 1] = nb_host[(size_t)t] + ub[(size_t)t];
     CUDA_TRY(e, cudaMemcpyAsync(nb_level(0), nb_host.data(), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
     bool pending = false;
+    bool h_prezeroed = false;  // the previous level's planning block already cleared this level's histogram region
     FusedRepart fr{};
     size_t rec_off = 0;
     int last_level = -1;
@@ -971,6 +979,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
                 const size_t at = all.size();
                 all.resize(at + rec_off);
                 CUDA_TRY(e, cudaMemcpy(all.data() + at, e->d_records.p, rec_off * sizeof(avt_grow_record), cudaMemcpyDeviceToHost));
+                flushed += rec_off;
                 rec_off = 0;
             }
             // tables of the previous level are still needed by this level's fused pass: preserve them
@@ -1000,15 +1009,10 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             }
         }
         if (pending) fr.prev_node_base = nb_level(level - 1);
+        e->skip_h_memset = h_prezeroed;
         if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr, nb_level(level))) return rc;
+        e->skip_h_memset = false;
         pending = false;
-        TimerSlot ts;
-        if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
-        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), nullptr, e->d_order.p, criterion, e->d_av.p, e->d_best.p,
-                                                        e->d_best_eval.p, nb_level(level) + T);
-        CUDA_TRY(e, cudaGetLastError());
-        if (int rc = timer_close(e, ts)) return rc;
-        e->stats.scan_launches += 1;
         PlanArgs pa{};
         pa.best = e->d_best.p;
         pa.best_eval = e->d_best_eval.p;
@@ -1023,15 +1027,24 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         pa.lut_w = lut_w;
         pa.level = level;
         pa.n_trees = T;
-        TimerSlot tp;
-        if (int rc = timer_open(e, &e->stats.eval_ms, &tp)) return rc;
-        if (want_records) CUDA_TRY(e, cudaMemsetAsync(e->d_records.p + rec_off, 0xFF, (size_t)NF * sizeof(avt_grow_record), e->stream));
-        plan_kernel<<<T, 256, 0, e->stream>>>(pa, make_table(e));
+        // the planning block also clears the next level's histogram region when that is small
+        {
+            long long next_nodes = 0;
+            for (int t = 0; t < T; ++t) next_nodes += std::min<long long>((long long)ub[(size_t)t] * g_max, (long long)AVT_NODE_NONE - 1);
+            const long long next_words = next_nodes * e->TB * e->C;
+            h_prezeroed = level + 1 < n_levels && next_nodes <= kAsyncNodeLimit && next_words <= (1 << 16) && (size_t)next_words <= e->d_H.cap;
+            pa.zero_ptr = h_prezeroed ? e->d_H.p : nullptr;
+            pa.zero_words = h_prezeroed ? next_words : 0;
+        }
+        TimerSlot ts;
+        if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
+        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), nullptr, e->d_order.p, criterion, e->d_av.p, e->d_best.p,
+                                                        e->d_best_eval.p, nb_level(level) + T, pa);
         CUDA_TRY(e, cudaGetLastError());
-        if (int rc = timer_close(e, tp)) return rc;
-        e->stats.eval_launches += 1;
+        if (int rc = timer_close(e, ts)) return rc;
+        e->stats.scan_launches += 1;
         if (want_records) {
-            rec_regions.push_back({rec_off, (size_t)NF});
+            rec_regions.push_back({level, flushed + rec_off, (size_t)NF});
             rec_off += (size_t)NF;
         }
         fr.node_attr = e->d_node_attr.p;
@@ -1058,14 +1071,22 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     e->NF = 0;
     int32_t err = 0;
     CUDA_TRY(e, cudaMemcpyAsync(&err, e->d_err.p, sizeof err, cudaMemcpyDeviceToHost, e->stream));
+    std::vector<int32_t> nb_all_host((size_t)(last_level + 2) * (T + 1));
     if (last_level >= 0)
-        CUDA_TRY(e, cudaMemcpyAsync(nb_host.data(), nb_level(last_level + 1), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(nb_all_host.data(), e->d_nb_all.p, nb_all_host.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+    const size_t tail_at = all.size();
     if (want_records && rec_off) {
-        const size_t at = all.size();
-        all.resize(at + rec_off);
-        CUDA_TRY(e, cudaMemcpyAsync(all.data() + at, e->d_records.p, rec_off * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
+        all.resize(tail_at + rec_off);
+        CUDA_TRY(e, cudaMemcpyAsync(all.data() + tail_at, e->d_records.p, rec_off * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
     }
     if (int rc = sync_and_resolve(e)) return rc;
+    if (last_level >= 0)
+        for (int t = 0; t <= T; ++t) nb_host[(size_t)t] = nb_all_host[(size_t)(last_level + 1) * (T + 1) + t];
+    // slots of a level's region beyond its true frontier were never written: mark them unused
+    for (auto& rg : rec_regions) {
+        const size_t true_nf = (size_t)nb_all_host[(size_t)rg.level * (T + 1) + T];
+        for (size_t i = true_nf; i < rg.count; ++i) all[rg.host_at + i].level = -1;
+    }
     if (err) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
     if (last_level >= 0)
         for (int t = 0; t < T; ++t) nodes_per_tree[t] = nb_host[(size_t)t + 1] - nb_host[(size_t)t];
@@ -1176,6 +1197,14 @@ int avt_set_hist_variant(avt_engine* e, int32_t variant) {
     if (!e) return AVT_E_INVALID;
     if (variant < -1 || variant > 1) return fail(e, AVT_E_INVALID, "avt_set_hist_variant: %d", variant);
     e->force_variant = variant;
+    return AVT_OK;
+}
+
+int avt_set_profiling(avt_engine* e, int32_t on) {
+    if (!e) return AVT_E_INVALID;
+    if (int rc = use_device(e)) return rc;
+    if (int rc = sync_and_resolve(e)) return rc;
+    e->profiling = on != 0;
     return AVT_OK;
 }
 

@@ -329,211 +329,11 @@ __device__ __forceinline__ void best_merge(ScanBest& a, const ScanBest& b) {
     }
 }
 
-// One block per frontier node.  Warps take the node's candidate attributes round-robin; a warp
-// stages the attribute's prefix counts in shared memory, its lanes evaluate the attribute's splits
-// and write av[node][split]; the block reduces to (min av, lowest split index, number of ties).
-__global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, SplitTable st,
-                                                            const uint32_t* cand_mask,
-                                                            const uint8_t* order, int criterion,
-                                                            double* av_buf, avt_node_best* out,
-                                                            avt_split_eval* best_eval, const int32_t* n_nodes_dev) {
-    __shared__ uint32_t Pbuf[kScanWarps][kScanWordsPerWarp];
-    __shared__ ScanBest wbest[kScanWarps];
-    const int node = blockIdx.x;
-    if (n_nodes_dev && node >= *n_nodes_dev) return;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int C = st.C;
-    const uint32_t* Hnode = H + (long long)node * st.TB * C;
-    const int mask_words = (st.A + 31) >> 5;
-    const double nan = __longlong_as_double(0x7ff8000000000000LL);
-    ScanBest best{0.0, -1, 0};
-    for (int at = warp; at < st.A; at += kScanWarps) {
-        const int s0 = st.attr_first[at], s1 = st.attr_first[at + 1];
-        if (s0 == s1) continue;
-        const bool cand = cand_mask == nullptr ||
-                          ((cand_mask[(long long)node * mask_words + (at >> 5)] >> (at & 31)) & 1u);
-        if (!cand) {
-            for (int s = s0 + lane; s < s1; s += 32) av_buf[(long long)node * st.S + s] = nan;
-            continue;
-        }
-        const int B = st.bin_off[at + 1] - st.bin_off[at];
-        const uint32_t* Hn = Hnode + (long long)st.bin_off[at] * C;
-        const uint32_t* P = nullptr;
-        if (B * C <= kScanWordsPerWarp) {
-            __syncwarp();
-            warp_prefix(Hn, Pbuf[warp], B, C);
-            P = Pbuf[warp];
-        }
-        for (int s = s0 + lane; s < s1; s += 32) {
-            const avt_split sp = st.splits[s];
-            const double av = split_av(st, sp, B, P, Hn, order, criterion, nullptr);
-            av_buf[(long long)node * st.S + s] = av;
-            ScanBest b{av, s, 1};
-            if (av == av) best_merge(best, b);  // NaN never wins (`av < min` is false in Java too)
-        }
-    }
-    // warp reduce
-#pragma unroll
-    for (int d = 16; d; d >>= 1) {
-        ScanBest o;
-        o.av = __shfl_xor_sync(0xffffffffu, best.av, d);
-        o.split = __shfl_xor_sync(0xffffffffu, best.split, d);
-        o.ties = __shfl_xor_sync(0xffffffffu, best.ties, d);
-        best_merge(best, o);
-    }
-    if (lane == 0) wbest[warp] = best;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        ScanBest b = wbest[0];
-        for (int w = 1; w < kScanWarps; ++w) best_merge(b, wbest[w]);
-        // the node's own class counts: bins of the first attribute that has any
-        uint32_t cnt[kMaxC];
-        for (int c = 0; c < C; ++c) cnt[c] = 0;
-        const int B0 = st.bin_off[1] - st.bin_off[0];
-        for (int bb = 0; bb < B0; ++bb)
-            for (int c = 0; c < C; ++c) cnt[c] += Hnode[bb * C + c];
-        uint32_t n = 0;
-        for (int c = 0; c < C; ++c) n += cnt[c];
-        avt_node_best r;
-        r.min_av = b.split >= 0 ? b.av : nan;
-        r.node_stat = impurity(cnt, C, order, criterion, n);
-        r.population = n;
-        r.best_split = b.split;
-        r.n_ties = b.ties;
-        out[node] = r;
-        // children of the (lowest-index) best split, so that a tie-free level needs no second pass
-        if (best_eval) {
-            avt_split_eval ev;
-            for (int j = 0; j < kMaxSeg; ++j) {
-                ev.seg_stat[j] = 0.0;
-                for (int c = 0; c < kMaxC; ++c) ev.seg_count[j][c] = 0;
-            }
-            ev.av = nan;
-            if (b.split >= 0 && n > 0) {
-                const avt_split sp = st.splits[b.split];
-                const int Bs = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
-                ev.av = split_av(st, sp, Bs, nullptr, Hnode + (long long)st.bin_off[sp.attr] * C, order, criterion, &ev);
-            }
-            best_eval[node] = ev;
-        }
-    }
-}
+}  // namespace avt
 
-// Device-side level planning: from the scan results derive, per tree, the numbering of the children,
-// the bin -> child table and split attribute of every frontier node (inputs of the next fused
-// repartition + histogram pass), the next frontier sizes, and one record per node.  grid = T blocks.
-struct PlanArgs {
-    const avt_node_best* best;
-    const avt_split_eval* best_eval;
-    const int32_t* node_base;  // [T+1] current frontier
-    int32_t* node_attr;        // [NF]
-    uint16_t* child_lut;       // [NF][lut_w]
-    int32_t* next_count;       // [T]
-    avt_grow_record* records;  // [NF] (nullable)
-    int32_t* err;              // set to 1 when a tree would exceed the node-id range
-    int32_t* next_node_base;   // [T+1] (nullable): written by the last block to finish
-    uint32_t* ticket;          // zero-initialised counter for the last-block election
-    int lut_w, level, n_trees;
-};
+#include "avt_scan.cuh"
 
-__global__ void __launch_bounds__(256) plan_kernel(PlanArgs p, SplitTable st) {
-    __shared__ int warp_tot[8];
-    __shared__ int running;
-    const int t = blockIdx.x;
-    const int nb = p.node_base[t], n = p.node_base[t + 1] - nb;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) running = 0;
-    __syncthreads();
-    for (int i0 = 0; i0 < n; i0 += blockDim.x) {
-        const int i = i0 + threadIdx.x;
-        const int g = nb + i;
-        int nkids = 0;
-        bool live = false;
-        avt_split sp{};
-        if (i < n) {
-            const avt_node_best b = p.best[g];
-            live = b.population > 0 && b.best_split >= 0;
-            if (live) {
-                sp = st.splits[b.best_split];
-                for (int sg = 0; sg < sp.n_seg; ++sg) {
-                    uint32_t pop = 0;
-                    for (int c = 0; c < st.C; ++c) pop += p.best_eval[g].seg_count[sg][c];
-                    nkids += pop != 0;
-                }
-            }
-        }
-        // block exclusive scan of nkids
-        int v = nkids;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int u = __shfl_up_sync(0xffffffffu, v, d);
-            if (lane >= d) v += u;
-        }
-        if (lane == 31) warp_tot[warp] = v;
-        __syncthreads();
-        int woff = 0, tot = 0;
-        for (int w = 0; w < 8; ++w) {
-            if (w < warp) woff += warp_tot[w];
-            tot += warp_tot[w];
-        }
-        const int first = running + woff + v - nkids;
-        if (i < n) {
-            p.node_attr[g] = live ? sp.attr : -1;
-            uint16_t* lut = p.child_lut + (long long)g * p.lut_w;
-            for (int b = 0; b < p.lut_w; ++b) lut[b] = (uint16_t)AVT_NODE_NONE;
-            avt_grow_record rec;
-            rec.level = p.level; rec.tree = t; rec.node = i;
-            rec.split = live ? p.best[g].best_split : -1;
-            rec.n_ties = p.best[g].n_ties;
-            rec.min_av = p.best[g].min_av;
-            for (int sg = 0; sg < kMaxSeg; ++sg) { rec.child[sg] = -1; rec.child_pop[sg] = 0; rec.child_stat[sg] = 0.0; }
-            if (live) {
-                int k = 0;
-                for (int sg = 0; sg < sp.n_seg; ++sg) {
-                    long long pop = 0;
-                    for (int c = 0; c < st.C; ++c) pop += p.best_eval[g].seg_count[sg][c];
-                    rec.child_pop[sg] = pop;
-                    rec.child_stat[sg] = p.best_eval[g].seg_stat[sg];
-                    if (pop) rec.child[sg] = first + k++;
-                }
-                if (first + k > (int)AVT_NODE_NONE - 1) *p.err = 1;
-                const int B = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
-                for (int b = 0; b < B; ++b) {
-                    int sg;
-                    if (sp.kind == AVT_SPLIT_NUMERIC) {
-                        sg = 0;
-                        while (sg < sp.n_seg - 1 && b > st.bounds[sp.off + sg]) ++sg;
-                    } else {
-                        sg = st.seg_lut[sp.off + b];
-                        if (sg >= sp.n_seg) continue;
-                    }
-                    if (rec.child[sg] >= 0) lut[b] = (uint16_t)rec.child[sg];
-                }
-            }
-            if (p.records) p.records[g] = rec;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) running += tot;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        p.next_count[t] = running;
-        if (p.next_node_base) {
-            __threadfence();
-            const uint32_t done = atomicAdd(p.ticket, 1u);
-            if (done == (uint32_t)p.n_trees - 1) {  // every tree's count is visible: prefix them
-                __threadfence();
-                int acc = 0;
-                for (int k = 0; k < p.n_trees; ++k) {
-                    p.next_node_base[k] = acc;
-                    acc += ((volatile int32_t*)p.next_count)[k];
-                }
-                p.next_node_base[p.n_trees] = acc;
-                *p.ticket = 0;
-            }
-        }
-    }
-}
+namespace avt {
 
 // Children statistics for chosen (node, split) pairs; one thread per pair (tiny).
 __global__ void eval_kernel(const uint32_t* H, SplitTable st, const uint8_t* order, int criterion, int n,

@@ -1,0 +1,292 @@
+// Kernel (b): fused impurity scan + per-node arg-min, with the children of the best split and -- in the
+// device-driven level loop -- the planning of the next level folded in (last block to finish).
+// Included by avt_kernels.cuh after SplitTable / split_av / warp_prefix / ScanBest.
+#pragma once
+
+namespace avt {
+
+// Level planning state (device-driven loop): from the scan results derive, per tree, the numbering of the
+// children, the bin -> child table and split attribute of every frontier node (inputs of the next fused
+// repartition + histogram pass), the next frontier's node_base, and one record per node.
+struct PlanArgs {
+    const avt_node_best* best;
+    const avt_split_eval* best_eval;
+    const int32_t* node_base;  // [T+1] current frontier
+    int32_t* node_attr;        // [NF]
+    uint16_t* child_lut;       // [NF][lut_w]
+    int32_t* next_count;       // [T]
+    avt_grow_record* records;  // [NF] (nullable)
+    int32_t* err;              // set to 1 when a tree would exceed the node-id range
+    int32_t* next_node_base;   // [T+1] (nullable)
+    uint32_t* ticket;          // zero-initialised counter for the last-block election (nullptr: no planning)
+    uint32_t* zero_ptr;        // words to clear for the next level's histogram (nullable)
+    long long zero_words;
+    int lut_w, level, n_trees;
+};
+
+// loads that bypass L1: the planning block reads what OTHER blocks of the same launch wrote
+__device__ __forceinline__ int32_t ldcg_i32(const int32_t* p) { return __ldcg(p); }
+__device__ __forceinline__ uint32_t ldcg_u32(const uint32_t* p) { return __ldcg(p); }
+__device__ __forceinline__ long long ldcg_i64(const int64_t* p) { return __ldcg((const long long*)p); }
+__device__ __forceinline__ double ldcg_f64(const double* p) { return __ldcg(p); }
+
+// Plans one tree with the whole block (blockDim.x = kScanThreads).
+__device__ void plan_tree(const PlanArgs& p, const SplitTable& st, int t, int* warp_tot, int* running) {
+    const int nb = p.node_base[t], n = p.node_base[t + 1] - nb;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) *running = 0;
+    __syncthreads();
+    for (int i0 = 0; i0 < n; i0 += blockDim.x) {
+        const int i = i0 + threadIdx.x;
+        const int g = nb + i;
+        int nkids = 0, best_split = -1;
+        bool live = false;
+        avt_split sp{};
+        if (i < n) {
+            best_split = ldcg_i32(&p.best[g].best_split);
+            live = ldcg_i64(&p.best[g].population) > 0 && best_split >= 0;
+            if (live) {
+                sp = st.splits[best_split];
+                for (int sg = 0; sg < sp.n_seg; ++sg) {
+                    uint32_t pop = 0;
+                    for (int c = 0; c < st.C; ++c) pop += ldcg_u32(&p.best_eval[g].seg_count[sg][c]);
+                    nkids += pop != 0;
+                }
+            }
+        }
+        int v = nkids;  // block exclusive scan of nkids
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int u = __shfl_up_sync(0xffffffffu, v, d);
+            if (lane >= d) v += u;
+        }
+        if (lane == 31) warp_tot[warp] = v;
+        __syncthreads();
+        int woff = 0, tot = 0;
+        for (int w = 0; w < kScanWarps; ++w) {
+            if (w < warp) woff += warp_tot[w];
+            tot += warp_tot[w];
+        }
+        const int first = *running + woff + v - nkids;
+        if (i < n) {
+            p.node_attr[g] = live ? sp.attr : -1;
+            uint16_t* lut = p.child_lut + (long long)g * p.lut_w;
+            for (int b = 0; b < p.lut_w; ++b) lut[b] = (uint16_t)AVT_NODE_NONE;
+            avt_grow_record rec;
+            rec.level = p.level; rec.tree = t; rec.node = i;
+            rec.split = live ? best_split : -1;
+            rec.n_ties = ldcg_i32(&p.best[g].n_ties);
+            rec.min_av = ldcg_f64(&p.best[g].min_av);
+            for (int sg = 0; sg < kMaxSeg; ++sg) { rec.child[sg] = -1; rec.child_pop[sg] = 0; rec.child_stat[sg] = 0.0; }
+            if (live) {
+                int k = 0;
+                for (int sg = 0; sg < sp.n_seg; ++sg) {
+                    long long pop = 0;
+                    for (int c = 0; c < st.C; ++c) pop += ldcg_u32(&p.best_eval[g].seg_count[sg][c]);
+                    rec.child_pop[sg] = pop;
+                    rec.child_stat[sg] = ldcg_f64(&p.best_eval[g].seg_stat[sg]);
+                    if (pop) rec.child[sg] = first + k++;
+                }
+                if (first + k > (int)AVT_NODE_NONE - 1) *p.err = 1;
+                const int B = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
+                for (int b = 0; b < B; ++b) {
+                    int sg;
+                    if (sp.kind == AVT_SPLIT_NUMERIC) {
+                        sg = 0;
+                        while (sg < sp.n_seg - 1 && b > st.bounds[sp.off + sg]) ++sg;
+                    } else {
+                        sg = st.seg_lut[sp.off + b];
+                        if (sg >= sp.n_seg) continue;
+                    }
+                    if (rec.child[sg] >= 0) lut[b] = (uint16_t)rec.child[sg];
+                }
+            }
+            if (p.records) p.records[g] = rec;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) *running += tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) p.next_count[t] = *running;
+    __syncthreads();
+}
+
+// Whole-level planning by one block: every tree, then the next frontier's node_base, then (optionally)
+// the zeroing of the next level's histogram region.
+__device__ void plan_level(const PlanArgs& p, const SplitTable& st, int* warp_tot, int* running) {
+    for (int t = 0; t < p.n_trees; ++t) plan_tree(p, st, t, warp_tot, running);
+    if (threadIdx.x == 0 && p.next_node_base) {
+        int acc = 0;
+        for (int k = 0; k < p.n_trees; ++k) {
+            p.next_node_base[k] = acc;
+            acc += p.next_count[k];
+        }
+        p.next_node_base[p.n_trees] = acc;
+    }
+    if (p.zero_ptr)
+        for (long long i = threadIdx.x; i < p.zero_words; i += blockDim.x) p.zero_ptr[i] = 0;
+}
+
+// One block per frontier node (blocks beyond the true frontier only take part in the last-block
+// election).  Warps take the node's candidate attributes round-robin; a warp stages the attribute's
+// prefix counts in shared memory, its lanes evaluate the attribute's splits and write av[node][split];
+// the block reduces to (min av, lowest split index, number of ties).  Meanwhile the last warp computes
+// the node's own class counts and impurity; afterwards warp 0 computes the children of the best split,
+// one lane per segment.
+__global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, SplitTable st, const uint32_t* cand_mask,
+                                                            const uint8_t* order_g, int criterion, double* av_buf,
+                                                            avt_node_best* out, avt_split_eval* best_eval,
+                                                            const int32_t* n_nodes_dev, PlanArgs plan) {
+    __shared__ uint32_t Pbuf[kScanWarps][kScanWordsPerWarp];
+    __shared__ ScanBest wbest[kScanWarps];
+    __shared__ uint8_t order[kMaxC];
+    __shared__ uint32_t s_cnt[kMaxC];
+    __shared__ double s_node_stat;
+    __shared__ uint32_t s_pop;
+    __shared__ avt_split_eval s_ev;
+    __shared__ int s_warp_tot[kScanWarps];
+    __shared__ int s_running;
+    __shared__ int s_is_last;
+    const int node = blockIdx.x;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int C = st.C;
+    const bool active = !(n_nodes_dev && node >= *n_nodes_dev);
+    if (active) {
+        if (threadIdx.x < C) order[threadIdx.x] = order_g[threadIdx.x];
+        __syncthreads();
+        const uint32_t* Hnode = H + (long long)node * st.TB * C;
+        const int mask_words = (st.A + 31) >> 5;
+        const double nan = __longlong_as_double(0x7ff8000000000000LL);
+        if (warp == kScanWarps - 1) {
+            // the node's own class counts (bins of attribute 0 partition its rows) and impurity
+            if (lane < C) {
+                const int B0 = st.bin_off[1] - st.bin_off[0];
+                uint32_t s = 0;
+                for (int bb = 0; bb < B0; ++bb) s += Hnode[bb * C + lane];
+                s_cnt[lane] = s;
+            }
+            __syncwarp();
+            if (lane == 0) {
+                uint32_t n = 0;
+                for (int c = 0; c < C; ++c) n += s_cnt[c];
+                s_pop = n;
+                s_node_stat = impurity(s_cnt, C, order, criterion, n);
+            }
+        }
+        ScanBest best{0.0, -1, 0};
+        for (int at = warp; at < st.A; at += kScanWarps) {
+            const int s0 = st.attr_first[at], s1 = st.attr_first[at + 1];
+            if (s0 == s1) continue;
+            const bool cand = cand_mask == nullptr || ((cand_mask[(long long)node * mask_words + (at >> 5)] >> (at & 31)) & 1u);
+            if (!cand) {
+                for (int s = s0 + lane; s < s1; s += 32) av_buf[(long long)node * st.S + s] = nan;
+                continue;
+            }
+            const int B = st.bin_off[at + 1] - st.bin_off[at];
+            const uint32_t* Hn = Hnode + (long long)st.bin_off[at] * C;
+            const uint32_t* P = nullptr;
+            if (B * C <= kScanWordsPerWarp) {
+                __syncwarp();
+                warp_prefix(Hn, Pbuf[warp], B, C);
+                P = Pbuf[warp];
+            }
+            for (int s = s0 + lane; s < s1; s += 32) {
+                const avt_split sp = st.splits[s];
+                const double av = split_av(st, sp, B, P, Hn, order, criterion, nullptr);
+                av_buf[(long long)node * st.S + s] = av;
+                ScanBest b{av, s, 1};
+                if (av == av) best_merge(best, b);  // NaN never wins (`av < min` is false in Java too)
+            }
+        }
+#pragma unroll
+        for (int d = 16; d; d >>= 1) {
+            ScanBest o;
+            o.av = __shfl_xor_sync(0xffffffffu, best.av, d);
+            o.split = __shfl_xor_sync(0xffffffffu, best.split, d);
+            o.ties = __shfl_xor_sync(0xffffffffu, best.ties, d);
+            best_merge(best, o);
+        }
+        if (lane == 0) wbest[warp] = best;
+        __syncthreads();
+        if (warp == 0) {
+            ScanBest b = wbest[0];
+            for (int w = 1; w < kScanWarps; ++w) best_merge(b, wbest[w]);
+            const uint32_t n = s_pop;
+            if (best_eval) {
+                // children of the (lowest-index) best split: one lane per segment, then lane 0 accumulates
+                // the weighted average in segment order exactly as split_av does
+                uint32_t* evw = reinterpret_cast<uint32_t*>(&s_ev);
+                for (int i = lane; i < (int)(sizeof(avt_split_eval) / 4); i += 32) evw[i] = 0;
+                __syncwarp();
+                const bool have = b.split >= 0 && n > 0;
+                avt_split sp{};
+                if (have) sp = st.splits[b.split];
+                if (have && lane < sp.n_seg) {
+                    const int Bs = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
+                    uint32_t cnt[kMaxC];
+                    segment_counts(st, sp, lane, Bs, nullptr, Hnode + (long long)st.bin_off[sp.attr] * C, cnt);
+                    uint32_t m = 0;
+                    for (int c = 0; c < C; ++c) {
+                        m += cnt[c];
+                        s_ev.seg_count[lane][c] = cnt[c];
+                    }
+                    s_ev.seg_stat[lane] = m ? impurity(cnt, C, order, criterion, m) : 0.0;
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    double av = nan;
+                    if (have) {
+                        double weighted = 0.0;
+                        uint32_t total = 0;
+                        for (int j = 0; j < sp.n_seg; ++j) {
+                            uint32_t m = 0;
+                            for (int c = 0; c < C; ++c) m += s_ev.seg_count[j][c];
+                            if (m) {
+                                weighted = __dadd_rn(weighted, __dmul_rn(s_ev.seg_stat[j], (double)m));
+                                total += m;
+                            }
+                        }
+                        av = __ddiv_rn(weighted, (double)total);
+                    }
+                    s_ev.av = av;
+                }
+                __syncwarp();
+                uint32_t* dst = reinterpret_cast<uint32_t*>(&best_eval[node]);
+                for (int i = lane; i < (int)(sizeof(avt_split_eval) / 4); i += 32) dst[i] = evw[i];
+            }
+            if (lane == 0) {
+                avt_node_best r;
+                r.min_av = b.split >= 0 ? b.av : nan;
+                r.node_stat = s_node_stat;
+                r.population = n;
+                r.best_split = b.split;
+                r.n_ties = b.ties;
+                out[node] = r;
+            }
+        }
+    }
+    if (plan.ticket == nullptr) return;
+    // ---- last block to finish plans the next level
+    __threadfence();  // every thread publishes its results before the block takes its ticket
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const uint32_t done = atomicAdd(plan.ticket, 1u);
+        s_is_last = done == gridDim.x - 1;
+        if (s_is_last) {
+            *plan.ticket = 0;
+            __threadfence();
+        }
+    }
+    __syncthreads();
+    if (s_is_last) plan_level(plan, st, s_warp_tot, &s_running);
+}
+
+// Stand-alone planning launch (one block), used by the read-back form of the device-driven loop.
+__global__ void __launch_bounds__(kScanThreads) plan_kernel(PlanArgs p, SplitTable st) {
+    __shared__ int s_warp_tot[kScanWarps];
+    __shared__ int s_running;
+    plan_level(p, st, s_warp_tot, &s_running);
+}
+
+}  // namespace avt

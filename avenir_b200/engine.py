@@ -250,6 +250,9 @@ class Engine:
     def reset_stats(self):
         self._check(self.lib.avt_reset_stats(self.h))
 
+    def set_profiling(self, on: bool):
+        self._check(self.lib.avt_set_profiling(self.h, 1 if on else 0))
+
     def set_hist_variant(self, v: int):
         self._check(self.lib.avt_set_hist_variant(self.h, v))
 

@@ -211,6 +211,9 @@ int avt_timer_end(avt_engine* e, float* ms);
 int avt_synchronize(avt_engine* e);
 int avt_get_stats(avt_engine* e, avt_stats* out);
 int avt_reset_stats(avt_engine* e);
+/* Turns the per-launch CUDA-event timing behind avt_stats on (default) or off (no event records between
+ * the launches of a level loop). */
+int avt_set_profiling(avt_engine* e, int32_t on);
 /* Forces a histogram variant (-1 auto, 0 shared-memory, 1 global atomics) -- for tests/profiling. */
 int avt_set_hist_variant(avt_engine* e, int32_t variant);
 
