@@ -414,6 +414,7 @@ struct FusedRepart {
     const int32_t* node_attr;
     const uint16_t* child_lut;
     int lut_w;
+    int prev_n_max;  // bound on the previous frontier's nodes per tree (sizes the shared-memory copy of the tables)
 };
 
 // Plans and launches kernel (a) for the frontier in e->node_base (already uploaded to d_node_base).
@@ -528,7 +529,15 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         ha.ent_attr = base + o_attr; ha.ent_locoff = base + o_loc; ha.ent_globoff = base + o_glob; ha.ent_wide = base + o_wide;
         ha.grp_start = base + o_gs; ha.grp_bins = base + o_gb; ha.grp_rlog = base + o_gr; ha.grp_l2g = base + o_l2g; ha.grp_l2g_off = base + o_lo;
         ha.codes_in_regs = (G == 1 && !any_wide && e->A <= 4) ? 1 : 0;
-        const size_t smem = smem_words * sizeof(uint32_t);
+        size_t smem = smem_words * sizeof(uint32_t);
+        if (fr && ha.codes_in_regs) {
+            // previous frontier (bounded like this one) + phantom entry: selector word + one bin->child row each
+            const size_t tbl = ((size_t)fr->prev_n_max + 2) * (4 + (size_t)fr->lut_w * 2) + 8;
+            if (tbl <= 16 * 1024 && smem + tbl <= kMaxDynSmem) {
+                ha.repart_smem = 1;
+                smem += tbl;
+            }
+        }
         int bpsm = (int)std::min<size_t>(4, std::max<size_t>(1, (kMaxDynSmem + 1024) / (smem + 1024)));
         long long resident = (long long)e->sm_count * bpsm;
         long long chunks = std::max<long long>(1, resident / ((long long)e->T * G));
@@ -874,6 +883,7 @@ static int grow_device_loop_sync(avt_engine* e, int32_t n_levels, int32_t criter
         fr.node_attr = e->d_node_attr.p;
         fr.child_lut = e->d_lut.p;
         fr.lut_w = lut_w;
+        fr.prev_n_max = n_max;
         pending = true;
     }
     if (pending) {
@@ -1050,6 +1060,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         fr.node_attr = e->d_node_attr.p;
         fr.child_lut = e->d_lut.p;
         fr.lut_w = lut_w;
+        fr.prev_n_max = n_max;
         pending = true;
         last_level = level;
         for (int t = 0; t < T; ++t) ub[(size_t)t] = (int)std::min<long long>((long long)ub[(size_t)t] * g_max, (long long)AVT_NODE_NONE - 1);

@@ -48,6 +48,15 @@ struct HistArgs {
     const int32_t* wide;            // [A]
     int lut_w;
     int codes_in_regs;  // 1: one group, <= 4 uint8 attributes, entry q == attribute q (the split code is in registers)
+    int repart_smem;    // 1: codes_in_regs and the previous level's tables fit the block's shared memory (fast path)
+};
+
+// Shared-memory copy of the previous level's tables for the fast fused repartition.
+struct RepartSmem {
+    const uint32_t* sel;   // [n_prev+1] byte-permute selector 0x4440|attr of each previous node
+    const uint16_t* lut;   // [n_prev+1][lut_w] bin -> child (entry n_prev: all NONE)
+    uint32_t n_prev;
+    bool fast;
 };
 
 // hist_rows16: 16 consecutive rows of one tree for one attribute group.
@@ -57,7 +66,7 @@ template <bool HAS_W, bool WIDE, bool REPART>
 __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a, int e0, int ne, long long base,
                                             const uint16_t* nid, uint16_t* nid_out, const uint8_t* wt,
                                             uint32_t node_stride, uint32_t cs4, int rlog, uint32_t rep, int prev_nb,
-                                            uint32_t phantom) {
+                                            uint32_t phantom, const RepartSmem& rp) {
     uint4 vn0 = ld_stream(nid + base);
     uint4 vn1 = ld_stream(nid + base + 8);
     const uint4 vc = ld_stream(a.cls + base);
@@ -72,27 +81,48 @@ __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a,
     }
     if (REPART) {
         uint32_t nw[8];
+        if (!WIDE && rp.fast) {
+            // Fast form (<= 4 uint8 attributes, small previous frontier): the split attribute (as a byte-
+            // permute selector) and the bin -> child rows of every previous node sit in shared memory; the
+            // row's four codes are gathered into one word by 4x4 byte transposes, so choosing "the code
+            // of the node's split attribute" is a single PRMT.
+            if (n0 < 4) v[3] = make_uint4(0, 0, 0, 0);
+            if (n0 < 3) v[2] = make_uint4(0, 0, 0, 0);
+            if (n0 < 2) v[1] = make_uint4(0, 0, 0, 0);
 #pragma unroll
-        for (int j = 0; j < kRowsPerThread; ++j) {
-            const uint32_t old = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
-            uint32_t nn = AVT_NODE_NONE;
-            if (old != AVT_NODE_NONE) {
-                const int gi = prev_nb + (int)old;
-                const int at = __ldg(a.node_attr + gi);
-                if (at >= 0) {
-                    uint32_t code;
-                    if (!WIDE && a.codes_in_regs) {
-                        const uint32_t c01 = at == 0 ? u4_byte(v[0], j) : u4_byte(v[1], j);
-                        const uint32_t c23 = at == 2 ? u4_byte(v[2], j) : u4_byte(v[3], j);
-                        code = at < 2 ? c01 : c23;
-                    } else {
-                        code = a.wide[at] ? ((const uint16_t*)a.cols[at])[base + j] : ((const uint8_t*)a.cols[at])[base + j];
-                    }
-                    nn = __ldg(a.child_lut + (long long)gi * a.lut_w + code);
+            for (int w = 0; w < 4; ++w) {
+                const uint32_t a0 = u4_word(v[0], w), a1 = u4_word(v[1], w), a2 = u4_word(v[2], w), a3 = u4_word(v[3], w);
+                const uint32_t t0 = __byte_perm(a0, a1, 0x5140), t1 = __byte_perm(a2, a3, 0x5140);
+                const uint32_t t2 = __byte_perm(a0, a1, 0x7362), t3 = __byte_perm(a2, a3, 0x7362);
+                const uint32_t pk[4] = {__byte_perm(t0, t1, 0x5410), __byte_perm(t0, t1, 0x7632), __byte_perm(t2, t3, 0x5410),
+                                        __byte_perm(t2, t3, 0x7632)};
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const int j = w * 4 + r;
+                    const uint32_t old = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
+                    const uint32_t idx = min(old, rp.n_prev);  // 0xFFFF -> the phantom entry (all-NONE row)
+                    const uint32_t code = __byte_perm(pk[r], 0u, rp.sel[idx]);
+                    const uint32_t nn = rp.lut[idx * a.lut_w + code];
+                    if (j & 1) nw[j >> 1] |= nn << 16;
+                    else nw[j >> 1] = nn;
                 }
             }
-            if (j & 1) nw[j >> 1] |= nn << 16;
-            else nw[j >> 1] = nn;
+        } else {
+#pragma unroll
+            for (int j = 0; j < kRowsPerThread; ++j) {
+                const uint32_t old = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
+                uint32_t nn = AVT_NODE_NONE;
+                if (old != AVT_NODE_NONE) {
+                    const int gi = prev_nb + (int)old;
+                    const int at = __ldg(a.node_attr + gi);
+                    if (at >= 0) {
+                        const uint32_t code = a.wide[at] ? ((const uint16_t*)a.cols[at])[base + j] : ((const uint8_t*)a.cols[at])[base + j];
+                        nn = __ldg(a.child_lut + (long long)gi * a.lut_w + code);
+                    }
+                }
+                if (j & 1) nw[j >> 1] |= nn << 16;
+                else nw[j >> 1] = nn;
+            }
         }
         vn0 = make_uint4(nw[0], nw[1], nw[2], nw[3]);
         vn1 = make_uint4(nw[4], nw[5], nw[6], nw[7]);
@@ -159,6 +189,19 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
     const int keys = n_nodes * GB * a.C;
     const int words = (keys + GB * a.C) << rlog;  // + one phantom node that swallows rows outside the frontier
     for (int i = threadIdx.x; i < words; i += blockDim.x) sh[i] = 0;
+    RepartSmem rp{nullptr, nullptr, 0u, false};
+    if (REPART && a.repart_smem) {
+        const int pnb = a.prev_node_base[t], n_prev = a.prev_node_base[t + 1] - pnb;
+        uint32_t* sel = sh + words;
+        uint16_t* lut = reinterpret_cast<uint16_t*>(sel + n_prev + 1);
+        for (int i = threadIdx.x; i <= n_prev; i += blockDim.x) {
+            const int at = i < n_prev ? a.node_attr[pnb + i] : -1;
+            sel[i] = 0x4440u | (uint32_t)(at < 0 ? 0 : at);
+        }
+        for (int i = threadIdx.x; i < (n_prev + 1) * a.lut_w; i += blockDim.x)
+            lut[i] = i < n_prev * a.lut_w ? a.child_lut[(long long)pnb * a.lut_w + i] : (uint16_t)AVT_NODE_NONE;
+        rp = RepartSmem{sel, lut, (uint32_t)n_prev, true};
+    }
     __syncthreads();
     const uint32_t sh_base = (uint32_t)__cvta_generic_to_shared(sh);
     const uint16_t* nid = a.nid + (long long)t * a.Npad;
@@ -173,8 +216,8 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
     const long long stride = (long long)gridDim.y * blockDim.x * kRowsPerThread;
     for (long long base = ((long long)blockIdx.y * blockDim.x + threadIdx.x) * kRowsPerThread;
          base < a.N; base += stride) {
-        if (tree_has_w) hist_rows16<true, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes);
-        else hist_rows16<false, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes);
+        if (tree_has_w) hist_rows16<true, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes, rp);
+        else hist_rows16<false, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes, rp);
     }
     __syncthreads();
     const int* l2g = a.grp_l2g + a.grp_l2g_off[g];
