@@ -100,6 +100,7 @@ struct avt_engine {
     // device-driven level loop
     DevBuf<int32_t> d_prev_node_base, d_next_count, d_err, d_nb_all;
     DevBuf<uint32_t> d_ticket;
+    DevBuf<unsigned int> d_tile_ctr;
     DevBuf<avt_split_eval> d_best_eval;
     DevBuf<avt_grow_record> d_records;
     // timing
@@ -275,7 +276,7 @@ void avt_destroy(avt_engine* e) {
     for (void* c : e->cols)
         if (c) cudaFree(c);
     e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
-    e->d_nid.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
+    e->d_nid.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_tile_ctr.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
     e->d_attr_first.release(); e->d_seg_lut.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
@@ -545,6 +546,9 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         chunks = std::min(chunks, tiles);
         chunks = std::min<long long>(chunks, 65535);
         dim3 grid((unsigned)e->T, (unsigned)chunks, (unsigned)G);
+        CUDA_TRY(e, e->d_tile_ctr.ensure((size_t)e->T * G));
+        CUDA_TRY(e, cudaMemsetAsync(e->d_tile_ctr.p, 0, (size_t)e->T * G * sizeof(unsigned int), e->stream));
+        ha.tile_ctr = e->d_tile_ctr.p;
         const int sel = (e->any_w ? 4 : 0) | (any_wide ? 2 : 0) | (fr ? 1 : 0);
         switch (sel) {
             case 0: hist_smem_kernel<false, false, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
