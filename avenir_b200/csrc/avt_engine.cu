@@ -8,6 +8,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <string>
 #include <vector>
 
@@ -77,7 +78,9 @@ struct avt_engine {
     DevBuf<int32_t> d_node_base;
     DevBuf<uint32_t> d_H;
     // histogram group tables
-    DevBuf<int32_t> d_grp;  // packed int tables
+    DevBuf<int32_t> d_grp;  // arena of packed group tables, one per distinct frontier bound
+    std::map<int, size_t> grp_cache;
+    size_t grp_used = 0;
     // splits
     int S = 0;
     std::vector<avt_split> splits;
@@ -112,6 +115,7 @@ struct avt_engine {
     bool skip_h_memset = false;
     bool profiling = true;  // CUDA-event timing of every launch (avt_set_profiling)
     long long hist_target_addrs = 4096;  // AVT_HIST_TARGET_ADDRS
+    int hist_max_bpsm = 4;               // AVT_HIST_BPSM: resident histogram blocks per SM
     int grow_host_loop = 0;              // AVT_GROW_HOST=1: host-driven level loop (3 round trips per level)
     // comm
     ncclComm_t comm = nullptr;
@@ -264,6 +268,7 @@ int avt_create(int device, avt_engine** out) {
     }
     if (const char* v = getenv("AVT_HIST_TARGET_ADDRS")) e->hist_target_addrs = std::max(1LL, atoll(v));
     if (const char* v = getenv("AVT_GROW_HOST")) e->grow_host_loop = atoi(v);
+    if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
     *out = e;
     return AVT_OK;
 }
@@ -297,11 +302,17 @@ int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32
     if (n_classes < 1 || n_classes > AVT_MAX_CLASSES)
         return fail(e, AVT_E_INVALID, "avt_dataset_load: n_classes %d outside 1..%d", n_classes, AVT_MAX_CLASSES);
     if (int rc = use_device(e)) return rc;
-    for (void* c : e->cols)
-        if (c) cudaFree(c);
-    e->cols.assign(n_attrs, nullptr);
+    // column buffers are kept when the new data set has the same shape (re-loading costs no cudaMalloc/cudaFree)
+    const long long new_npad = (n_rows + 15) & ~15LL;
+    bool same_shape = (int)e->cols.size() == n_attrs && e->Npad == new_npad && (int)e->wide.size() == n_attrs;
+    for (int a = 0; same_shape && a < n_attrs; ++a) same_shape = e->cols[a] != nullptr && e->wide[a] == (n_bins[a] > 256 ? 1 : 0);
+    if (!same_shape) {
+        for (void* c : e->cols)
+            if (c) cudaFree(c);
+        e->cols.assign(n_attrs, nullptr);
+    }
     e->N = n_rows;
-    e->Npad = (n_rows + 15) & ~15LL;
+    e->Npad = new_npad;
     e->A = n_attrs;
     e->C = n_classes;
     e->n_bins.assign(n_bins, n_bins + n_attrs);
@@ -317,7 +328,7 @@ int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32
     if (int rc = timer_open(e, &e->stats.h2d_ms, &ts)) return rc;
     for (int a = 0; a < n_attrs; ++a) {
         const size_t w = e->wide[a] ? 2 : 1;
-        CUDA_TRY(e, cudaMalloc(&e->cols[a], (size_t)e->Npad * w));
+        if (!e->cols[a]) CUDA_TRY(e, cudaMalloc(&e->cols[a], (size_t)e->Npad * w));
         CUDA_TRY(e, cudaMemsetAsync((char*)e->cols[a] + (size_t)n_rows * w, 0, (size_t)(e->Npad - n_rows) * w, e->stream));
         CUDA_TRY(e, cudaMemcpyAsync(e->cols[a], columns[a], (size_t)n_rows * w, cudaMemcpyHostToDevice, e->stream));
     }
@@ -330,6 +341,8 @@ int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32
     if (int rc = timer_close(e, ts)) return rc;
     e->T = 0;
     e->S = 0;
+    e->grp_cache.clear();
+    e->grp_used = 0;
     e->hist_valid = e->scan_valid = false;
     return sync_and_resolve(e);
 }
@@ -525,8 +538,29 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         };
         const size_t o_attr = put(ent_attr), o_loc = put(ent_loc), o_glob = put(ent_glob), o_wide = put(ent_wide),
                      o_gs = put(grp_start), o_gb = put(grp_bins), o_gr = put(grp_rlog), o_l2g = put(l2g), o_lo = put(l2g_off);
-        if (int rc = upload(e, e->d_grp, pack.data(), pack.size())) return rc;
-        const int32_t* base = e->d_grp.p;
+        // The tables depend only on (data set, frontier bound): keep every distinct one in a device arena so
+        // that steady-state levels issue no host->device copy at all.
+        constexpr size_t kGrpArenaInts = 1u << 20;
+        if (e->d_grp.cap < kGrpArenaInts) {
+            CUDA_TRY(e, e->d_grp.ensure(kGrpArenaInts));
+            e->grp_cache.clear();
+            e->grp_used = 0;
+        }
+        size_t at;
+        auto hit = e->grp_cache.find(n_max);
+        if (hit != e->grp_cache.end()) {
+            at = hit->second;
+        } else {
+            if (e->grp_used + pack.size() > e->d_grp.cap) {  // arena full: start over (in-flight launches are stream-ordered before the overwrite)
+                e->grp_cache.clear();
+                e->grp_used = 0;
+            }
+            at = e->grp_used;
+            CUDA_TRY(e, cudaMemcpyAsync(e->d_grp.p + at, pack.data(), pack.size() * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+            e->grp_cache[n_max] = at;
+            e->grp_used += pack.size();
+        }
+        const int32_t* base = e->d_grp.p + at;
         ha.ent_attr = base + o_attr; ha.ent_locoff = base + o_loc; ha.ent_globoff = base + o_glob; ha.ent_wide = base + o_wide;
         ha.grp_start = base + o_gs; ha.grp_bins = base + o_gb; ha.grp_rlog = base + o_gr; ha.grp_l2g = base + o_l2g; ha.grp_l2g_off = base + o_lo;
         ha.codes_in_regs = (G == 1 && !any_wide && e->A <= 4) ? 1 : 0;
@@ -539,16 +573,13 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
                 smem += tbl;
             }
         }
-        int bpsm = (int)std::min<size_t>(4, std::max<size_t>(1, (kMaxDynSmem + 1024) / (smem + 1024)));
+        int bpsm = (int)std::min<size_t>((size_t)e->hist_max_bpsm, std::max<size_t>(1, (kMaxDynSmem + 1024) / (smem + 1024)));
         long long resident = (long long)e->sm_count * bpsm;
         long long chunks = std::max<long long>(1, resident / ((long long)e->T * G));
         const long long tiles = (e->N + (long long)kHistThreads * kRowsPerThread - 1) / ((long long)kHistThreads * kRowsPerThread);
         chunks = std::min(chunks, tiles);
         chunks = std::min<long long>(chunks, 65535);
         dim3 grid((unsigned)e->T, (unsigned)chunks, (unsigned)G);
-        CUDA_TRY(e, e->d_tile_ctr.ensure((size_t)e->T * G));
-        CUDA_TRY(e, cudaMemsetAsync(e->d_tile_ctr.p, 0, (size_t)e->T * G * sizeof(unsigned int), e->stream));
-        ha.tile_ctr = e->d_tile_ctr.p;
         const int sel = (e->any_w ? 4 : 0) | (any_wide ? 2 : 0) | (fr ? 1 : 0);
         switch (sel) {
             case 0: hist_smem_kernel<false, false, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;

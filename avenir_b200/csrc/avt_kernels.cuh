@@ -48,7 +48,6 @@ struct HistArgs {
     const int32_t* wide;            // [A]
     int lut_w;
     int codes_in_regs;  // 1: one group, <= 4 uint8 attributes, entry q == attribute q (the split code is in registers)
-    unsigned int* tile_ctr;  // [T][G] zero-initialised row-tile counters (dynamic row distribution)
     int repart_smem;    // 1: codes_in_regs and the previous level's tables fit the block's shared memory (fast path)
 };
 
@@ -214,24 +213,11 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
     const uint32_t node_stride = (uint32_t)(GB * a.C) << rlog;
     const int e0 = a.grp_start[g], ne = a.grp_start[g + 1] - e0;
     const int prev_nb = REPART ? a.prev_node_base[t] : 0;
-    // Rows are handed out dynamically, one 512-row tile (32 lanes x 16 rows) per warp at a time, from a
-    // counter per (tree, group): a static split leaves every warp with 2 or 3 tiles and the launch
-    // waiting for the 3-tile warps; here the tail is one tile deep.  The next tile is claimed before
-    // the current one is processed so the atomic's round trip is hidden.
-    unsigned int* ctr = a.tile_ctr + (t * gridDim.z + g);
     const int lane = threadIdx.x & 31;
-    const long long n_tiles = (a.N + 511) >> 9;
-    unsigned int nxt = 0;
-    if (lane == 0) nxt = atomicAdd(ctr, 1u);
-    nxt = __shfl_sync(0xffffffffu, nxt, 0);
-    while ((long long)nxt < n_tiles) {
-        const long long base = ((long long)nxt << 9) + lane * kRowsPerThread;
-        if (lane == 0) nxt = atomicAdd(ctr, 1u);
-        nxt = __shfl_sync(0xffffffffu, nxt, 0);
-        if (base < a.N) {
-            if (tree_has_w) hist_rows16<true, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes, rp);
-            else hist_rows16<false, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes, rp);
-        }
+    const long long stride = (long long)gridDim.y * blockDim.x * kRowsPerThread;
+    for (long long base = ((long long)blockIdx.y * blockDim.x + threadIdx.x) * kRowsPerThread; base < a.N; base += stride) {
+        if (tree_has_w) hist_rows16<true, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes, rp);
+        else hist_rows16<false, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes, rp);
     }
     __syncthreads();
     // fold the copies and add them to H: one warp per node, lanes over the node's (bin, class) slots

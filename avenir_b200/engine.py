@@ -220,8 +220,9 @@ class Engine:
         self._check(self.lib.avt_cpg_sweep(self.h, node, criterion, _ptr(o), out))
         return out
 
-    def node_ids(self, tree: int = 0) -> np.ndarray:
-        out = np.empty(self.n_rows, dtype=np.uint16)
+    def node_ids(self, tree: int = 0, out: Optional[np.ndarray] = None) -> np.ndarray:
+        if out is None:
+            out = np.empty(self.n_rows, dtype=np.uint16)
         self._check(self.lib.avt_forest_node_ids(self.h, tree, _ptr(out)))
         return out
 

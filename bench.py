@@ -237,13 +237,15 @@ def main():
     sampler.join()
 
     # ---- e2e: host buffers -> tree, through the C-ABI
+    nid_pinned = torch.empty(N, dtype=torch.uint16).pin_memory().numpy()
+
     def step_e2e():
         t = time.perf_counter()
-        eng.load_dataset(cols_p, cls_p, n_bins, 2)
+        eng.load_dataset(cols_p, cls_p, n_bins, 2)          # H2D of the step's inputs (pinned host buffers)
         eng.set_splits(table)
         eng.forest_init(1)
-        eng.grow(L, CRIT_ENTROPY, [1])
-        nid = eng.node_ids(0)
+        (rec, nrec), _ = eng.grow(L, CRIT_ENTROPY, [1], max_records=1024)   # D2H of the tree (one record per expanded node)
+        nid = eng.node_ids(0, out=nid_pinned)                # D2H of every row's leaf
         return time.perf_counter() - t, nid
 
     step_e2e()
