@@ -299,6 +299,7 @@ struct Node {
 struct Tree {
     std::vector<Node> frontier;
     std::vector<uint8_t> weights;  // empty = all ones
+    JavaRandom rng{0};             // the tree's Math.random() stand-in: sampling first, then randomAmongTop draws
 };
 
 class DtbJob {
@@ -401,8 +402,7 @@ private:
         algorithm_ = conf_.get("dtb.split.algorithm", "giniIndex");
         total_population_ = conf_.get_int("dtb.total.population", -1);
         split_sel_ = conf_.get("dtb.split.select.strategy", "best");
-        if (split_sel_ == "randomAmongTop") throw Unsupported("dtb.split.select.strategy=randomAmongTop is not implemented yet");
-        if (split_sel_ != "best") throw ReferenceError("ivalid split slection strategy");
+        if (split_sel_ != "best" && split_sel_ != "randomAmongTop") throw ReferenceError("ivalid split slection strategy");
         top_split_count_ = conf_.get_int("dtb.top.split.count", 3);
         stop_strategy_ = conf_.get("dtb.path.stopping.strategy", "minInfoGain");
         if (stop_strategy_ == "maxDepth") {
@@ -499,7 +499,8 @@ private:
         std::vector<const uint8_t*> wptr((size_t)num_trees_, nullptr);
         for (int t = 0; t < num_trees_; ++t) {
             Tree& tr = trees_[(size_t)t];
-            JavaRandom rng(seed_ + t);
+            tr.rng = JavaRandom(seed_ + t);
+            JavaRandom& rng = tr.rng;
             if (sampling_ == "withReplace") {
                 tr.weights.assign(n, 0);
                 const size_t B = (size_t)std::max(1, sampling_buffer_);
@@ -531,6 +532,7 @@ private:
         if (num_trees_ != 1) throw Unsupported("avt.forest.num.trees > 1 needs the in-process level loop (no dtb.decision.file.path.in)");
         trees_.assign(1, Tree());
         Tree& tr = trees_[0];
+        tr.rng = JavaRandom(seed_);
         tr.frontier.resize(dec_in.size());
         for (size_t i = 0; i < dec_in.size(); ++i) tr.frontier[i].path = dec_in[i];
         if (dec_in.size() >= AVT_NODE_NONE) throw Unsupported("more than 65534 frontier nodes");
@@ -755,13 +757,38 @@ private:
                 const avt_node_best& b = best[(size_t)g];
                 if (b.population == 0 || b.best_split < 0) continue;  // no rows or no candidate split: nothing is emitted for this parent
                 chosen[(size_t)g] = b.best_split;
-                if (b.n_ties > 1) {
+                if (split_sel_ == "best" && b.n_ties > 1) {
                     need_order(g, nd);
                     eng_->check(avt_level_fetch_av(eng_->raw(), g, av.data()));
                     for (int ti : orders[(size_t)g].split_order)
                         if (av[(size_t)ti] == b.min_av) { chosen[(size_t)g] = ti; break; }
                 }
             }
+        if (split_sel_ == "randomAmongTop") {
+            // selectRandomSplitFromTop (tree/DecisionTreeBuilder.java:549-572, 622-631): a TreeMap keyed by av
+            // (equal keys overwrite, in splitInfoContent.keySet() order), its first dtb.top.split.count entries,
+            // one uniform draw per parent -- parents in decPathsInfoContentBySplit.keySet() order
+            for (int t = 0; t < num_trees_; ++t) {
+                Tree& tr = trees_[(size_t)t];
+                std::vector<int> live;
+                for (size_t i = 0; i < tr.frontier.size(); ++i)
+                    if (chosen[(size_t)(base[(size_t)t] + (int)i)] >= 0) live.push_back((int)i);
+                for (int i : parent_order(tr, live)) {
+                    const int g = base[(size_t)t] + i;
+                    need_order(g, tr.frontier[(size_t)i]);
+                    eng_->check(avt_level_fetch_av(eng_->raw(), g, av.data()));
+                    std::map<double, int> ranked;
+                    for (int ti : orders[(size_t)g].split_order) ranked[av[(size_t)ti]] = ti;
+                    std::vector<int> top;
+                    for (auto& kv : ranked) {
+                        top.push_back(kv.second);
+                        if ((int)top.size() == top_split_count_) break;
+                    }
+                    if (top.empty()) continue;
+                    chosen[(size_t)g] = top[(size_t)java_int_cast(tr.rng.next_double() * (double)top.size())];
+                }
+            }
+        }
         std::vector<int32_t> ev_nodes, ev_splits;
         for (int g = 0; g < NF; ++g)
             if (chosen[(size_t)g] >= 0) { ev_nodes.push_back(g); ev_splits.push_back(chosen[(size_t)g]); }

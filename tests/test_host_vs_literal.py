@@ -238,3 +238,15 @@ def test_cpg_three_classes_and_root(hostmock, tmp_path):
     conf = {"cpg.at.root": "true", "cpg.split.algorithm": "giniIndex", "cpg.parent.info": "0"}
     got, want = run_cpg_both(hostmock, str(tmp_path / "b"), cpg_rows(400), cpg_schema(), conf)
     assert got == want and len(got) == 1
+
+
+@pytest.mark.parametrize("seed", [0, 7])
+def test_random_among_top_follows_the_seeded_stream(hostmock, tmp_path, seed):
+    """dtb.split.select.strategy=randomAmongTop: TreeMap of av -> split (equal keys overwrite), first
+    dtb.top.split.count entries, one draw per parent from the seeded java.util.Random stream."""
+    schema = json.load(open(os.path.join(helpers.SCHEMA_DIR, "schemas.json")))["call_hangup.json"]
+    conf = dict(BASE, **{"dtb.split.attribute.selection.strategy": "all", "dtb.split.select.strategy": "randomAmongTop",
+                         "dtb.top.split.count": "3", "avt.random.seed": str(seed), "dtb.sub.sampling.strategy": "withReplace",
+                         "dtb.sub.sampling.buffer.size": "300"})
+    got, want = run_dtb_both(hostmock, str(tmp_path), synth.call_hangup_csv(900), schema, conf, 4)
+    assert got == want
