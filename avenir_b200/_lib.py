@@ -78,6 +78,8 @@ SIGNATURES = {
     "avt_set_hist_variant": (C.c_int, [_P, C.c_int32]),
     "avt_comm_unique_id": (C.c_int, [_P]),
     "avt_comm_init_rank": (C.c_int, [_P, C.c_int32, C.c_int32, _P]),
+    "avt_peer_export": (C.c_int, [_P, _P]),
+    "avt_peer_import": (C.c_int, [_P, C.c_int32, C.c_int32, _P]),
     "avt_histogram_static": (C.c_int, [C.c_int, C.c_int64, C.c_int32, C.POINTER(C.c_int32), C.POINTER(_P), _P, C.c_int32, _P, C.c_int32, _P]),
     "avt_tool_run": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_char_p), C.c_char_p, C.c_size_t]),
 }

@@ -120,6 +120,19 @@ struct avt_engine {
     // comm
     ncclComm_t comm = nullptr;
     int n_ranks = 1, rank = 0;
+    // peer exchange over NVLink (avt_peer_export / avt_peer_import): the level loop's all-reduce fused into the scan
+    struct Peer {
+        bool active = false;
+        int n = 0, rank = 0;
+        uint32_t* arena = nullptr;     // local: [64 flag words | pad to 256 B | H buffer 0 | H buffer 1]
+        size_t cap_words = 0;          // words per H buffer
+        void* base[16] = {};           // every rank's arena mapped here (own arena for own rank)
+        uint32_t epoch = 0;
+    } peer;
+    DevBuf<const uint32_t*> d_peer_H[2];
+    DevBuf<uint32_t*> d_remote_flags;
+    DevBuf<uint32_t> d_hsum;
+    uint32_t* H_cur = nullptr;         // histogram buffer of the pass being launched (nullptr: d_H)
 };
 
 namespace {
@@ -278,6 +291,10 @@ void avt_destroy(avt_engine* e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     if (e->comm) ncclCommDestroy(e->comm);
+    for (int r = 0; r < e->peer.n; ++r)
+        if (r != e->peer.rank && e->peer.base[r]) cudaIpcCloseMemHandle(e->peer.base[r]);
+    if (e->peer.arena) cudaFree(e->peer.arena);
+    e->d_peer_H[0].release(); e->d_peer_H[1].release(); e->d_remote_flags.release(); e->d_hsum.release();
     for (void* c : e->cols)
         if (c) cudaFree(c);
     e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
@@ -436,7 +453,8 @@ struct FusedRepart {
 // buffers); without it the node ids are read in place.
 static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, const int32_t* d_node_base = nullptr) {
     const size_t hwords = (size_t)e->NF * e->TB * e->C;
-    CUDA_TRY(e, e->d_H.ensure(hwords));
+    if (!e->H_cur) CUDA_TRY(e, e->d_H.ensure(hwords));
+    uint32_t* const Hbuf = e->H_cur ? e->H_cur : e->d_H.p;
     // ---- plan: attribute groups whose per-tree histogram fits the shared-memory budget
     const long long per_bin = (long long)(std::max(n_max, 1) + 1) * e->C;  // words per bin: all nodes of a tree + the phantom node
     int max_bins = 0;
@@ -478,7 +496,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
     ha.nid = nid_in;
     ha.wts = e->any_w ? e->d_w.p : nullptr;
     ha.has_w = e->d_has_w.p;
-    ha.H = e->d_H.p;
+    ha.H = Hbuf;
     ha.node_base = d_node_base ? d_node_base : e->d_node_base.p;
     ha.N = e->N;
     ha.Npad = e->Npad;
@@ -496,7 +514,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
 
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.hist_ms, &ts)) return rc;
-    if (!e->skip_h_memset) CUDA_TRY(e, cudaMemsetAsync(e->d_H.p, 0, hwords * sizeof(uint32_t), e->stream));
+    if (!e->skip_h_memset) CUDA_TRY(e, cudaMemsetAsync(Hbuf, 0, hwords * sizeof(uint32_t), e->stream));
     if (variant == 0) {
         // Replication policy: enough copies that a warp's 32 updates spread over >= kTargetAddrs distinct
         // words, but no more -- smaller histograms mean more resident blocks per SM (latency hiding).
@@ -616,7 +634,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         for (int t = 0; t < e->T; ++t) per_row += 2 + ((e->any_w) ? 1 : 0) + (fr ? 2 : 0);  // fused: + the node-id write
         e->stats.hist_alg_bytes += per_row * e->N;
     }
-    if (e->comm) {
+    if (e->comm && !e->H_cur) {
         TimerSlot tc;
         if (int rc = timer_open(e, &e->stats.comm_ms, &tc)) return rc;
         NCCL_TRY(e, ncclAllReduce(e->d_H.p, e->d_H.p, hwords, ncclUint32, ncclSum, e->comm, e->stream));
@@ -985,6 +1003,9 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     nb_host[0] = 0;
     for (int t = 0; t < T; ++t) nb_host[(size_t)t + 1] = nb_host[(size_t)t] + ub[(size_t)t];
     CUDA_TRY(e, cudaMemcpyAsync(nb_level(0), nb_host.data(), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+    const bool peer_on = e->peer.active && e->peer.n > 1;
+    auto arena_H = [&](int parity) { return e->peer.arena + 64 + (size_t)parity * e->peer.cap_words; };
+    bool peer_used = false;
     bool pending = false;
     bool h_prezeroed = false;  // the previous level's planning block already cleared this level's histogram region
     FusedRepart fr{};
@@ -1014,10 +1035,12 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         const int NF = (int)nf_ub;
         e->NF = NF;
         e->hist_valid = e->scan_valid = false;
+        const bool peer_level = peer_on && (size_t)NF * e->TB * e->C <= e->peer.cap_words;   // same decision on every rank (same bounds)
+        if (!peer_level) h_prezeroed = h_prezeroed && !peer_on;
         // every buffer of this level is sized BEFORE anything is enqueued (a reallocation frees memory
         // that earlier, still running launches may use)
         if (e->d_av.cap < (size_t)NF * e->S || e->d_best.cap < (size_t)NF || e->d_best_eval.cap < (size_t)NF || e->d_node_attr.cap < (size_t)NF ||
-            e->d_lut.cap < (size_t)NF * lut_w || e->d_H.cap < (size_t)NF * e->TB * e->C || (want_records && e->d_records.cap < rec_off + (size_t)NF)) {
+            e->d_lut.cap < (size_t)NF * lut_w || (!peer_level && e->d_H.cap < (size_t)NF * e->TB * e->C) || (peer_level && e->d_hsum.cap < (size_t)NF * e->TB * e->C) || (want_records && e->d_records.cap < rec_off + (size_t)NF)) {
             if (int rc = sync_and_resolve(e)) return rc;
             // flush records gathered so far: the record buffer may move
             if (want_records && rec_off) {
@@ -1044,7 +1067,8 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             CUDA_TRY(e, e->d_best_eval.ensure(grow));
             CUDA_TRY(e, e->d_node_attr.ensure(grow));
             CUDA_TRY(e, e->d_lut.ensure(grow * lut_w));
-            CUDA_TRY(e, e->d_H.ensure(grow * e->TB * e->C));
+            if (!peer_level) CUDA_TRY(e, e->d_H.ensure(grow * e->TB * e->C));
+            else CUDA_TRY(e, e->d_hsum.ensure(std::min(grow * e->TB * e->C, e->peer.cap_words)));
             if (want_records) CUDA_TRY(e, e->d_records.ensure(grow * 2));
             if (pending) {
                 CUDA_TRY(e, cudaMemcpy(e->d_node_attr.p, keep_attr.data(), prev_nf * sizeof(int32_t), cudaMemcpyHostToDevice));
@@ -1055,8 +1079,21 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         }
         if (pending) fr.prev_node_base = nb_level(level - 1);
         e->skip_h_memset = h_prezeroed;
+        e->H_cur = peer_level ? arena_H(level & 1) : nullptr;
         if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr, nb_level(level))) return rc;
         e->skip_h_memset = false;
+        e->H_cur = nullptr;
+        if (peer_level) {
+            // this rank's partial counts are complete: tell every rank (the scan blocks wait for all of them)
+            TimerSlot tc;
+            if (int rc = timer_open(e, &e->stats.comm_ms, &tc)) return rc;
+            ++e->peer.epoch;
+            peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
+            CUDA_TRY(e, cudaGetLastError());
+            if (int rc = timer_close(e, tc)) return rc;
+            e->stats.comm_calls += 1;
+            peer_used = true;
+        }
         pending = false;
         PlanArgs pa{};
         pa.best = e->d_best.p;
@@ -1077,14 +1114,23 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             long long next_nodes = 0;
             for (int t = 0; t < T; ++t) next_nodes += std::min<long long>((long long)ub[(size_t)t] * g_max, (long long)AVT_NODE_NONE - 1);
             const long long next_words = next_nodes * e->TB * e->C;
-            h_prezeroed = level + 1 < n_levels && next_nodes <= kAsyncNodeLimit && next_words <= (1 << 16) && (size_t)next_words <= e->d_H.cap;
-            pa.zero_ptr = h_prezeroed ? e->d_H.p : nullptr;
+            const bool next_peer = peer_on && (size_t)next_words <= e->peer.cap_words;
+            h_prezeroed = level + 1 < n_levels && next_nodes <= kAsyncNodeLimit && next_words <= (1 << 16) &&
+                          (next_peer || (!peer_on && (size_t)next_words <= e->d_H.cap));
+            pa.zero_ptr = h_prezeroed ? (next_peer ? arena_H((level + 1) & 1) : e->d_H.p) : nullptr;
             pa.zero_words = h_prezeroed ? next_words : 0;
+        }
+        if (peer_level) {
+            pa.peer_H = e->d_peer_H[level & 1].p;
+            pa.peer_flags = e->peer.arena;
+            pa.h_sum = e->d_hsum.p;
+            pa.peer_epoch = e->peer.epoch;
+            pa.n_ranks = e->peer.n;
         }
         TimerSlot ts;
         if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
-        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), nullptr, e->d_order.p, criterion, e->d_av.p, e->d_best.p,
-                                                        e->d_best_eval.p, nb_level(level) + T, pa);
+        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(peer_level ? e->d_hsum.p : e->d_H.p, make_table(e), nullptr, e->d_order.p, criterion,
+                                                        e->d_av.p, e->d_best.p, e->d_best_eval.p, nb_level(level) + T, pa);
         CUDA_TRY(e, cudaGetLastError());
         if (int rc = timer_close(e, ts)) return rc;
         e->stats.scan_launches += 1;
@@ -1112,6 +1158,13 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         if (int rc = timer_close(e, tr)) return rc;
         e->stats.repart_launches += 1;
         e->stats.repart_alg_bytes += (long long)e->N * T * 5;
+    }
+    if (peer_used) {
+        // no rank may reuse its exchange buffers (next call, level 0) while another still reads them
+        ++e->peer.epoch;
+        peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
+        peer_wait_kernel<<<1, 32, 0, e->stream>>>(e->peer.arena, e->peer.n, e->peer.epoch);
+        CUDA_TRY(e, cudaGetLastError());
     }
     e->hist_valid = e->scan_valid = false;
     e->NF = 0;
@@ -1244,6 +1297,52 @@ int avt_set_hist_variant(avt_engine* e, int32_t variant) {
     if (variant < -1 || variant > 1) return fail(e, AVT_E_INVALID, "avt_set_hist_variant: %d", variant);
     e->force_variant = variant;
     return AVT_OK;
+}
+
+int avt_peer_export(avt_engine* e, void* handle64) {
+    if (!e || !handle64) return fail(e, AVT_E_INVALID, "avt_peer_export: NULL argument");
+    if (int rc = use_device(e)) return rc;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    if (!e->peer.arena) {
+        e->peer.cap_words = (size_t)2 << 20;  // 8 MiB per histogram buffer
+        const size_t bytes = (64 + 2 * e->peer.cap_words) * sizeof(uint32_t);
+        CUDA_TRY(e, cudaMalloc((void**)&e->peer.arena, bytes));
+        CUDA_TRY(e, cudaMemset(e->peer.arena, 0, bytes));
+    }
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(e, cudaIpcGetMemHandle(&h, e->peer.arena));
+    memcpy(handle64, &h, 64);
+    return AVT_OK;
+}
+
+int avt_peer_import(avt_engine* e, int32_t n_ranks, int32_t rank, const void* handles) {
+    if (!e || !handles || n_ranks < 1 || n_ranks > 16 || rank < 0 || rank >= n_ranks) return fail(e, AVT_E_INVALID, "avt_peer_import: bad argument (1..16 ranks)");
+    if (!e->peer.arena) return fail(e, AVT_E_STATE, "avt_peer_import: call avt_peer_export first");
+    if (int rc = use_device(e)) return rc;
+    if (int rc = sync_and_resolve(e)) return rc;
+    e->peer.n = n_ranks;
+    e->peer.rank = rank;
+    std::vector<const uint32_t*> h0((size_t)n_ranks), h1((size_t)n_ranks);
+    std::vector<uint32_t*> rf((size_t)n_ranks);
+    for (int r = 0; r < n_ranks; ++r) {
+        void* base = e->peer.arena;
+        if (r != rank) {
+            cudaIpcMemHandle_t h;
+            memcpy(&h, (const char*)handles + (size_t)r * 64, 64);
+            CUDA_TRY(e, cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+        }
+        e->peer.base[r] = base;
+        uint32_t* b = (uint32_t*)base;
+        h0[(size_t)r] = b + 64;
+        h1[(size_t)r] = b + 64 + e->peer.cap_words;
+        rf[(size_t)r] = b + rank;  // this rank's flag word inside rank r's arena
+    }
+    if (int rc = upload(e, e->d_peer_H[0], h0.data(), h0.size())) return rc;
+    if (int rc = upload(e, e->d_peer_H[1], h1.data(), h1.size())) return rc;
+    if (int rc = upload(e, e->d_remote_flags, rf.data(), rf.size())) return rc;
+    e->peer.epoch = 0;
+    e->peer.active = getenv("AVT_PEER_OFF") == nullptr;
+    return sync_and_resolve(e);
 }
 
 int avt_set_profiling(avt_engine* e, int32_t on) {

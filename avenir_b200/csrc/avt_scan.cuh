@@ -22,7 +22,44 @@ struct PlanArgs {
     uint32_t* zero_ptr;        // words to clear for the next level's histogram (nullable)
     long long zero_words;
     int lut_w, level, n_trees;
+    // peer exchange (rows sharded over several GPUs): the scan block itself sums the node's partial
+    // histograms out of every rank's memory over NVLink -- the all-reduce is fused into kernel (b)
+    const uint32_t* const* peer_H;  // [n_ranks] this level's partial histogram on every rank (self included); nullptr = single GPU
+    const uint32_t* peer_flags;     // [n_ranks] local words; rank r stores its epoch here when its partial histogram is complete
+    uint32_t* h_sum;                // local buffer that receives the summed histogram (== the kernel's H argument)
+    uint32_t peer_epoch;
+    int n_ranks;
 };
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Tells every rank (itself included) that this rank's partial histogram of epoch `epoch` is complete.
+// Launched on the stream right after the histogram pass; remote_flags[r] points INTO rank r's memory.
+__global__ void peer_signal_kernel(uint32_t* const* remote_flags, int n_ranks, uint32_t epoch) {
+    if ((int)threadIdx.x < n_ranks) {
+        __threadfence_system();
+        st_release_sys(remote_flags[threadIdx.x], epoch);
+    }
+}
+
+// Waits until every rank has signalled `epoch` (used once at the end of a level loop, so that no rank
+// reuses its exchange buffers while another is still reading them).
+__global__ void peer_wait_kernel(const uint32_t* flags, int n_ranks, uint32_t epoch) {
+    if ((int)threadIdx.x < n_ranks)
+        while ((int32_t)(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) {}
+}
 
 // loads that bypass L1: the planning block reads what OTHER blocks of the same launch wrote
 __device__ __forceinline__ int32_t ldcg_i32(const int32_t* p) { return __ldcg(p); }
@@ -154,6 +191,20 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, S
     if (active) {
         if (threadIdx.x < C) order[threadIdx.x] = order_g[threadIdx.x];
         __syncthreads();
+        if (plan.peer_H) {
+            // every rank's partial counts for this node, pulled over NVLink and summed; the ranks' frontiers are
+            // identical, so node indices agree.  Wait first until all of them have finished their histogram pass.
+            if ((int)threadIdx.x < plan.n_ranks)
+                while ((int32_t)(ld_acquire_sys(plan.peer_flags + threadIdx.x) - plan.peer_epoch) < 0) {}
+            __syncthreads();
+            const long long words = (long long)st.TB * C, off = (long long)node * words;
+            for (long long i = threadIdx.x; i < words; i += blockDim.x) {
+                uint32_t sum = 0;
+                for (int r = 0; r < plan.n_ranks; ++r) sum += ld_relaxed_sys(plan.peer_H[r] + off + i);
+                plan.h_sum[off + i] = sum;
+            }
+            __syncthreads();
+        }
         const uint32_t* Hnode = H + (long long)node * st.TB * C;
         const int mask_words = (st.A + 31) >> 5;
         const double nan = __longlong_as_double(0x7ff8000000000000LL);

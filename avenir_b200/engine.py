@@ -257,6 +257,15 @@ class Engine:
     def set_hist_variant(self, v: int):
         self._check(self.lib.avt_set_hist_variant(self.h, v))
 
+    def peer_export(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._check(self.lib.avt_peer_export(self.h, buf))
+        return buf.raw
+
+    def peer_import(self, n_ranks: int, rank: int, handles: Sequence[bytes]):
+        blob = C.create_string_buffer(b"".join(handles), 64 * n_ranks)
+        self._check(self.lib.avt_peer_import(self.h, n_ranks, rank, blob))
+
     def comm_init(self, n_ranks: int, rank: int, unique_id: bytes):
         buf = C.create_string_buffer(unique_id, 128)
         self._check(self.lib.avt_comm_init_rank(self.h, n_ranks, rank, buf))

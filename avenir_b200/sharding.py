@@ -25,3 +25,14 @@ def share_unique_id(dist, make_id, device=None) -> bytes:
         buf.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
     dist.broadcast(buf, 0)
     return bytes(buf.cpu().numpy().tobytes())
+
+
+def connect_peers(dist, engine, device="cuda") -> None:
+    """NVLink peer exchange for the level loop: gathers every rank's 64-byte IPC handle (avt_peer_export)
+    through torch.distributed and maps them (avt_peer_import)."""
+    import torch
+    world, rank = dist.get_world_size(), dist.get_rank()
+    mine = torch.frombuffer(bytearray(engine.peer_export()), dtype=torch.uint8).to(device)
+    gathered = [torch.zeros(64, dtype=torch.uint8, device=device) for _ in range(world)]
+    dist.all_gather(gathered, mine)
+    engine.peer_import(world, rank, [bytes(g.cpu().numpy().tobytes()) for g in gathered])

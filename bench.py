@@ -191,8 +191,10 @@ def main():
 
     eng = Engine(local)
     if world > 1:
-        from avenir_b200.sharding import share_unique_id
-        eng.comm_init(world, rank, share_unique_id(dist, comm_unique_id, device="cuda"))
+        from avenir_b200.sharding import connect_peers, share_unique_id
+        eng.comm_init(world, rank, share_unique_id(dist, comm_unique_id, device="cuda"))   # NCCL: fallback for oversized levels
+        if os.environ.get("AVT_BENCH_NCCL") != "1":
+            connect_peers(dist, eng)       # histograms are summed out of peer memory inside the scan kernel
     eng.load_dataset(cols_p, cls_p, n_bins, 2)
     eng.set_splits(table)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
@@ -279,7 +281,7 @@ def main():
             "config": {"workload": "C2: call_hangup decision tree (call_hangup.json schema), entropy, attribute strategy all, 8 expansions",
                        "rows_per_gpu": N, "levels": L, "attrs": 4, "bins": 18, "splits": 18, "classes": 2, "trees": 1,
                        "l2": "flushed between steps (256 MiB memset); the 70 MB working set is L2-resident within a step",
-                       "final_frontier_nodes": int(frontier[0]), "parallelism": f"rows sharded over {world} rank(s), NCCL all-reduce of uint32 histograms"},
+                       "final_frontier_nodes": int(frontier[0]), "parallelism": f"rows sharded over {world} rank(s), per-level histograms summed out of NVLink peer memory inside the scan kernel" if world > 1 and os.environ.get("AVT_BENCH_NCCL") != "1" else f"rows sharded over {world} rank(s), NCCL all-reduce of uint32 histograms"},
             "kernel_ms_per_step": {"histogram": st.hist_ms / prof_steps, "scan_plan": st.scan_ms / prof_steps, "eval": st.eval_ms / prof_steps,
                                    "repartition": st.repart_ms / prof_steps, "allreduce": st.comm_ms / prof_steps,
                                    "note": f"CUDA events per launch, from {prof_steps} extra profiled steps"},

@@ -242,6 +242,16 @@ int avt_comm_unique_id(void* id128);
  * BuilderReducer, tree/DecisionTreeBuilder.java:80-93). */
 int avt_comm_init_rank(avt_engine* e, int32_t n_ranks, int32_t rank, const void* id128);
 
+/* NVLink peer exchange for avt_grow_levels (optional, ranks on one node): instead of an NCCL all-reduce per
+ * level, every rank leaves its partial histogram in a buffer the others have mapped, and the scan kernel of
+ * each rank sums the ranks' counts for its node straight out of peer memory -- the exchange step is fused
+ * into kernel (b).  avt_peer_export allocates the exchange buffers (2 x 8 MiB + flags) and returns their
+ * 64-byte CUDA IPC handle; the host gathers all ranks' handles (rank order) and passes the n_ranks x 64 bytes
+ * to avt_peer_import.  Levels whose histogram exceeds the buffers fall back to the NCCL path (which then
+ * needs avt_comm_init_rank).  Same role as avt_comm_*: Hadoop's shuffle between mapper and reducer. */
+int avt_peer_export(avt_engine* e, void* handle64);
+int avt_peer_import(avt_engine* e, int32_t n_ranks, int32_t rank, const void* handles);
+
 /* ---- tool level: the reference's own entry points -------------------------------------------- */
 /* ToolRunner.run(new <tool>(), args): tool is "org.avenir.tree.DecisionTreeBuilder" or
  * "org.avenir.explore.ClassPartitionGenerator" (short names accepted); args are the Hadoop-style

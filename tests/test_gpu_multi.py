@@ -14,10 +14,10 @@ from avenir_b200.sharding import shard_range
 pytestmark = pytest.mark.gpu
 
 
-def _worker(rank, world, port, n, levels, out_dir):
+def _worker(rank, world, port, n, levels, out_dir, peer):
     import torch.distributed as dist
     from avenir_b200.engine import Engine, comm_unique_id
-    from avenir_b200.sharding import share_unique_id
+    from avenir_b200.sharding import connect_peers, share_unique_id
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
@@ -28,22 +28,30 @@ def _worker(rank, world, port, n, levels, out_dir):
         cols, cls, n_bins, _ = synth.call_hangup_encoded(n)
         eng = Engine(rank)
         eng.comm_init(world, rank, uid)
+        if peer:
+            connect_peers(dist, eng)
         eng.load_dataset([c[lo:hi] for c in cols], cls[lo:hi], n_bins, 2)
         eng.set_splits(binary_split_table(n_bins, [True, True, True, False]))
         eng.forest_init(1)
         (rec, nrec), frontier = eng.grow(levels, CRIT_ENTROPY, [1], max_records=4096)
         flat = [(rec[i].level, rec[i].node, rec[i].split, tuple(rec[i].child_pop), rec[i].min_av.hex()) for i in range(nrec)]
+        if peer:      # a second build right away: exchange buffers are reused across calls
+            eng.forest_init(1)
+            (rec2, nrec2), frontier2 = eng.grow(levels, CRIT_ENTROPY, [1], max_records=4096)
+            assert frontier2 == frontier and nrec2 == nrec and all(rec2[i].split == rec[i].split for i in range(nrec))
+            assert eng.stats().comm_calls > 0
         torch.save({"records": flat, "frontier": frontier, "range": (lo, hi), "nid": eng.node_ids(0)}, os.path.join(out_dir, f"rank{rank}.pt"))
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_two_gpus_equal_one(tmp_path):
+@pytest.mark.parametrize("peer", [False, True], ids=["nccl", "nvlink-peer"])
+def test_two_gpus_equal_one(tmp_path, peer):
     import torch.multiprocessing as mp
     from avenir_b200.engine import Engine
     n, levels = 1_000_003, 6
-    mp.spawn(_worker, args=(2, 29400 + os.getpid() % 500, n, levels, str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, 29400 + os.getpid() % 500 + int(peer), n, levels, str(tmp_path), peer), nprocs=2, join=True)
     cols, cls, n_bins, _ = synth.call_hangup_encoded(n)
     eng = Engine(0)
     eng.load_dataset(cols, cls, n_bins, 2)
