@@ -131,8 +131,11 @@ struct avt_engine {
     } peer;
     DevBuf<const uint32_t*> d_peer_H[2];
     DevBuf<uint32_t*> d_remote_flags;
-    DevBuf<uint32_t> d_hsum;
+    DevBuf<uint32_t> d_hsum, d_ticket2;
+    bool ticket2_zeroed = false;
     uint32_t* H_cur = nullptr;         // histogram buffer of the pass being launched (nullptr: d_H)
+    bool signal_pending = false;       // the pass being launched must signal peer.epoch to every rank
+    bool signal_in_hist = false;       // ... and did so from inside the histogram kernel
 };
 
 namespace {
@@ -294,7 +297,7 @@ void avt_destroy(avt_engine* e) {
     for (int r = 0; r < e->peer.n; ++r)
         if (r != e->peer.rank && e->peer.base[r]) cudaIpcCloseMemHandle(e->peer.base[r]);
     if (e->peer.arena) cudaFree(e->peer.arena);
-    e->d_peer_H[0].release(); e->d_peer_H[1].release(); e->d_remote_flags.release(); e->d_hsum.release();
+    e->d_peer_H[0].release(); e->d_peer_H[1].release(); e->d_remote_flags.release(); e->d_hsum.release(); e->d_ticket2.release();
     for (void* c : e->cols)
         if (c) cudaFree(c);
     e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
@@ -598,6 +601,19 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         chunks = std::min(chunks, tiles);
         chunks = std::min<long long>(chunks, 65535);
         dim3 grid((unsigned)e->T, (unsigned)chunks, (unsigned)G);
+        e->signal_in_hist = false;
+        if (e->signal_pending) {
+            CUDA_TRY(e, e->d_ticket2.ensure(1));
+            if (!e->ticket2_zeroed) {
+                CUDA_TRY(e, cudaMemsetAsync(e->d_ticket2.p, 0, sizeof(uint32_t), e->stream));
+                e->ticket2_zeroed = true;
+            }
+            ha.signal_flags = e->d_remote_flags.p;
+            ha.signal_ticket = e->d_ticket2.p;
+            ha.signal_epoch = e->peer.epoch;
+            ha.signal_ranks = e->peer.n;
+            e->signal_in_hist = true;
+        }
         const int sel = (e->any_w ? 4 : 0) | (any_wide ? 2 : 0) | (fr ? 1 : 0);
         switch (sel) {
             case 0: hist_smem_kernel<false, false, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
@@ -1080,17 +1096,21 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         if (pending) fr.prev_node_base = nb_level(level - 1);
         e->skip_h_memset = h_prezeroed;
         e->H_cur = peer_level ? arena_H(level & 1) : nullptr;
+        if (peer_level) ++e->peer.epoch;   // the pass signals this epoch when its last block finishes
+        e->signal_pending = peer_level;
         if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr, nb_level(level))) return rc;
         e->skip_h_memset = false;
         e->H_cur = nullptr;
+        e->signal_pending = false;
         if (peer_level) {
-            // this rank's partial counts are complete: tell every rank (the scan blocks wait for all of them)
-            TimerSlot tc;
-            if (int rc = timer_open(e, &e->stats.comm_ms, &tc)) return rc;
-            ++e->peer.epoch;
-            peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
-            CUDA_TRY(e, cudaGetLastError());
-            if (int rc = timer_close(e, tc)) return rc;
+            if (!e->signal_in_hist) {
+                // global-atomics fallback pass: signal with a separate launch
+                TimerSlot tc;
+                if (int rc = timer_open(e, &e->stats.comm_ms, &tc)) return rc;
+                peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
+                CUDA_TRY(e, cudaGetLastError());
+                if (int rc = timer_close(e, tc)) return rc;
+            }
             e->stats.comm_calls += 1;
             peer_used = true;
         }

@@ -48,6 +48,12 @@ struct HistArgs {
     const int32_t* wide;            // [A]
     int lut_w;
     int codes_in_regs;  // 1: one group, <= 4 uint8 attributes, entry q == attribute q (the split code is in registers)
+    // multi-GPU peer exchange: the last block of the pass to finish tells every rank that this rank's
+    // partial histogram is complete (no separate signalling launch)
+    uint32_t* const* signal_flags;  // [signal_ranks] this rank's flag word inside every rank's memory (nullptr: no signalling)
+    uint32_t* signal_ticket;        // zero-initialised block counter
+    uint32_t signal_epoch;
+    int signal_ranks;
     int repart_smem;    // 1: codes_in_regs and the previous level's tables fit the block's shared memory (fast path)
 };
 
@@ -237,6 +243,18 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
             lb += step_b;
             c += step_c;
             if (c >= a.C) { c -= a.C; ++lb; }
+        }
+    }
+    if (a.signal_flags) {
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const uint32_t total = gridDim.x * gridDim.y * gridDim.z;
+            if (atomicAdd(a.signal_ticket, 1u) == total - 1) {
+                *a.signal_ticket = 0;
+                __threadfence_system();
+                for (int r = 0; r < a.signal_ranks; ++r) st_release_sys(a.signal_flags[r], a.signal_epoch);
+            }
         }
     }
 }

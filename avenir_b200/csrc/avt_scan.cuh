@@ -31,20 +31,6 @@ struct PlanArgs {
     int n_ranks;
 };
 
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-
 // Tells every rank (itself included) that this rank's partial histogram of epoch `epoch` is complete.
 // Launched on the stream right after the histogram pass; remote_flags[r] points INTO rank r's memory.
 __global__ void peer_signal_kernel(uint32_t* const* remote_flags, int n_ranks, uint32_t epoch) {
