@@ -36,7 +36,7 @@ __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
 }
 __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
     uint32_t v;
-    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
 }
 

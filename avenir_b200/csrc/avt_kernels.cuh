@@ -246,15 +246,19 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
         }
     }
     if (a.signal_flags) {
+        __shared__ int s_last;
         __threadfence();
         __syncthreads();
         if (threadIdx.x == 0) {
             const uint32_t total = gridDim.x * gridDim.y * gridDim.z;
-            if (atomicAdd(a.signal_ticket, 1u) == total - 1) {
-                *a.signal_ticket = 0;
-                __threadfence_system();
-                for (int r = 0; r < a.signal_ranks; ++r) st_release_sys(a.signal_flags[r], a.signal_epoch);
-            }
+            s_last = atomicAdd(a.signal_ticket, 1u) == total - 1;
+            if (s_last) *a.signal_ticket = 0;
+        }
+        __syncthreads();
+        // one lane per rank, so the system-scope fences and the NVLink stores overlap instead of queueing
+        if (s_last && (int)threadIdx.x < a.signal_ranks) {
+            __threadfence_system();
+            st_release_sys(a.signal_flags[threadIdx.x], a.signal_epoch);
         }
     }
 }

@@ -186,7 +186,13 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, S
             const long long words = (long long)st.TB * C, off = (long long)node * words;
             for (long long i = threadIdx.x; i < words; i += blockDim.x) {
                 uint32_t sum = 0;
-                for (int r = 0; r < plan.n_ranks; ++r) sum += ld_relaxed_sys(plan.peer_H[r] + off + i);
+                for (int r0 = 0; r0 < plan.n_ranks; r0 += 8) {   // 8 NVLink loads in flight per thread
+                    uint32_t v[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) v[k] = r0 + k < plan.n_ranks ? ld_relaxed_sys(plan.peer_H[r0 + k] + off + i) : 0u;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) sum += v[k];
+                }
                 plan.h_sum[off + i] = sum;
             }
             __syncthreads();
