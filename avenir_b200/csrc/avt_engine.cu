@@ -21,7 +21,7 @@ namespace {
 thread_local std::string g_create_error;
 
 constexpr int kSmCountFallback = 148;
-constexpr size_t kMaxDynSmem = 227 * 1024;        // B200: 227 KB of shared memory per CTA
+constexpr size_t kMaxDynSmem = 226 * 1024;        // B200: 227 KB of shared memory per CTA, 1 KB left for static shared variables
 constexpr int kHistWordsBudget = 220 * 1024 / 4;  // shared-memory words one histogram block may use
 
 struct TimerSlot {
