@@ -22,7 +22,7 @@ thread_local std::string g_create_error;
 
 constexpr int kSmCountFallback = 148;
 constexpr size_t kMaxDynSmem = 226 * 1024;        // B200: 227 KB of shared memory per CTA, 1 KB left for static shared variables
-constexpr int kHistWordsBudget = 220 * 1024 / 4;  // shared-memory words one histogram block may use
+constexpr int kHistWordsBudget = 200 * 1024 / 4;  // shared-memory words of one block's histogram copies (the rest: repartition tables, skip marks)
 
 struct TimerSlot {
     cudaEvent_t a, b;
@@ -131,7 +131,11 @@ struct avt_engine {
     } peer;
     DevBuf<const uint32_t*> d_peer_H[2];
     DevBuf<uint32_t*> d_remote_flags;
-    DevBuf<uint32_t> d_hsum, d_ticket2;
+    DevBuf<uint32_t> d_hsum, d_hsum2, d_H2, d_ticket2;
+    DevBuf<uint8_t> d_skip;
+    DevBuf<int32_t> d_drv_parent, d_kids;
+    bool subtract = true;              // AVT_SUBTRACT=0: count every child (no sibling subtraction)
+    const uint8_t* skip_cur = nullptr; // skip marks for the pass being launched
     bool ticket2_zeroed = false;
     uint32_t* H_cur = nullptr;         // histogram buffer of the pass being launched (nullptr: d_H)
     bool signal_pending = false;       // the pass being launched must signal peer.epoch to every rank
@@ -284,6 +288,7 @@ int avt_create(int device, avt_engine** out) {
     }
     if (const char* v = getenv("AVT_HIST_TARGET_ADDRS")) e->hist_target_addrs = std::max(1LL, atoll(v));
     if (const char* v = getenv("AVT_GROW_HOST")) e->grow_host_loop = atoi(v);
+    if (const char* v = getenv("AVT_SUBTRACT")) e->subtract = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
     *out = e;
     return AVT_OK;
@@ -297,7 +302,7 @@ void avt_destroy(avt_engine* e) {
     for (int r = 0; r < e->peer.n; ++r)
         if (r != e->peer.rank && e->peer.base[r]) cudaIpcCloseMemHandle(e->peer.base[r]);
     if (e->peer.arena) cudaFree(e->peer.arena);
-    e->d_peer_H[0].release(); e->d_peer_H[1].release(); e->d_remote_flags.release(); e->d_hsum.release(); e->d_ticket2.release();
+    e->d_peer_H[0].release(); e->d_peer_H[1].release(); e->d_remote_flags.release(); e->d_hsum.release(); e->d_ticket2.release(); e->d_hsum2.release(); e->d_H2.release(); e->d_skip.release(); e->d_drv_parent.release(); e->d_kids.release();
     for (void* c : e->cols)
         if (c) cudaFree(c);
     e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
@@ -507,6 +512,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
     ha.TB = e->TB;
     ha.T = e->T;
     ha.wide = e->d_wide.p;
+    ha.skip = e->skip_cur;
     if (fr) {
         ha.nid_out = nid_out;
         ha.prev_node_base = fr->prev_node_base;
@@ -600,6 +606,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         const long long tiles = (e->N + (long long)kHistThreads * kRowsPerThread - 1) / ((long long)kHistThreads * kRowsPerThread);
         chunks = std::min(chunks, tiles);
         chunks = std::min<long long>(chunks, 65535);
+        if (ha.skip) smem += (size_t)n_max + 16;   // skip marks of the frontier, staged behind the histogram (and the repartition tables)
         dim3 grid((unsigned)e->T, (unsigned)chunks, (unsigned)G);
         e->signal_in_hist = false;
         if (e->signal_pending) {
@@ -650,10 +657,10 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         for (int t = 0; t < e->T; ++t) per_row += 2 + ((e->any_w) ? 1 : 0) + (fr ? 2 : 0);  // fused: + the node-id write
         e->stats.hist_alg_bytes += per_row * e->N;
     }
-    if (e->comm && !e->H_cur) {
+    if (e->comm && !e->signal_pending) {
         TimerSlot tc;
         if (int rc = timer_open(e, &e->stats.comm_ms, &tc)) return rc;
-        NCCL_TRY(e, ncclAllReduce(e->d_H.p, e->d_H.p, hwords, ncclUint32, ncclSum, e->comm, e->stream));
+        NCCL_TRY(e, ncclAllReduce(Hbuf, Hbuf, hwords, ncclUint32, ncclSum, e->comm, e->stream));
         if (int rc = timer_close(e, tc)) return rc;
         e->stats.comm_calls += 1;
     }
@@ -1020,9 +1027,16 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     for (int t = 0; t < T; ++t) nb_host[(size_t)t + 1] = nb_host[(size_t)t] + ub[(size_t)t];
     CUDA_TRY(e, cudaMemcpyAsync(nb_level(0), nb_host.data(), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
     const bool peer_on = e->peer.active && e->peer.n > 1;
+    const bool subtract = e->subtract;
+    // complete counts of a level: single GPU = the (ping-pong) histogram buffer itself; peer mode = the local sums
+    auto H_level = [&](int level) { return (level & 1) ? e->d_H2.p : e->d_H.p; };
+    auto hsum_level = [&](int level) { return (level & 1) ? e->d_hsum2.p : e->d_hsum.p; };
+    bool prev_peer = false;
     auto arena_H = [&](int parity) { return e->peer.arena + 64 + (size_t)parity * e->peer.cap_words; };
     bool peer_used = false;
     bool pending = false;
+    bool planned_skip = false;   // the previous level's planning marked this level's derived nodes
+    bool derive_ok = true;       // the previous level's complete counts survived (no reallocation since)
     bool h_prezeroed = false;  // the previous level's planning block already cleared this level's histogram region
     FusedRepart fr{};
     size_t rec_off = 0;
@@ -1056,7 +1070,9 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         // every buffer of this level is sized BEFORE anything is enqueued (a reallocation frees memory
         // that earlier, still running launches may use)
         if (e->d_av.cap < (size_t)NF * e->S || e->d_best.cap < (size_t)NF || e->d_best_eval.cap < (size_t)NF || e->d_node_attr.cap < (size_t)NF ||
-            e->d_lut.cap < (size_t)NF * lut_w || (!peer_level && e->d_H.cap < (size_t)NF * e->TB * e->C) || (peer_level && e->d_hsum.cap < (size_t)NF * e->TB * e->C) || (want_records && e->d_records.cap < rec_off + (size_t)NF)) {
+            e->d_lut.cap < (size_t)NF * lut_w || (!peer_level && (e->d_H.cap < (size_t)NF * e->TB * e->C || e->d_H2.cap < (size_t)NF * e->TB * e->C)) ||
+            (peer_level && (e->d_hsum.cap < (size_t)NF * e->TB * e->C || e->d_hsum2.cap < (size_t)NF * e->TB * e->C)) ||
+            (subtract && (e->d_skip.cap < (size_t)NF * g_max || e->d_drv_parent.cap < (size_t)NF * g_max || e->d_kids.cap < (size_t)NF * kMaxSeg)) || (want_records && e->d_records.cap < rec_off + (size_t)NF)) {
             if (int rc = sync_and_resolve(e)) return rc;
             // flush records gathered so far: the record buffer may move
             if (want_records && rec_off) {
@@ -1083,8 +1099,36 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             CUDA_TRY(e, e->d_best_eval.ensure(grow));
             CUDA_TRY(e, e->d_node_attr.ensure(grow));
             CUDA_TRY(e, e->d_lut.ensure(grow * lut_w));
-            if (!peer_level) CUDA_TRY(e, e->d_H.ensure(grow * e->TB * e->C));
-            else CUDA_TRY(e, e->d_hsum.ensure(std::min(grow * e->TB * e->C, e->peer.cap_words)));
+            // (a reallocation here drops the previous level's complete counts: no derivation on this level)
+            const bool had_prev = level > 0;
+            if (!peer_level) {
+                if (e->d_H.cap < grow * e->TB * e->C || e->d_H2.cap < grow * e->TB * e->C) derive_ok = !had_prev;
+                CUDA_TRY(e, e->d_H.ensure(grow * e->TB * e->C));
+                CUDA_TRY(e, e->d_H2.ensure(grow * e->TB * e->C));
+            } else {
+                const size_t hs = std::min(grow * e->TB * e->C, e->peer.cap_words);
+                if (e->d_hsum.cap < hs || e->d_hsum2.cap < hs) derive_ok = !had_prev;
+                CUDA_TRY(e, e->d_hsum.ensure(hs));
+                CUDA_TRY(e, e->d_hsum2.ensure(hs));
+            }
+            if (subtract) {
+                // plan tables of the previous level are consumed by this level: keep them across the reallocation
+                std::vector<uint8_t> k_skip(e->d_skip.cap);
+                std::vector<int32_t> k_par(e->d_drv_parent.cap), k_kids(e->d_kids.cap);
+                if (had_prev && e->d_skip.cap) {
+                    CUDA_TRY(e, cudaMemcpy(k_skip.data(), e->d_skip.p, k_skip.size(), cudaMemcpyDeviceToHost));
+                    CUDA_TRY(e, cudaMemcpy(k_par.data(), e->d_drv_parent.p, k_par.size() * 4, cudaMemcpyDeviceToHost));
+                    CUDA_TRY(e, cudaMemcpy(k_kids.data(), e->d_kids.p, k_kids.size() * 4, cudaMemcpyDeviceToHost));
+                }
+                CUDA_TRY(e, e->d_skip.ensure(grow * g_max));
+                CUDA_TRY(e, e->d_drv_parent.ensure(grow * g_max));
+                CUDA_TRY(e, e->d_kids.ensure(grow * kMaxSeg));
+                if (had_prev && !k_skip.empty()) {
+                    CUDA_TRY(e, cudaMemcpy(e->d_skip.p, k_skip.data(), k_skip.size(), cudaMemcpyHostToDevice));
+                    CUDA_TRY(e, cudaMemcpy(e->d_drv_parent.p, k_par.data(), k_par.size() * 4, cudaMemcpyHostToDevice));
+                    CUDA_TRY(e, cudaMemcpy(e->d_kids.p, k_kids.data(), k_kids.size() * 4, cudaMemcpyHostToDevice));
+                }
+            }
             if (want_records) CUDA_TRY(e, e->d_records.ensure(grow * 2));
             if (pending) {
                 CUDA_TRY(e, cudaMemcpy(e->d_node_attr.p, keep_attr.data(), prev_nf * sizeof(int32_t), cudaMemcpyHostToDevice));
@@ -1094,13 +1138,23 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             }
         }
         if (pending) fr.prev_node_base = nb_level(level - 1);
+        // derivation needs this level's skip marks (from the previous planning) AND the previous level's complete
+        // counts in the same mode (single GPU <-> peer switches and reallocations lose them)
+        const bool derive = subtract && level > 0 && planned_skip && derive_ok && prev_peer == peer_level;
+        if (subtract && level > 0 && planned_skip && !derive) {
+            // the rows of "derived" nodes must be counted after all: clear the marks
+            CUDA_TRY(e, cudaMemsetAsync(e->d_skip.p, 0, (size_t)NF, e->stream));
+        }
+        derive_ok = true;
+        e->skip_cur = (subtract && level > 0 && planned_skip) ? e->d_skip.p : nullptr;
         e->skip_h_memset = h_prezeroed;
-        e->H_cur = peer_level ? arena_H(level & 1) : nullptr;
+        e->H_cur = peer_level ? arena_H(level & 1) : H_level(level);
         if (peer_level) ++e->peer.epoch;   // the pass signals this epoch when its last block finishes
         e->signal_pending = peer_level;
         if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr, nb_level(level))) return rc;
         e->skip_h_memset = false;
         e->H_cur = nullptr;
+        e->skip_cur = nullptr;
         e->signal_pending = false;
         if (peer_level) {
             if (!e->signal_in_hist) {
@@ -1136,20 +1190,35 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             const long long next_words = next_nodes * e->TB * e->C;
             const bool next_peer = peer_on && (size_t)next_words <= e->peer.cap_words;
             h_prezeroed = level + 1 < n_levels && next_nodes <= kAsyncNodeLimit && next_words <= (1 << 16) &&
-                          (next_peer || (!peer_on && (size_t)next_words <= e->d_H.cap));
-            pa.zero_ptr = h_prezeroed ? (next_peer ? arena_H((level + 1) & 1) : e->d_H.p) : nullptr;
+                          (next_peer || (!peer_on && (size_t)next_words <= std::min(e->d_H.cap, e->d_H2.cap)));
+            pa.zero_ptr = h_prezeroed ? (next_peer ? arena_H((level + 1) & 1) : H_level(level + 1)) : nullptr;
             pa.zero_words = h_prezeroed ? next_words : 0;
         }
+        uint32_t* const Hc = peer_level ? hsum_level(level) : H_level(level);   // this level's complete counts
         if (peer_level) {
             pa.peer_H = e->d_peer_H[level & 1].p;
             pa.peer_flags = e->peer.arena;
-            pa.h_sum = e->d_hsum.p;
+            pa.h_sum = Hc;
             pa.peer_epoch = e->peer.epoch;
             pa.n_ranks = e->peer.n;
         }
+        if (subtract) {
+            const bool next_plannable = level + 1 < n_levels;
+            pa.kids = e->d_kids.p;
+            pa.next_skip = next_plannable ? e->d_skip.p : nullptr;
+            pa.next_parent = next_plannable ? e->d_drv_parent.p : nullptr;
+            if (derive) {
+                pa.drv_parent = e->d_drv_parent.p;
+                pa.prev_kids = e->d_kids.p;
+                pa.H_prev = peer_level ? hsum_level(level - 1) : H_level(level - 1);
+            }
+            pa.H_mut = Hc;
+            planned_skip = next_plannable;
+        }
+        prev_peer = peer_level;
         TimerSlot ts;
         if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
-        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(peer_level ? e->d_hsum.p : e->d_H.p, make_table(e), nullptr, e->d_order.p, criterion,
+        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(Hc, make_table(e), nullptr, e->d_order.p, criterion,
                                                         e->d_av.p, e->d_best.p, e->d_best_eval.p, nb_level(level) + T, pa);
         CUDA_TRY(e, cudaGetLastError());
         if (int rc = timer_close(e, ts)) return rc;

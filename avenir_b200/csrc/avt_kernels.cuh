@@ -50,6 +50,7 @@ struct HistArgs {
     int codes_in_regs;  // 1: one group, <= 4 uint8 attributes, entry q == attribute q (the split code is in registers)
     // multi-GPU peer exchange: the last block of the pass to finish tells every rank that this rank's
     // partial histogram is complete (no separate signalling launch)
+    const uint8_t* skip;            // [NF] nodes of this frontier whose rows are not counted (sibling subtraction), nullptr = none
     uint32_t* const* signal_flags;  // [signal_ranks] this rank's flag word inside every rank's memory (nullptr: no signalling)
     uint32_t* signal_ticket;        // zero-initialised block counter
     uint32_t signal_epoch;
@@ -63,6 +64,7 @@ struct RepartSmem {
     const uint16_t* lut;   // [n_prev+1][lut_w] bin -> child (entry n_prev: all NONE)
     uint32_t n_prev;
     bool fast;
+    const uint8_t* skip;   // [n_nodes+1] 1 = node is derived by subtraction, its rows are not counted (nullptr: count all)
 };
 
 // hist_rows16: 16 consecutive rows of one tree for one attribute group.
@@ -144,6 +146,7 @@ __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a,
         uint32_t node = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
         const bool dead = node == AVT_NODE_NONE || (HAS_W && u4_byte(vw, j) == 0);
         node = dead ? phantom : node;
+        if (rp.skip) node = rp.skip[node] ? phantom : node;
         rowkey[j] = sh_base + (node * node_stride + (u4_byte(vc, j) << rlog) + rep) * 4u;
     }
     if (!WIDE) {
@@ -195,7 +198,8 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
     const int keys = n_nodes * GB * a.C;
     const int words = (keys + GB * a.C) << rlog;  // + one phantom node that swallows rows outside the frontier
     for (int i = threadIdx.x; i < words; i += blockDim.x) sh[i] = 0;
-    RepartSmem rp{nullptr, nullptr, 0u, false};
+    RepartSmem rp{nullptr, nullptr, 0u, false, nullptr};
+    uint8_t* smem_tail = reinterpret_cast<uint8_t*>(sh + words);
     if (REPART && a.repart_smem) {
         const int pnb = a.prev_node_base[t], n_prev = a.prev_node_base[t + 1] - pnb;
         uint32_t* sel = sh + words;
@@ -206,7 +210,12 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
         }
         for (int i = threadIdx.x; i < (n_prev + 1) * a.lut_w; i += blockDim.x)
             lut[i] = i < n_prev * a.lut_w ? a.child_lut[(long long)pnb * a.lut_w + i] : (uint16_t)AVT_NODE_NONE;
-        rp = RepartSmem{sel, lut, (uint32_t)n_prev, true};
+        rp = RepartSmem{sel, lut, (uint32_t)n_prev, true, nullptr};
+        smem_tail = reinterpret_cast<uint8_t*>(lut + (n_prev + 1) * a.lut_w);
+    }
+    if (a.skip) {
+        for (int i = threadIdx.x; i <= n_nodes; i += blockDim.x) smem_tail[i] = i < n_nodes ? a.skip[nb + i] : 0;
+        rp.skip = smem_tail;
     }
     __syncthreads();
     const uint32_t sh_base = (uint32_t)__cvta_generic_to_shared(sh);
@@ -283,6 +292,7 @@ __global__ void __launch_bounds__(256) hist_global_kernel(const HistArgs a, int 
         uint32_t node = live ? nid[r] : AVT_NODE_NONE;
         uint32_t w = live ? (hw ? wt[r] : 1u) : 0u;
         live = live && node != AVT_NODE_NONE && w != 0;
+        if (live && a.skip) live = a.skip[nb + node] == 0;
         const uint32_t cl = live ? a.cls[r] : 0;
         for (int at = 0; at < n_attrs; ++at) {
             unsigned long long idx = ~0ULL - lane;  // unique dummy key for idle lanes

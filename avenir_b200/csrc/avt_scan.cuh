@@ -29,6 +29,15 @@ struct PlanArgs {
     uint32_t* h_sum;                // local buffer that receives the summed histogram (== the kernel's H argument)
     uint32_t peer_epoch;
     int n_ranks;
+    // sibling subtraction: the most populous child of every split is NOT counted by the next histogram pass; its
+    // counts are derived as parent - (other children), exact in integers, by that child's scan block
+    uint8_t* next_skip;         // [NF_next] 1 = derived (nullptr: subtraction off)
+    int32_t* next_parent;       // [NF_next] global index (this frontier) of a derived node's parent, else -1
+    int32_t* kids;              // [NF][kMaxSeg] global index (next frontier) of each segment's child, -1 = none
+    const int32_t* drv_parent;  // [NF] the same table for THIS frontier, written by the previous level's planning (nullptr at level 0)
+    const int32_t* prev_kids;   // [NF_prev][kMaxSeg] written by the previous level's planning
+    const uint32_t* H_prev;     // complete counts of the previous level
+    uint32_t* H_mut;            // this level's counts (the kernel's H argument), completed in place for derived nodes
 };
 
 // Tells every rank (itself included) that this rank's partial histogram of epoch `epoch` is complete.
@@ -54,7 +63,7 @@ __device__ __forceinline__ long long ldcg_i64(const int64_t* p) { return __ldcg(
 __device__ __forceinline__ double ldcg_f64(const double* p) { return __ldcg(p); }
 
 // Plans one tree with the whole block (blockDim.x = kScanThreads).
-__device__ void plan_tree(const PlanArgs& p, const SplitTable& st, int t, int* warp_tot, int* running) {
+__device__ void plan_tree(const PlanArgs& p, const SplitTable& st, int t, int next_base, int* warp_tot, int* running) {
     const int nb = p.node_base[t], n = p.node_base[t + 1] - nb;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) *running = 0;
@@ -124,6 +133,23 @@ __device__ void plan_tree(const PlanArgs& p, const SplitTable& st, int t, int* w
                     if (rec.child[sg] >= 0) lut[b] = (uint16_t)rec.child[sg];
                 }
             }
+            if (p.kids) {
+                int32_t* kd = p.kids + (long long)g * kMaxSeg;
+                int derived = -1;
+                if (live && p.next_skip) {   // the most populous child (lowest segment on ties) is derived, not counted
+                    long long mx = -1;
+                    for (int sg = 0; sg < sp.n_seg; ++sg)
+                        if (rec.child[sg] >= 0 && rec.child_pop[sg] > mx) { mx = rec.child_pop[sg]; derived = sg; }
+                }
+                for (int sg = 0; sg < kMaxSeg; ++sg) {
+                    const int gi = rec.child[sg] >= 0 ? next_base + rec.child[sg] : -1;
+                    kd[sg] = gi;
+                    if (gi >= 0 && p.next_skip) {
+                        p.next_skip[gi] = sg == derived;
+                        p.next_parent[gi] = sg == derived ? g : -1;
+                    }
+                }
+            }
             if (p.records) p.records[g] = rec;
         }
         __syncthreads();
@@ -137,7 +163,11 @@ __device__ void plan_tree(const PlanArgs& p, const SplitTable& st, int t, int* w
 // Whole-level planning by one block: every tree, then the next frontier's node_base, then (optionally)
 // the zeroing of the next level's histogram region.
 __device__ void plan_level(const PlanArgs& p, const SplitTable& st, int* warp_tot, int* running) {
-    for (int t = 0; t < p.n_trees; ++t) plan_tree(p, st, t, warp_tot, running);
+    int next_base = 0;
+    for (int t = 0; t < p.n_trees; ++t) {
+        plan_tree(p, st, t, next_base, warp_tot, running);   // ends with a block barrier after next_count[t] is written
+        next_base += p.next_count[t];
+    }
     if (threadIdx.x == 0 && p.next_node_base) {
         int acc = 0;
         for (int k = 0; k < p.n_trees; ++k) {
@@ -184,16 +214,44 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, S
                 while ((int32_t)(ld_acquire_sys(plan.peer_flags + threadIdx.x) - plan.peer_epoch) < 0) {}
             __syncthreads();
             const long long words = (long long)st.TB * C, off = (long long)node * words;
-            for (long long i = threadIdx.x; i < words; i += blockDim.x) {
+            const int dp = plan.drv_parent ? plan.drv_parent[node] : -1;
+            auto pull = [&](long long o, long long i) {
                 uint32_t sum = 0;
                 for (int r0 = 0; r0 < plan.n_ranks; r0 += 8) {   // 8 NVLink loads in flight per thread
                     uint32_t v[8];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) v[k] = r0 + k < plan.n_ranks ? ld_relaxed_sys(plan.peer_H[r0 + k] + off + i) : 0u;
+                    for (int k = 0; k < 8; ++k) v[k] = r0 + k < plan.n_ranks ? ld_relaxed_sys(plan.peer_H[r0 + k] + o + i) : 0u;
 #pragma unroll
                     for (int k = 0; k < 8; ++k) sum += v[k];
                 }
+                return sum;
+            };
+            for (long long i = threadIdx.x; i < words; i += blockDim.x) {
+                uint32_t sum;
+                if (dp < 0) {
+                    sum = pull(off, i);
+                } else {   // derived node: parent's complete counts minus the counted siblings' (summed over the ranks)
+                    sum = plan.H_prev[(long long)dp * words + i];
+                    for (int k = 0; k < kMaxSeg; ++k) {
+                        const int kid = plan.prev_kids[(long long)dp * kMaxSeg + k];
+                        if (kid >= 0 && kid != node) sum -= pull((long long)kid * words, i);
+                    }
+                }
                 plan.h_sum[off + i] = sum;
+            }
+            __syncthreads();
+        } else if (plan.drv_parent) {
+            const int dp = plan.drv_parent[node];
+            if (dp >= 0) {   // derived node: complete its (uncounted) slots in place
+                const long long words = (long long)st.TB * C;
+                for (long long i = threadIdx.x; i < words; i += blockDim.x) {
+                    uint32_t v = plan.H_prev[(long long)dp * words + i];
+                    for (int k = 0; k < kMaxSeg; ++k) {
+                        const int kid = plan.prev_kids[(long long)dp * kMaxSeg + k];
+                        if (kid >= 0 && kid != node) v -= plan.H_mut[(long long)kid * words + i];
+                    }
+                    plan.H_mut[(long long)node * words + i] = v;
+                }
             }
             __syncthreads();
         }
