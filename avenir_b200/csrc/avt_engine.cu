@@ -134,7 +134,8 @@ struct avt_engine {
     DevBuf<uint32_t> d_hsum, d_hsum2, d_H2, d_ticket2;
     DevBuf<uint8_t> d_skip;
     DevBuf<int32_t> d_drv_parent, d_kids;
-    bool subtract = true;              // AVT_SUBTRACT=0: count every child (no sibling subtraction)
+    bool subtract = false;             // AVT_SUBTRACT=1: sibling subtraction (count the smaller children, derive the largest); measured
+                                       // neutral on C2/C3/C5 shapes in round 1 -- the pass is not bound by update issue -- so off by default
     const uint8_t* skip_cur = nullptr; // skip marks for the pass being launched
     bool ticket2_zeroed = false;
     uint32_t* H_cur = nullptr;         // histogram buffer of the pass being launched (nullptr: d_H)
