@@ -25,6 +25,12 @@ __device__ __forceinline__ void red_shared_add(uint32_t addr, uint32_t v) {
     asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
 
+// programmatic dependent launch: a kernel launched with the programmatic-serialization attribute may start
+// while its predecessor in the stream is still running; everything that depends on the predecessor's
+// results must come after pdl_wait().  Both are no-ops for ordinary launches.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+
 // system-scope accesses for memory shared with other GPUs over NVLink
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
     uint32_t v;

@@ -113,6 +113,8 @@ struct avt_engine {
     avt_stats stats{};
     int force_variant = -1;
     bool skip_h_memset = false;
+    bool pdl = true;          // AVT_PDL=0: plain stream launches in the level loop
+    bool pdl_chain = false;   // the launch being issued directly follows a kernel of the level loop (no memset/copy between)
     bool profiling = true;  // CUDA-event timing of every launch (avt_set_profiling)
     long long hist_target_addrs = 4096;  // AVT_HIST_TARGET_ADDRS
     int hist_max_bpsm = 4;               // AVT_HIST_BPSM: resident histogram blocks per SM
@@ -289,6 +291,7 @@ int avt_create(int device, avt_engine** out) {
     }
     if (const char* v = getenv("AVT_HIST_TARGET_ADDRS")) e->hist_target_addrs = std::max(1LL, atoll(v));
     if (const char* v = getenv("AVT_GROW_HOST")) e->grow_host_loop = atoi(v);
+    if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
     *out = e;
@@ -592,6 +595,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         ha.ent_attr = base + o_attr; ha.ent_locoff = base + o_loc; ha.ent_globoff = base + o_glob; ha.ent_wide = base + o_wide;
         ha.grp_start = base + o_gs; ha.grp_bins = base + o_gb; ha.grp_rlog = base + o_gr; ha.grp_l2g = base + o_l2g; ha.grp_l2g_off = base + o_lo;
         ha.codes_in_regs = (G == 1 && !any_wide && e->A <= 4) ? 1 : 0;
+        ha.zero_words = (int)smem_words;
         size_t smem = smem_words * sizeof(uint32_t);
         if (fr && ha.codes_in_regs) {
             // previous frontier (bounded like this one) + phantom entry: selector word + one bin->child row each
@@ -623,15 +627,29 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
             e->signal_in_hist = true;
         }
         const int sel = (e->any_w ? 4 : 0) | (any_wide ? 2 : 0) | (fr ? 1 : 0);
+        void (*kern)(const HistArgs) = nullptr;
         switch (sel) {
-            case 0: hist_smem_kernel<false, false, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
-            case 1: hist_smem_kernel<false, false, true><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
-            case 2: hist_smem_kernel<false, true, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
-            case 3: hist_smem_kernel<false, true, true><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
-            case 4: hist_smem_kernel<true, false, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
-            case 5: hist_smem_kernel<true, false, true><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
-            case 6: hist_smem_kernel<true, true, false><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
-            default: hist_smem_kernel<true, true, true><<<grid, kHistThreads, smem, e->stream>>>(ha); break;
+            case 0: kern = hist_smem_kernel<false, false, false>; break;
+            case 1: kern = hist_smem_kernel<false, false, true>; break;
+            case 2: kern = hist_smem_kernel<false, true, false>; break;
+            case 3: kern = hist_smem_kernel<false, true, true>; break;
+            case 4: kern = hist_smem_kernel<true, false, false>; break;
+            case 5: kern = hist_smem_kernel<true, false, true>; break;
+            case 6: kern = hist_smem_kernel<true, true, false>; break;
+            default: kern = hist_smem_kernel<true, true, true>; break;
+        }
+        {
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = grid;
+            cfg.blockDim = dim3(kHistThreads);
+            cfg.dynamicSmemBytes = smem;
+            cfg.stream = e->stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = (e->pdl && e->pdl_chain) ? 1 : 0;   // only directly behind another kernel of the level loop
+            CUDA_TRY(e, cudaLaunchKernelEx(&cfg, kern, ha));
         }
         e->stats.last_hist_replicas = 1 << rlog_min;
         e->stats.last_hist_grid = (int)(grid.x * grid.y * grid.z);
@@ -1149,11 +1167,14 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         derive_ok = true;
         e->skip_cur = (subtract && level > 0 && planned_skip) ? e->d_skip.p : nullptr;
         e->skip_h_memset = h_prezeroed;
+        // programmatic dependent launch: legal when nothing but the previous scan kernel precedes this pass
+        e->pdl_chain = level > 0 && h_prezeroed && !e->profiling && !(subtract && planned_skip && !derive);
         e->H_cur = peer_level ? arena_H(level & 1) : H_level(level);
         if (peer_level) ++e->peer.epoch;   // the pass signals this epoch when its last block finishes
         e->signal_pending = peer_level;
         if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr, nb_level(level))) return rc;
         e->skip_h_memset = false;
+        e->pdl_chain = false;
         e->H_cur = nullptr;
         e->skip_cur = nullptr;
         e->signal_pending = false;
@@ -1219,8 +1240,21 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         prev_peer = peer_level;
         TimerSlot ts;
         if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
-        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(Hc, make_table(e), nullptr, e->d_order.p, criterion,
-                                                        e->d_av.p, e->d_best.p, e->d_best_eval.p, nb_level(level) + T, pa);
+        {
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3((unsigned)NF);
+            cfg.blockDim = dim3(kScanThreads);
+            cfg.stream = e->stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            // directly behind the histogram kernel unless an NCCL all-reduce or a signalling launch sits between
+            const bool chain = e->pdl && !e->profiling && e->stats.last_hist_variant == 0 && (peer_level ? e->signal_in_hist : e->comm == nullptr);
+            cfg.numAttrs = chain ? 1 : 0;
+            CUDA_TRY(e, cudaLaunchKernelEx(&cfg, scan_kernel, (const uint32_t*)Hc, make_table(e), (const uint32_t*)nullptr, (const uint8_t*)e->d_order.p,
+                                           (int)criterion, e->d_av.p, e->d_best.p, e->d_best_eval.p, (const int32_t*)(nb_level(level) + T), pa));
+        }
         CUDA_TRY(e, cudaGetLastError());
         if (int rc = timer_close(e, ts)) return rc;
         e->stats.scan_launches += 1;

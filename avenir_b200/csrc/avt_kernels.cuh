@@ -50,6 +50,7 @@ struct HistArgs {
     int codes_in_regs;  // 1: one group, <= 4 uint8 attributes, entry q == attribute q (the split code is in registers)
     // multi-GPU peer exchange: the last block of the pass to finish tells every rank that this rank's
     // partial histogram is complete (no separate signalling launch)
+    int zero_words;                 // shared-memory words the block may clear before it waits for the previous launch
     const uint8_t* skip;            // [NF] nodes of this frontier whose rows are not counted (sibling subtraction), nullptr = none
     uint32_t* const* signal_flags;  // [signal_ranks] this rank's flag word inside every rank's memory (nullptr: no signalling)
     uint32_t* signal_ticket;        // zero-initialised block counter
@@ -192,12 +193,16 @@ __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a,
 template <bool HAS_W, bool WIDE, bool REPART>
 __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs a) {
     extern __shared__ uint32_t sh[];
+    pdl_launch_dependents();
+    // clear the block's histogram copies (sized by the host's bound) while the previous launch may still run
+    for (int i = threadIdx.x; i < a.zero_words; i += blockDim.x) sh[i] = 0;
+    pdl_wait();   // node_base, the repartition tables and the node ids come from the previous launches
     const int t = blockIdx.x, g = blockIdx.z;
     const int nb = a.node_base[t], n_nodes = a.node_base[t + 1] - nb;
     const int GB = a.grp_bins[g], rlog = a.grp_rlog[g];
     const int keys = n_nodes * GB * a.C;
     const int words = (keys + GB * a.C) << rlog;  // + one phantom node that swallows rows outside the frontier
-    for (int i = threadIdx.x; i < words; i += blockDim.x) sh[i] = 0;
+    for (int i = a.zero_words + threadIdx.x; i < words; i += blockDim.x) sh[i] = 0;   // (only if the bound was not given)
     RepartSmem rp{nullptr, nullptr, 0u, false, nullptr};
     uint8_t* smem_tail = reinterpret_cast<uint8_t*>(sh + words);
     if (REPART && a.repart_smem) {

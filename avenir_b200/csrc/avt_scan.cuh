@@ -200,6 +200,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, S
     __shared__ int s_warp_tot[kScanWarps];
     __shared__ int s_running;
     __shared__ int s_is_last;
+    pdl_launch_dependents();
+    pdl_wait();   // the histogram (and the frontier size) come from the previous launch
     const int node = blockIdx.x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int C = st.C;
