@@ -197,6 +197,7 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
     // clear the block's histogram copies (sized by the host's bound) while the previous launch may still run
     for (int i = threadIdx.x; i < a.zero_words; i += blockDim.x) sh[i] = 0;
     pdl_wait();   // node_base, the repartition tables and the node ids come from the previous launches
+    __syncthreads();  // the cleared region may extend past this frontier's counters into where the tables are staged below
     const int t = blockIdx.x, g = blockIdx.z;
     const int nb = a.node_base[t], n_nodes = a.node_base[t + 1] - nb;
     const int GB = a.grp_bins[g], rlog = a.grp_rlog[g];
