@@ -67,6 +67,7 @@ SIGNATURES = {
     "avt_level_repartition": (C.c_int, [_P, C.POINTER(C.c_int32), _P, C.c_int32]),
     "avt_grow_levels": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.POINTER(C.c_int32), C.POINTER(GrowRecord), C.c_int64, C.POINTER(C.c_int64)]),
     "avt_cpg_sweep": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.POINTER(CpgStat)]),
+    "avt_predict": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_int32), _P, _P, _P, C.c_int32, _P, _P]),
     "avt_forest_node_ids": (C.c_int, [_P, C.c_int32, _P]),
     "avt_level_class_counts": (C.c_int, [_P, _P]),
     "avt_timer_begin": (C.c_int, [_P]),

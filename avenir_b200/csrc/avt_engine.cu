@@ -97,6 +97,12 @@ struct avt_engine {
     DevBuf<int32_t> d_pairs;
     DevBuf<avt_split_eval> d_eval;
     DevBuf<avt_cpg_stat> d_cpg;
+    // prediction
+    DevBuf<uint32_t> d_pmask;
+    DevBuf<int64_t> d_pmoff;
+    DevBuf<int32_t> d_pint, d_ppoff;
+    DevBuf<uint8_t> d_pcls, d_pout;
+    DevBuf<double> d_pw;
     DevBuf<uint32_t> d_ccnt;
     DevBuf<int32_t> d_node_attr;
     DevBuf<uint16_t> d_lut;
@@ -311,6 +317,7 @@ void avt_destroy(avt_engine* e) {
         if (c) cudaFree(c);
     e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
     e->d_nid.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_tile_ctr.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
+    e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
     e->d_attr_first.release(); e->d_seg_lut.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
@@ -1353,6 +1360,63 @@ int avt_cpg_sweep(avt_engine* e, int32_t node, int32_t criterion, const uint8_t*
     if (int rc = timer_close(e, ts)) return rc;
     e->stats.scan_launches += 1;
     CUDA_TRY(e, cudaMemcpyAsync(out, e->d_cpg.p, (size_t)e->S * sizeof(avt_cpg_stat), cudaMemcpyDeviceToHost, e->stream));
+    return sync_and_resolve(e);
+}
+
+int avt_predict(avt_engine* e, int32_t n_models, const int32_t* n_paths, const uint32_t* masks, const uint8_t* path_class,
+                const double* weights, int32_t n_classes, const uint8_t* class_rank, uint8_t* pred_out) {
+    if (!e) return AVT_E_INVALID;
+    if (e->N == 0) return fail(e, AVT_E_STATE, "avt_predict: no data set loaded");
+    if (n_models < 1 || !n_paths || !masks || !path_class || !class_rank || !pred_out) return fail(e, AVT_E_INVALID, "avt_predict: NULL argument");
+    if (n_classes < 1 || n_classes > AVT_MAX_CLASSES) return fail(e, AVT_E_INVALID, "avt_predict: n_classes %d outside 1..%d", n_classes, AVT_MAX_CLASSES);
+    if (int rc = use_device(e)) return rc;
+    std::vector<int64_t> mask_off((size_t)n_models);
+    std::vector<int32_t> path_off((size_t)n_models);
+    std::vector<double> w((size_t)n_models, 1.0);
+    int64_t mo = 0;
+    int32_t po = 0;
+    for (int m = 0; m < n_models; ++m) {
+        if (n_paths[m] < 1) return fail(e, AVT_E_INVALID, "avt_predict: model %d has no decision path", m);
+        mask_off[(size_t)m] = mo;
+        path_off[(size_t)m] = po;
+        mo += (int64_t)e->TB * ((n_paths[m] + 31) / 32);
+        po += n_paths[m];
+        if (weights) w[(size_t)m] = weights[m];
+    }
+    for (int p = 0; p < po; ++p)
+        if (path_class[p] >= n_classes) return fail(e, AVT_E_INVALID, "avt_predict: path %d predicts class code %d >= n_classes", p, path_class[p]);
+    if (int rc = upload(e, e->d_pmask, masks, (size_t)mo)) return rc;
+    if (int rc = upload(e, e->d_pmoff, mask_off.data(), mask_off.size())) return rc;
+    if (int rc = upload(e, e->d_pint, n_paths, (size_t)n_models)) return rc;
+    if (int rc = upload(e, e->d_ppoff, path_off.data(), path_off.size())) return rc;
+    if (int rc = upload(e, e->d_pcls, path_class, (size_t)po)) return rc;
+    if (int rc = upload(e, e->d_pw, w.data(), w.size())) return rc;
+    if (int rc = upload(e, e->d_order, class_rank, (size_t)n_classes)) return rc;
+    CUDA_TRY(e, e->d_pout.ensure((size_t)e->N));
+    PredictArgs pa{};
+    pa.cols = (const void* const*)e->d_colptrs.p;
+    pa.wide = e->d_wide.p;
+    pa.bin_off = e->d_bin_off.p;
+    pa.masks = e->d_pmask.p;
+    pa.mask_off = e->d_pmoff.p;
+    pa.n_paths = e->d_pint.p;
+    pa.path_off = e->d_ppoff.p;
+    pa.path_class = e->d_pcls.p;
+    pa.weights = e->d_pw.p;
+    pa.class_rank = e->d_order.p;
+    pa.out = e->d_pout.p;
+    pa.N = e->N;
+    pa.A = e->A;
+    pa.M = n_models;
+    pa.n_classes = n_classes;
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.eval_ms, &ts)) return rc;
+    const long long blocks = std::min<long long>((e->N + 255) / 256, (long long)e->sm_count * 8);
+    predict_kernel<<<(unsigned)blocks, 256, 0, e->stream>>>(pa);
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = timer_close(e, ts)) return rc;
+    e->stats.eval_launches += 1;
+    CUDA_TRY(e, cudaMemcpyAsync(pred_out, e->d_pout.p, (size_t)e->N, cudaMemcpyDeviceToHost, e->stream));
     return sync_and_resolve(e);
 }
 

@@ -578,3 +578,5 @@ __global__ void __launch_bounds__(256) repartition_kernel(uint16_t* nid_all, con
 }
 
 }  // namespace avt
+
+#include "avt_predict.cuh"

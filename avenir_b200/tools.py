@@ -46,6 +46,10 @@ class ClassPartitionGenerator(_Tool):
     java_class = "org.avenir.explore.ClassPartitionGenerator"
 
 
+class ModelPredictor(_Tool):
+    java_class = "org.avenir.model.ModelPredictor"
+
+
 def main(argv: List[str] | None = None) -> int:
     argv = list(sys.argv[1:] if argv is None else argv)
     if not argv:

@@ -200,6 +200,20 @@ int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const ui
 int avt_cpg_sweep(avt_engine* e, int32_t node, int32_t criterion, const uint8_t* class_order,
                   avt_cpg_stat* out);
 
+/* Batch prediction with decision-path models on the loaded columns.  Replaces ModelPredictor.PredictorMapper.map
+ * -> DecisionTreeModel.predictClassProb (tree/DecisionTreeModel.java:56-93: the first decision path, in list
+ * order, whose predicates all hold) and, for n_models > 1, EnsemblePredictiveModel.predict
+ * (model/EnsemblePredictiveModel.java:69-110: weighted vote, ties in the vote map's iteration order).
+ * The host encodes each model as admission masks: masks of model m are total_bins x ceil(n_paths[m]/32) uint32
+ * words, word w of (attribute a, bin b) at ((bin_off[a] + b) * words_m + w), bit p set when path 32*w+p admits
+ * that bin; the models' blocks are concatenated in `masks`.  path_class holds, for every path of every model
+ * (concatenated), the class code the path predicts (after cost-based thresholding, if any).  weights NULL = 1.0
+ * each.  class_rank[c] = position of class c in the vote map's iteration order.  pred_out[r] = class code, or
+ * 0xFF when some model has no matching path for row r (the reference dies with a NullPointerException). */
+int avt_predict(avt_engine* e, int32_t n_models, const int32_t* n_paths, const uint32_t* masks,
+                const uint8_t* path_class, const double* weights, int32_t n_classes,
+                const uint8_t* class_rank, uint8_t* pred_out);
+
 /* Copies back tree t's node ids (uint16[n_rows]). */
 int avt_forest_node_ids(avt_engine* e, int32_t tree, uint16_t* out);
 /* Copies back the class counts of every frontier node of the last histogram ([nodes][n_classes]). */

@@ -429,3 +429,53 @@ int ora_cpg(const uint32_t* H, int node, int A, const int32_t* n_bins, int C, in
     free(bin_off);
     return 0;
 }
+
+/* Batch prediction on admission masks (tree/DecisionTreeModel.java:56-93: first decision path, in list order,
+ * whose predicates all hold; model/EnsemblePredictiveModel.java:69-110: weighted vote, stable sort by count).
+ * Deliberately the slow way round: path by path, attribute by attribute. */
+int ora_predict(int64_t n_rows, int A, const int32_t* n_bins, const void* const* cols, int M, const int32_t* n_paths,
+                const uint32_t* masks, const uint8_t* path_class, const double* weights, int n_classes,
+                const uint8_t* class_rank, uint8_t* out) {
+    int32_t* bin_off = (int32_t*)malloc(sizeof(int32_t) * (size_t)(A + 1));
+    int a, m, p, c;
+    int64_t r;
+    bin_off[0] = 0;
+    for (a = 0; a < A; ++a) bin_off[a + 1] = bin_off[a] + n_bins[a];
+    for (r = 0; r < n_rows; ++r) {
+        double votes[ORA_MAX_C];
+        int voted[ORA_MAX_C], unmatched = 0, last = 0, path_base = 0;
+        const uint32_t* mk = masks;
+        for (c = 0; c < n_classes; ++c) { votes[c] = 0.0; voted[c] = 0; }
+        for (m = 0; m < M; ++m) {
+            const int P = n_paths[m], W = (P + 31) / 32;
+            int found = -1;
+            for (p = 0; p < P && found < 0; ++p) {
+                int ok = 1;
+                for (a = 0; a < A && ok; ++a) {
+                    const uint32_t code = n_bins[a] > 256 ? ((const uint16_t*)cols[a])[r] : ((const uint8_t*)cols[a])[r];
+                    ok = (mk[(size_t)(bin_off[a] + code) * W + (p >> 5)] >> (p & 31)) & 1u;
+                }
+                if (ok) found = p;
+            }
+            if (found < 0) { unmatched = 1; break; }
+            c = path_class[path_base + found];
+            votes[c] += weights ? weights[m] : 1.0;
+            voted[c] = 1;
+            last = c;
+            mk += (size_t)bin_off[A] * W;
+            path_base += P;
+        }
+        if (unmatched) { out[r] = 0xFF; continue; }
+        if (M == 1) { out[r] = (uint8_t)last; continue; }
+        {
+            int best = -1;
+            for (c = 0; c < n_classes; ++c) {
+                if (!voted[c]) continue;
+                if (best < 0 || votes[c] > votes[best] || (votes[c] == votes[best] && class_rank[c] < class_rank[best])) best = c;
+            }
+            out[r] = (uint8_t)best;
+        }
+    }
+    free(bin_off);
+    return 0;
+}

@@ -22,6 +22,8 @@ int ora_eval(const uint32_t*, int, const int32_t*, int, const ora_split*, const 
              int, int, const int32_t*, const int32_t*, avt_split_eval*);
 int ora_repartition(int64_t, const int32_t*, const void* const*, int, uint16_t* const*, const int32_t*, const int32_t*,
                     const uint16_t*, int);
+int ora_predict(int64_t, int, const int32_t*, const void* const*, int, const int32_t*, const uint32_t*, const uint8_t*, const double*, int,
+                const uint8_t*, uint8_t*);
 int ora_cpg(const uint32_t*, int, int, const int32_t*, int, int, const ora_split*, const int32_t*, const uint8_t*,
             const uint8_t*, int, avt_cpg_stat*);
 }
@@ -114,6 +116,10 @@ int avt_cpg_sweep(avt_engine* e, int32_t node, int32_t crit, const uint8_t* orde
     auto o = order_or_identity(e, order);
     return ora_cpg(e->H.data(), node, e->A, e->n_bins.data(), e->C, (int)e->splits.size(), (const ora_split*)e->splits.data(), e->bounds.data(),
                    e->lut.data(), o.data(), crit, out);
+}
+int avt_predict(avt_engine* e, int32_t M, const int32_t* n_paths, const uint32_t* masks, const uint8_t* path_class, const double* weights,
+                int32_t n_classes, const uint8_t* class_rank, uint8_t* out) {
+    return ora_predict(e->N, e->A, e->n_bins.data(), e->cols.data(), M, n_paths, masks, path_class, weights, n_classes, class_rank, out);
 }
 int avt_forest_node_ids(avt_engine* e, int32_t t, uint16_t* out) { memcpy(out, e->nid[t].data(), e->N * 2); return 0; }
 int avt_level_class_counts(avt_engine* e, uint32_t* out) {
