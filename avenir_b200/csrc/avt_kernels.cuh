@@ -190,15 +190,11 @@ __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a,
 // private copy of H[t][*][bins of group g][*] kept in shared memory, replicated 2^rlog times (copy =
 // lane mod replicas) so that lanes of a warp that hit the same counter land in different banks; the
 // block then folds the copies and adds them to global H.
+// Work of one block: tree t, row chunk `chunk` of `n_chunks`, attribute group g (of n_groups).  `sh` is the
+// block's dynamic shared memory, its first a.zero_words words already cleared.
 template <bool HAS_W, bool WIDE, bool REPART>
-__global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs a) {
-    extern __shared__ uint32_t sh[];
-    pdl_launch_dependents();
-    // clear the block's histogram copies (sized by the host's bound) while the previous launch may still run
-    for (int i = threadIdx.x; i < a.zero_words; i += blockDim.x) sh[i] = 0;
-    pdl_wait();   // node_base, the repartition tables and the node ids come from the previous launches
-    __syncthreads();  // the cleared region may extend past this frontier's counters into where the tables are staged below
-    const int t = blockIdx.x, g = blockIdx.z;
+__device__ __forceinline__ void hist_block(const HistArgs& a, uint32_t* sh, int t, int chunk, int n_chunks, int g, int n_groups,
+                                           uint32_t total_blocks) {
     const int nb = a.node_base[t], n_nodes = a.node_base[t + 1] - nb;
     const int GB = a.grp_bins[g], rlog = a.grp_rlog[g];
     const int keys = n_nodes * GB * a.C;
@@ -235,8 +231,8 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
     const int e0 = a.grp_start[g], ne = a.grp_start[g + 1] - e0;
     const int prev_nb = REPART ? a.prev_node_base[t] : 0;
     const int lane = threadIdx.x & 31;
-    const long long stride = (long long)gridDim.y * blockDim.x * kRowsPerThread;
-    for (long long base = ((long long)blockIdx.y * blockDim.x + threadIdx.x) * kRowsPerThread; base < a.N; base += stride) {
+    const long long stride = (long long)n_chunks * blockDim.x * kRowsPerThread;
+    for (long long base = ((long long)chunk * blockDim.x + threadIdx.x) * kRowsPerThread; base < a.N; base += stride) {
         if (tree_has_w) hist_rows16<true, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes, rp);
         else hist_rows16<false, WIDE, REPART>(sh_base, a, e0, ne, base, nid, nid_out, wt, node_stride, cs4, rlog, rep, prev_nb, (uint32_t)n_nodes, rp);
     }
@@ -265,7 +261,7 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
         __threadfence();
         __syncthreads();
         if (threadIdx.x == 0) {
-            const uint32_t total = gridDim.x * gridDim.y * gridDim.z;
+            const uint32_t total = total_blocks;
             s_last = atomicAdd(a.signal_ticket, 1u) == total - 1;
             if (s_last) *a.signal_ticket = 0;
         }
@@ -276,6 +272,19 @@ __global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs 
             st_release_sys(a.signal_flags[threadIdx.x], a.signal_epoch);
         }
     }
+}
+
+// Shared-memory privatised histogram, optionally with the previous level's repartition folded in.
+// grid = (T, chunks, G); see hist_block.
+template <bool HAS_W, bool WIDE, bool REPART>
+__global__ void __launch_bounds__(kHistThreads) hist_smem_kernel(const HistArgs a) {
+    extern __shared__ uint32_t sh[];
+    pdl_launch_dependents();
+    // clear the block's histogram copies (sized by the host's bound) while the previous launch may still run
+    for (int i = threadIdx.x; i < a.zero_words; i += blockDim.x) sh[i] = 0;
+    pdl_wait();   // node_base, the repartition tables and the node ids come from the previous launches
+    __syncthreads();  // the cleared region may extend past this frontier's counters into where the tables are staged below
+    hist_block<HAS_W, WIDE, REPART>(a, sh, blockIdx.x, blockIdx.y, gridDim.y, blockIdx.z, gridDim.z, gridDim.x * gridDim.y * gridDim.z);
 }
 
 // Fallback for frontiers whose per-tree histogram does not fit in shared memory: warp-aggregated
@@ -580,3 +589,4 @@ __global__ void __launch_bounds__(256) repartition_kernel(uint16_t* nid_all, con
 }  // namespace avt
 
 #include "avt_predict.cuh"
+#include "avt_persistent.cuh"

@@ -186,10 +186,10 @@ __device__ void plan_level(const PlanArgs& p, const SplitTable& st, int* warp_to
 // the block reduces to (min av, lowest split index, number of ties).  Meanwhile the last warp computes
 // the node's own class counts and impurity; afterwards warp 0 computes the children of the best split,
 // one lane per segment.
-__global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, SplitTable st, const uint32_t* cand_mask,
-                                                            const uint8_t* order_g, int criterion, double* av_buf,
-                                                            avt_node_best* out, avt_split_eval* best_eval,
-                                                            const int32_t* n_nodes_dev, PlanArgs plan) {
+// The scan of ONE node by one block of kScanThreads threads (see scan_kernel).
+__device__ __forceinline__ void scan_node(const uint32_t* H, const SplitTable& st, const uint32_t* cand_mask, const uint8_t* order_g,
+                                          int criterion, double* av_buf, avt_node_best* out, avt_split_eval* best_eval, int node,
+                                          const PlanArgs& plan) {
     __shared__ uint32_t Pbuf[kScanWarps][kScanWordsPerWarp];
     __shared__ ScanBest wbest[kScanWarps];
     __shared__ uint8_t order[kMaxC];
@@ -197,16 +197,9 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, S
     __shared__ double s_node_stat;
     __shared__ uint32_t s_pop;
     __shared__ avt_split_eval s_ev;
-    __shared__ int s_warp_tot[kScanWarps];
-    __shared__ int s_running;
-    __shared__ int s_is_last;
-    pdl_launch_dependents();
-    pdl_wait();   // the histogram (and the frontier size) come from the previous launch
-    const int node = blockIdx.x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int C = st.C;
-    const bool active = !(n_nodes_dev && node >= *n_nodes_dev);
-    if (active) {
+    {
         if (threadIdx.x < C) order[threadIdx.x] = order_g[threadIdx.x];
         __syncthreads();
         if (plan.peer_H) {
@@ -368,6 +361,19 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, S
             }
         }
     }
+}
+
+__global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, SplitTable st, const uint32_t* cand_mask,
+                                                            const uint8_t* order_g, int criterion, double* av_buf,
+                                                            avt_node_best* out, avt_split_eval* best_eval,
+                                                            const int32_t* n_nodes_dev, PlanArgs plan) {
+    __shared__ int s_warp_tot[kScanWarps];
+    __shared__ int s_running;
+    __shared__ int s_is_last;
+    pdl_launch_dependents();
+    pdl_wait();   // the histogram (and the frontier size) come from the previous launch
+    const int node = blockIdx.x;
+    if (!(n_nodes_dev && node >= *n_nodes_dev)) scan_node(H, st, cand_mask, order_g, criterion, av_buf, out, best_eval, node, plan);
     if (plan.ticket == nullptr) return;
     // ---- last block to finish plans the next level
     __threadfence();  // every thread publishes its results before the block takes its ticket

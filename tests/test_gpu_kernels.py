@@ -206,12 +206,13 @@ def test_api_misuse_is_reported():
         g.set_splits(t)                                  # bound outside the attribute's bins
 
 
-@pytest.mark.parametrize("host_loop", [0, 1, 2])
+@pytest.mark.parametrize("host_loop", [0, 1, 2, 3], ids=["persistent", "host-driven", "device-sync", "device-async"])
 @pytest.mark.parametrize("criterion", [CRIT_GINI, CRIT_ENTROPY])
 def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
     """avt_grow_levels (device-driven: fused repartition+histogram, scan, on-device planning; and its
     host-driven twin) against the oracle's level loop: every record and every final node id."""
-    monkeypatch.setenv("AVT_GROW_HOST", str(host_loop))
+    monkeypatch.setenv("AVT_GROW_HOST", str(host_loop if host_loop < 3 else 0))
+    monkeypatch.setenv("AVT_PERSISTENT", "0" if host_loop == 3 else "1")
     n = 150001
     rng = np.random.default_rng(12)
     cols, cls, n_bins, _ = synth.call_hangup_encoded(n)
