@@ -119,8 +119,11 @@ struct avt_engine {
     avt_stats stats{};
     int force_variant = -1;
     bool skip_h_memset = false;
-    bool persistent = true;   // AVT_PERSISTENT=0: stream-ordered level loop only
+    bool persistent = false;  // AVT_PERSISTENT=1: whole level loop in one cooperative kernel.  Measured slower than the stream-ordered
+                              // loop with programmatic dependent launch (0.62 vs 0.52 ms on C2): the per-level cost is the phases'
+                              // own dependency chains, not launches, and the cooperative grid runs at 2 blocks/SM.  Kept for round 2.
     DevBuf<unsigned char> d_levels;
+    DevBuf<unsigned long long> d_phase;
     bool pdl = true;          // AVT_PDL=0: plain stream launches in the level loop
     bool pdl_chain = false;   // the launch being issued directly follows a kernel of the level loop (no memset/copy between)
     bool profiling = true;  // CUDA-event timing of every launch (avt_set_profiling)
@@ -1518,6 +1521,11 @@ static int grow_persistent_loop(avt_engine* e, int32_t n_levels, int32_t criteri
     pg.T = T;
     pg.N = e->N;
     pg.Npad = e->Npad;
+    const bool stamps = getenv("AVT_PHASE_NS") != nullptr;
+    if (stamps) {
+        CUDA_TRY(e, e->d_phase.ensure((size_t)n_levels * 3 + 2));
+        pg.phase_ns = e->d_phase.p;
+    }
     void* kargs[] = {(void*)&pg};
     CUDA_TRY(e, cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)n_blocks), dim3(kScanThreads), kargs, smem_max, e->stream));
     e->stats.hist_launches += n_levels;
@@ -1543,6 +1551,15 @@ static int grow_persistent_loop(avt_engine* e, int32_t n_levels, int32_t criteri
         CUDA_TRY(e, cudaMemcpyAsync(all.data(), e->d_records.p, rec_total * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
     }
     if (int rc = sync_and_resolve(e)) return rc;
+    if (stamps) {   // developer timing: phase durations of every level
+        std::vector<unsigned long long> ns((size_t)n_levels * 3 + 2);
+        CUDA_TRY(e, cudaMemcpy(ns.data(), e->d_phase.p, ns.size() * 8, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "[avt] persistent loop, grid %d x %d threads, %zu B dynamic smem\n", n_blocks, kScanThreads, smem_max);
+        for (int level = 0; level < n_levels; ++level)
+            fprintf(stderr, "[avt]   level %d: hist %.1f us, scan %.1f us, plan+clear %.1f us\n", level, (ns[1 + level * 3] - ns[level * 3]) * 1e-3,
+                    (ns[2 + level * 3] - ns[1 + level * 3]) * 1e-3, (ns[3 + level * 3] - ns[2 + level * 3]) * 1e-3);
+        fprintf(stderr, "[avt]   final repartition %.1f us, total %.1f us\n", (ns[1 + n_levels * 3] - ns[n_levels * 3]) * 1e-3, (ns[1 + n_levels * 3] - ns[0]) * 1e-3);
+    }
     if (err) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
     for (int t = 0; t < T; ++t) nodes_per_tree[t] = nb_all_host[(size_t)n_levels * (T + 1) + t + 1] - nb_all_host[(size_t)n_levels * (T + 1) + t];
     int64_t nrec = 0;

@@ -39,6 +39,7 @@ struct PersistArgs {
     const uint16_t* child_lut;
     int lut_w, T;
     long long N, Npad;
+    unsigned long long* phase_ns;   // optional [n_levels*3 + 2] %globaltimer stamps written by block 0 (developer timing)
 };
 
 // rows [base, base+8) of tree t: nid <- child_lut[node][code of the node's split attribute]
@@ -71,6 +72,14 @@ __global__ void __launch_bounds__(kScanThreads) grow_persistent_kernel(const Per
     __shared__ int s_warp_tot[kScanWarps];
     __shared__ int s_running;
     cg::grid_group grid = cg::this_grid();
+    auto stamp = [&](int slot) {
+        if (g.phase_ns && blockIdx.x == 0 && threadIdx.x == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+            g.phase_ns[slot] = t;
+        }
+    };
+    stamp(0);
     for (int level = 0; level < g.n_levels; ++level) {
         __syncthreads();
         {   // this level's parameters, once per block
@@ -91,6 +100,7 @@ __global__ void __launch_bounds__(kScanThreads) grow_persistent_kernel(const Per
         }
         __threadfence();
         grid.sync();
+        stamp(1 + level * 3);
         // ---- (b) scan: one node per block at a time
         const int NF = *lp.n_nodes_dev;
         for (int node = blockIdx.x; node < NF; node += gridDim.x) {
@@ -99,12 +109,14 @@ __global__ void __launch_bounds__(kScanThreads) grow_persistent_kernel(const Per
         }
         __threadfence();
         grid.sync();
+        stamp(2 + level * 3);
         // ---- planning of the next level (one block) + clearing of its histogram region (everyone)
         if (blockIdx.x == 0) plan_level(lp.pa, g.st, s_warp_tot, &s_running);
         for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < lp.zero_next_words; i += (long long)gridDim.x * blockDim.x)
             lp.zero_next_ptr[i] = 0;
         __threadfence();
         grid.sync();
+        stamp(3 + level * 3);
     }
     // ---- final repartition
     for (int t = 0; t < g.T; ++t) {
@@ -113,6 +125,8 @@ __global__ void __launch_bounds__(kScanThreads) grow_persistent_kernel(const Per
         for (long long base = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8; base < g.N; base += (long long)gridDim.x * blockDim.x * 8)
             repartition_rows8(nid, g.cols, g.wide, nb, g.node_attr, g.child_lut, g.lut_w, base, g.N);
     }
+    grid.sync();
+    stamp(1 + g.n_levels * 3);
 }
 
 }  // namespace avt

@@ -219,6 +219,8 @@ def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
     table = binary_split_table(n_bins, [True, True, True, False])
     weights = [None, rng.poisson(1.0, n).clip(0, 255).astype(np.uint8), None]
     g, o = make_pair(cols, cls, n_bins, 2, table, 3, weights, None)
+    if host_loop == 0:
+        g.set_profiling(False)     # the persistent kernel has no per-launch timing; with it on the library uses the stream-ordered loop
     (rec, nrec), frontier = g.grow(7, criterion, [1, 1, 1], max_records=4096)
     ho, fo = grow_levels(o, table, 7, criterion, n_trees=3)
     want = [(lvl, t, nd, s, pops, av, ties) for lvl, level in enumerate(ho) for (t, nd, s, pops, av, ties) in level]

@@ -9,4 +9,5 @@ eng = Engine(0)
 eng.load_dataset(cols, cls, n_bins, 2)
 eng.set_splits(binary_split_table(n_bins, [True, True, True, False]))
 eng.forest_init(1)
+eng.set_profiling(False)
 print(eng.grow(8, CRIT_ENTROPY, [1])[1])
