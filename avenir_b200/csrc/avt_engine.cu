@@ -89,6 +89,11 @@ struct avt_engine {
     DevBuf<avt_split> d_splits;
     DevBuf<int32_t> d_bounds, d_attr_first;
     DevBuf<uint8_t> d_seg_lut;
+    // item-parallel scan (avt_scan_fast.cuh): (split, segment) items, first item of every split, per-node child counts
+    DevBuf<uint32_t> d_items;
+    DevBuf<int32_t> d_seg_first, d_nkids;
+    int n_items = 0;
+    bool fast_scan_ok = false;   // the split table is small enough for scan_fast_kernel
     // scan
     DevBuf<double> d_av;
     DevBuf<avt_node_best> d_best;
@@ -124,6 +129,7 @@ struct avt_engine {
                               // own dependency chains, not launches, and the cooperative grid runs at 2 blocks/SM.  Kept for round 2.
     DevBuf<unsigned char> d_levels;
     DevBuf<unsigned long long> d_phase;
+    bool scan_fast = true;    // AVT_SCAN_FAST=0: always the general scan kernel in the level loop
     bool pdl = true;          // AVT_PDL=0: plain stream launches in the level loop
     bool pdl_chain = false;   // the launch being issued directly follows a kernel of the level loop (no memset/copy between)
     bool profiling = true;  // CUDA-event timing of every launch (avt_set_profiling)
@@ -304,6 +310,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_GROW_HOST")) e->grow_host_loop = atoi(v);
     if (const char* v = getenv("AVT_PERSISTENT")) e->persistent = atoi(v) != 0;
     if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
+    if (const char* v = getenv("AVT_SCAN_FAST")) e->scan_fast = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
     *out = e;
@@ -325,7 +332,7 @@ void avt_destroy(avt_engine* e) {
     e->d_nid.release(); e->d_levels.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_tile_ctr.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
-    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_av.release(); e->d_best.release();
+    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release();
     for (auto& s : e->pending) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
@@ -460,6 +467,24 @@ int avt_split_table_set(avt_engine* e, int32_t n_splits, const avt_split* splits
     if (int rc = upload(e, e->d_bounds, bounds, (size_t)std::max(n_bounds, 0))) return rc;
     if (int rc = upload(e, e->d_seg_lut, seg_lut, (size_t)std::max<int64_t>(n_lut, 0))) return rc;
     if (int rc = upload(e, e->d_attr_first, attr_first.data(), attr_first.size())) return rc;
+    {
+        // tables of the item-parallel scan, and whether this split table fits it (limits: avt_scan_fast.cuh)
+        std::vector<uint32_t> items;
+        std::vector<int32_t> seg_first((size_t)n_splits + 1, 0);
+        bool ok = e->A <= kScanWarps && n_splits >= 1 && n_splits <= kScanThreads;
+        for (int s = 0; s < n_splits; ++s) {
+            seg_first[(size_t)s] = (int32_t)items.size();
+            for (int j = 0; j < splits[s].n_seg; ++j) items.push_back(((uint32_t)s << 4) | (uint32_t)j);
+            const int B = e->n_bins[splits[s].attr];
+            ok = ok && (long long)B * e->C <= kFastWordsPerAttr && (splits[s].kind == AVT_SPLIT_NUMERIC || B <= 64);
+        }
+        seg_first[(size_t)n_splits] = (int32_t)items.size();
+        ok = ok && items.size() <= (size_t)kFastItems && items.size() * (size_t)e->C <= (size_t)kFastCntWords;
+        e->n_items = (int)items.size();
+        e->fast_scan_ok = ok;
+        if (int rc = upload(e, e->d_items, items.data(), items.size())) return rc;
+        if (int rc = upload(e, e->d_seg_first, seg_first.data(), seg_first.size())) return rc;
+    }
     e->scan_valid = false;
     return sync_and_resolve(e);
 }
@@ -1084,6 +1109,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     CUDA_TRY(e, cudaMemcpyAsync(nb_level(0), nb_host.data(), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
     const bool peer_on = e->peer.active && e->peer.n > 1;
     const bool subtract = e->subtract;
+    const bool fast_scan = e->scan_fast && e->fast_scan_ok && !subtract;   // latency-optimised scan + planning (avt_scan_fast.cuh)
     // complete counts of a level: single GPU = the (ping-pong) histogram buffer itself; peer mode = the local sums
     auto H_level = [&](int level) { return (level & 1) ? e->d_H2.p : e->d_H.p; };
     auto hsum_level = [&](int level) { return (level & 1) ? e->d_hsum2.p : e->d_hsum.p; };
@@ -1128,7 +1154,8 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         if (e->d_av.cap < (size_t)NF * e->S || e->d_best.cap < (size_t)NF || e->d_best_eval.cap < (size_t)NF || e->d_node_attr.cap < (size_t)NF ||
             e->d_lut.cap < (size_t)NF * lut_w || (!peer_level && (e->d_H.cap < (size_t)NF * e->TB * e->C || e->d_H2.cap < (size_t)NF * e->TB * e->C)) ||
             (peer_level && (e->d_hsum.cap < (size_t)NF * e->TB * e->C || e->d_hsum2.cap < (size_t)NF * e->TB * e->C)) ||
-            (subtract && (e->d_skip.cap < (size_t)NF * g_max || e->d_drv_parent.cap < (size_t)NF * g_max || e->d_kids.cap < (size_t)NF * kMaxSeg)) || (want_records && e->d_records.cap < rec_off + (size_t)NF)) {
+            (subtract && (e->d_skip.cap < (size_t)NF * g_max || e->d_drv_parent.cap < (size_t)NF * g_max || e->d_kids.cap < (size_t)NF * kMaxSeg)) || (want_records && e->d_records.cap < rec_off + (size_t)NF) ||
+            (fast_scan && e->d_nkids.cap < (size_t)NF)) {
             if (int rc = sync_and_resolve(e)) return rc;
             // flush records gathered so far: the record buffer may move
             if (want_records && rec_off) {
@@ -1155,6 +1182,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             CUDA_TRY(e, e->d_best_eval.ensure(grow));
             CUDA_TRY(e, e->d_node_attr.ensure(grow));
             CUDA_TRY(e, e->d_lut.ensure(grow * lut_w));
+            if (fast_scan) CUDA_TRY(e, e->d_nkids.ensure(grow));
             // (a reallocation here drops the previous level's complete counts: no derivation on this level)
             const bool had_prev = level > 0;
             if (!peer_level) {
@@ -1289,6 +1317,11 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             // directly behind the histogram kernel unless an NCCL all-reduce or a signalling launch sits between
             const bool chain = e->pdl && !e->profiling && e->stats.last_hist_variant == 0 && (peer_level ? e->signal_in_hist : e->comm == nullptr);
             cfg.numAttrs = chain ? 1 : 0;
+            if (fast_scan) {
+                FastTable ft{e->d_items.p, e->d_seg_first.p, e->d_nkids.p, e->n_items};
+                CUDA_TRY(e, cudaLaunchKernelEx(&cfg, scan_fast_kernel, (const uint32_t*)Hc, make_table(e), ft, (const uint8_t*)e->d_order.p, (int)criterion,
+                                               (const int32_t*)(nb_level(level) + T), pa));
+            } else
             CUDA_TRY(e, cudaLaunchKernelEx(&cfg, scan_kernel, (const uint32_t*)Hc, make_table(e), (const uint32_t*)nullptr, (const uint8_t*)e->d_order.p,
                                            (int)criterion, e->d_av.p, e->d_best.p, e->d_best_eval.p, (const int32_t*)(nb_level(level) + T), pa));
         }

@@ -146,10 +146,15 @@ __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a,
     for (int j = 0; j < kRowsPerThread; ++j) {
         uint32_t node = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
         const bool dead = node == AVT_NODE_NONE || (HAS_W && u4_byte(vw, j) == 0);
-        node = dead ? phantom : node;
-        if (rp.skip) node = rp.skip[node] ? phantom : node;
-        rowkey[j] = sh_base + (node * node_stride + (u4_byte(vc, j) << rlog) + rep) * 4u;
+        rowkey[j] = dead ? phantom : node;
     }
+    if (rp.skip) {   // sibling subtraction: rows of derived nodes are not counted (tested once per 16 rows, not per row)
+#pragma unroll
+        for (int j = 0; j < kRowsPerThread; ++j) rowkey[j] = rp.skip[rowkey[j]] ? phantom : rowkey[j];
+    }
+#pragma unroll
+    for (int j = 0; j < kRowsPerThread; ++j)
+        rowkey[j] = sh_base + (rowkey[j] * node_stride + (u4_byte(vc, j) << rlog) + rep) * 4u;
     if (!WIDE) {
         for (int c0 = 0; c0 < ne; c0 += 4) {
             const int nq = ne - c0 < 4 ? ne - c0 : 4;
@@ -242,6 +247,16 @@ __device__ __forceinline__ void hist_block(const HistArgs& a, uint32_t* sh, int 
     const int R = 1 << rlog;
     const int GBC = GB * a.C;
     const int warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    if (n_groups == 1) {
+        // one group holds every attribute: local and global bin indices coincide, so the block's counters map onto
+        // H[nb..nb+n_nodes) word for word -- a flat loop without the per-node bookkeeping below
+        uint32_t* Hb = a.H + (long long)nb * a.TB * a.C;
+        for (int k = threadIdx.x; k < keys; k += blockDim.x) {
+            uint32_t sum = 0;
+            for (int r = 0; r < R; ++r) sum += sh[(k << rlog) + ((r + lane) & (R - 1))];
+            if (sum) atomicAdd(Hb + k, sum);
+        }
+    } else
     for (int node = warp; node < n_nodes; node += n_warps) {
         uint32_t* Hn = a.H + (long long)(nb + node) * a.TB * a.C;
         int lb = lane / a.C, c = lane - lb * a.C;       // (bin, class) of slot kk = lane; advanced without divisions
@@ -588,5 +603,6 @@ __global__ void __launch_bounds__(256) repartition_kernel(uint16_t* nid_all, con
 
 }  // namespace avt
 
+#include "avt_scan_fast.cuh"
 #include "avt_predict.cuh"
 #include "avt_persistent.cuh"

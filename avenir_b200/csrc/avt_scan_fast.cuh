@@ -1,0 +1,334 @@
+// Kernel (b), latency-optimised form for small split tables (the level loop of narrow schemas such as
+// call_hangup.json is bound by the serial dependency chain of this kernel, not by its throughput):
+//   * everything that depends only on the split table -- the thread's (split, segment) item, its bounds or
+//     bin mask, the class order -- is loaded BEFORE the kernel waits for the histogram pass (programmatic
+//     dependent launch), so it costs nothing on the critical path;
+//   * one thread per (split, segment) evaluates that segment's impurity, instead of one thread per split
+//     walking its segments one after the other; one thread per split then combines the segments in order
+//     with exactly the operations of split_av, so the results are bit-identical;
+//   * the children of the best split are read back from those per-segment results instead of being recomputed;
+//   * the part of the level planning that concerns one node only (split attribute, number of children, the
+//     bin -> child row with child ranks LOCAL to the node, the node's record) is done by the node's own block;
+//     the block that finishes last only turns the local ranks into frontier ids with a prefix sum.
+// Same inputs and outputs as scan_kernel + plan_level (node_attr, child_lut, next_count, next_node_base,
+// records); av / best / best_eval are not produced (nothing in the level loop reads them).
+// Included by avt_kernels.cuh after avt_scan.cuh.
+#pragma once
+
+namespace avt {
+
+constexpr int kFastItems = kScanThreads;   // (split, segment) pairs: one per thread
+constexpr int kFastCntWords = 2048;        // class counts of all items
+
+// Extra device tables of the split table, built by avt_split_table_set.
+struct FastTable {
+    const uint32_t* items;     // [n_items] (split << 4) | segment, splits in table order, segments ascending
+    const int32_t* seg_first;  // [S+1] first item of every split
+    int32_t* nkids;            // [NF] children of every node of the current frontier (scratch between the blocks and the planner)
+    int n_items;
+};
+
+__device__ __forceinline__ uint16_t ldcg_u16(const uint16_t* p) { return __ldcg(p); }
+
+// The planning that is left for the last block: per tree, an exclusive prefix sum over the nodes' child counts
+// turns node-local child ranks into ids of the next frontier.
+__device__ void plan_level_fast(const PlanArgs& p, const int32_t* nkids, int* warp_tot, int* running, int* s_first) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int t = 0; t < p.n_trees; ++t) {
+        const int nb = p.node_base[t], n = p.node_base[t + 1] - nb;
+        if (threadIdx.x == 0) *running = 0;
+        __syncthreads();
+        for (int i0 = 0; i0 < n; i0 += blockDim.x) {
+            const int i = i0 + threadIdx.x;
+            const int nk = i < n ? ldcg_i32(nkids + nb + i) : 0;
+            int v = nk;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int u = __shfl_up_sync(0xffffffffu, v, d);
+                if (lane >= d) v += u;
+            }
+            if (lane == 31) warp_tot[warp] = v;
+            __syncthreads();
+            int woff = 0, tot = 0;
+            for (int w = 0; w < kScanWarps; ++w) {
+                if (w < warp) woff += warp_tot[w];
+                tot += warp_tot[w];
+            }
+            const int first = *running + woff + v - nk;
+            s_first[threadIdx.x] = first;
+            if (nk && first + nk > (int)AVT_NODE_NONE - 1) *p.err = 1;
+            __syncthreads();
+            const int cnt = min((int)blockDim.x, n - i0);
+            uint16_t* lut = p.child_lut + (long long)(nb + i0) * p.lut_w;
+            for (int e = threadIdx.x; e < cnt * p.lut_w; e += blockDim.x) {
+                const uint16_t c = ldcg_u16(lut + e);
+                if (c != (uint16_t)AVT_NODE_NONE) lut[e] = (uint16_t)(c + s_first[e / p.lut_w]);
+            }
+            if (p.records) {
+                for (int e = threadIdx.x; e < cnt * kMaxSeg; e += blockDim.x) {
+                    int32_t* c = &p.records[nb + i0 + e / kMaxSeg].child[e % kMaxSeg];
+                    const int32_t r = ldcg_i32(c);
+                    if (r >= 0) *c = r + s_first[e / kMaxSeg];
+                }
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) *running += tot;
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) p.next_count[t] = *running;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && p.next_node_base) {
+        int acc = 0;
+        for (int k = 0; k < p.n_trees; ++k) {
+            p.next_node_base[k] = acc;
+            acc += p.next_count[k];
+        }
+        p.next_node_base[p.n_trees] = acc;
+    }
+    if (p.zero_ptr)
+        for (long long i = threadIdx.x; i < p.zero_words; i += blockDim.x) p.zero_ptr[i] = 0;
+}
+
+constexpr int kFastWordsPerAttr = 512;     // prefix counts of one attribute ([bins][classes])
+
+// grid = frontier bound (blocks beyond the true frontier only take part in the last-block election),
+// block = kScanThreads.  Requires (checked by the host, see fast_scan_ok): A <= kScanWarps, S <= kScanThreads,
+// n_items <= kFastItems, n_items * C <= kFastCntWords, bins * C <= kFastWordsPerAttr for every attribute with
+// splits, <= 64 bins for attributes with segment-table splits.
+__global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t* H, SplitTable st, FastTable ft, const uint8_t* order_g,
+                                                                 int criterion, const int32_t* n_nodes_dev, PlanArgs plan) {
+    __shared__ uint32_t Pbuf[kScanWarps][kFastWordsPerAttr];
+    __shared__ double it_stat[kFastItems];
+    __shared__ uint32_t it_n[kFastItems];
+    __shared__ uint32_t it_cnt[kFastCntWords];
+    __shared__ avt_split s_splits[kScanThreads];
+    __shared__ int32_t s_seg_first[kScanThreads + 1];
+    __shared__ ScanBest wbest[kScanWarps];
+    __shared__ uint8_t order[kMaxC];
+    __shared__ uint32_t s_cnt[kMaxC];
+    __shared__ uint32_t s_pop;
+    __shared__ avt_grow_record s_rec;
+    __shared__ int s_warp_tot[kScanWarps];
+    __shared__ int s_running;
+    __shared__ int s_is_last;
+    __shared__ int s_first[kScanThreads];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int C = st.C;
+    pdl_launch_dependents();
+    // ---- before the wait: the thread's item and split, the class order, the warp's attribute
+    int my_attr = -1, my_kind = 0, my_lo = -1, my_hi = -1;
+    unsigned long long my_mask = 0;
+    if (tid < ft.n_items) {
+        const uint32_t it = ft.items[tid];
+        const avt_split sp = st.splits[it >> 4];
+        const int j = (int)(it & 15u);
+        const int B = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
+        my_attr = sp.attr;
+        my_kind = sp.kind;
+        if (sp.kind == AVT_SPLIT_NUMERIC) {
+            my_lo = (j == 0) ? -1 : st.bounds[sp.off + j - 1];
+            my_hi = (j == sp.n_seg - 1) ? B - 1 : st.bounds[sp.off + j];
+        } else {
+            const uint8_t* lut = st.seg_lut + sp.off;
+            for (int b = 0; b < B; ++b)
+                if (lut[b] == j) my_mask |= 1ull << b;
+        }
+    }
+    if (tid < st.S) s_splits[tid] = st.splits[tid];
+    if (tid <= st.S) s_seg_first[tid] = ft.seg_first[tid];
+    if (tid == kScanThreads - 1 && st.S == kScanThreads) s_seg_first[st.S] = ft.seg_first[st.S];
+    if (tid < C) order[tid] = order_g[tid];
+    int w_B = 0, w_off = 0;
+    bool w_has = false;
+    if (warp < st.A) {
+        w_off = st.bin_off[warp];
+        w_B = st.bin_off[warp + 1] - w_off;
+        w_has = st.attr_first[warp + 1] > st.attr_first[warp];
+    }
+    const int B0 = st.bin_off[1] - st.bin_off[0];
+    pdl_wait();   // the histogram (and the frontier) come from the previous launch
+    __syncthreads();
+    const int node = blockIdx.x;
+    if (node < *n_nodes_dev) {
+        if (plan.peer_H) {
+            // every rank's partial counts for this node, pulled over NVLink and summed (see scan_node)
+            if (tid < plan.n_ranks)
+                while ((int32_t)(ld_acquire_sys(plan.peer_flags + tid) - plan.peer_epoch) < 0) {}
+            __syncthreads();
+            const long long words = (long long)st.TB * C, off = (long long)node * words;
+            for (long long i = tid; i < words; i += blockDim.x) {
+                uint32_t sum = 0;
+                for (int r0 = 0; r0 < plan.n_ranks; r0 += 8) {   // 8 NVLink loads in flight per thread
+                    uint32_t v[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) v[k] = r0 + k < plan.n_ranks ? ld_relaxed_sys(plan.peer_H[r0 + k] + off + i) : 0u;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) sum += v[k];
+                }
+                plan.h_sum[off + i] = sum;
+            }
+            __syncthreads();
+        }
+        const uint32_t* Hnode = H + (long long)node * st.TB * C;
+        const double nan = __longlong_as_double(0x7ff8000000000000LL);
+        // ---- phase 1: warp a stages the prefix counts of attribute a; the last warp adds the node's row count
+        if (w_has) warp_prefix(Hnode + (long long)w_off * C, Pbuf[warp], w_B, C);
+        if (warp == kScanWarps - 1) {
+            if (lane < C) {
+                uint32_t s = 0;
+                for (int bb = 0; bb < B0; ++bb) s += Hnode[bb * C + lane];
+                s_cnt[lane] = s;
+            }
+            __syncwarp();
+            if (lane == 0) {
+                uint32_t n = 0;
+                for (int c = 0; c < C; ++c) n += s_cnt[c];
+                s_pop = n;
+            }
+        }
+        __syncthreads();
+        // ---- phase 2: one thread per (split, segment): class counts from the prefix table, impurity
+        if (tid < ft.n_items) {
+            const uint32_t* P = Pbuf[my_attr];
+            uint32_t* cnt = it_cnt + tid * C;
+            uint32_t n = 0;
+            if (my_kind == AVT_SPLIT_NUMERIC) {
+                const bool some = !(my_hi < 0 || my_hi <= my_lo);
+                for (int c = 0; c < C; ++c) {
+                    const uint32_t v = some ? P[my_hi * C + c] - (my_lo >= 0 ? P[my_lo * C + c] : 0u) : 0u;
+                    cnt[c] = v;
+                    n += v;
+                }
+            } else {
+                for (int c = 0; c < C; ++c) {
+                    uint32_t v = 0;
+                    for (unsigned long long m = my_mask; m; m &= m - 1) {
+                        const int b = __ffsll((long long)m) - 1;
+                        v += P[b * C + c] - (b ? P[(b - 1) * C + c] : 0u);
+                    }
+                    cnt[c] = v;
+                    n += v;
+                }
+            }
+            it_n[tid] = n;
+            it_stat[tid] = n ? impurity(cnt, C, order, criterion, n) : 0.0;
+        }
+        __syncthreads();
+        // ---- phase 3: one thread per split combines its segments in order (the operations of split_av)
+        ScanBest best{0.0, -1, 0};
+        if (tid < st.S) {
+            const int i0 = s_seg_first[tid], i1 = s_seg_first[tid + 1];
+            double weighted = 0.0;
+            uint32_t total = 0;
+            for (int i = i0; i < i1; ++i) {
+                const uint32_t n = it_n[i];
+                if (n) {
+                    weighted = __dadd_rn(weighted, __dmul_rn(it_stat[i], (double)n));
+                    total += n;
+                }
+            }
+            const double av = __ddiv_rn(weighted, (double)total);
+            if (av == av) best = ScanBest{av, tid, 1};   // NaN never wins
+        }
+#pragma unroll
+        for (int d = 16; d; d >>= 1) {
+            ScanBest o;
+            o.av = __shfl_xor_sync(0xffffffffu, best.av, d);
+            o.split = __shfl_xor_sync(0xffffffffu, best.split, d);
+            o.ties = __shfl_xor_sync(0xffffffffu, best.ties, d);
+            best_merge(best, o);
+        }
+        if (lane == 0) wbest[warp] = best;
+        __syncthreads();
+        // ---- phase 4 (warp 0): block arg-min, then this node's share of the level planning
+        if (warp == 0) {
+            ScanBest b = wbest[0];
+            for (int w = 1; w < kScanWarps; ++w) best_merge(b, wbest[w]);
+            const uint32_t n = s_pop;
+            const bool live = n > 0 && b.split >= 0;
+            avt_split sp{};
+            int i0 = 0;
+            if (live) {
+                sp = s_splits[b.split];
+                i0 = s_seg_first[b.split];
+            }
+            // children: segment `lane` of the best split; a child exists where the segment has rows; its rank
+            // among the node's children is the number of non-empty segments before it
+            const bool seg = live && lane < sp.n_seg;
+            const uint32_t pop = seg ? it_n[i0 + lane] : 0u;
+            const unsigned has_mask = __ballot_sync(0xffffffffu, pop != 0);
+            const int rank = __popc(has_mask & ((1u << lane) - 1u));
+            const int nk = __popc(has_mask);
+            // bin -> child row (local ranks)
+            const int Bs = live ? st.bin_off[sp.attr + 1] - st.bin_off[sp.attr] : 0;
+            uint16_t* lut = plan.child_lut + (long long)node * plan.lut_w;
+            for (int b0 = 0; b0 < plan.lut_w; b0 += 32) {
+                const int bin = b0 + lane;
+                int sg = -1;
+                if (bin < Bs) {
+                    if (sp.kind == AVT_SPLIT_NUMERIC) {
+                        sg = 0;
+                        while (sg < sp.n_seg - 1 && bin > st.bounds[sp.off + sg]) ++sg;
+                    } else {
+                        sg = st.seg_lut[sp.off + bin];
+                        if (sg >= sp.n_seg) sg = -1;
+                    }
+                }
+                const int src = sg < 0 ? 0 : sg;
+                const int r = __shfl_sync(0xffffffffu, rank, src);
+                const bool ok = sg >= 0 && ((has_mask >> src) & 1u);
+                if (bin < plan.lut_w) lut[bin] = ok ? (uint16_t)r : (uint16_t)AVT_NODE_NONE;
+            }
+            if (lane == 0) {
+                plan.node_attr[node] = live ? sp.attr : -1;
+                ft.nkids[node] = nk;
+            }
+            if (plan.records) {
+                // tree and tree-local index of this node
+                int t = 0;
+                for (int t0 = 0; t0 < plan.n_trees; t0 += 32) {
+                    const int tt = t0 + lane;
+                    const bool mine = tt < plan.n_trees && node >= plan.node_base[tt] && node < plan.node_base[tt + 1];
+                    const unsigned m = __ballot_sync(0xffffffffu, mine);
+                    if (m) { t = t0 + __ffs(m) - 1; break; }
+                }
+                for (int i = lane; i < (int)(sizeof(avt_grow_record) / 4); i += 32) reinterpret_cast<uint32_t*>(&s_rec)[i] = 0;
+                __syncwarp();
+                if (lane == 0) {
+                    s_rec.level = plan.level;
+                    s_rec.tree = t;
+                    s_rec.node = node - plan.node_base[t];
+                    s_rec.split = live ? b.split : -1;
+                    s_rec.n_ties = b.ties;
+                    s_rec.min_av = b.split >= 0 ? b.av : nan;
+                }
+                if (lane < kMaxSeg) {
+                    s_rec.child[lane] = pop ? rank : -1;
+                    s_rec.child_pop[lane] = (long long)pop;
+                    s_rec.child_stat[lane] = seg ? it_stat[i0 + lane] : 0.0;
+                }
+                __syncwarp();
+                const uint32_t* src = reinterpret_cast<const uint32_t*>(&s_rec);
+                uint32_t* dst = reinterpret_cast<uint32_t*>(&plan.records[node]);
+                for (int i = lane; i < (int)(sizeof(avt_grow_record) / 4); i += 32) dst[i] = src[i];
+            }
+        }
+    }
+    // ---- last block to finish turns the local child ranks into ids of the next frontier
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        const uint32_t done = atomicAdd(plan.ticket, 1u);
+        s_is_last = done == gridDim.x - 1;
+        if (s_is_last) {
+            *plan.ticket = 0;
+            __threadfence();
+        }
+    }
+    __syncthreads();
+    if (s_is_last) plan_level_fast(plan, ft.nkids, s_warp_tot, &s_running, s_first);
+}
+
+}  // namespace avt

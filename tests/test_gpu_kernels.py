@@ -206,13 +206,14 @@ def test_api_misuse_is_reported():
         g.set_splits(t)                                  # bound outside the attribute's bins
 
 
-@pytest.mark.parametrize("host_loop", [0, 1, 2, 3], ids=["persistent", "host-driven", "device-sync", "device-async"])
+@pytest.mark.parametrize("host_loop", [0, 1, 2, 3, 4], ids=["persistent", "host-driven", "device-sync", "device-async", "device-async-general-scan"])
 @pytest.mark.parametrize("criterion", [CRIT_GINI, CRIT_ENTROPY])
 def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
     """avt_grow_levels (device-driven: fused repartition+histogram, scan, on-device planning; and its
     host-driven twin) against the oracle's level loop: every record and every final node id."""
     monkeypatch.setenv("AVT_GROW_HOST", str(host_loop if host_loop < 3 else 0))
-    monkeypatch.setenv("AVT_PERSISTENT", "0" if host_loop == 3 else "1")
+    monkeypatch.setenv("AVT_PERSISTENT", "0" if host_loop >= 3 else "1")
+    monkeypatch.setenv("AVT_SCAN_FAST", "0" if host_loop == 4 else "1")   # 3: item-parallel scan (the table fits it), 4: general kernel
     n = 150001
     rng = np.random.default_rng(12)
     cols, cls, n_bins, _ = synth.call_hangup_encoded(n)
@@ -232,6 +233,59 @@ def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
         assert helpers.bits(r.min_av) == helpers.bits(av)
     for t in range(3):
         assert np.array_equal(g.node_ids(t), o.node_ids(t))
+
+
+def multi_segment_table():
+    """4 attributes; numeric splits with 2 and 3 segments, segment tables with 2, 3 and 4 segments (one of
+    them with a segment no bin maps to, one with bins outside every segment)."""
+    n_bins = [7, 5, 6, 3]
+    t = SplitTable()
+    for b in range(6):
+        t.add_numeric(0, [b])
+    for lo in range(5):
+        for hi in range(lo + 1, 6):
+            t.add_numeric(0, [lo, hi])
+    t.add_lut(1, [0, 1, 0, 1, 1])
+    t.add_lut(1, [0, 1, 2, 1, 0])
+    t.add_lut(1, [2, 1, 1, 2, 1], n_seg=3)        # segment 0 is empty by construction
+    t.add_lut(1, [0, 1, 2, 3, 3])
+    for b in range(5):
+        t.add_numeric(2, [b])
+    t.add_numeric(2, [0, 2, 4])
+    t.add_lut(3, [0, 1, 1])
+    t.add_lut(3, [0, 1, 2])
+    t.add_lut(3, [0, 1, 5], n_seg=2)              # bin 2 belongs to no segment: its rows leave the tree
+    return n_bins, t
+
+
+@pytest.mark.parametrize("criterion", [CRIT_GINI, CRIT_ENTROPY])
+def test_item_parallel_scan_equals_general_scan_and_oracle(criterion, monkeypatch):
+    """The latency-optimised scan + planning (avt_scan_fast.cuh) against the general kernels, field by field and
+    bit by bit, and both against the oracle's level loop; multi-segment splits, 3 classes, 2 trees, weights."""
+    n = 60013
+    n_bins, table = multi_segment_table()
+    cols, cls = synth.binned_dataset(n, n_bins, 3, seed=21)
+    rng = np.random.default_rng(5)
+    weights = [None, rng.poisson(1.0, n).clip(0, 255).astype(np.uint8)]
+    runs = {}
+    for fast in ("1", "0"):
+        monkeypatch.setenv("AVT_SCAN_FAST", fast)
+        g, o = make_pair(cols, cls, n_bins, 3, table, 2, weights, None)
+        (rec, nrec), frontier = g.grow(5, criterion, [1, 1], class_order=[1, 2, 0], max_records=8192)
+        runs[fast] = ([(r.level, r.tree, r.node, r.split, r.n_ties, list(r.child), list(r.child_pop),
+                        [helpers.bits(x) for x in r.child_stat], helpers.bits(r.min_av)) for r in rec[:nrec]],
+                      frontier, [g.node_ids(t).copy() for t in range(2)])
+    assert runs["1"][0] == runs["0"][0] and runs["1"][1] == runs["0"][1]
+    ho, fo = grow_levels(o, table, 5, criterion, n_trees=2, class_order=[1, 2, 0])
+    want = [(lvl, t, nd, s, pops, av, ties) for lvl, level in enumerate(ho) for (t, nd, s, pops, av, ties) in level]
+    got, frontier, nids = runs["1"]
+    assert frontier == fo and len(got) == len(want) and len(want) > 20
+    for r, (lvl, t, nd, s, pops, av, ties) in zip(got, want):
+        assert r[:5] == (lvl, t, nd, s, ties)
+        assert [p for p in r[6] if p] == pops and r[8] == helpers.bits(av)
+    assert any(sum(1 for p in r[6] if p) >= 3 for r in got)              # three-way expansions do occur
+    for t in range(2):
+        assert np.array_equal(nids[t], runs["0"][2][t]) and np.array_equal(nids[t], o.node_ids(t))
 
 
 def test_level_loop_with_wide_codes_and_many_attrs():
