@@ -51,11 +51,11 @@ __device__ __forceinline__ uint32_t u4_word(const uint4& v, int i) {
 }
 // j-th byte (0..15) of a 16-byte vector
 __device__ __forceinline__ uint32_t u4_byte(const uint4& v, int j) {
-    return (u4_word(v, j >> 2) >> ((j & 3) * 8)) & 0xFFu;
+    return __byte_perm(u4_word(v, j >> 2), 0u, 0x4440u | (uint32_t)(j & 3));   // one PRMT (j is a compile-time constant at every use)
 }
 // j-th halfword (0..7)
 __device__ __forceinline__ uint32_t u4_half(const uint4& v, int j) {
-    return (u4_word(v, j >> 1) >> ((j & 1) * 16)) & 0xFFFFu;
+    return __byte_perm(u4_word(v, j >> 1), 0u, (j & 1) ? 0x4432u : 0x4410u);
 }
 
 // Impurity of one class-count vector, evaluated exactly as InfoContentStat.processStat

@@ -134,7 +134,8 @@ struct avt_engine {
     bool pdl_chain = false;   // the launch being issued directly follows a kernel of the level loop (no memset/copy between)
     bool profiling = true;  // CUDA-event timing of every launch (avt_set_profiling)
     long long hist_target_addrs = 4096;  // AVT_HIST_TARGET_ADDRS
-    int hist_max_bpsm = 4;               // AVT_HIST_BPSM: resident histogram blocks per SM
+    int hist_max_bpsm = 2;               // AVT_HIST_BPSM: histogram blocks per SM.  2 x 512 threads x 64 registers fill the register file, so more
+                                         // blocks only queue behind them and add flushes (measured on C2: 0.383 ms/step with 2, 0.403 with 4, 0.52 with 1)
     int grow_host_loop = 0;              // AVT_GROW_HOST=1: host-driven level loop (3 round trips per level)
     // comm
     ncclComm_t comm = nullptr;
@@ -649,6 +650,8 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         ha.grp_start = base + o_gs; ha.grp_bins = base + o_gb; ha.grp_rlog = base + o_gr; ha.grp_l2g = base + o_l2g; ha.grp_l2g_off = base + o_lo;
         ha.codes_in_regs = (G == 1 && !any_wide && e->A <= 4) ? 1 : 0;
         ha.zero_words = (int)smem_words;
+        ha.packed_bins = 1;
+        for (int g = 0; g < G; ++g) ha.packed_bins = ha.packed_bins && grp_bins[(size_t)g] <= 256;
         size_t smem = smem_words * sizeof(uint32_t);
         if (fr && ha.codes_in_regs) {
             // previous frontier (bounded like this one) + phantom entry: selector word + one bin->child row each

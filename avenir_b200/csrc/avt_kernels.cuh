@@ -56,6 +56,7 @@ struct HistArgs {
     uint32_t* signal_ticket;        // zero-initialised block counter
     uint32_t signal_epoch;
     int signal_ranks;
+    int packed_bins;    // 1: every attribute group has <= 256 bins (group-local bin indices fit a byte)
     int repart_smem;    // 1: codes_in_regs and the previous level's tables fit the block's shared memory (fast path)
 };
 
@@ -152,9 +153,11 @@ __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a,
 #pragma unroll
         for (int j = 0; j < kRowsPerThread; ++j) rowkey[j] = rp.skip[rowkey[j]] ? phantom : rowkey[j];
     }
+    {
+        const uint32_t ns4 = node_stride * 4u, cl4 = 4u << rlog, base_rep = sh_base + rep * 4u;
 #pragma unroll
-    for (int j = 0; j < kRowsPerThread; ++j)
-        rowkey[j] = sh_base + (rowkey[j] * node_stride + (u4_byte(vc, j) << rlog) + rep) * 4u;
+        for (int j = 0; j < kRowsPerThread; ++j) rowkey[j] = rowkey[j] * ns4 + (u4_byte(vc, j) * cl4 + base_rep);   // two IMADs
+    }
     if (!WIDE) {
         for (int c0 = 0; c0 < ne; c0 += 4) {
             const int nq = ne - c0 < 4 ? ne - c0 : 4;
@@ -163,13 +166,28 @@ __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a,
                 for (int q = 0; q < 4; ++q)
                     if (q < nq) v[q] = ld_stream((const char*)a.cols[a.ent_attr[e0 + c0 + q]] + base);
             }
+            if (a.packed_bins) {
+                // the group has <= 256 bins: the attribute's first bin is added to its 16 codes four at a time (no carry
+                // between the bytes), which leaves extract + multiply-add + update per counter
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                if (q < nq) {
-                    const uint32_t offs = ((uint32_t)(a.ent_locoff[e0 + c0 + q] * a.C) << rlog) * 4u;
+                for (int q = 0; q < 4; ++q) {
+                    if (q < nq) {
+                        const uint32_t lo4 = (uint32_t)a.ent_locoff[e0 + c0 + q] * 0x01010101u;
+                        const uint4 vv = make_uint4(v[q].x + lo4, v[q].y + lo4, v[q].z + lo4, v[q].w + lo4);
 #pragma unroll
-                    for (int j = 0; j < kRowsPerThread; ++j)
-                        red_shared_add(rowkey[j] + offs + u4_byte(v[q], j) * cs4, HAS_W ? u4_byte(vw, j) : 1u);
+                        for (int j = 0; j < kRowsPerThread; ++j)
+                            red_shared_add(rowkey[j] + u4_byte(vv, j) * cs4, HAS_W ? u4_byte(vw, j) : 1u);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (q < nq) {
+                        const uint32_t offs = ((uint32_t)(a.ent_locoff[e0 + c0 + q] * a.C) << rlog) * 4u;
+#pragma unroll
+                        for (int j = 0; j < kRowsPerThread; ++j)
+                            red_shared_add(rowkey[j] + offs + u4_byte(v[q], j) * cs4, HAS_W ? u4_byte(vw, j) : 1u);
+                    }
                 }
             }
         }
