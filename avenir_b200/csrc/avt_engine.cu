@@ -89,6 +89,10 @@ struct avt_engine {
     DevBuf<avt_split> d_splits;
     DevBuf<int32_t> d_bounds, d_attr_first;
     DevBuf<uint8_t> d_seg_lut;
+    // all attributes' codes in one byte per row (narrow schemas; see HistArgs::packed)
+    DevBuf<uint8_t> d_packed;
+    bool packed_ok = false;
+    uint32_t pk_shift[4] = {0, 0, 0, 0}, pk_mask4[4] = {0, 0, 0, 0};
     // item-parallel scan (avt_scan_fast.cuh): (split, segment) items, first item of every split, per-node child counts
     DevBuf<uint32_t> d_items;
     DevBuf<int32_t> d_seg_first, d_nkids;
@@ -129,6 +133,7 @@ struct avt_engine {
                               // own dependency chains, not launches, and the cooperative grid runs at 2 blocks/SM.  Kept for round 2.
     DevBuf<unsigned char> d_levels;
     DevBuf<unsigned long long> d_phase;
+    bool hist_pack = true;    // AVT_HIST_PACK=0: never use the bit-packed copy of the codes
     bool scan_fast = true;    // AVT_SCAN_FAST=0: always the general scan kernel in the level loop
     bool pdl = true;          // AVT_PDL=0: plain stream launches in the level loop
     bool pdl_chain = false;   // the launch being issued directly follows a kernel of the level loop (no memset/copy between)
@@ -312,6 +317,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_PERSISTENT")) e->persistent = atoi(v) != 0;
     if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
     if (const char* v = getenv("AVT_SCAN_FAST")) e->scan_fast = atoi(v) != 0;
+    if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
     *out = e;
@@ -333,7 +339,7 @@ void avt_destroy(avt_engine* e) {
     e->d_nid.release(); e->d_levels.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_tile_ctr.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
-    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_av.release(); e->d_best.release();
+    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release();
     for (auto& s : e->pending) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
@@ -388,6 +394,27 @@ int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32
     if (int rc = upload(e, e->d_colptrs, e->cols.data(), (size_t)n_attrs)) return rc;
     if (int rc = upload(e, e->d_bin_off, e->bin_off.data(), (size_t)n_attrs + 1)) return rc;
     if (int rc = upload(e, e->d_wide, e->wide.data(), (size_t)n_attrs)) return rc;
+    {
+        // bit-packed copy of the codes for the histogram pass: one byte per row instead of one per attribute
+        int bits = 0;
+        bool ok = e->hist_pack && n_attrs <= 4;
+        for (int a = 0; a < n_attrs && ok; ++a) {
+            int w = 0;
+            while ((1 << w) < n_bins[a]) ++w;
+            e->pk_shift[a] = (uint32_t)bits;
+            e->pk_mask4[a] = ((1u << w) - 1u) * 0x01010101u;
+            bits += w;
+            ok = !e->wide[a] && bits <= 8;
+        }
+        e->packed_ok = ok;
+        if (ok) {
+            CUDA_TRY(e, e->d_packed.ensure((size_t)e->Npad));
+            const long long groups = e->Npad / 16;
+            pack_codes_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, e->stream>>>((const void* const*)e->d_colptrs.p, n_attrs,
+                                                                                      make_uint4(e->pk_shift[0], e->pk_shift[1], e->pk_shift[2], e->pk_shift[3]), e->Npad, e->d_packed.p);
+            CUDA_TRY(e, cudaGetLastError());
+        }
+    }
     if (int rc = timer_close(e, ts)) return rc;
     e->T = 0;
     e->S = 0;
@@ -650,6 +677,10 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         ha.grp_start = base + o_gs; ha.grp_bins = base + o_gb; ha.grp_rlog = base + o_gr; ha.grp_l2g = base + o_l2g; ha.grp_l2g_off = base + o_lo;
         ha.codes_in_regs = (G == 1 && !any_wide && e->A <= 4) ? 1 : 0;
         ha.zero_words = (int)smem_words;
+        if (ha.codes_in_regs && e->packed_ok) {
+            ha.packed = e->d_packed.p;
+            for (int q = 0; q < 4; ++q) { ha.pk_shift[q] = e->pk_shift[q]; ha.pk_mask4[q] = e->pk_mask4[q]; }
+        }
         ha.packed_bins = 1;
         for (int g = 0; g < G; ++g) ha.packed_bins = ha.packed_bins && grp_bins[(size_t)g] <= 256;
         size_t smem = smem_words * sizeof(uint32_t);

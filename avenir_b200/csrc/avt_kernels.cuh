@@ -56,6 +56,11 @@ struct HistArgs {
     uint32_t* signal_ticket;        // zero-initialised block counter
     uint32_t signal_epoch;
     int signal_ranks;
+    // bit-packed codes: when the data set has <= 4 narrow attributes whose codes fit one byte together, the pass reads that
+    // one byte per row instead of one byte per attribute (pack_codes_kernel builds it when the data set is loaded)
+    const uint8_t* packed;   // [Npad] or nullptr
+    uint32_t pk_shift[4];    // bit position of attribute q's code
+    uint32_t pk_mask4[4];    // its mask, replicated into the four bytes of a word
     int packed_bins;    // 1: every attribute group has <= 256 bins (group-local bin indices fit a byte)
     int repart_smem;    // 1: codes_in_regs and the previous level's tables fit the block's shared memory (fast path)
 };
@@ -85,9 +90,20 @@ __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a,
     uint4 v[4];
     const int n0 = ne < 4 ? ne : 4;
     if (!WIDE) {
+        if (a.packed) {
+            // entry q == attribute q here (codes_in_regs); unpack 4 rows at a time: shift, then mask every byte
+            const uint4 vp = ld_stream(a.packed + base);
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-            if (q < n0) v[q] = ld_stream((const char*)a.cols[a.ent_attr[e0 + q]] + base);
+            for (int q = 0; q < 4; ++q)
+                if (q < n0) {
+                    const uint32_t sh = a.pk_shift[q], m = a.pk_mask4[q];
+                    v[q] = make_uint4((vp.x >> sh) & m, (vp.y >> sh) & m, (vp.z >> sh) & m, (vp.w >> sh) & m);
+                }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (q < n0) v[q] = ld_stream((const char*)a.cols[a.ent_attr[e0 + q]] + base);
+        }
     }
     if (REPART) {
         uint32_t nw[8];
@@ -353,6 +369,20 @@ __global__ void __launch_bounds__(256) hist_global_kernel(const HistArgs a, int 
             if (live && (unsigned)(__ffs(peers) - 1) == lane) atomicAdd(&a.H[idx], sum);
         }
     }
+}
+
+// One byte per row holding the codes of all (<= 4, narrow) attributes: attribute q at bit shift[q].
+// One thread packs 16 rows; the shifted codes never leave their byte (the widths add up to <= 8 bits).
+__global__ void pack_codes_kernel(const void* const* cols, int n_attrs, uint4 shifts, long long npad, uint8_t* out) {
+    const long long base = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+    if (base >= npad) return;
+    const uint32_t sh[4] = {shifts.x, shifts.y, shifts.z, shifts.w};
+    uint4 acc = make_uint4(0, 0, 0, 0);
+    for (int q = 0; q < n_attrs; ++q) {
+        const uint4 v = *reinterpret_cast<const uint4*>((const char*)cols[q] + base);
+        acc.x |= v.x << sh[q]; acc.y |= v.y << sh[q]; acc.z |= v.z << sh[q]; acc.w |= v.w << sh[q];
+    }
+    *reinterpret_cast<uint4*>(out + base) = acc;
 }
 
 // ------------------------------------------------------------------------------------------------

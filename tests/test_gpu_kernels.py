@@ -214,6 +214,7 @@ def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
     monkeypatch.setenv("AVT_GROW_HOST", str(host_loop if host_loop < 3 else 0))
     monkeypatch.setenv("AVT_PERSISTENT", "0" if host_loop >= 3 else "1")
     monkeypatch.setenv("AVT_SCAN_FAST", "0" if host_loop == 4 else "1")   # 3: item-parallel scan (the table fits it), 4: general kernel
+    monkeypatch.setenv("AVT_HIST_PACK", "0" if host_loop == 4 else "1")   # 4: one byte per attribute instead of the bit-packed copy
     n = 150001
     rng = np.random.default_rng(12)
     cols, cls, n_bins, _ = synth.call_hangup_encoded(n)
