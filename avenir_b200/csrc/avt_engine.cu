@@ -1378,10 +1378,33 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         // apply the last planned split so that the node ids match the returned frontier
         TimerSlot tr;
         if (int rc = timer_open(e, &e->stats.repart_ms, &tr)) return rc;
-        long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
-        dim3 grid((unsigned)blocks, (unsigned)T);
-        repartition_kernel<<<grid, 256, 0, e->stream>>>(e->nid_cur, (const void* const*)e->d_colptrs.p, e->d_wide.p, nb_level(last_level),
-                                                        e->d_node_attr.p, e->d_lut.p, lut_w, e->N, e->Npad);
+        bool narrow = e->A <= 4;
+        for (int a = 0; a < e->A; ++a) narrow = narrow && !e->wide[a];
+        const size_t tbl = ((size_t)fr.prev_n_max + 2) * (4 + (size_t)lut_w * 2) + 8;
+        if (narrow && tbl <= 16 * 1024) {
+            RepartFastArgs ra{};
+            ra.nid = e->nid_cur;
+            ra.cols = (const void* const*)e->d_colptrs.p;
+            if (e->packed_ok) {
+                ra.packed = e->d_packed.p;
+                for (int q = 0; q < 4; ++q) { ra.pk_shift[q] = e->pk_shift[q]; ra.pk_mask4[q] = e->pk_mask4[q]; }
+            }
+            ra.node_base = nb_level(last_level);
+            ra.node_attr = e->d_node_attr.p;
+            ra.child_lut = e->d_lut.p;
+            ra.lut_w = lut_w;
+            ra.n_attrs = e->A;
+            ra.N = e->N;
+            ra.Npad = e->Npad;
+            const long long tiles = (e->N + 256 * kRowsPerThread - 1) / (256 * kRowsPerThread);
+            dim3 grid((unsigned)std::min<long long>(tiles, std::max<long long>(1, (long long)e->sm_count * 8 / T)), (unsigned)T);
+            repartition_fast_kernel<<<grid, 256, tbl, e->stream>>>(ra);
+        } else {
+            long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
+            dim3 grid((unsigned)blocks, (unsigned)T);
+            repartition_kernel<<<grid, 256, 0, e->stream>>>(e->nid_cur, (const void* const*)e->d_colptrs.p, e->d_wide.p, nb_level(last_level),
+                                                            e->d_node_attr.p, e->d_lut.p, lut_w, e->N, e->Npad);
+        }
         CUDA_TRY(e, cudaGetLastError());
         if (int rc = timer_close(e, tr)) return rc;
         e->stats.repart_launches += 1;

@@ -74,6 +74,33 @@ struct RepartSmem {
     const uint8_t* skip;   // [n_nodes+1] 1 = node is derived by subtraction, its rows are not counted (nullptr: count all)
 };
 
+// Fast fused repartition of 16 rows (<= 4 uint8 attributes, previous frontier's tables in shared memory): new node id
+// of every row into nw[] (two ids per word).  v[] holds the rows' codes, one vector per attribute.
+__device__ __forceinline__ void repart16_fast(const uint4& vn0, const uint4& vn1, uint4 (&v)[4], int n0, const RepartSmem& rp, int lut_w,
+                                              uint32_t (&nw)[8]) {
+    if (n0 < 4) v[3] = make_uint4(0, 0, 0, 0);
+    if (n0 < 3) v[2] = make_uint4(0, 0, 0, 0);
+    if (n0 < 2) v[1] = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+        const uint32_t a0 = u4_word(v[0], w), a1 = u4_word(v[1], w), a2 = u4_word(v[2], w), a3 = u4_word(v[3], w);
+        const uint32_t t0 = __byte_perm(a0, a1, 0x5140), t1 = __byte_perm(a2, a3, 0x5140);
+        const uint32_t t2 = __byte_perm(a0, a1, 0x7362), t3 = __byte_perm(a2, a3, 0x7362);
+        const uint32_t pk[4] = {__byte_perm(t0, t1, 0x5410), __byte_perm(t0, t1, 0x7632), __byte_perm(t2, t3, 0x5410),
+                                __byte_perm(t2, t3, 0x7632)};
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int j = w * 4 + r;
+            const uint32_t old = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
+            const uint32_t idx = min(old, rp.n_prev);  // 0xFFFF -> the phantom entry (all-NONE row)
+            const uint32_t code = __byte_perm(pk[r], 0u, rp.sel[idx]);
+            const uint32_t nn = rp.lut[idx * lut_w + code];
+            if (j & 1) nw[j >> 1] |= nn << 16;
+            else nw[j >> 1] = nn;
+        }
+    }
+}
+
 // hist_rows16: 16 consecutive rows of one tree for one attribute group.
 //   rowkey[j] = ((node * GB * C + cls) << rlog) + replica   (word index of the row's class slot of bin 0)
 //   counter   = rowkey[j] + ((locoff * C) << rlog) + code * (C << rlog)          (all kept as byte addresses)
@@ -112,27 +139,7 @@ __device__ __forceinline__ void hist_rows16(uint32_t sh_base, const HistArgs& a,
             // permute selector) and the bin -> child rows of every previous node sit in shared memory; the
             // row's four codes are gathered into one word by 4x4 byte transposes, so choosing "the code
             // of the node's split attribute" is a single PRMT.
-            if (n0 < 4) v[3] = make_uint4(0, 0, 0, 0);
-            if (n0 < 3) v[2] = make_uint4(0, 0, 0, 0);
-            if (n0 < 2) v[1] = make_uint4(0, 0, 0, 0);
-#pragma unroll
-            for (int w = 0; w < 4; ++w) {
-                const uint32_t a0 = u4_word(v[0], w), a1 = u4_word(v[1], w), a2 = u4_word(v[2], w), a3 = u4_word(v[3], w);
-                const uint32_t t0 = __byte_perm(a0, a1, 0x5140), t1 = __byte_perm(a2, a3, 0x5140);
-                const uint32_t t2 = __byte_perm(a0, a1, 0x7362), t3 = __byte_perm(a2, a3, 0x7362);
-                const uint32_t pk[4] = {__byte_perm(t0, t1, 0x5410), __byte_perm(t0, t1, 0x7632), __byte_perm(t2, t3, 0x5410),
-                                        __byte_perm(t2, t3, 0x7632)};
-#pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    const int j = w * 4 + r;
-                    const uint32_t old = j < 8 ? u4_half(vn0, j) : u4_half(vn1, j - 8);
-                    const uint32_t idx = min(old, rp.n_prev);  // 0xFFFF -> the phantom entry (all-NONE row)
-                    const uint32_t code = __byte_perm(pk[r], 0u, rp.sel[idx]);
-                    const uint32_t nn = rp.lut[idx * a.lut_w + code];
-                    if (j & 1) nw[j >> 1] |= nn << 16;
-                    else nw[j >> 1] = nn;
-                }
-            }
+            repart16_fast(vn0, vn1, v, n0, rp, a.lut_w, nw);
         } else {
 #pragma unroll
             for (int j = 0; j < kRowsPerThread; ++j) {
@@ -646,6 +653,58 @@ __global__ void __launch_bounds__(256) repartition_kernel(uint16_t* nid_all, con
             wds[j >> 1] = (wds[j >> 1] & ~(0xFFFFu << ((j & 1) * 16))) | (nw << ((j & 1) * 16));
         }
         *reinterpret_cast<uint4*>(nid + base) = make_uint4(wds[0], wds[1], wds[2], wds[3]);
+    }
+}
+
+// The same for narrow schemas (<= 4 uint8 attributes) and frontiers whose tables fit shared memory: the tables are
+// staged once per block and a thread moves 16 rows with vector loads and the byte-permute selection of
+// repart16_fast -- no per-row gathers.  grid = (chunks, T), dynamic smem = (n_max + 2) * (4 + 2 * lut_w) + 8.
+struct RepartFastArgs {
+    uint16_t* nid;             // [T][Npad], updated in place
+    const void* const* cols;   // [A]
+    const uint8_t* packed;     // bit-packed codes (HistArgs::packed) or nullptr
+    uint32_t pk_shift[4], pk_mask4[4];
+    const int32_t* node_base;  // [T+1] frontier the ids refer to
+    const int32_t* node_attr;
+    const uint16_t* child_lut;
+    int lut_w, n_attrs;
+    long long N, Npad;
+};
+
+__global__ void __launch_bounds__(256) repartition_fast_kernel(const RepartFastArgs a) {
+    extern __shared__ uint32_t rsh[];
+    const int t = blockIdx.y;
+    const int nb = a.node_base[t], n_prev = a.node_base[t + 1] - nb;
+    uint32_t* sel = rsh;
+    uint16_t* lut = reinterpret_cast<uint16_t*>(sel + n_prev + 1);
+    for (int i = threadIdx.x; i <= n_prev; i += blockDim.x) {
+        const int at = i < n_prev ? a.node_attr[nb + i] : -1;
+        sel[i] = 0x4440u | (uint32_t)(at < 0 ? 0 : at);
+    }
+    for (int i = threadIdx.x; i < (n_prev + 1) * a.lut_w; i += blockDim.x)
+        lut[i] = i < n_prev * a.lut_w ? a.child_lut[(long long)nb * a.lut_w + i] : (uint16_t)AVT_NODE_NONE;
+    __syncthreads();
+    const RepartSmem rp{sel, lut, (uint32_t)n_prev, true, nullptr};
+    uint16_t* nid = a.nid + (long long)t * a.Npad;
+    const long long stride = (long long)gridDim.x * blockDim.x * kRowsPerThread;
+    for (long long base = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * kRowsPerThread; base < a.N; base += stride) {
+        const uint4 vn0 = ld_stream(nid + base), vn1 = ld_stream(nid + base + 8);
+        uint4 v[4];
+        if (a.packed) {
+            const uint4 vp = ld_stream(a.packed + base);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint32_t sh = a.pk_shift[q], m = q < a.n_attrs ? a.pk_mask4[q] : 0u;
+                v[q] = make_uint4((vp.x >> sh) & m, (vp.y >> sh) & m, (vp.z >> sh) & m, (vp.w >> sh) & m);
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) v[q] = q < a.n_attrs ? ld_stream((const char*)a.cols[q] + base) : make_uint4(0, 0, 0, 0);
+        }
+        uint32_t nw[8];
+        repart16_fast(vn0, vn1, v, 4, rp, a.lut_w, nw);
+        *reinterpret_cast<uint4*>(nid + base) = make_uint4(nw[0], nw[1], nw[2], nw[3]);
+        *reinterpret_cast<uint4*>(nid + base + 8) = make_uint4(nw[4], nw[5], nw[6], nw[7]);
     }
 }
 
