@@ -133,6 +133,13 @@ struct avt_engine {
                               // own dependency chains, not launches, and the cooperative grid runs at 2 blocks/SM.  Kept for round 2.
     DevBuf<unsigned char> d_levels;
     DevBuf<unsigned long long> d_phase;
+    // level loop control block: [0] error flag, [1] last-block ticket, [16 ...] node_base of every level; initialised by one
+    // copy from, and read back by one copy into, page-locked host memory (pageable copies cost ~10 us each and serialise)
+    DevBuf<int32_t> d_ctrl;
+    int32_t* h_ctrl = nullptr;      // page-locked, kCtrlHostInts ints
+    avt_grow_record* h_rec = nullptr;   // page-locked staging for the records, kRecHostCount of them
+    uint8_t order_cached[AVT_MAX_CLASSES];
+    int order_cached_n = -1;        // classes covered by order_cached (-1: nothing uploaded yet)
     bool hist_pack = true;    // AVT_HIST_PACK=0: never use the bit-packed copy of the codes
     bool scan_fast = true;    // AVT_SCAN_FAST=0: always the general scan kernel in the level loop
     bool pdl = true;          // AVT_PDL=0: plain stream launches in the level loop
@@ -244,6 +251,9 @@ int upload(avt_engine* e, DevBuf<T>& buf, const T* host, size_t n) {
     return AVT_OK;
 }
 
+constexpr size_t kCtrlHostInts = 1 << 16;
+constexpr size_t kRecHostCount = 4096;
+
 SplitTable make_table(avt_engine* e) {
     SplitTable st;
     st.splits = e->d_splits.p;
@@ -266,7 +276,11 @@ int upload_order(avt_engine* e, const uint8_t* class_order) {
         if (ord[i] >= e->C || seen[ord[i]]) return fail(e, AVT_E_INVALID, "class_order is not a permutation of 0..%d", e->C - 1);
         seen[ord[i]] = true;
     }
-    return upload(e, e->d_order, ord, (size_t)e->C);
+    if (e->order_cached_n == e->C && memcmp(ord, e->order_cached, (size_t)e->C) == 0) return AVT_OK;   // already on the device
+    if (int rc = upload(e, e->d_order, ord, (size_t)e->C)) return rc;
+    memcpy(e->order_cached, ord, (size_t)e->C);
+    e->order_cached_n = e->C;
+    return AVT_OK;
 }
 
 }  // namespace
@@ -341,7 +355,9 @@ void avt_destroy(avt_engine* e) {
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
     e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
-    e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release();
+    e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release(); e->d_ctrl.release();
+    if (e->h_ctrl) cudaFreeHost(e->h_ctrl);
+    if (e->h_rec) cudaFreeHost(e->h_rec);
     for (auto& s : e->pending) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
     for (auto& p : e->free_events) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     if (e->tev0) cudaEventDestroy(e->tev0);
@@ -1126,21 +1142,36 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     if (int rc = upload_order(e, class_order)) return rc;
     const bool want_records = records != nullptr || n_records != nullptr;
     CUDA_TRY(e, e->d_next_count.ensure((size_t)T));
-    CUDA_TRY(e, e->d_err.ensure(1));
-    CUDA_TRY(e, e->d_ticket.ensure(1));
-    CUDA_TRY(e, e->d_nb_all.ensure((size_t)(n_levels + 1) * (T + 1)));
-    CUDA_TRY(e, cudaMemsetAsync(e->d_err.p, 0, sizeof(int32_t), e->stream));
-    CUDA_TRY(e, cudaMemsetAsync(e->d_ticket.p, 0, sizeof(uint32_t), e->stream));
+    // control block (see d_ctrl): error flag, ticket and level 0's node_base go down in one copy from page-locked memory
+    const size_t ctrl_ints = 16 + (size_t)(n_levels + 1) * (T + 1);
+    const bool ctrl_pinned = ctrl_ints <= kCtrlHostInts;
+    if (!e->h_ctrl) CUDA_TRY(e, cudaHostAlloc((void**)&e->h_ctrl, kCtrlHostInts * sizeof(int32_t), cudaHostAllocDefault));
+    if (!e->h_rec) CUDA_TRY(e, cudaHostAlloc((void**)&e->h_rec, kRecHostCount * sizeof(avt_grow_record), cudaHostAllocDefault));
+    CUDA_TRY(e, e->d_ctrl.ensure(ctrl_ints));
+    int32_t* const d_err_p = e->d_ctrl.p;
+    uint32_t* const d_ticket_p = reinterpret_cast<uint32_t*>(e->d_ctrl.p + 1);
+    int32_t* const d_nb_all_p = e->d_ctrl.p + 16;
     std::vector<avt_grow_record> all;
     std::vector<int32_t> ub(nodes_per_tree, nodes_per_tree + T), nb_host((size_t)T + 1);
     struct RecRegion { int level; size_t host_at, count; };
     std::vector<RecRegion> rec_regions;  // where each level's record slots end up in `all`
     size_t flushed = 0;                  // records already copied to `all` by a mid-loop flush
-    auto nb_level = [&](int level) { return e->d_nb_all.p + (size_t)level * (T + 1); };
+    auto nb_level = [&](int level) { return d_nb_all_p + (size_t)level * (T + 1); };
     // level 0: the caller's frontier is exact
     nb_host[0] = 0;
     for (int t = 0; t < T; ++t) nb_host[(size_t)t + 1] = nb_host[(size_t)t] + ub[(size_t)t];
-    CUDA_TRY(e, cudaMemcpyAsync(nb_level(0), nb_host.data(), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+    {
+        std::vector<int32_t> init_pageable;
+        int32_t* init = e->h_ctrl;
+        if (!ctrl_pinned || 16 + (size_t)T + 1 > kCtrlHostInts) {
+            init_pageable.resize(16 + (size_t)T + 1);
+            init = init_pageable.data();
+        }
+        for (int i = 0; i < 16; ++i) init[i] = 0;
+        for (int t = 0; t <= T; ++t) init[16 + t] = nb_host[(size_t)t];
+        CUDA_TRY(e, cudaMemcpyAsync(e->d_ctrl.p, init, (16 + (size_t)T + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+        if (init != e->h_ctrl) CUDA_TRY(e, cudaStreamSynchronize(e->stream));   // the pageable source goes out of scope
+    }
     const bool peer_on = e->peer.active && e->peer.n > 1;
     const bool subtract = e->subtract;
     const bool fast_scan = e->scan_fast && e->fast_scan_ok && !subtract;   // latency-optimised scan + planning (avt_scan_fast.cuh)
@@ -1298,9 +1329,9 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         pa.child_lut = e->d_lut.p;
         pa.next_count = e->d_next_count.p;
         pa.records = want_records ? e->d_records.p + rec_off : nullptr;
-        pa.err = e->d_err.p;
+        pa.err = d_err_p;
         pa.next_node_base = nb_level(level + 1);
-        pa.ticket = e->d_ticket.p;
+        pa.ticket = d_ticket_p;
         pa.lut_w = lut_w;
         pa.level = level;
         pa.n_trees = T;
@@ -1419,17 +1450,25 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     }
     e->hist_valid = e->scan_valid = false;
     e->NF = 0;
-    int32_t err = 0;
-    CUDA_TRY(e, cudaMemcpyAsync(&err, e->d_err.p, sizeof err, cudaMemcpyDeviceToHost, e->stream));
-    std::vector<int32_t> nb_all_host((size_t)(last_level + 2) * (T + 1));
-    if (last_level >= 0)
-        CUDA_TRY(e, cudaMemcpyAsync(nb_all_host.data(), e->d_nb_all.p, nb_all_host.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+    // error flag + every level's node_base in one copy, the records in another, both into page-locked memory: one wait
+    const size_t back_ints = 16 + (size_t)(last_level + 2) * (T + 1);
+    std::vector<int32_t> back_pageable;
+    int32_t* back = e->h_ctrl;
+    if (!ctrl_pinned) {
+        back_pageable.resize(back_ints);
+        back = back_pageable.data();
+    }
+    CUDA_TRY(e, cudaMemcpyAsync(back, e->d_ctrl.p, back_ints * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
     const size_t tail_at = all.size();
+    const bool rec_pinned = want_records && rec_off && rec_off <= kRecHostCount;
     if (want_records && rec_off) {
         all.resize(tail_at + rec_off);
-        CUDA_TRY(e, cudaMemcpyAsync(all.data() + tail_at, e->d_records.p, rec_off * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(rec_pinned ? e->h_rec : all.data() + tail_at, e->d_records.p, rec_off * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
     }
     if (int rc = sync_and_resolve(e)) return rc;
+    if (rec_pinned) memcpy(all.data() + tail_at, e->h_rec, rec_off * sizeof(avt_grow_record));
+    const int32_t err = back[0];
+    const int32_t* nb_all_host = back + 16;
     if (last_level >= 0)
         for (int t = 0; t <= T; ++t) nb_host[(size_t)t] = nb_all_host[(size_t)(last_level + 1) * (T + 1) + t];
     // slots of a level's region beyond its true frontier were never written: mark them unused
