@@ -47,7 +47,8 @@ class Stats(C.Structure):
                 ("repart_launches", C.c_int64), ("comm_calls", C.c_int64),
                 ("hist_alg_bytes", C.c_int64), ("repart_alg_bytes", C.c_int64),
                 ("last_hist_variant", C.c_int32), ("last_hist_replicas", C.c_int32),
-                ("last_hist_grid", C.c_int32), ("last_hist_block", C.c_int32), ("last_hist_smem", C.c_int32)]
+                ("last_hist_grid", C.c_int32), ("last_hist_block", C.c_int32), ("last_hist_smem", C.c_int32),
+                ("reserved0", C.c_int32), ("last_grow_ms", C.c_double)]
 
 
 # every symbol include/avenir_tree.h declares: name -> (restype, argtypes)

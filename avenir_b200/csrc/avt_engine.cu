@@ -125,6 +125,8 @@ struct avt_engine {
     std::vector<TimerSlot> pending;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> free_events;
     cudaEvent_t tev0 = nullptr, tev1 = nullptr;
+    cudaEvent_t gev0 = nullptr, gev1 = nullptr;   // around one avt_grow_levels call (stats.last_grow_ms)
+    bool gev1_recorded = false;
     avt_stats stats{};
     int force_variant = -1;
     bool skip_h_memset = false;
@@ -304,6 +306,8 @@ int avt_create(int device, avt_engine** out) {
     if (st == cudaSuccess) st = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     if (st == cudaSuccess) st = cudaEventCreate(&e->tev0);
     if (st == cudaSuccess) st = cudaEventCreate(&e->tev1);
+    if (st == cudaSuccess) st = cudaEventCreate(&e->gev0);
+    if (st == cudaSuccess) st = cudaEventCreate(&e->gev1);
     cudaDeviceProp prop;
     if (st == cudaSuccess) st = cudaGetDeviceProperties(&prop, device);
     if (st == cudaSuccess) {
@@ -362,6 +366,8 @@ void avt_destroy(avt_engine* e) {
     for (auto& p : e->free_events) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     if (e->tev0) cudaEventDestroy(e->tev0);
     if (e->tev1) cudaEventDestroy(e->tev1);
+    if (e->gev0) cudaEventDestroy(e->gev0);
+    if (e->gev1) cudaEventDestroy(e->gev1);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -1465,6 +1471,8 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         all.resize(tail_at + rec_off);
         CUDA_TRY(e, cudaMemcpyAsync(rec_pinned ? e->h_rec : all.data() + tail_at, e->d_records.p, rec_off * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
     }
+    CUDA_TRY(e, cudaEventRecord(e->gev1, e->stream));   // end of the call's device work (stats.last_grow_ms)
+    e->gev1_recorded = true;
     if (int rc = sync_and_resolve(e)) return rc;
     if (rec_pinned) memcpy(all.data() + tail_at, e->h_rec, rec_off * sizeof(avt_grow_record));
     const int32_t err = back[0];
@@ -1713,13 +1721,24 @@ int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const ui
     if (e->T == 0 || e->S == 0) return fail(e, AVT_E_STATE, "avt_grow_levels: needs avt_forest_init and avt_split_table_set first");
     if (criterion != AVT_CRIT_GINI && criterion != AVT_CRIT_ENTROPY) return fail(e, AVT_E_INVALID, "avt_grow_levels: criterion %d", criterion);
     if (int rc = use_device(e)) return rc;
-    if (e->grow_host_loop == 0 && e->persistent) {
-        const int rc = grow_persistent_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
-        if (rc <= 0) return rc;
+    CUDA_TRY(e, cudaEventRecord(e->gev0, e->stream));
+    e->gev1_recorded = false;
+    int rc = 1;
+    if (e->grow_host_loop == 0 && e->persistent) rc = grow_persistent_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
+    if (rc > 0) {
+        if (e->grow_host_loop == 2) rc = grow_device_loop_sync(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
+        else if (e->grow_host_loop) rc = grow_host_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
+        else rc = grow_device_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
     }
-    if (e->grow_host_loop == 2) return grow_device_loop_sync(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
-    if (e->grow_host_loop) return grow_host_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
-    return grow_device_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
+    if (rc != AVT_OK) return rc;
+    if (!e->gev1_recorded) {   // loops that read back between levels: the stream is idle here
+        CUDA_TRY(e, cudaEventRecord(e->gev1, e->stream));
+        CUDA_TRY(e, cudaEventSynchronize(e->gev1));
+    }
+    float ms = 0.f;
+    CUDA_TRY(e, cudaEventElapsedTime(&ms, e->gev0, e->gev1));
+    e->stats.last_grow_ms = ms;
+    return AVT_OK;
 }
 
 int avt_cpg_sweep(avt_engine* e, int32_t node, int32_t criterion, const uint8_t* class_order, avt_cpg_stat* out) {

@@ -9,8 +9,10 @@ GPU (weak scaling: rows shard across ranks, the per-level histograms are all-red
 entropy, attribute strategy `all`, 8 expansions below the root.  A "step" builds the whole tree once:
 8 x (histogram -> fused entropy scan/arg-min -> children statistics -> repartition).
 
-  value   rows/sec = ranks * rows * levels / step time, inputs resident in HBM, timed with CUDA events on
-          the library's own stream (max over ranks);  L2 is flushed between steps
+  value   rows/sec = ranks * rows * levels / step time, inputs resident in HBM; step time = CUDA events the
+          library records on its own stream around everything avt_grow_levels enqueues, result copies included
+          (avt_stats.last_grow_ms; max over ranks);  L2 is flushed between steps.  api_ms_per_step is the same
+          step timed by events recorded from Python around the call (adds ctypes marshalling on both sides)
   e2e     same metric through the C-ABI from HOST buffers: avt_dataset_load (H2D from pinned memory) +
           avt_forest_init + avt_grow_levels + read-back of the node ids, wall clock
   roofline  dominant kernel = the histogram pass: algorithmic bytes / its CUDA-event time
@@ -211,7 +213,8 @@ def main():
         torch.cuda.synchronize()
         eng.timer_begin()
         _, frontier = eng.grow(L, CRIT_ENTROPY, [1])
-        return eng.timer_end(), frontier
+        api_ms = eng.timer_end()               # events around the Python call: includes ctypes marshalling on both sides
+        return eng.stats().last_grow_ms, api_ms, frontier   # the library's own events around the call's device work
 
     for _ in range(max(3, args.warmup)):
         step_resident()
@@ -220,11 +223,12 @@ def main():
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
-    dev_ms = 0.0
+    dev_ms = api_ms_sum = 0.0
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ms, frontier = step_resident()
+        ms, api_ms, frontier = step_resident()
         dev_ms += ms
+        api_ms_sum += api_ms
     barrier()
     wall = time.perf_counter() - t0
     # ---- same steps again with per-launch CUDA events on: kernel breakdown + roofline of the dominant kernel
@@ -285,7 +289,7 @@ def main():
             "kernel_ms_per_step": {"histogram": st.hist_ms / prof_steps, "scan_plan": st.scan_ms / prof_steps, "eval": st.eval_ms / prof_steps,
                                    "repartition": st.repart_ms / prof_steps, "allreduce": st.comm_ms / prof_steps,
                                    "note": f"CUDA events per launch, from {prof_steps} extra profiled steps"},
-            "wall_ms_per_step": wall * 1e3 / args.steps,
+            "wall_ms_per_step": wall * 1e3 / args.steps, "api_ms_per_step": api_ms_sum / args.steps,
             "gpu_launches": int((st.hist_launches + st.scan_launches + st.eval_launches + st.repart_launches) * args.steps // prof_steps),
             "e2e": {"value": world * N * L / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(sum(c.nbytes for c in cols_p) + cls_p.nbytes), "d2h_bytes_per_step": int(nid.nbytes)},

@@ -99,6 +99,9 @@ typedef struct avt_stats {
     int32_t last_hist_variant; /* 0 shared-memory privatised, 1 global atomics (match_any) */
     int32_t last_hist_replicas;
     int32_t last_hist_grid, last_hist_block, last_hist_smem;
+    int32_t reserved0;
+    double last_grow_ms; /* device time of the last avt_grow_levels call: CUDA events on the library's stream around everything
+                          * the call enqueued, result copies included (host-side argument handling excluded) */
 } avt_stats;
 
 /* ---- engine ------------------------------------------------------------------------------- */
