@@ -96,6 +96,8 @@ struct avt_engine {
     // item-parallel scan (avt_scan_fast.cuh): (split, segment) items, first item of every split, per-node child counts
     DevBuf<uint32_t> d_items;
     DevBuf<int32_t> d_seg_first, d_nkids;
+    DevBuf<uint32_t> d_pub;        // look-back planning: published child counts (FastTable::pub)
+    uint32_t scan_epoch = 0;       // tag of the last scan_fast_kernel launch that used d_pub
     int n_items = 0;
     bool fast_scan_ok = false;   // the split table is small enough for scan_fast_kernel
     // scan
@@ -143,6 +145,7 @@ struct avt_engine {
     uint8_t order_cached[AVT_MAX_CLASSES];
     int order_cached_n = -1;        // classes covered by order_cached (-1: nothing uploaded yet)
     bool hist_pack = true;    // AVT_HIST_PACK=0: never use the bit-packed copy of the codes
+    bool lookback = true;     // AVT_LOOKBACK=0: the last scan block plans the level (ticket) even for small frontiers
     bool scan_fast = true;    // AVT_SCAN_FAST=0: always the general scan kernel in the level loop
     bool pdl = true;          // AVT_PDL=0: plain stream launches in the level loop
     bool pdl_chain = false;   // the launch being issued directly follows a kernel of the level loop (no memset/copy between)
@@ -335,6 +338,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_PERSISTENT")) e->persistent = atoi(v) != 0;
     if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
     if (const char* v = getenv("AVT_SCAN_FAST")) e->scan_fast = atoi(v) != 0;
+    if (const char* v = getenv("AVT_LOOKBACK")) e->lookback = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
@@ -357,7 +361,7 @@ void avt_destroy(avt_engine* e) {
     e->d_nid.release(); e->d_levels.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_tile_ctr.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
-    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
+    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_pub.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release(); e->d_ctrl.release();
     if (e->h_ctrl) cudaFreeHost(e->h_ctrl);
@@ -1389,7 +1393,17 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             const bool chain = e->pdl && !e->profiling && e->stats.last_hist_variant == 0 && (peer_level ? e->signal_in_hist : e->comm == nullptr);
             cfg.numAttrs = chain ? 1 : 0;
             if (fast_scan) {
-                FastTable ft{e->d_items.p, e->d_seg_first.p, e->d_nkids.p, e->n_items};
+                FastTable ft{e->d_items.p, e->d_seg_first.p, e->d_nkids.p, e->n_items, nullptr, 0u};
+                if (e->lookback && NF <= kLookbackNodes) {
+                    if (e->d_pub.cap < (size_t)kLookbackNodes || e->scan_epoch >= (1u << 24) - 1) {
+                        // (re)start the tags: no earlier launch may have left this value behind
+                        CUDA_TRY(e, e->d_pub.ensure((size_t)kLookbackNodes));
+                        CUDA_TRY(e, cudaMemsetAsync(e->d_pub.p, 0, (size_t)kLookbackNodes * sizeof(uint32_t), e->stream));
+                        e->scan_epoch = 0;
+                    }
+                    ft.pub = e->d_pub.p;
+                    ft.epoch = ++e->scan_epoch;
+                }
                 CUDA_TRY(e, cudaLaunchKernelEx(&cfg, scan_fast_kernel, (const uint32_t*)Hc, make_table(e), ft, (const uint8_t*)e->d_order.p, (int)criterion,
                                                (const int32_t*)(nb_level(level) + T), pa));
             } else
@@ -1484,6 +1498,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         const size_t true_nf = (size_t)nb_all_host[(size_t)rg.level * (T + 1) + T];
         for (size_t i = true_nf; i < rg.count; ++i) all[rg.host_at + i].level = -1;
     }
+    if (err == 2) return fail(e, AVT_E_CUDA, "avt_grow_levels: a scan block waited too long for its predecessors (look-back planning)");
     if (err) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
     if (last_level >= 0)
         for (int t = 0; t < T; ++t) nodes_per_tree[t] = nb_host[(size_t)t + 1] - nb_host[(size_t)t];

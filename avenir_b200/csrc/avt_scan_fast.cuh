@@ -26,7 +26,22 @@ struct FastTable {
     const int32_t* seg_first;  // [S+1] first item of every split
     int32_t* nkids;            // [NF] children of every node of the current frontier (scratch between the blocks and the planner)
     int n_items;
+    // look-back planning (frontier bound <= kLookbackNodes): every node's block publishes its child count tagged with this
+    // launch's epoch and reads the counts of the nodes before it, so no block has to wait for the whole grid
+    uint32_t* pub;             // [kLookbackNodes], nullptr = the last block plans the level (ticket)
+    uint32_t epoch;            // 1 .. 2^24-1, different from the tags any earlier launch left in `pub`
 };
+
+constexpr int kLookbackNodes = 512;
+
+__device__ __forceinline__ void st_relaxed_gpu(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_gpu(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
 __device__ __forceinline__ uint16_t ldcg_u16(const uint16_t* p) { return __ldcg(p); }
 
@@ -150,12 +165,23 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
     pdl_wait();   // the histogram (and the frontier) come from the previous launch
     __syncthreads();
     const int node = blockIdx.x;
+    const bool lookback = ft.pub != nullptr;
+    if (plan.peer_H) {
+        // wait until every rank has finished this level's histogram pass (which also means: its previous scan)
+        if (tid < plan.n_ranks)
+            while ((int32_t)(ld_acquire_sys(plan.peer_flags + tid) - plan.peer_epoch) < 0) {}
+        __syncthreads();
+    }
+    if (lookback && plan.zero_ptr) {
+        // every block clears its share of the next level's histogram region (nobody reads that buffer any more:
+        // it held the counts of the level before this one)
+        const long long per = (plan.zero_words + gridDim.x - 1) / gridDim.x;
+        const long long z1 = min(plan.zero_words, (long long)(blockIdx.x + 1) * per);
+        for (long long i = (long long)blockIdx.x * per + tid; i < z1; i += blockDim.x) plan.zero_ptr[i] = 0;
+    }
     if (node < *n_nodes_dev) {
         if (plan.peer_H) {
             // every rank's partial counts for this node, pulled over NVLink and summed (see scan_node)
-            if (tid < plan.n_ranks)
-                while ((int32_t)(ld_acquire_sys(plan.peer_flags + tid) - plan.peer_epoch) < 0) {}
-            __syncthreads();
             const long long words = (long long)st.TB * C, off = (long long)node * words;
             for (long long i = tid; i < words; i += blockDim.x) {
                 uint32_t sum = 0;
@@ -260,7 +286,49 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
             const unsigned has_mask = __ballot_sync(0xffffffffu, pop != 0);
             const int rank = __popc(has_mask & ((1u << lane) - 1u));
             const int nk = __popc(has_mask);
-            // bin -> child row (local ranks)
+            // tree of this node
+            int t = 0;
+            for (int t0 = 0; t0 < plan.n_trees; t0 += 32) {
+                const int tt = t0 + lane;
+                const bool mine = tt < plan.n_trees && node >= plan.node_base[tt] && node < plan.node_base[tt + 1];
+                const unsigned m = __ballot_sync(0xffffffffu, mine);
+                if (m) { t = t0 + __ffs(m) - 1; break; }
+            }
+            int first = 0;   // id of this node's first child in the next frontier (look-back mode; else added by the planner)
+            if (lookback) {
+                if (lane == 0) st_relaxed_gpu(ft.pub + node, (ft.epoch << 8) | (uint32_t)nk);
+                // child counts of all nodes before this one: before its tree / inside its tree
+                const int nbt = plan.node_base[t];
+                int before = 0, inside = 0;
+                bool timeout = false;
+                for (int i = lane; i < node; i += 32) {
+                    uint32_t v = 0;
+                    int spin = 0;
+                    for (;;) {
+                        v = ld_relaxed_gpu(ft.pub + i);
+                        if ((v >> 8) == ft.epoch) break;
+                        if (++spin > (1 << 22)) { timeout = true; break; }   // never hang the GPU: report instead
+                    }
+                    if (i < nbt) before += (int)(v & 0xFFu);
+                    else inside += (int)(v & 0xFFu);
+                }
+#pragma unroll
+                for (int d = 16; d; d >>= 1) {
+                    before += __shfl_xor_sync(0xffffffffu, before, d);
+                    inside += __shfl_xor_sync(0xffffffffu, inside, d);
+                }
+                first = inside;
+                if (__any_sync(0xffffffffu, timeout) && lane == 0) *plan.err = 2;
+                if (lane == 0 && nk && first + nk > (int)AVT_NODE_NONE - 1) *plan.err = 1;
+                // next level's node_base: entry k is the number of children of all nodes before node_base[k]
+                const int total = before + inside + nk;
+                for (int k = lane; k <= plan.n_trees; k += 32) {
+                    const int nbk = plan.node_base[k];
+                    if (nbk == node + 1) plan.next_node_base[k] = total;
+                    if (nbk == 0 && node == 0) plan.next_node_base[k] = 0;
+                }
+            }
+            // bin -> child row (node-local ranks + first)
             const int Bs = live ? st.bin_off[sp.attr + 1] - st.bin_off[sp.attr] : 0;
             uint16_t* lut = plan.child_lut + (long long)node * plan.lut_w;
             for (int b0 = 0; b0 < plan.lut_w; b0 += 32) {
@@ -278,21 +346,13 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
                 const int src = sg < 0 ? 0 : sg;
                 const int r = __shfl_sync(0xffffffffu, rank, src);
                 const bool ok = sg >= 0 && ((has_mask >> src) & 1u);
-                if (bin < plan.lut_w) lut[bin] = ok ? (uint16_t)r : (uint16_t)AVT_NODE_NONE;
+                if (bin < plan.lut_w) lut[bin] = ok ? (uint16_t)(r + first) : (uint16_t)AVT_NODE_NONE;
             }
             if (lane == 0) {
                 plan.node_attr[node] = live ? sp.attr : -1;
                 ft.nkids[node] = nk;
             }
             if (plan.records) {
-                // tree and tree-local index of this node
-                int t = 0;
-                for (int t0 = 0; t0 < plan.n_trees; t0 += 32) {
-                    const int tt = t0 + lane;
-                    const bool mine = tt < plan.n_trees && node >= plan.node_base[tt] && node < plan.node_base[tt + 1];
-                    const unsigned m = __ballot_sync(0xffffffffu, mine);
-                    if (m) { t = t0 + __ffs(m) - 1; break; }
-                }
                 for (int i = lane; i < (int)(sizeof(avt_grow_record) / 4); i += 32) reinterpret_cast<uint32_t*>(&s_rec)[i] = 0;
                 __syncwarp();
                 if (lane == 0) {
@@ -304,7 +364,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
                     s_rec.min_av = b.split >= 0 ? b.av : nan;
                 }
                 if (lane < kMaxSeg) {
-                    s_rec.child[lane] = pop ? rank : -1;
+                    s_rec.child[lane] = pop ? rank + first : -1;
                     s_rec.child_pop[lane] = (long long)pop;
                     s_rec.child_stat[lane] = seg ? it_stat[i0 + lane] : 0.0;
                 }
@@ -314,6 +374,12 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
                 for (int i = lane; i < (int)(sizeof(avt_grow_record) / 4); i += 32) dst[i] = src[i];
             }
         }
+    }
+    if (lookback) {
+        // an empty frontier has no block that owns the next level's node_base: block 0 writes it (all zero)
+        if (blockIdx.x == 0 && *n_nodes_dev == 0)
+            for (int k = tid; k <= plan.n_trees; k += blockDim.x) plan.next_node_base[k] = 0;
+        return;
     }
     // ---- last block to finish turns the local child ranks into ids of the next frontier
     __threadfence();

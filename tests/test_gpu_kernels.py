@@ -206,7 +206,8 @@ def test_api_misuse_is_reported():
         g.set_splits(t)                                  # bound outside the attribute's bins
 
 
-@pytest.mark.parametrize("host_loop", [0, 1, 2, 3, 4], ids=["persistent", "host-driven", "device-sync", "device-async", "device-async-general-scan"])
+@pytest.mark.parametrize("host_loop", [0, 1, 2, 3, 4, 5],
+                         ids=["persistent", "host-driven", "device-sync", "device-async", "device-async-general-scan", "device-async-ticket"])
 @pytest.mark.parametrize("criterion", [CRIT_GINI, CRIT_ENTROPY])
 def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
     """avt_grow_levels (device-driven: fused repartition+histogram, scan, on-device planning; and its
@@ -215,6 +216,7 @@ def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
     monkeypatch.setenv("AVT_PERSISTENT", "0" if host_loop >= 3 else "1")
     monkeypatch.setenv("AVT_SCAN_FAST", "0" if host_loop == 4 else "1")   # 3: item-parallel scan (the table fits it), 4: general kernel
     monkeypatch.setenv("AVT_HIST_PACK", "0" if host_loop == 4 else "1")   # 4: one byte per attribute instead of the bit-packed copy
+    monkeypatch.setenv("AVT_LOOKBACK", "0" if host_loop == 5 else "1")    # 5: the last scan block plans the level instead of look-back
     n = 150001
     rng = np.random.default_rng(12)
     cols, cls, n_bins, _ = synth.call_hangup_encoded(n)
@@ -269,14 +271,16 @@ def test_item_parallel_scan_equals_general_scan_and_oracle(criterion, monkeypatc
     rng = np.random.default_rng(5)
     weights = [None, rng.poisson(1.0, n).clip(0, 255).astype(np.uint8)]
     runs = {}
-    for fast in ("1", "0"):
-        monkeypatch.setenv("AVT_SCAN_FAST", fast)
+    for fast in ("1", "ticket", "0"):
+        monkeypatch.setenv("AVT_SCAN_FAST", "0" if fast == "0" else "1")
+        monkeypatch.setenv("AVT_LOOKBACK", "0" if fast == "ticket" else "1")
         g, o = make_pair(cols, cls, n_bins, 3, table, 2, weights, None)
         (rec, nrec), frontier = g.grow(5, criterion, [1, 1], class_order=[1, 2, 0], max_records=8192)
         runs[fast] = ([(r.level, r.tree, r.node, r.split, r.n_ties, list(r.child), list(r.child_pop),
                         [helpers.bits(x) for x in r.child_stat], helpers.bits(r.min_av)) for r in rec[:nrec]],
                       frontier, [g.node_ids(t).copy() for t in range(2)])
     assert runs["1"][0] == runs["0"][0] and runs["1"][1] == runs["0"][1]
+    assert runs["ticket"][0] == runs["0"][0] and runs["ticket"][1] == runs["0"][1]
     ho, fo = grow_levels(o, table, 5, criterion, n_trees=2, class_order=[1, 2, 0])
     want = [(lvl, t, nd, s, pops, av, ties) for lvl, level in enumerate(ho) for (t, nd, s, pops, av, ties) in level]
     got, frontier, nids = runs["1"]
