@@ -146,6 +146,7 @@ struct avt_engine {
     int order_cached_n = -1;        // classes covered by order_cached (-1: nothing uploaded yet)
     bool hist_pack = true;    // AVT_HIST_PACK=0: never use the bit-packed copy of the codes
     bool lookback = true;     // AVT_LOOKBACK=0: the last scan block plans the level (ticket) even for small frontiers
+    bool peer_trailing_round = false;   // AVT_PEER_TRAIL=1: end every level loop with a round of flags over all ranks
     bool scan_fast = true;    // AVT_SCAN_FAST=0: always the general scan kernel in the level loop
     bool pdl = true;          // AVT_PDL=0: plain stream launches in the level loop
     bool pdl_chain = false;   // the launch being issued directly follows a kernel of the level loop (no memset/copy between)
@@ -165,6 +166,11 @@ struct avt_engine {
         size_t cap_words = 0;          // words per H buffer
         void* base[16] = {};           // every rank's arena mapped here (own arena for own rank)
         uint32_t epoch = 0;
+        // Peer levels are numbered across calls; level k uses exchange buffer k & 1.  A rank zeroes or writes buffer k & 1
+        // only after it has seen every rank's flag of level k-1, i.e. after every rank finished reading that buffer at
+        // level k-2 -- so consecutive level-loop calls need no extra round of flags between them.
+        unsigned long long seq = 0;
+        bool lazy = false;             // the last level loop ended without a trailing flag round (see grow_device_loop)
     } peer;
     DevBuf<const uint32_t*> d_peer_H[2];
     DevBuf<uint32_t*> d_remote_flags;
@@ -338,6 +344,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_PERSISTENT")) e->persistent = atoi(v) != 0;
     if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
     if (const char* v = getenv("AVT_SCAN_FAST")) e->scan_fast = atoi(v) != 0;
+    if (const char* v = getenv("AVT_PEER_TRAIL")) e->peer_trailing_round = atoi(v) != 0;
     if (const char* v = getenv("AVT_LOOKBACK")) e->lookback = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract = atoi(v) != 0;
@@ -349,6 +356,14 @@ int avt_create(int device, avt_engine** out) {
 void avt_destroy(avt_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
+    if (e->stream && e->peer.active && e->peer.lazy) {
+        // the last level loop left out its trailing round of flags: another rank may still be reading this rank's exchange
+        // buffers.  Tell every rank we are done and wait (bounded) until all of them are, before the arena is freed.
+        ++e->peer.epoch;
+        peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
+        peer_wait_bounded_kernel<<<1, 32, 0, e->stream>>>(e->peer.arena, e->peer.n, e->peer.epoch, 1 << 24);
+        e->peer.lazy = false;
+    }
     if (e->stream) cudaStreamSynchronize(e->stream);
     if (e->comm) ncclCommDestroy(e->comm);
     for (int r = 0; r < e->peer.n; ++r)
@@ -1191,6 +1206,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     bool prev_peer = false;
     auto arena_H = [&](int parity) { return e->peer.arena + 64 + (size_t)parity * e->peer.cap_words; };
     bool peer_used = false;
+    bool all_peer = true;        // every level of this call exchanged through peer memory
     bool pending = false;
     bool planned_skip = false;   // the previous level's planning marked this level's derived nodes
     bool derive_ok = true;       // the previous level's complete counts survived (no reallocation since)
@@ -1309,8 +1325,14 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         e->skip_h_memset = h_prezeroed;
         // programmatic dependent launch: legal when nothing but the previous scan kernel precedes this pass
         e->pdl_chain = level > 0 && h_prezeroed && !e->profiling && !(subtract && planned_skip && !derive);
-        e->H_cur = peer_level ? arena_H(level & 1) : H_level(level);
-        if (peer_level) ++e->peer.epoch;   // the pass signals this epoch when its last block finishes
+        const int par = (int)(e->peer.seq & 1);   // exchange buffer of this level (peer levels only)
+        e->H_cur = peer_level ? arena_H(par) : H_level(level);
+        if (peer_level) {
+            ++e->peer.epoch;   // the pass signals this epoch when its last block finishes
+            ++e->peer.seq;
+        } else {
+            all_peer = false;
+        }
         e->signal_pending = peer_level;
         if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr, nb_level(level))) return rc;
         e->skip_h_memset = false;
@@ -1353,12 +1375,12 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             const bool next_peer = peer_on && (size_t)next_words <= e->peer.cap_words;
             h_prezeroed = level + 1 < n_levels && next_nodes <= kAsyncNodeLimit && next_words <= (1 << 16) &&
                           (next_peer || (!peer_on && (size_t)next_words <= std::min(e->d_H.cap, e->d_H2.cap)));
-            pa.zero_ptr = h_prezeroed ? (next_peer ? arena_H((level + 1) & 1) : H_level(level + 1)) : nullptr;
+            pa.zero_ptr = h_prezeroed ? (next_peer ? arena_H((int)(e->peer.seq & 1)) : H_level(level + 1)) : nullptr;
             pa.zero_words = h_prezeroed ? next_words : 0;
         }
         uint32_t* const Hc = peer_level ? hsum_level(level) : H_level(level);   // this level's complete counts
         if (peer_level) {
-            pa.peer_H = e->d_peer_H[level & 1].p;
+            pa.peer_H = e->d_peer_H[par].p;
             pa.peer_flags = e->peer.arena;
             pa.h_sum = Hc;
             pa.peer_epoch = e->peer.epoch;
@@ -1461,8 +1483,11 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         e->stats.repart_launches += 1;
         e->stats.repart_alg_bytes += (long long)e->N * T * 5;
     }
-    if (peer_used) {
-        // no rank may reuse its exchange buffers (next call, level 0) while another still reads them
+    if (peer_used && all_peer && !e->peer_trailing_round) {
+        e->peer.lazy = true;   // the buffer numbering continues in the next call (see Peer::seq): no trailing round
+    } else if (peer_used) {
+        // mixed call: finish with a round of flags so that any numbering is safe afterwards
+        e->peer.lazy = false;
         ++e->peer.epoch;
         peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
         peer_wait_kernel<<<1, 32, 0, e->stream>>>(e->peer.arena, e->peer.n, e->peer.epoch);
@@ -1577,6 +1602,15 @@ static int grow_persistent_loop(avt_engine* e, int32_t n_levels, int32_t criteri
     size_t smem_max = 0, rec_total = 0;
     FusedRepart fr{};
     uint16_t* const nid_start = e->nid_cur;
+    if (peer_on && e->peer.lazy) {
+        // the stream-ordered loop left its buffers without a trailing round and this loop restarts the numbering
+        ++e->peer.epoch;
+        peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
+        peer_wait_kernel<<<1, 32, 0, e->stream>>>(e->peer.arena, e->peer.n, e->peer.epoch);
+        CUDA_TRY(e, cudaGetLastError());
+        e->peer.lazy = false;
+        e->peer.seq = 0;
+    }
     const uint32_t epoch_start = e->peer.epoch;
     bool ok = true;
     for (int level = 0; level < n_levels && ok; ++level) {
@@ -1943,6 +1977,8 @@ int avt_peer_import(avt_engine* e, int32_t n_ranks, int32_t rank, const void* ha
     if (int rc = upload(e, e->d_peer_H[1], h1.data(), h1.size())) return rc;
     if (int rc = upload(e, e->d_remote_flags, rf.data(), rf.size())) return rc;
     e->peer.epoch = 0;
+    e->peer.seq = 0;
+    e->peer.lazy = false;
     e->peer.active = getenv("AVT_PEER_OFF") == nullptr;
     return sync_and_resolve(e);
 }

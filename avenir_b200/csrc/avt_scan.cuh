@@ -56,6 +56,12 @@ __global__ void peer_wait_kernel(const uint32_t* flags, int n_ranks, uint32_t ep
         while ((int32_t)(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) {}
 }
 
+// The same with a bound on the wait (engine teardown: a rank that is gone must not hang the others).
+__global__ void peer_wait_bounded_kernel(const uint32_t* flags, int n_ranks, uint32_t epoch, int max_spins) {
+    if ((int)threadIdx.x < n_ranks)
+        for (int i = 0; i < max_spins && (int32_t)(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0; ++i) {}
+}
+
 // loads that bypass L1: the planning block reads what OTHER blocks of the same launch wrote
 __device__ __forceinline__ int32_t ldcg_i32(const int32_t* p) { return __ldcg(p); }
 __device__ __forceinline__ uint32_t ldcg_u32(const uint32_t* p) { return __ldcg(p); }

@@ -40,6 +40,7 @@ def _worker(rank, world, port, n, levels, out_dir, peer):
             (rec2, nrec2), frontier2 = eng.grow(levels, CRIT_ENTROPY, [1], max_records=4096)
             assert frontier2 == frontier and nrec2 == nrec and all(rec2[i].split == rec[i].split for i in range(nrec))
             assert eng.stats().comm_calls > 0
+        dist.barrier()      # (ranks synchronise before tearing their engines down)
         torch.save({"records": flat, "frontier": frontier, "range": (lo, hi), "nid": eng.node_ids(0)}, os.path.join(out_dir, f"rank{rank}.pt"))
     finally:
         dist.destroy_process_group()
