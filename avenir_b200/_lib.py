@@ -19,6 +19,14 @@ class Split(C.Structure):
     _fields_ = [("attr", C.c_int32), ("kind", C.c_int32), ("n_seg", C.c_int32), ("off", C.c_int32)]
 
 
+class CsvAttr(C.Structure):
+    _fields_ = [("ordinal", C.c_int32), ("kind", C.c_int32), ("n", C.c_int32), ("off", C.c_int32)]
+
+
+CSV_INT, CSV_DOUBLE, CSV_CATEGORICAL = 0, 1, 2
+CSV_BAD_SHORT_ROW, CSV_BAD_INT, CSV_BAD_DOUBLE, CSV_BAD_CATEGORY, CSV_BAD_CLASS = 1, 2, 3, 4, 5
+
+
 class NodeBest(C.Structure):
     _fields_ = [("min_av", C.c_double), ("node_stat", C.c_double), ("population", C.c_int64),
                 ("best_split", C.c_int32), ("n_ties", C.c_int32)]
@@ -58,6 +66,9 @@ SIGNATURES = {
     "avt_destroy": (None, [_P]),
     "avt_last_error": (C.c_char_p, [_P]),
     "avt_dataset_load": (C.c_int, [_P, C.c_int64, C.c_int32, C.POINTER(C.c_int32), C.POINTER(_P), _P, C.c_int32]),
+    "avt_dataset_load_csv": (C.c_int, [_P, _P, C.c_int64, C.c_char, C.c_int32, C.c_int32, C.POINTER(CsvAttr), _P, _P, _P, _P,
+                                      C.c_int32, C.c_int32, _P, _P, C.POINTER(C.c_int64), _P, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
+    "avt_dataset_fetch_column": (C.c_int, [_P, C.c_int32, _P]),
     "avt_forest_init": (C.c_int, [_P, C.c_int32, C.POINTER(_P), C.POINTER(_P)]),
     "avt_split_table_set": (C.c_int, [_P, C.c_int32, C.POINTER(Split), C.POINTER(C.c_int32), C.c_int32, _P, C.c_int64]),
     "avt_level_histogram": (C.c_int, [_P, C.POINTER(C.c_int32), _P]),

@@ -3,6 +3,7 @@
 // a CUDA device and fails with AVT_E_CUDA when there is none.
 #include <cuda_runtime.h>
 #include <nccl.h>
+#include <cub/device/device_scan.cuh>
 
 #include <algorithm>
 #include <cstdarg>
@@ -89,6 +90,12 @@ struct avt_engine {
     DevBuf<avt_split> d_splits;
     DevBuf<int32_t> d_bounds, d_attr_first;
     DevBuf<uint8_t> d_seg_lut;
+    // on-device CSV encode (avt_csv.cuh): text, line index, scan scratch, tables, results
+    DevBuf<char> d_csv_text, d_csv_bytes;
+    DevBuf<uint32_t> d_csv_counts;
+    DevBuf<unsigned long long> d_csv_first;
+    DevBuf<long long> d_csv_lines, d_csv_ll;
+    DevBuf<uint8_t> d_csv_tmp, d_csv_tables;
     // all attributes' codes in one byte per row (narrow schemas; see HistArgs::packed)
     DevBuf<uint8_t> d_packed;
     bool packed_ok = false;
@@ -376,7 +383,7 @@ void avt_destroy(avt_engine* e) {
     e->d_nid.release(); e->d_levels.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_tile_ctr.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
-    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_pub.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
+    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_bytes.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_pub.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release(); e->d_ctrl.release();
     if (e->h_ctrl) cudaFreeHost(e->h_ctrl);
@@ -391,15 +398,11 @@ void avt_destroy(avt_engine* e) {
     delete e;
 }
 
-int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins,
-                     const void* const* columns, const uint8_t* class_codes, int32_t n_classes) {
-    if (!e) return AVT_E_INVALID;
-    if (n_rows <= 0 || n_attrs <= 0 || !n_bins || !columns || !class_codes)
-        return fail(e, AVT_E_INVALID, "avt_dataset_load: empty data set or NULL argument");
+// Shape of a new data set: metadata, column / class buffers (kept when the shape is unchanged: re-loading costs no
+// cudaMalloc/cudaFree), zeroed padding rows.  The caller fills the first n_rows entries, then calls dataset_install.
+static int dataset_shape(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins, int32_t n_classes, const char* who) {
     if (n_classes < 1 || n_classes > AVT_MAX_CLASSES)
-        return fail(e, AVT_E_INVALID, "avt_dataset_load: n_classes %d outside 1..%d", n_classes, AVT_MAX_CLASSES);
-    if (int rc = use_device(e)) return rc;
-    // column buffers are kept when the new data set has the same shape (re-loading costs no cudaMalloc/cudaFree)
+        return fail(e, AVT_E_INVALID, "%s: n_classes %d outside 1..%d", who, n_classes, AVT_MAX_CLASSES);
     const long long new_npad = (n_rows + 15) & ~15LL;
     bool same_shape = (int)e->cols.size() == n_attrs && e->Npad == new_npad && (int)e->wide.size() == n_attrs;
     for (int a = 0; same_shape && a < n_attrs; ++a) same_shape = e->cols[a] != nullptr && e->wide[a] == (n_bins[a] > 256 ? 1 : 0);
@@ -416,32 +419,34 @@ int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32
     e->bin_off.assign(n_attrs + 1, 0);
     e->wide.assign(n_attrs, 0);
     for (int a = 0; a < n_attrs; ++a) {
-        if (n_bins[a] < 1 || n_bins[a] > 65535) return fail(e, AVT_E_INVALID, "avt_dataset_load: n_bins[%d]=%d outside 1..65535", a, n_bins[a]);
+        if (n_bins[a] < 1 || n_bins[a] > 65535) return fail(e, AVT_E_INVALID, "%s: n_bins[%d]=%d outside 1..65535", who, a, n_bins[a]);
         e->bin_off[a + 1] = e->bin_off[a] + n_bins[a];
         e->wide[a] = n_bins[a] > 256;
     }
     e->TB = e->bin_off[n_attrs];
-    TimerSlot ts;
-    if (int rc = timer_open(e, &e->stats.h2d_ms, &ts)) return rc;
     for (int a = 0; a < n_attrs; ++a) {
         const size_t w = e->wide[a] ? 2 : 1;
         if (!e->cols[a]) CUDA_TRY(e, cudaMalloc(&e->cols[a], (size_t)e->Npad * w));
         CUDA_TRY(e, cudaMemsetAsync((char*)e->cols[a] + (size_t)n_rows * w, 0, (size_t)(e->Npad - n_rows) * w, e->stream));
-        CUDA_TRY(e, cudaMemcpyAsync(e->cols[a], columns[a], (size_t)n_rows * w, cudaMemcpyHostToDevice, e->stream));
     }
     CUDA_TRY(e, e->d_cls.ensure((size_t)e->Npad));
-    CUDA_TRY(e, cudaMemsetAsync(e->d_cls.p, 0, (size_t)e->Npad, e->stream));
-    CUDA_TRY(e, cudaMemcpyAsync(e->d_cls.p, class_codes, (size_t)n_rows, cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_cls.p + n_rows, 0, (size_t)(e->Npad - n_rows), e->stream));
     if (int rc = upload(e, e->d_colptrs, e->cols.data(), (size_t)n_attrs)) return rc;
     if (int rc = upload(e, e->d_bin_off, e->bin_off.data(), (size_t)n_attrs + 1)) return rc;
     if (int rc = upload(e, e->d_wide, e->wide.data(), (size_t)n_attrs)) return rc;
+    return AVT_OK;
+}
+
+// The columns are filled (stream-ordered): derived copies, state reset.
+static int dataset_install(avt_engine* e) {
+    const int n_attrs = e->A;
     {
         // bit-packed copy of the codes for the histogram pass: one byte per row instead of one per attribute
         int bits = 0;
         bool ok = e->hist_pack && n_attrs <= 4;
         for (int a = 0; a < n_attrs && ok; ++a) {
             int w = 0;
-            while ((1 << w) < n_bins[a]) ++w;
+            while ((1 << w) < e->n_bins[a]) ++w;
             e->pk_shift[a] = (uint32_t)bits;
             e->pk_mask4[a] = ((1u << w) - 1u) * 0x01010101u;
             bits += w;
@@ -456,12 +461,214 @@ int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32
             CUDA_TRY(e, cudaGetLastError());
         }
     }
-    if (int rc = timer_close(e, ts)) return rc;
     e->T = 0;
     e->S = 0;
     e->grp_cache.clear();
     e->grp_used = 0;
     e->hist_valid = e->scan_valid = false;
+    return AVT_OK;
+}
+
+int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins,
+                     const void* const* columns, const uint8_t* class_codes, int32_t n_classes) {
+    if (!e) return AVT_E_INVALID;
+    if (n_rows <= 0 || n_attrs <= 0 || !n_bins || !columns || !class_codes)
+        return fail(e, AVT_E_INVALID, "avt_dataset_load: empty data set or NULL argument");
+    if (int rc = use_device(e)) return rc;
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.h2d_ms, &ts)) return rc;
+    if (int rc = dataset_shape(e, n_rows, n_attrs, n_bins, n_classes, "avt_dataset_load")) return rc;
+    for (int a = 0; a < n_attrs; ++a) {
+        const size_t w = e->wide[a] ? 2 : 1;
+        CUDA_TRY(e, cudaMemcpyAsync(e->cols[a], columns[a], (size_t)n_rows * w, cudaMemcpyHostToDevice, e->stream));
+    }
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_cls.p, class_codes, (size_t)n_rows, cudaMemcpyHostToDevice, e->stream));
+    if (int rc = dataset_install(e)) return rc;
+    if (int rc = timer_close(e, ts)) return rc;
+    return sync_and_resolve(e);
+}
+
+int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char delim, int32_t skip_fields,
+                         int32_t n_attrs, const avt_csv_attr* attrs, const int32_t* int_points,
+                         const double* dbl_points, const char* cat_bytes, const int32_t* cat_offsets,
+                         int32_t class_ordinal, int32_t n_class_values, const char* class_bytes,
+                         const int32_t* class_offsets, int64_t* n_rows_out, int64_t* class_first_row,
+                         int64_t* bad_row, int32_t* bad_reason) {
+    if (!e) return AVT_E_INVALID;
+    if (bad_row) *bad_row = -1;
+    if (bad_reason) *bad_reason = 0;
+    if (!text || n_bytes <= 0 || n_attrs <= 0 || !attrs || n_class_values < 1 || !class_bytes || !class_offsets || skip_fields < 0)
+        return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: empty text or NULL argument");
+    if (delim == '\n' || delim == '\r') return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: the field delimiter cannot be a line terminator");
+    if (class_ordinal < 0 || class_ordinal >= kCsvMaxFields) return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: class ordinal %d outside 0..%d", class_ordinal, kCsvMaxFields - 1);
+    // ---- tables: attribute of every field, grids, value lists with their byte-sorted permutations
+    std::vector<int32_t> n_bins((size_t)n_attrs);
+    int n_int = 0, n_dbl = 0, n_cat = 0, max_ord = class_ordinal;
+    for (int a = 0; a < n_attrs; ++a) {
+        const avt_csv_attr& A = attrs[a];
+        if (A.ordinal < 0 || A.ordinal >= kCsvMaxFields || (a && A.ordinal <= attrs[a - 1].ordinal) || A.ordinal == class_ordinal)
+            return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: attribute %d: ordinals must increase, stay below %d and differ from the class ordinal", a, kCsvMaxFields);
+        if (A.n < 0 || A.off < 0) return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: attribute %d: negative size or offset", a);
+        max_ord = std::max(max_ord, A.ordinal);
+        if (A.kind == AVT_CSV_INT) {
+            if (A.n && !int_points) return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: int_points is NULL");
+            n_int = std::max(n_int, A.off + A.n);
+            n_bins[(size_t)a] = A.n + 1;
+        } else if (A.kind == AVT_CSV_DOUBLE) {
+            if (A.n && !dbl_points) return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: dbl_points is NULL");
+            n_dbl = std::max(n_dbl, A.off + A.n);
+            n_bins[(size_t)a] = A.n + 1;
+        } else if (A.kind == AVT_CSV_CATEGORICAL) {
+            if (A.n < 1 || !cat_bytes || !cat_offsets) return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: attribute %d: empty value list", a);
+            n_cat = std::max(n_cat, A.off + A.n);
+            n_bins[(size_t)a] = A.n;
+        } else {
+            return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: attribute %d: unknown kind %d", a, A.kind);
+        }
+    }
+    auto sorted_perm = [](const char* bytes, const int32_t* off, int n, int32_t* out) {
+        for (int k = 0; k < n; ++k) out[k] = k;
+        std::sort(out, out + n, [&](int32_t x, int32_t y) {
+            const int lx = off[x + 1] - off[x], ly = off[y + 1] - off[y];
+            const int c = memcmp(bytes + off[x], bytes + off[y], (size_t)std::min(lx, ly));
+            return c != 0 ? c < 0 : lx < ly;
+        });
+    };
+    std::vector<int16_t> field_attr((size_t)max_ord + 1, (int16_t)-1);
+    for (int a = 0; a < n_attrs; ++a) field_attr[(size_t)attrs[a].ordinal] = (int16_t)a;
+    std::vector<int32_t> cat_sorted((size_t)std::max(n_cat, 1)), class_sorted((size_t)n_class_values);
+    for (int a = 0; a < n_attrs; ++a)
+        if (attrs[a].kind == AVT_CSV_CATEGORICAL) sorted_perm(cat_bytes, cat_offsets + attrs[a].off, attrs[a].n, cat_sorted.data() + attrs[a].off);
+    sorted_perm(class_bytes, class_offsets, n_class_values, class_sorted.data());
+    const size_t cat_nbytes = n_cat ? (size_t)cat_offsets[n_cat] : 0, class_nbytes = (size_t)class_offsets[n_class_values];
+    // one packed upload: every table 16-byte aligned inside d_csv_tables, the two byte pools in d_csv_bytes
+    std::vector<uint8_t> pack;
+    auto put = [&](const void* src, size_t bytes) {
+        const size_t at = (pack.size() + 15) & ~(size_t)15;
+        pack.resize(at + bytes);
+        if (bytes) memcpy(pack.data() + at, src, bytes);
+        return at;
+    };
+    const size_t o_attrs = put(attrs, (size_t)n_attrs * sizeof(avt_csv_attr)), o_fa = put(field_attr.data(), field_attr.size() * sizeof(int16_t)),
+                 o_ip = put(int_points, (size_t)n_int * 4), o_dp = put(dbl_points, (size_t)n_dbl * 8), o_co = put(cat_offsets, n_cat ? ((size_t)n_cat + 1) * 4 : 0),
+                 o_cs = put(cat_sorted.data(), (size_t)n_cat * 4), o_klo = put(class_offsets, ((size_t)n_class_values + 1) * 4),
+                 o_kls = put(class_sorted.data(), (size_t)n_class_values * 4), o_cb = put(cat_bytes, cat_nbytes), o_kb = put(class_bytes, class_nbytes);
+    if (int rc = use_device(e)) return rc;
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.h2d_ms, &ts)) return rc;
+    CUDA_TRY(e, e->d_csv_tables.ensure(pack.size()));
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_csv_tables.p, pack.data(), pack.size(), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, e->d_csv_text.ensure((size_t)n_bytes + 16));
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_csv_text.p, text, (size_t)n_bytes, cudaMemcpyHostToDevice, e->stream));
+    // ---- line index: newlines per chunk, exclusive prefix sum, row starts
+    const long long n_chunks = (n_bytes + kCsvChunk - 1) / kCsvChunk;
+    CUDA_TRY(e, e->d_csv_counts.ensure((size_t)n_chunks));
+    CUDA_TRY(e, e->d_csv_first.ensure((size_t)n_chunks + 1));
+    csv_count_kernel<<<(unsigned)((n_chunks + 255) / 256), 256, 0, e->stream>>>(e->d_csv_text.p, n_bytes, e->d_csv_counts.p, n_chunks);
+    CUDA_TRY(e, cudaGetLastError());
+    size_t tmp_bytes = 0;
+    CUDA_TRY(e, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, e->d_csv_counts.p, e->d_csv_first.p, (int)n_chunks, e->stream));
+    CUDA_TRY(e, e->d_csv_tmp.ensure(tmp_bytes));
+    CUDA_TRY(e, cub::DeviceScan::ExclusiveSum(e->d_csv_tmp.p, tmp_bytes, e->d_csv_counts.p, e->d_csv_first.p, (int)n_chunks, e->stream));
+    unsigned long long last_first = 0;
+    uint32_t last_count = 0;
+    CUDA_TRY(e, cudaMemcpyAsync(&last_first, e->d_csv_first.p + (n_chunks - 1), sizeof last_first, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(&last_count, e->d_csv_counts.p + (n_chunks - 1), sizeof last_count, cudaMemcpyDeviceToHost, e->stream));
+    if (int rc = sync_and_resolve(e)) return rc;
+    const long long newlines = (long long)last_first + last_count;
+    const bool open_tail = text[n_bytes - 1] != '\n';
+    const long long n_rows = newlines + (open_tail ? 1 : 0);
+    if (n_rows_out) *n_rows_out = n_rows;
+    if (n_rows <= 0) return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: no rows");
+    CUDA_TRY(e, e->d_csv_lines.ensure((size_t)n_rows + 1));
+    const long long first_start = 0, tail_end = n_bytes + 1;   // a virtual '\n' behind an unterminated last row
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_csv_lines.p, &first_start, sizeof first_start, cudaMemcpyHostToDevice, e->stream));
+    if (open_tail) CUDA_TRY(e, cudaMemcpyAsync(e->d_csv_lines.p + n_rows, &tail_end, sizeof tail_end, cudaMemcpyHostToDevice, e->stream));
+    csv_lines_kernel<<<(unsigned)((n_chunks + 255) / 256), 256, 0, e->stream>>>(e->d_csv_text.p, n_bytes, e->d_csv_first.p, e->d_csv_lines.p, n_chunks);
+    CUDA_TRY(e, cudaGetLastError());
+    // ---- the data set's buffers, then one thread per row
+    if (int rc = dataset_shape(e, n_rows, n_attrs, n_bins.data(), n_class_values, "avt_dataset_load_csv")) return rc;
+    CUDA_TRY(e, e->d_csv_ll.ensure((size_t)n_class_values + 2 + ((size_t)kCsvSlowCap * sizeof(CsvSlow) + 7) / 8));
+    std::vector<long long> init((size_t)n_class_values + 2, 0x7fffffffffffffffLL);
+    init[(size_t)n_class_values] = -1LL;   // bad: all ones
+    init[(size_t)n_class_values + 1] = 0;  // n_slow
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_csv_ll.p, init.data(), init.size() * 8, cudaMemcpyHostToDevice, e->stream));
+    CsvArgs ca{};
+    const uint8_t* tb = e->d_csv_tables.p;
+    ca.text = e->d_csv_text.p; ca.n_bytes = n_bytes; ca.line_start = e->d_csv_lines.p; ca.n_rows = n_rows;
+    ca.delim = delim; ca.skip_fields = skip_fields; ca.n_attrs = n_attrs;
+    ca.attrs = (const avt_csv_attr*)(tb + o_attrs); ca.field_attr = (const int16_t*)(tb + o_fa); ca.n_fields_used = (int)field_attr.size();
+    ca.int_points = (const int32_t*)(tb + o_ip); ca.dbl_points = (const double*)(tb + o_dp);
+    ca.cat_bytes = (const char*)(tb + o_cb); ca.cat_offsets = (const int32_t*)(tb + o_co); ca.cat_sorted = (const int32_t*)(tb + o_cs);
+    ca.class_field = class_ordinal; ca.n_class_values = n_class_values;
+    ca.class_bytes = (const char*)(tb + o_kb); ca.class_offsets = (const int32_t*)(tb + o_klo); ca.class_sorted = (const int32_t*)(tb + o_kls);
+    ca.cols = (void* const*)e->d_colptrs.p; ca.wide = e->d_wide.p; ca.cls = e->d_cls.p;
+    ca.class_first_row = e->d_csv_ll.p;
+    ca.bad = (unsigned long long*)(e->d_csv_ll.p + n_class_values);
+    ca.n_slow = (uint32_t*)(e->d_csv_ll.p + n_class_values + 1);
+    ca.slow = (CsvSlow*)(e->d_csv_ll.p + n_class_values + 2);
+    csv_encode_kernel<<<(unsigned)((n_rows + 127) / 128), 128, 0, e->stream>>>(ca);
+    CUDA_TRY(e, cudaGetLastError());
+    std::vector<long long> back((size_t)n_class_values + 2);
+    CUDA_TRY(e, cudaMemcpyAsync(back.data(), e->d_csv_ll.p, back.size() * 8, cudaMemcpyDeviceToHost, e->stream));
+    if (int rc = sync_and_resolve(e)) return rc;
+    unsigned long long bad = (unsigned long long)back[(size_t)n_class_values];
+    const uint32_t n_slow = (uint32_t)(back[(size_t)n_class_values + 1] & 0xffffffffLL);
+    if (n_slow > (uint32_t)kCsvSlowCap)
+        return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: %u values need the host's strtod (limit %d): encode this input on the host", n_slow, kCsvSlowCap);
+    if (n_slow) {
+        // Double.parseDouble inputs outside the device parser's exact range: convert here, patch the codes in
+        std::vector<CsvSlow> slow(n_slow);
+        CUDA_TRY(e, cudaMemcpy(slow.data(), ca.slow, (size_t)n_slow * sizeof(CsvSlow), cudaMemcpyDeviceToHost));
+        std::vector<CsvPatch> patches;
+        for (const CsvSlow& sv : slow) {
+            std::string t(text + sv.start, (size_t)sv.len);
+            size_t b0 = 0, b1 = t.size();
+            while (b0 < b1 && (unsigned char)t[b0] <= ' ') ++b0;
+            while (b1 > b0 && (unsigned char)t[b1 - 1] <= ' ') --b1;
+            t = t.substr(b0, b1 - b0);
+            char* end = nullptr;
+            const double v = t.empty() ? 0.0 : strtod(t.c_str(), &end);
+            if (t.empty() || *end) {
+                bad = std::min(bad, ((unsigned long long)sv.row << 8) | (unsigned long long)AVT_CSV_BAD_DOUBLE);
+                continue;
+            }
+            const avt_csv_attr& A = attrs[sv.attr];
+            const int bin = (int)(std::lower_bound(dbl_points + A.off, dbl_points + A.off + A.n, v) - (dbl_points + A.off));
+            patches.push_back(CsvPatch{sv.row, sv.attr, bin});
+        }
+        if (!patches.empty()) {
+            CsvPatch* d_p = (CsvPatch*)ca.slow;   // the list has been copied out: reuse its storage (24 -> 16 bytes per entry)
+            CUDA_TRY(e, cudaMemcpyAsync(d_p, patches.data(), patches.size() * sizeof(CsvPatch), cudaMemcpyHostToDevice, e->stream));
+            csv_patch_kernel<<<(unsigned)((patches.size() + 127) / 128), 128, 0, e->stream>>>(d_p, (int)patches.size(), (void* const*)e->d_colptrs.p, e->d_wide.p);
+            CUDA_TRY(e, cudaGetLastError());
+            if (int rc = sync_and_resolve(e)) return rc;   // `patches` goes out of scope
+        }
+    }
+    if (bad != ~0ULL) {
+        const long long row = (long long)(bad >> 8);
+        const int reason = (int)(bad & 0xff);
+        if (bad_row) *bad_row = row;
+        if (bad_reason) *bad_reason = reason;
+        e->N = 0;   // nothing is installed
+        static const char* const what[] = {"", "row shorter than an attribute's or the class's ordinal", "NumberFormatException (Integer.parseInt)",
+                                           "NumberFormatException (Double.parseDouble)", "no matching predicate for a categorical value", "class value not in the class list"};
+        return fail(e, AVT_E_REFERENCE, "avt_dataset_load_csv: row %lld: %s", row, what[reason >= 1 && reason <= 5 ? reason : 0]);
+    }
+    if (class_first_row)
+        for (int k = 0; k < n_class_values; ++k) class_first_row[k] = back[(size_t)k] == 0x7fffffffffffffffLL ? -1 : back[(size_t)k];
+    if (int rc = dataset_install(e)) return rc;
+    if (int rc = timer_close(e, ts)) return rc;
+    return sync_and_resolve(e);
+}
+
+int avt_dataset_fetch_column(avt_engine* e, int32_t attr, void* out) {
+    if (!e) return AVT_E_INVALID;
+    if (e->N == 0) return fail(e, AVT_E_STATE, "avt_dataset_fetch_column: no data set loaded");
+    if (!out || attr < -1 || attr >= e->A) return fail(e, AVT_E_INVALID, "avt_dataset_fetch_column: attribute %d out of range", attr);
+    if (int rc = use_device(e)) return rc;
+    if (attr < 0) CUDA_TRY(e, cudaMemcpyAsync(out, e->d_cls.p, (size_t)e->N, cudaMemcpyDeviceToHost, e->stream));
+    else CUDA_TRY(e, cudaMemcpyAsync(out, e->cols[(size_t)attr], (size_t)e->N * (e->wide[(size_t)attr] ? 2 : 1), cudaMemcpyDeviceToHost, e->stream));
     return sync_and_resolve(e);
 }
 

@@ -19,6 +19,14 @@ class EngineError(RuntimeError):
         self.code = code
 
 
+class CsvRowError(EngineError):
+    """avt_dataset_load_csv met a row the reference would throw on (reason = _lib.CSV_BAD_*)."""
+
+    def __init__(self, row: int, reason: int, msg: str):
+        super().__init__(-7, msg)
+        self.row, self.reason = row, reason
+
+
 def _ptr(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
@@ -142,6 +150,57 @@ class Engine:
         self._check(self.lib.avt_dataset_load(self.h, n, len(fixed), nb, ptrs, _ptr(cls), int(n_classes)))
         self.n_rows, self.n_bins, self.n_classes = n, [int(b) for b in n_bins], int(n_classes)
         self.total_bins = sum(self.n_bins)
+
+    def load_csv(self, text: bytes, delim: str, attrs: Sequence[tuple], class_ordinal: int, class_values: Sequence[str],
+                 skip_fields: int = 0):
+        """avt_dataset_load_csv: CSV text -> data set, encoded on the device.  `attrs`: (ordinal, "int", [points]) |
+        (ordinal, "double", [points]) | (ordinal, "categorical", [values]), ordinals increasing.  Returns
+        (n_rows, first row of every class value or -1).  A row the reference would throw on raises CsvRowError."""
+        spec = (_lib.CsvAttr * len(attrs))()
+        ints, dbls, cat_bytes, cat_off, n_bins = [], [], b"", [], []
+        for i, (ordinal, kind, vals) in enumerate(attrs):
+            if kind == "int":
+                spec[i] = _lib.CsvAttr(ordinal, _lib.CSV_INT, len(vals), len(ints))
+                ints.extend(int(v) for v in vals)
+                n_bins.append(len(vals) + 1)
+            elif kind == "double":
+                spec[i] = _lib.CsvAttr(ordinal, _lib.CSV_DOUBLE, len(vals), len(dbls))
+                dbls.extend(float(v) for v in vals)
+                n_bins.append(len(vals) + 1)
+            else:
+                spec[i] = _lib.CsvAttr(ordinal, _lib.CSV_CATEGORICAL, len(vals), len(cat_off))
+                for v in vals:
+                    cat_off.append(len(cat_bytes))
+                    cat_bytes += v.encode()
+                n_bins.append(len(vals))
+        cat_off.append(len(cat_bytes))
+        cls_bytes, cls_off = b"", []
+        for v in class_values:
+            cls_off.append(len(cls_bytes))
+            cls_bytes += v.encode()
+        cls_off.append(len(cls_bytes))
+        ip = np.asarray(ints if ints else [0], dtype=np.int32)
+        dp = np.asarray(dbls if dbls else [0.0], dtype=np.float64)
+        co = np.asarray(cat_off, dtype=np.int32)
+        ko = np.asarray(cls_off, dtype=np.int32)
+        first = np.zeros(len(class_values), dtype=np.int64)
+        n_rows, bad_row, bad_reason = C.c_int64(0), C.c_int64(-1), C.c_int32(0)
+        rc = self.lib.avt_dataset_load_csv(self.h, text, len(text), delim.encode(), skip_fields, len(attrs), spec, _ptr(ip), _ptr(dp),
+                                           cat_bytes if cat_bytes else b"\0", _ptr(co), class_ordinal, len(class_values), cls_bytes, _ptr(ko),
+                                           C.byref(n_rows), _ptr(first), C.byref(bad_row), C.byref(bad_reason))
+        if rc != 0 and bad_row.value >= 0:
+            raise CsvRowError(int(bad_row.value), int(bad_reason.value), self.lib.avt_last_error(self.h).decode())
+        self._check(rc)
+        self.n_rows, self.n_bins, self.n_classes = int(n_rows.value), n_bins, len(class_values)
+        self.total_bins = sum(n_bins)
+        return self.n_rows, [int(x) for x in first]
+
+    def fetch_column(self, attr: int) -> np.ndarray:
+        """The installed data set's codes of one attribute (-1: class codes)."""
+        dt = np.uint8 if attr < 0 or self.n_bins[attr] <= 256 else np.uint16
+        out = np.empty(self.n_rows, dtype=dt)
+        self._check(self.lib.avt_dataset_fetch_column(self.h, attr, _ptr(out)))
+        return out
 
     def forest_init(self, n_trees: int = 1, weights: Optional[Sequence[Optional[np.ndarray]]] = None,
                     node_ids: Optional[Sequence[Optional[np.ndarray]]] = None):

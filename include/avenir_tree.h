@@ -120,6 +120,51 @@ const char* avt_last_error(const avt_engine* e);
 int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins,
                      const void* const* columns, const uint8_t* class_codes, int32_t n_classes);
 
+/* One feature attribute of a CSV row for avt_dataset_load_csv. */
+#define AVT_CSV_INT 0         /* Integer.parseInt, bin = number of grid points < value */
+#define AVT_CSV_DOUBLE 1      /* Double.parseDouble (surrounding blanks ignored), same binning */
+#define AVT_CSV_CATEGORICAL 2 /* bin = index of the value in the attribute's value list */
+typedef struct avt_csv_attr {
+    int32_t ordinal; /* field index in the row (0-based, after `skip_fields` leading fields) */
+    int32_t kind;    /* AVT_CSV_* */
+    int32_t n;       /* grid points (numeric) or values (categorical); bins = n + 1 or n */
+    int32_t off;     /* first entry in int_points / dbl_points / (value index in) cat_offsets */
+} avt_csv_attr;
+
+/* Why avt_dataset_load_csv rejected a row (bad_reason). */
+#define AVT_CSV_BAD_SHORT_ROW 1 /* fewer fields than an attribute's or the class's ordinal needs */
+#define AVT_CSV_BAD_INT 2       /* NumberFormatException of Integer.parseInt */
+#define AVT_CSV_BAD_DOUBLE 3    /* NumberFormatException of Double.parseDouble */
+#define AVT_CSV_BAD_CATEGORY 4  /* value not in the attribute's list ("no matching predicate") */
+#define AVT_CSV_BAD_CLASS 5     /* class value not in class list */
+
+/* Encodes CSV text into the columnar data set ON THE DEVICE and installs it like avt_dataset_load: the step
+ * before the path.  Replaces, per row, the `split(fieldDelimRegex)` + Integer.parseInt /
+ * Double.parseDouble + predicate-grid evaluation of BuilderMapper.pathMapHelper
+ * (tree/DecisionTreeBuilder.java:268, 309-320) and the class extraction of BuilderReducer.reduce (:749).
+ *   text/n_bytes   rows separated by '\n' (a '\r' before it is dropped; the last row may lack the '\n')
+ *   delim          single-byte field delimiter (literal `field.delim.regex`)
+ *   skip_fields    leading fields that are not part of the record (1 for rows tagged with their path)
+ *   attrs          n_attrs attributes, ordinals strictly increasing; numeric grids in int_points / dbl_points
+ *                  (ascending), categorical values as bytes cat_bytes[cat_offsets[off+k] .. cat_offsets[off+k+1])
+ *   class values   n_class_values strings, class_bytes[class_offsets[k] .. class_offsets[k+1]); class code = k
+ *   class_first_row (nullable) [n_class_values]: first row each class value occurs in, -1 = never (lets the
+ *                  caller rebuild the first-seen order the reference's HashMap insertion depends on)
+ * On a row the reference would throw on, returns AVT_E_REFERENCE with *bad_row = the first such row and
+ * *bad_reason = AVT_CSV_BAD_*; nothing is installed.  Values Double.parseDouble accepts but the device parser
+ * cannot convert exactly (more than 15 significant digits, exponent beyond +-22, NaN/Infinity, hex) are
+ * converted on the host with strtod and patched in; more than 65536 such values fail with AVT_E_INVALID. */
+int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char delim, int32_t skip_fields,
+                         int32_t n_attrs, const avt_csv_attr* attrs, const int32_t* int_points,
+                         const double* dbl_points, const char* cat_bytes, const int32_t* cat_offsets,
+                         int32_t class_ordinal, int32_t n_class_values, const char* class_bytes,
+                         const int32_t* class_offsets, int64_t* n_rows, int64_t* class_first_row,
+                         int64_t* bad_row, int32_t* bad_reason);
+
+/* Copies the installed data set's codes back: column `attr` (uint8 or uint16 per row, as in avt_dataset_load;
+ * attr == -1: the class codes).  For tests and for callers that keep a host copy. */
+int avt_dataset_fetch_column(avt_engine* e, int32_t attr, void* out);
+
 /* Starts `n_trees` trees over the loaded rows.  weights == NULL or weights[t] == NULL means
  * multiplicity 1 for every row (dtb.sub.sampling.strategy=none); otherwise weights[t][r] is the
  * number of times row r was drawn for tree t (explore/BaggingSampler.java:101-122 semantics).
