@@ -56,7 +56,8 @@ class Stats(C.Structure):
                 ("hist_alg_bytes", C.c_int64), ("repart_alg_bytes", C.c_int64),
                 ("last_hist_variant", C.c_int32), ("last_hist_replicas", C.c_int32),
                 ("last_hist_grid", C.c_int32), ("last_hist_block", C.c_int32), ("last_hist_smem", C.c_int32),
-                ("reserved0", C.c_int32), ("last_grow_ms", C.c_double)]
+                ("reserved0", C.c_int32), ("last_csv_h2d_ms", C.c_double), ("last_csv_index_ms", C.c_double),
+                ("last_csv_encode_ms", C.c_double), ("last_grow_ms", C.c_double)]
 
 
 # every symbol include/avenir_tree.h declares: name -> (restype, argtypes)

@@ -15,6 +15,7 @@ namespace avt {
 constexpr int kCsvChunk = 128;          // bytes per thread of the line-indexing kernels
 constexpr int kCsvMaxFields = 1024;     // highest field index + 1 that may be referenced
 constexpr int kCsvSlowCap = 65536;      // values left to the host's strtod per call
+constexpr int kCsvStageBytes = 24 * 1024;   // text span of one block of rows staged in shared memory (longer spans: read in place)
 
 struct CsvSlow {                        // one value the device parser could not convert exactly
     long long row;
@@ -176,10 +177,26 @@ __device__ __forceinline__ bool csv_parse_double_exact(const char* p, int len, d
 // first failure met is the one the reference's loop over the attributes would throw on; Java's String.split drops
 // trailing empty fields, so a row is as long as its last non-empty field.
 __global__ void __launch_bounds__(128) csv_encode_kernel(const CsvArgs a) {
-    const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    // the block's rows are one contiguous span of the text: stage it in shared memory with coalesced 16-byte loads
+    // (a thread walking its own row straight from global memory touches a new sector every few bytes)
+    __shared__ __align__(16) char stage[kCsvStageBytes + 16];
+    const long long r0 = (long long)blockIdx.x * blockDim.x;
+    const long long r1 = min(a.n_rows, r0 + blockDim.x);
+    const long long span0 = a.line_start[r0], span1 = min(a.n_bytes, a.line_start[r1]);
+    const long long a0 = span0 & ~15LL;                    // the text buffer is 16-byte aligned and padded by 16 bytes
+    const bool staged = span1 - a0 <= kCsvStageBytes;
+    if (staged) {
+        const int n16 = (int)((span1 - a0 + 15) >> 4);
+        const uint4* src = reinterpret_cast<const uint4*>(a.text + a0);
+        uint4* dst = reinterpret_cast<uint4*>(stage);
+        for (int i = threadIdx.x; i < n16; i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+    const long long r = r0 + threadIdx.x;
     if (r >= a.n_rows) return;
-    const char* row = a.text + a.line_start[r];
-    long long len_ll = a.line_start[r + 1] - 1 - a.line_start[r];
+    const long long row_at = a.line_start[r];
+    const char* row = staged ? stage + (row_at - a0) : a.text + row_at;
+    long long len_ll = a.line_start[r + 1] - 1 - row_at;
     int len = (int)len_ll;
     if (len > 0 && row[len - 1] == '\r') --len;
     int field = -a.skip_fields;     // index after the skipped fields
@@ -225,7 +242,7 @@ __global__ void __launch_bounds__(128) csv_encode_kernel(const CsvArgs a) {
                     } else {
                         // valid or not is the host's call (strtod); bin 0 until it patches the value in
                         const uint32_t k = atomicAdd(a.n_slow, 1u);
-                        if (k < (uint32_t)kCsvSlowCap) a.slow[k] = CsvSlow{r, (long long)(p - a.text), fl, at};
+                        if (k < (uint32_t)kCsvSlowCap) a.slow[k] = CsvSlow{r, row_at + (long long)(p - row), fl, at};
                         bin = 0;
                     }
                 } else {
@@ -245,7 +262,10 @@ __global__ void __launch_bounds__(128) csv_encode_kernel(const CsvArgs a) {
             const int c = csv_find_value(a.class_bytes, a.class_offsets, a.class_sorted, a.n_class_values, p, fl);
             if (c >= 0) {
                 a.cls[r] = (uint8_t)c;
-                atomicMin(reinterpret_cast<unsigned long long*>(a.class_first_row + c), (unsigned long long)r);
+                // first row of the class value: the stored minimum only ever decreases, so a plain look first spares almost
+                // every row the atomic (millions of them on two or three addresses serialise in L2: 1 ms per 2 M rows)
+                if (r < *reinterpret_cast<volatile long long*>(a.class_first_row + c))
+                    atomicMin(reinterpret_cast<unsigned long long*>(a.class_first_row + c), (unsigned long long)r);
                 class_state = 1;
             } else {
                 class_state = 2;

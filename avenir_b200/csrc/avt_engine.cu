@@ -134,6 +134,7 @@ struct avt_engine {
     std::vector<TimerSlot> pending;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> free_events;
     cudaEvent_t tev0 = nullptr, tev1 = nullptr;
+    cudaEvent_t cev[4] = {nullptr, nullptr, nullptr, nullptr};   // avt_dataset_load_csv phases
     cudaEvent_t gev0 = nullptr, gev1 = nullptr;   // around one avt_grow_levels call (stats.last_grow_ms)
     bool gev1_recorded = false;
     avt_stats stats{};
@@ -392,6 +393,7 @@ void avt_destroy(avt_engine* e) {
     for (auto& p : e->free_events) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     if (e->tev0) cudaEventDestroy(e->tev0);
     if (e->tev1) cudaEventDestroy(e->tev1);
+    for (auto& ev : e->cev) if (ev) cudaEventDestroy(ev);
     if (e->gev0) cudaEventDestroy(e->gev0);
     if (e->gev1) cudaEventDestroy(e->gev1);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -556,10 +558,13 @@ int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char 
     if (int rc = use_device(e)) return rc;
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.h2d_ms, &ts)) return rc;
+    for (auto& ev : e->cev) if (!ev) CUDA_TRY(e, cudaEventCreate(&ev));
+    CUDA_TRY(e, cudaEventRecord(e->cev[0], e->stream));
     CUDA_TRY(e, e->d_csv_tables.ensure(pack.size()));
     CUDA_TRY(e, cudaMemcpyAsync(e->d_csv_tables.p, pack.data(), pack.size(), cudaMemcpyHostToDevice, e->stream));
     CUDA_TRY(e, e->d_csv_text.ensure((size_t)n_bytes + 16));
     CUDA_TRY(e, cudaMemcpyAsync(e->d_csv_text.p, text, (size_t)n_bytes, cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaEventRecord(e->cev[1], e->stream));
     // ---- line index: newlines per chunk, exclusive prefix sum, row starts
     const long long n_chunks = (n_bytes + kCsvChunk - 1) / kCsvChunk;
     CUDA_TRY(e, e->d_csv_counts.ensure((size_t)n_chunks));
@@ -586,6 +591,7 @@ int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char 
     if (open_tail) CUDA_TRY(e, cudaMemcpyAsync(e->d_csv_lines.p + n_rows, &tail_end, sizeof tail_end, cudaMemcpyHostToDevice, e->stream));
     csv_lines_kernel<<<(unsigned)((n_chunks + 255) / 256), 256, 0, e->stream>>>(e->d_csv_text.p, n_bytes, e->d_csv_first.p, e->d_csv_lines.p, n_chunks);
     CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaEventRecord(e->cev[2], e->stream));
     // ---- the data set's buffers, then one thread per row
     if (int rc = dataset_shape(e, n_rows, n_attrs, n_bins.data(), n_class_values, "avt_dataset_load_csv")) return rc;
     CUDA_TRY(e, e->d_csv_ll.ensure((size_t)n_class_values + 2 + ((size_t)kCsvSlowCap * sizeof(CsvSlow) + 7) / 8));
@@ -609,9 +615,17 @@ int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char 
     ca.slow = (CsvSlow*)(e->d_csv_ll.p + n_class_values + 2);
     csv_encode_kernel<<<(unsigned)((n_rows + 127) / 128), 128, 0, e->stream>>>(ca);
     CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaEventRecord(e->cev[3], e->stream));
     std::vector<long long> back((size_t)n_class_values + 2);
     CUDA_TRY(e, cudaMemcpyAsync(back.data(), e->d_csv_ll.p, back.size() * 8, cudaMemcpyDeviceToHost, e->stream));
     if (int rc = sync_and_resolve(e)) return rc;
+    {
+        float ms[3] = {0.f, 0.f, 0.f};
+        for (int k = 0; k < 3; ++k) CUDA_TRY(e, cudaEventElapsedTime(&ms[k], e->cev[k], e->cev[k + 1]));
+        e->stats.last_csv_h2d_ms = ms[0];
+        e->stats.last_csv_index_ms = ms[1];
+        e->stats.last_csv_encode_ms = ms[2];   // includes the allocation of the columns on a first call of this shape
+    }
     unsigned long long bad = (unsigned long long)back[(size_t)n_class_values];
     const uint32_t n_slow = (uint32_t)(back[(size_t)n_class_values + 1] & 0xffffffffLL);
     if (n_slow > (uint32_t)kCsvSlowCap)

@@ -100,6 +100,7 @@ typedef struct avt_stats {
     int32_t last_hist_replicas;
     int32_t last_hist_grid, last_hist_block, last_hist_smem;
     int32_t reserved0;
+    double last_csv_h2d_ms, last_csv_index_ms, last_csv_encode_ms; /* last avt_dataset_load_csv: text upload, line index, per-row encode */
     double last_grow_ms; /* device time of the last avt_grow_levels call: CUDA events on the library's stream around everything
                           * the call enqueued, result copies included (host-side argument handling excluded) */
 } avt_stats;

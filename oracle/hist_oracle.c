@@ -479,3 +479,153 @@ int ora_predict(int64_t n_rows, int A, const int32_t* n_bins, const void* const*
     free(bin_off);
     return 0;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * CSV encode.  Plain-C restatement of the reference's per-row parsing
+ * (tree/DecisionTreeBuilder.java:268, 309-320, 749; grid semantics tree/SplitManager.java:256-330) in
+ * the histogram form: checker for avt_dataset_load_csv at sizes the Python restatement
+ * (oracle/encode_literal.py) cannot reach, and the timed CPU baseline of tools/encode_bench.py.
+ * Same arguments as the C-ABI call; out_cols[a] is int32[n_rows], out_cls uint8[n_rows].
+ * Returns the number of rows, or -(row+1) of the first row the reference would throw on.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct { int32_t ordinal, kind, n, off; } ora_csv_attr;
+
+typedef struct {
+    const char* text; int64_t b0, b1, row0, rows, bad;
+    char delim; int skip, n_attrs; const ora_csv_attr* attrs;
+    const int32_t* ip; const double* dp; const char* cb; const int32_t* co;
+    int class_ord, n_class; const char* kb; const int32_t* ko;
+    int32_t* const* out_cols; uint8_t* out_cls;
+} csv_job;
+
+static int find_str(const char* bytes, const int32_t* off, int n, const char* p, int len) {
+    int k;
+    for (k = 0; k < n; ++k)
+        if (off[k + 1] - off[k] == len && memcmp(bytes + off[k], p, (size_t)len) == 0) return k;
+    return -1;
+}
+
+static int parse_int32(const char* p, int len, long long* out) {
+    int i = 0, neg = 0;
+    long long v = 0;
+    if (len <= 0) return 0;
+    if (p[0] == '-' || p[0] == '+') { neg = p[0] == '-'; i = 1; }
+    if (i >= len) return 0;
+    for (; i < len; ++i) {
+        if (p[i] < '0' || p[i] > '9') return 0;
+        v = v * 10 + (p[i] - '0');
+        if (v > 2147483648LL) return 0;
+    }
+    v = neg ? -v : v;
+    if (v > 2147483647LL || v < -2147483648LL) return 0;
+    *out = v;
+    return 1;
+}
+
+static int encode_one(const csv_job* j, const char* row, int len, int64_t r) {
+    const char* fs[64]; int fl[64];
+    int nf = 0, s = 0, i, a, need = j->class_ord;
+    if (len > 0 && row[len - 1] == '\r') --len;
+    for (a = 0; a < j->n_attrs; ++a) if (j->attrs[a].ordinal > need) need = j->attrs[a].ordinal;
+    need += j->skip + 1;
+    if (need > 64) return 0;
+    for (i = 0; i <= len && nf < 64; ++i)
+        if (i == len || row[i] == j->delim) { fs[nf] = row + s; fl[nf] = i - s; ++nf; s = i + 1; }
+    if (i <= len) { /* more than 64 fields: only whether the tail is empty matters for the length */
+        int k; for (k = i; k < len; ++k) if (row[k] != j->delim) { nf = 65; break; }
+    }
+    while (nf > 1 && nf <= 64 && fl[nf - 1] == 0) --nf;          /* String.split drops trailing empty strings */
+    if (nf == 1 && fl[0] == 0 && len > 0) nf = 0;
+    for (a = 0; a < j->n_attrs; ++a) {
+        const ora_csv_attr* A = &j->attrs[a];
+        const int f = A->ordinal + j->skip;
+        int bin = 0, k;
+        if (f >= nf) return 0;
+        if (A->kind == 0) {
+            long long v;
+            if (!parse_int32(fs[f], fl[f], &v)) return 0;
+            for (k = 0; k < A->n && (long long)j->ip[A->off + k] < v; ++k) {}
+            bin = k;
+        } else if (A->kind == 1) {
+            char buf[128]; char* end; double v; int b0 = 0, b1 = fl[f];
+            while (b0 < b1 && (unsigned char)fs[f][b0] <= ' ') ++b0;
+            while (b1 > b0 && (unsigned char)fs[f][b1 - 1] <= ' ') --b1;
+            if (b1 - b0 <= 0 || b1 - b0 >= (int)sizeof buf) return 0;
+            memcpy(buf, fs[f] + b0, (size_t)(b1 - b0)); buf[b1 - b0] = 0;
+            v = strtod(buf, &end);
+            if (*end) return 0;
+            for (k = 0; k < A->n && j->dp[A->off + k] < v; ++k) {}
+            bin = k;
+        } else {
+            bin = find_str(j->cb, j->co + A->off, A->n, fs[f], fl[f]);
+            if (bin < 0) return 0;
+        }
+        j->out_cols[a][r] = bin;
+    }
+    {
+        const int f = j->class_ord + j->skip;
+        int c;
+        if (f >= nf) return 0;
+        c = find_str(j->kb, j->ko, j->n_class, fs[f], fl[f]);
+        if (c < 0) return 0;
+        j->out_cls[r] = (uint8_t)c;
+    }
+    return 1;
+}
+
+static void* csv_count_worker(void* arg) {
+    csv_job* j = (csv_job*)arg;
+    const char* p = j->text + j->b0; const char* e = j->text + j->b1;
+    int64_t c = 0;
+    while (p < e && (p = (const char*)memchr(p, '\n', (size_t)(e - p))) != NULL) { ++c; ++p; }
+    j->rows = c;
+    return NULL;
+}
+
+static void* csv_parse_worker(void* arg) {
+    csv_job* j = (csv_job*)arg;
+    int64_t pos = j->b0, r = j->row0;
+    j->bad = -1;
+    while (pos < j->b1) {
+        const char* nl = (const char*)memchr(j->text + pos, '\n', (size_t)(j->b1 - pos));
+        const int64_t end = nl ? (int64_t)(nl - j->text) : j->b1;
+        if (!encode_one(j, j->text + pos, (int)(end - pos), r) && j->bad < 0) j->bad = r;
+        ++r;
+        pos = end + 1;
+    }
+    return NULL;
+}
+
+int64_t ora_encode_csv(const char* text, int64_t n_bytes, char delim, int skip, int n_attrs, const ora_csv_attr* attrs,
+                       const int32_t* ip, const double* dp, const char* cb, const int32_t* co, int class_ord, int n_class,
+                       const char* kb, const int32_t* ko, int32_t* const* out_cols, uint8_t* out_cls, int n_threads) {
+    csv_job* jobs; pthread_t* th; int i; int64_t rows = 0, bad = -1;
+    if (n_threads < 1) n_threads = 1;
+    jobs = (csv_job*)calloc((size_t)n_threads, sizeof(csv_job));
+    th = (pthread_t*)calloc((size_t)n_threads, sizeof(pthread_t));
+    for (i = 0; i < n_threads; ++i) {   /* byte ranges cut at row boundaries */
+        int64_t b = n_bytes * i / n_threads;
+        if (i > 0) { while (b < n_bytes && text[b - 1] != '\n') ++b; }
+        jobs[i].b0 = b;
+        jobs[i].text = text; jobs[i].delim = delim; jobs[i].skip = skip; jobs[i].n_attrs = n_attrs; jobs[i].attrs = attrs;
+        jobs[i].ip = ip; jobs[i].dp = dp; jobs[i].cb = cb; jobs[i].co = co; jobs[i].class_ord = class_ord; jobs[i].n_class = n_class;
+        jobs[i].kb = kb; jobs[i].ko = ko; jobs[i].out_cols = out_cols; jobs[i].out_cls = out_cls;
+    }
+    for (i = 0; i < n_threads; ++i) jobs[i].b1 = i + 1 < n_threads ? jobs[i + 1].b0 : n_bytes;
+    for (i = 1; i < n_threads; ++i) pthread_create(&th[i], NULL, csv_count_worker, &jobs[i]);
+    csv_count_worker(&jobs[0]);
+    for (i = 1; i < n_threads; ++i) pthread_join(th[i], NULL);
+    for (i = 0; i < n_threads; ++i) {
+        jobs[i].row0 = rows;
+        rows += jobs[i].rows;
+        if (i == n_threads - 1 && n_bytes > 0 && text[n_bytes - 1] != '\n') ++rows;   /* unterminated last row */
+    }
+    if (out_cols) {
+        for (i = 1; i < n_threads; ++i) pthread_create(&th[i], NULL, csv_parse_worker, &jobs[i]);
+        csv_parse_worker(&jobs[0]);
+        for (i = 1; i < n_threads; ++i) pthread_join(th[i], NULL);
+        for (i = 0; i < n_threads; ++i) if (jobs[i].bad >= 0 && (bad < 0 || jobs[i].bad < bad)) bad = jobs[i].bad;
+    }
+    free(jobs); free(th);
+    return bad >= 0 ? -(bad + 1) : rows;
+}

@@ -180,3 +180,46 @@ class OracleEngine:
 def bits(x: float) -> int:
     import struct
     return struct.unpack("<Q", struct.pack("<d", x))[0]
+
+
+class _OraCsvAttr(C.Structure):
+    _fields_ = [("ordinal", C.c_int32), ("kind", C.c_int32), ("n", C.c_int32), ("off", C.c_int32)]
+
+
+def oracle_encode_csv(text: bytes, delim: str, attrs, class_ordinal: int, class_values, skip_fields: int = 0, threads: int = 1,
+                      count_only: bool = False):
+    """oracle/hist_oracle.c:ora_encode_csv.  Returns (columns as int32 arrays, class codes) or the first bad row (int)."""
+    import numpy as np
+    lib = oracle_lib()
+    lib.ora_encode_csv.restype = C.c_int64
+    spec = (_OraCsvAttr * len(attrs))()
+    ints, dbls, cb, co = [], [], b"", []
+    for i, (ordinal, kind, vals) in enumerate(attrs):
+        if kind == "int":
+            spec[i] = _OraCsvAttr(ordinal, 0, len(vals), len(ints)); ints.extend(int(v) for v in vals)
+        elif kind == "double":
+            spec[i] = _OraCsvAttr(ordinal, 1, len(vals), len(dbls)); dbls.extend(float(v) for v in vals)
+        else:
+            spec[i] = _OraCsvAttr(ordinal, 2, len(vals), len(co))
+            for v in vals:
+                co.append(len(cb)); cb += v.encode()
+    co.append(len(cb))
+    kb, ko = b"", []
+    for v in class_values:
+        ko.append(len(kb)); kb += v.encode()
+    ko.append(len(kb))
+    ip = np.asarray(ints or [0], dtype=np.int32); dp = np.asarray(dbls or [0.0], dtype=np.float64)
+    coa = np.asarray(co, dtype=np.int32); koa = np.asarray(ko, dtype=np.int32)
+    args = [C.c_char_p(text), C.c_int64(len(text)), C.c_char(delim.encode()), C.c_int(skip_fields), C.c_int(len(attrs)), spec,
+            C.c_void_p(ip.ctypes.data), C.c_void_p(dp.ctypes.data), C.c_char_p(cb or b"\0"), C.c_void_p(coa.ctypes.data),
+            C.c_int(class_ordinal), C.c_int(len(class_values)), C.c_char_p(kb), C.c_void_p(koa.ctypes.data)]
+    n = lib.ora_encode_csv(*args, None, None, C.c_int(threads))
+    if count_only:
+        return int(n)
+    cols = [np.zeros(n, dtype=np.int32) for _ in attrs]
+    cls = np.zeros(n, dtype=np.uint8)
+    ptrs = (C.c_void_p * len(cols))(*[c.ctypes.data for c in cols])
+    rc = lib.ora_encode_csv(*args, ptrs, C.c_void_p(cls.ctypes.data), C.c_int(threads))
+    if rc < 0:
+        return int(-rc - 1)
+    return cols, cls

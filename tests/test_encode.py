@@ -124,3 +124,34 @@ def test_csv_path_grows_the_same_tree_as_encoded_columns():
         (rec, nrec), frontier = e.grow(6, CRIT_ENTROPY, [1], max_records=2048)
         out.append(([(r.level, r.node, r.split, list(r.child_pop), r.min_av.hex()) for r in rec[:nrec]], frontier, e.node_ids(0).copy()))
     assert out[0][0] == out[1][0] and out[0][1] == out[1][1] and np.array_equal(out[0][2], out[1][2])
+
+
+def test_c_restatement_equals_python_restatement():
+    """oracle/hist_oracle.c:ora_encode_csv (the checker at large sizes and the timed CPU baseline) against
+    oracle/encode_literal.py, accepted rows and first rejected row."""
+    from tests import helpers
+    rng = np.random.default_rng(3)
+    attrs, classes, text, lines = random_schema_text(rng, 4000)
+    cols, cls, first, bad = enc.encode_text(text + "\n", ",", attrs, 5, classes)
+    for threads in (1, 5):
+        got_cols, got_cls = helpers.oracle_encode_csv((text + "\n").encode(), ",", attrs, 5, classes, threads=threads)
+        assert all(np.array_equal(got_cols[a], np.asarray(cols[a])) for a in range(len(attrs))) and np.array_equal(got_cls, np.asarray(cls))
+    lines[1234] = lines[1234].replace(",", ",z", 1)        # attribute 1 (double) of row 1234 becomes unparsable
+    lines[3000] = "7"
+    assert enc.encode_text("\n".join(lines), ",", attrs, 5, classes)[3][0] == 1234
+    assert helpers.oracle_encode_csv("\n".join(lines).encode(), ",", attrs, 5, classes, threads=3) == 1234
+
+
+@pytest.mark.gpu
+def test_device_encode_two_million_rows_equals_c_restatement():
+    from avenir_b200.engine import Engine
+    from tests import helpers
+    n = 2_000_000
+    text = ("\n".join(synth.call_hangup_csv(n)) + "\n").encode()
+    cols, cls = helpers.oracle_encode_csv(text, ",", HANGUP_ATTRS, 6, ["T", "F"], threads=8)
+    g = Engine(0)
+    rows, first = g.load_csv(text, ",", HANGUP_ATTRS, 6, ["T", "F"])
+    assert rows == n == len(cls) and min(first) == 0
+    for a in range(4):
+        assert np.array_equal(g.fetch_column(a), cols[a].astype(np.uint8))
+    assert np.array_equal(g.fetch_column(-1), cls)
