@@ -191,6 +191,8 @@ struct avt_engine {
     bool ticket2_zeroed = false;
     uint32_t* H_cur = nullptr;         // histogram buffer of the pass being launched (nullptr: d_H)
     bool signal_pending = false;       // the pass being launched must signal peer.epoch to every rank
+    bool peer_signal_scan = true;      // AVT_PEER_SIGNAL_SCAN=0: the histogram pass's last block signals (fence + election in every block)
+    bool scan_will_signal = false;     // set by the stream-ordered level loop around its launch_histogram call
     bool signal_in_hist = false;       // ... and did so from inside the histogram kernel
 };
 
@@ -352,6 +354,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_PERSISTENT")) e->persistent = atoi(v) != 0;
     if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
     if (const char* v = getenv("AVT_SCAN_FAST")) e->scan_fast = atoi(v) != 0;
+    if (const char* v = getenv("AVT_PEER_SIGNAL_SCAN")) e->peer_signal_scan = atoi(v) != 0;
     if (const char* v = getenv("AVT_PEER_TRAIL")) e->peer_trailing_round = atoi(v) != 0;
     if (const char* v = getenv("AVT_LOOKBACK")) e->lookback = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
@@ -963,7 +966,9 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         if (ha.skip) smem += (size_t)n_max + 16;   // skip marks of the frontier, staged behind the histogram (and the repartition tables)
         dim3 grid((unsigned)e->T, (unsigned)chunks, (unsigned)G);
         e->signal_in_hist = false;
-        if (e->signal_pending) {
+        if (e->signal_pending && e->peer_signal_scan && e->scan_will_signal) {
+            e->signal_in_hist = true;   // nothing to do here: the scan kernel behind this pass signals (PlanArgs::signal_flags)
+        } else if (e->signal_pending) {
             CUDA_TRY(e, e->d_ticket2.ensure(1));
             if (!e->ticket2_zeroed) {
                 CUDA_TRY(e, cudaMemsetAsync(e->d_ticket2.p, 0, sizeof(uint32_t), e->stream));
@@ -1555,7 +1560,10 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             all_peer = false;
         }
         e->signal_pending = peer_level;
+        e->scan_will_signal = peer_level;
         if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr, nb_level(level))) return rc;
+        e->scan_will_signal = false;
+        const bool scan_signals = peer_level && e->peer_signal_scan && e->stats.last_hist_variant == 0;
         e->skip_h_memset = false;
         e->pdl_chain = false;
         e->H_cur = nullptr;
@@ -1606,6 +1614,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             pa.h_sum = Hc;
             pa.peer_epoch = e->peer.epoch;
             pa.n_ranks = e->peer.n;
+            if (scan_signals) pa.signal_flags = e->d_remote_flags.p;
         }
         if (subtract) {
             const bool next_plannable = level + 1 < n_levels;

@@ -29,6 +29,8 @@ struct PlanArgs {
     uint32_t* h_sum;                // local buffer that receives the summed histogram (== the kernel's H argument)
     uint32_t peer_epoch;
     int n_ranks;
+    uint32_t* const* signal_flags;  // [n_ranks] non-null: THIS kernel tells the ranks that this rank's histogram is complete (its first
+                                    // block, right after the wait for the histogram pass) instead of the pass's last block
     // sibling subtraction: the most populous child of every split is NOT counted by the next histogram pass; its
     // counts are derived as parent - (other children), exact in integers, by that child's scan block
     uint8_t* next_skip;         // [NF_next] 1 = derived (nullptr: subtraction off)
@@ -378,6 +380,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_kernel(const uint32_t* H, S
     __shared__ int s_is_last;
     pdl_launch_dependents();
     pdl_wait();   // the histogram (and the frontier size) come from the previous launch
+    if (plan.signal_flags && blockIdx.x == 0 && (int)threadIdx.x < plan.n_ranks)
+        st_release_sys(plan.signal_flags[threadIdx.x], plan.peer_epoch);   // the pass is complete: its counts are in this GPU's L2
     const int node = blockIdx.x;
     if (!(n_nodes_dev && node >= *n_nodes_dev)) scan_node(H, st, cand_mask, order_g, criterion, av_buf, out, best_eval, node, plan);
     if (plan.ticket == nullptr) return;

@@ -163,6 +163,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
     }
     const int B0 = st.bin_off[1] - st.bin_off[0];
     pdl_wait();   // the histogram (and the frontier) come from the previous launch
+    if (plan.signal_flags && blockIdx.x == 0 && tid < plan.n_ranks)
+        st_release_sys(plan.signal_flags[tid], plan.peer_epoch);   // the pass is complete: its counts are in this GPU's L2
     __syncthreads();
     const int node = blockIdx.x;
     const bool lookback = ft.pub != nullptr;
