@@ -177,10 +177,12 @@ struct avt_engine {
         // Peer levels are numbered across calls; level k uses exchange buffer k & 1.  A rank zeroes or writes buffer k & 1
         // only after it has seen every rank's flag of level k-1, i.e. after every rank finished reading that buffer at
         // level k-2 -- so consecutive level-loop calls need no extra round of flags between them.
+        size_t recv_off_words = 0;     // receive slots of the push exchange behind the histogram buffers (in uint32 words from the arena's start)
         unsigned long long seq = 0;
         bool lazy = false;             // the last level loop ended without a trailing flag round (see grow_device_loop)
     } peer;
     DevBuf<const uint32_t*> d_peer_H[2];
+    DevBuf<unsigned long long*> d_push_dst[2];   // per buffer: this rank's slot array inside every rank's arena
     DevBuf<uint32_t*> d_remote_flags;
     DevBuf<uint32_t> d_hsum, d_hsum2, d_H2, d_ticket2;
     DevBuf<uint8_t> d_skip;
@@ -191,6 +193,7 @@ struct avt_engine {
     bool ticket2_zeroed = false;
     uint32_t* H_cur = nullptr;         // histogram buffer of the pass being launched (nullptr: d_H)
     bool signal_pending = false;       // the pass being launched must signal peer.epoch to every rank
+    bool peer_push = true;             // AVT_PEER_PUSH=0: always the pull form of the peer exchange
     bool peer_signal_scan = true;      // AVT_PEER_SIGNAL_SCAN=0: the histogram pass's last block signals (fence + election in every block)
     bool scan_will_signal = false;     // set by the stream-ordered level loop around its launch_histogram call
     bool signal_in_hist = false;       // ... and did so from inside the histogram kernel
@@ -355,6 +358,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
     if (const char* v = getenv("AVT_SCAN_FAST")) e->scan_fast = atoi(v) != 0;
     if (const char* v = getenv("AVT_PEER_SIGNAL_SCAN")) e->peer_signal_scan = atoi(v) != 0;
+    if (const char* v = getenv("AVT_PEER_PUSH")) e->peer_push = atoi(v) != 0;
     if (const char* v = getenv("AVT_PEER_TRAIL")) e->peer_trailing_round = atoi(v) != 0;
     if (const char* v = getenv("AVT_LOOKBACK")) e->lookback = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
@@ -380,7 +384,7 @@ void avt_destroy(avt_engine* e) {
     for (int r = 0; r < e->peer.n; ++r)
         if (r != e->peer.rank && e->peer.base[r]) cudaIpcCloseMemHandle(e->peer.base[r]);
     if (e->peer.arena) cudaFree(e->peer.arena);
-    e->d_peer_H[0].release(); e->d_peer_H[1].release(); e->d_remote_flags.release(); e->d_hsum.release(); e->d_ticket2.release(); e->d_hsum2.release(); e->d_H2.release(); e->d_skip.release(); e->d_drv_parent.release(); e->d_kids.release();
+    e->d_peer_H[0].release(); e->d_peer_H[1].release(); e->d_push_dst[0].release(); e->d_push_dst[1].release(); e->d_remote_flags.release(); e->d_hsum.release(); e->d_ticket2.release(); e->d_hsum2.release(); e->d_H2.release(); e->d_skip.release(); e->d_drv_parent.release(); e->d_kids.release();
     for (void* c : e->cols)
         if (c) cudaFree(c);
     e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
@@ -1559,11 +1563,15 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         } else {
             all_peer = false;
         }
+        const bool push_ok = peer_level && fast_scan && e->peer_push && e->peer.n > 1 && (long long)e->TB * e->C <= kPushWords &&
+                             (long long)NF * e->TB * e->C <= kPushCap;
         e->signal_pending = peer_level;
         e->scan_will_signal = peer_level;
         if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr, nb_level(level))) return rc;
         e->scan_will_signal = false;
-        const bool scan_signals = peer_level && e->peer_signal_scan && e->stats.last_hist_variant == 0;
+        // small levels: push form of the exchange (no flags at all); needs the item-parallel scan kernel behind a shared-memory pass
+        const bool push_level = peer_level && push_ok;
+        const bool scan_signals = peer_level && !push_level && e->peer_signal_scan && e->stats.last_hist_variant == 0;
         e->skip_h_memset = false;
         e->pdl_chain = false;
         e->H_cur = nullptr;
@@ -1615,6 +1623,14 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             pa.peer_epoch = e->peer.epoch;
             pa.n_ranks = e->peer.n;
             if (scan_signals) pa.signal_flags = e->d_remote_flags.p;
+            if (push_level) {
+                pa.peer_H = nullptr;   // nothing is pulled
+                pa.push_dst = e->d_push_dst[par].p;
+                pa.push_recv = reinterpret_cast<const unsigned long long*>(e->peer.arena + e->peer.recv_off_words) + (size_t)par * 16 * kPushCap;
+                pa.H_local = arena_H(par);
+                pa.push_cap = kPushCap;
+                pa.my_rank = e->peer.rank;
+            }
         }
         if (subtract) {
             const bool next_plannable = level + 1 < n_levels;
@@ -2171,7 +2187,9 @@ int avt_peer_export(avt_engine* e, void* handle64) {
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
     if (!e->peer.arena) {
         e->peer.cap_words = (size_t)2 << 20;  // 8 MiB per histogram buffer
-        const size_t bytes = (64 + 2 * e->peer.cap_words) * sizeof(uint32_t);
+        e->peer.recv_off_words = 64 + 2 * e->peer.cap_words;
+        // + receive slots of the push exchange: 2 buffers x 16 source ranks x kPushCap 64-bit (tag, count) words
+        const size_t bytes = e->peer.recv_off_words * sizeof(uint32_t) + (size_t)2 * 16 * kPushCap * sizeof(unsigned long long);
         CUDA_TRY(e, cudaMalloc((void**)&e->peer.arena, bytes));
         CUDA_TRY(e, cudaMemset(e->peer.arena, 0, bytes));
     }
@@ -2206,6 +2224,12 @@ int avt_peer_import(avt_engine* e, int32_t n_ranks, int32_t rank, const void* ha
     if (int rc = upload(e, e->d_peer_H[0], h0.data(), h0.size())) return rc;
     if (int rc = upload(e, e->d_peer_H[1], h1.data(), h1.size())) return rc;
     if (int rc = upload(e, e->d_remote_flags, rf.data(), rf.size())) return rc;
+    for (int par = 0; par < 2; ++par) {
+        std::vector<unsigned long long*> dst((size_t)n_ranks);
+        for (int r = 0; r < n_ranks; ++r)
+            dst[(size_t)r] = reinterpret_cast<unsigned long long*>((uint32_t*)e->peer.base[r] + e->peer.recv_off_words) + ((size_t)par * 16 + (size_t)rank) * kPushCap;
+        if (int rc = upload(e, e->d_push_dst[par], dst.data(), dst.size())) return rc;
+    }
     e->peer.epoch = 0;
     e->peer.seq = 0;
     e->peer.lazy = false;

@@ -29,6 +29,12 @@ struct PlanArgs {
     uint32_t* h_sum;                // local buffer that receives the summed histogram (== the kernel's H argument)
     uint32_t peer_epoch;
     int n_ranks;
+    // push form of the peer exchange (small levels, item-parallel scan): each node's block stores its partial counts as
+    // (tag << 32 | count) words into every other rank's receive slots and polls its own slots -- local memory only
+    unsigned long long* const* push_dst;    // [n_ranks] this rank's slot array inside rank d's memory (nullptr: pull form or single GPU)
+    const unsigned long long* push_recv;    // local: slots of source rank s at [s * push_cap, (s + 1) * push_cap)
+    const uint32_t* H_local;                // this rank's partial counts of the level
+    int push_cap, my_rank;
     uint32_t* const* signal_flags;  // [n_ranks] non-null: THIS kernel tells the ranks that this rank's histogram is complete (its first
                                     // block, right after the wait for the histogram pass) instead of the pass's last block
     // sibling subtraction: the most populous child of every split is NOT counted by the next histogram pass; its

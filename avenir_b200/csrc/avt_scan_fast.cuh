@@ -33,6 +33,8 @@ struct FastTable {
 };
 
 constexpr int kLookbackNodes = 512;
+constexpr int kPushWords = 1024;    // push form of the peer exchange: counters per node (bins x classes) at most
+constexpr int kPushCap = 1 << 16;   // ... and counters per level (receive slots per source rank and buffer)
 
 __device__ __forceinline__ void st_relaxed_gpu(uint32_t* p, uint32_t v) {
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -128,6 +130,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
     __shared__ int s_running;
     __shared__ int s_is_last;
     __shared__ int s_first[kScanThreads];
+    __shared__ uint32_t s_sum[kPushWords];   // push exchange: the node's counts summed over the ranks
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int C = st.C;
     pdl_launch_dependents();
@@ -174,6 +177,47 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
             while ((int32_t)(ld_acquire_sys(plan.peer_flags + tid) - plan.peer_epoch) < 0) {}
         __syncthreads();
     }
+    const int n_nodes = *n_nodes_dev;
+    const bool push = plan.push_dst != nullptr;
+    if (push && n_nodes > 0) {
+        // Push form of the exchange.  Tags are the level's epoch, so the slots never need clearing; slot buffers alternate
+        // by level like the histogram buffers.  A rank's words for a node arrive only after that rank finished its previous
+        // scan, so "all ranks' words are here" also licenses clearing the next level's histogram buffer below.
+        const int words = st.TB * C;
+        const int src_node = node < n_nodes ? node : 0;             // blocks without a node only wait (on node 0's first word)
+        const long long off = (long long)src_node * words;
+        const int others = plan.n_ranks - 1;
+        const unsigned long long tag = (unsigned long long)plan.peer_epoch << 32;
+        if (node < n_nodes) {
+            for (int q = tid; q < words * others; q += blockDim.x) {
+                const int w = q / others, k = q - w * others;
+                const int d = k + (k >= plan.my_rank);
+                st_relaxed_sys_u64(plan.push_dst[d] + off + w, tag | __ldcg(plan.H_local + off + w));
+            }
+            for (int w = tid; w < words; w += blockDim.x) s_sum[w] = __ldcg(plan.H_local + off + w);
+            __syncthreads();
+        }
+        const int n_poll = node < n_nodes ? words * others : others;
+        bool timeout = false;
+        for (int q = tid; q < n_poll; q += blockDim.x) {
+            const int w = node < n_nodes ? q / others : 0, k = node < n_nodes ? q - w * others : q;
+            const int src = k + (k >= plan.my_rank);
+            const unsigned long long* slot = plan.push_recv + (long long)src * plan.push_cap + off + w;
+            unsigned long long v = 0;
+            for (int spin = 0;; ++spin) {
+                v = ld_relaxed_sys_u64(slot);
+                if ((v >> 32) == plan.peer_epoch) break;
+                if (spin > (1 << 24)) { timeout = true; break; }   // never hang the GPU: report instead
+            }
+            if (node < n_nodes) atomicAdd(&s_sum[w], (uint32_t)v);
+        }
+        if (timeout) *plan.err = 2;
+        __syncthreads();
+        if (node < n_nodes) {
+            for (int w = tid; w < words; w += blockDim.x) plan.h_sum[off + w] = s_sum[w];
+            __syncthreads();
+        }
+    }
     if (lookback && plan.zero_ptr) {
         // every block clears its share of the next level's histogram region (nobody reads that buffer any more:
         // it held the counts of the level before this one)
@@ -181,7 +225,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
         const long long z1 = min(plan.zero_words, (long long)(blockIdx.x + 1) * per);
         for (long long i = (long long)blockIdx.x * per + tid; i < z1; i += blockDim.x) plan.zero_ptr[i] = 0;
     }
-    if (node < *n_nodes_dev) {
+    if (node < n_nodes) {
         if (plan.peer_H) {
             // every rank's partial counts for this node, pulled over NVLink and summed (see scan_node)
             const long long words = (long long)st.TB * C, off = (long long)node * words;
@@ -379,7 +423,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
     }
     if (lookback) {
         // an empty frontier has no block that owns the next level's node_base: block 0 writes it (all zero)
-        if (blockIdx.x == 0 && *n_nodes_dev == 0)
+        if (blockIdx.x == 0 && n_nodes == 0)
             for (int k = tid; k <= plan.n_trees; k += blockDim.x) plan.next_node_base[k] = 0;
         return;
     }
