@@ -91,7 +91,7 @@ struct avt_engine {
     DevBuf<int32_t> d_bounds, d_attr_first;
     DevBuf<uint8_t> d_seg_lut;
     // on-device CSV encode (avt_csv.cuh): text, line index, scan scratch, tables, results
-    DevBuf<char> d_csv_text, d_csv_bytes;
+    DevBuf<char> d_csv_text;
     DevBuf<uint32_t> d_csv_counts;
     DevBuf<unsigned long long> d_csv_first;
     DevBuf<long long> d_csv_lines, d_csv_ll;
@@ -127,7 +127,6 @@ struct avt_engine {
     // device-driven level loop
     DevBuf<int32_t> d_prev_node_base, d_next_count, d_err, d_nb_all;
     DevBuf<uint32_t> d_ticket;
-    DevBuf<unsigned int> d_tile_ctr;
     DevBuf<avt_split_eval> d_best_eval;
     DevBuf<avt_grow_record> d_records;
     // timing
@@ -388,10 +387,10 @@ void avt_destroy(avt_engine* e) {
     for (void* c : e->cols)
         if (c) cudaFree(c);
     e->d_colptrs.release(); e->d_cls.release(); e->d_bin_off.release(); e->d_wide.release();
-    e->d_nid.release(); e->d_levels.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_tile_ctr.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
+    e->d_nid.release(); e->d_levels.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
-    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_bytes.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_pub.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
+    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_pub.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release(); e->d_ctrl.release();
     if (e->h_ctrl) cudaFreeHost(e->h_ctrl);
@@ -550,7 +549,7 @@ int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char 
         if (attrs[a].kind == AVT_CSV_CATEGORICAL) sorted_perm(cat_bytes, cat_offsets + attrs[a].off, attrs[a].n, cat_sorted.data() + attrs[a].off);
     sorted_perm(class_bytes, class_offsets, n_class_values, class_sorted.data());
     const size_t cat_nbytes = n_cat ? (size_t)cat_offsets[n_cat] : 0, class_nbytes = (size_t)class_offsets[n_class_values];
-    // one packed upload: every table 16-byte aligned inside d_csv_tables, the two byte pools in d_csv_bytes
+    // one packed upload: every table (and the two byte pools) 16-byte aligned inside d_csv_tables
     std::vector<uint8_t> pack;
     auto put = [&](const void* src, size_t bytes) {
         const size_t at = (pack.size() + 15) & ~(size_t)15;

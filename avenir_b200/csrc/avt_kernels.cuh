@@ -1,7 +1,10 @@
 // Hand-written sm_100a kernels of the split-evaluation path.
 //   (a) hist_smem_kernel / hist_global_kernel : (tree,node,attr,bin,class) count histograms
 //   (b) scan_kernel / eval_kernel / cpg_kernel: fused fp64 impurity scan + per-node arg-min
-//   (c) repartition_kernel                    : row -> child node
+//       scan_fast_kernel (avt_scan_fast.cuh)  : latency-optimised scan + level planning for small split tables
+//   (c) repartition_kernel / repartition_fast_kernel : row -> child node
+//       csv_* kernels (avt_csv.cuh)           : CSV text -> bin codes (the step before the path)
+//       predict_kernel (avt_predict.cuh)      : scoring with the emitted models
 // All of it is HBM-/atomic-bound integer work: no tensor cores (DESIGN.md "Roofline").
 #pragma once
 #include "avt_device.cuh"
