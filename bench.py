@@ -5,7 +5,8 @@
 
 Workload at every N: config C2 of BASELINE.json -- the call_hangup decision tree (resource/call_hangup.json
 schema: 4 feature attributes, 18 bins, 18 binary candidate splits, 2 classes), 10 M synthetic rows PER
-GPU (weak scaling: rows shard across ranks, the per-level histograms are all-reduced over NCCL),
+GPU (weak scaling: rows shard across ranks, the per-level histograms are exchanged through NVLink peer memory
+inside the scan kernel; AVT_BENCH_NCCL=1 uses one NCCL all-reduce per level instead),
 entropy, attribute strategy `all`, 8 expansions below the root.  A "step" builds the whole tree once:
 8 x (histogram -> fused entropy scan/arg-min -> children statistics -> repartition).
 
@@ -287,7 +288,9 @@ def main():
             "config": {"workload": "C2: call_hangup decision tree (call_hangup.json schema), entropy, attribute strategy all, 8 expansions",
                        "rows_per_gpu": N, "levels": L, "attrs": 4, "bins": 18, "splits": 18, "classes": 2, "trees": 1,
                        "l2": "flushed between steps (256 MiB memset); the 70 MB working set is L2-resident within a step",
-                       "final_frontier_nodes": int(frontier[0]), "parallelism": f"rows sharded over {world} rank(s), per-level histograms summed out of NVLink peer memory inside the scan kernel" if world > 1 and os.environ.get("AVT_BENCH_NCCL") != "1" else f"rows sharded over {world} rank(s), NCCL all-reduce of uint32 histograms"},
+                       "final_frontier_nodes": int(frontier[0]), "parallelism": (f"rows sharded over {world} ranks, per-level histograms exchanged through NVLink peer memory inside the scan kernel (no NCCL call on the path)"
+                                       if world > 1 and os.environ.get("AVT_BENCH_NCCL") != "1" else
+                                       (f"rows sharded over {world} ranks, NCCL all-reduce of uint32 histograms per level" if world > 1 else "1 rank (no exchange)"))},
             "kernel_ms_per_step": {"histogram": st.hist_ms / prof_steps, "scan_plan": st.scan_ms / prof_steps, "eval": st.eval_ms / prof_steps,
                                    "repartition": st.repart_ms / prof_steps, "allreduce": st.comm_ms / prof_steps,
                                    "note": f"CUDA events per launch, from {prof_steps} extra profiled steps"},
