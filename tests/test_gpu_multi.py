@@ -1,5 +1,6 @@
 """Multi-GPU parity (needs >= 2 GPUs; skipped otherwise): rows sharded over 2 ranks, histograms summed by
-NCCL inside the library, against the single-GPU run on all rows -- shard-count invariance, bit for bit."""
+NCCL, or exchanged through NVLink peer memory inside the scan kernel (push and pull form), against the single-GPU
+run on all rows -- shard-count invariance, bit for bit."""
 import os
 
 import numpy as np
@@ -20,6 +21,8 @@ def _worker(rank, world, port, n, levels, out_dir, peer):
     from avenir_b200.sharding import connect_peers, share_unique_id
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
+    if peer == "pull":
+        os.environ["AVT_PEER_PUSH"] = "0"     # flags + pull out of the ranks' buffers (what large levels and the general scan kernel use)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
@@ -47,12 +50,12 @@ def _worker(rank, world, port, n, levels, out_dir, peer):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("peer", [False, True], ids=["nccl", "nvlink-peer"])
+@pytest.mark.parametrize("peer", [False, True, "pull"], ids=["nccl", "nvlink-peer-push", "nvlink-peer-pull"])
 def test_two_gpus_equal_one(tmp_path, peer):
     import torch.multiprocessing as mp
     from avenir_b200.engine import Engine
     n, levels = 1_000_003, 6
-    mp.spawn(_worker, args=(2, 29400 + os.getpid() % 500 + int(peer), n, levels, str(tmp_path), peer), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, 29400 + os.getpid() % 500 + [False, True, "pull"].index(peer), n, levels, str(tmp_path), peer), nprocs=2, join=True)
     cols, cls, n_bins, _ = synth.call_hangup_encoded(n)
     eng = Engine(0)
     eng.load_dataset(cols, cls, n_bins, 2)
