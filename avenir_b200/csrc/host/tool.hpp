@@ -15,6 +15,9 @@ int run_class_partition_generator(const Props& conf, const std::string& in_path,
 // org.avenir.model.ModelPredictor.run(args)  (model/ModelPredictor.java:52-68)
 int run_model_predictor(const Props& conf, const std::string& in_path, const std::string& out_path);
 
+// org.avenir.explore.CramerCorrelation.run(args)  (explore/CramerCorrelation.java:56-81)
+int run_cramer_correlation(const Props& conf, const std::string& in_path, const std::string& out_path);
+
 // Input "path" as Hadoop takes it: a file, or a directory whose regular files (not starting with
 // '_' or '.') are read in name order.
 std::vector<std::string> read_input_lines(const std::string& path);

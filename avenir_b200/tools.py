@@ -50,10 +50,14 @@ class ModelPredictor(_Tool):
     java_class = "org.avenir.model.ModelPredictor"
 
 
+class CramerCorrelation(_Tool):
+    java_class = "org.avenir.explore.CramerCorrelation"
+
+
 def main(argv: List[str] | None = None) -> int:
     argv = list(sys.argv[1:] if argv is None else argv)
     if not argv:
-        print("usage: python -m avenir_b200 <DecisionTreeBuilder|ClassPartitionGenerator> -Dconf.path=<props> <in> <out>", file=sys.stderr)
+        print("usage: python -m avenir_b200 <DecisionTreeBuilder|ClassPartitionGenerator|ModelPredictor|CramerCorrelation> -Dconf.path=<props> <in> <out>", file=sys.stderr)
         return 2
     tool = _Tool()
     tool.java_class = argv[0]

@@ -1,0 +1,100 @@
+"""
+ORACLE / TEST INFRASTRUCTURE ONLY -- never imported by the product (avenir_b200/).
+
+Literal restatement of org.avenir.explore.CramerCorrelation, row by row and matrix by matrix:
+  explore/CramerCorrelation.java:104-141   mapper set-up: one ContingencyMatrix per (source, destination) pair with
+                                           src != dst, pairs in source-major order; the destination field list is
+                                           built while the FIRST source attribute is handled
+  explore/CramerCorrelation.java:157-183   map: items = row.split(delim); for every source field, for every
+                                           destination field: matrix of attrPairs[k++] gets increment(srcIndex, dstIndex)
+  explore/CramerCorrelation.java:146-152   cleanup: every pair's matrix is emitted
+  explore/CramerCorrelation.java:215-235   reduce (keys sorted): sum the matrices, `srcName,dstName,cramerIndex`
+  util/ContingencyMatrix.java:87-124       cramerIndex
+PARITY UNPINNED (no JVM, no reference tests for this job).  chombo's FeatureField.cardinalityIndex is taken to be
+List.indexOf (-1 when absent => ArrayIndexOutOfBoundsException in TabularData.increment); Tuple keys are taken to
+sort element by element.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence, Tuple
+
+from .javaemu import double_to_string
+from .literal import FeatureSchema, java_split
+
+
+class ArrayIndexOutOfBounds(Exception):
+    """The reference's mapper would die with an ArrayIndexOutOfBoundsException / IndexOutOfBoundsException here."""
+
+
+def cramer_index(table: List[List[int]]) -> float:
+    """ContingencyMatrix.cramerIndex (util/ContingencyMatrix.java:87-124)."""
+    n_row, n_col = len(table), len(table[0])
+    row_sum = []
+    for i in range(n_row):
+        s = 0
+        for j in range(n_col):
+            s += table[i][j]
+        row_sum.append(1 if s == 0 else s)
+    col_sum = []
+    for j in range(n_col):
+        s = 0
+        for i in range(n_row):
+            s += table[i][j]
+        col_sum.append(1 if s == 0 else s)
+    pearson = 0.0
+    for i in range(n_row):
+        for j in range(n_col):
+            pearson += (float(table[i][j]) * table[i][j]) / (float(row_sum[i]) * col_sum[j])
+    pearson -= 1.0
+    smaller = n_row if n_row < n_col else n_col
+    return pearson / (smaller - 1)
+
+
+def cramer_correlation(lines: Sequence[str], conf: Dict[str, str], schema: FeatureSchema) -> List[str]:
+    """The whole job with one mapper and one reducer: output lines of part-r-00000."""
+    delim_regex = conf.get("field.delim.regex", ",")
+    delim_out = conf.get("field.delim.out", ",")
+    source = [int(x) for x in conf["crc.source.attributes"].split(",")]
+    dest = [int(x) for x in conf["crc.dest.attributes"].split(",")]
+    # ---- mapper set-up
+    matrices: Dict[Tuple[int, int], List[List[int]]] = {}
+    src_fields, dst_fields, pairs = [], [], []
+    dst_initialized = False
+    for s in source:
+        sf = schema.find_field_by_ordinal(s)
+        src_fields.append(sf)
+        for d in dest:
+            if s != d:
+                df = schema.find_field_by_ordinal(d)
+                matrices[(s, d)] = [[0] * len(df.cardinality) for _ in sf.cardinality]
+                if not dst_initialized:
+                    dst_fields.append(df)
+                pairs.append((s, d))
+        dst_initialized = True
+    # ---- map
+    for ln in lines:
+        items = java_split(ln, delim_regex, False)
+        k = 0
+        for sf in src_fields:
+            if sf.ordinal >= len(items):
+                raise ArrayIndexOutOfBounds(ln)
+            v = items[sf.ordinal]
+            si = sf.cardinality.index(v) if v in sf.cardinality else -1
+            for df in dst_fields:
+                if df.ordinal >= len(items):
+                    raise ArrayIndexOutOfBounds(ln)
+                w = items[df.ordinal]
+                di = df.cardinality.index(w) if w in df.cardinality else -1
+                if k >= len(pairs):
+                    raise ArrayIndexOutOfBounds("attrPairs.get(%d)" % k)
+                m = matrices[pairs[k]]
+                k += 1
+                if si < 0 or di < 0 or si >= len(m) or di >= len(m[0]):
+                    raise ArrayIndexOutOfBounds(ln)
+                m[si][di] += 1
+    # ---- reduce: keys in sorted order
+    out = []
+    for (s, d) in sorted(set(pairs)):
+        sf, df = schema.find_field_by_ordinal(s), schema.find_field_by_ordinal(d)
+        out.append(sf.name + delim_out + df.name + delim_out + double_to_string(cramer_index(matrices[(s, d)])))
+    return out

@@ -26,6 +26,8 @@ int ora_predict(int64_t, int, const int32_t*, const void* const*, int, const int
                 const uint8_t*, uint8_t*);
 int ora_cpg(const uint32_t*, int, int, const int32_t*, int, int, const ora_split*, const int32_t*, const uint8_t*,
             const uint8_t*, int, avt_cpg_stat*);
+int64_t ora_encode_csv(const char*, int64_t, char, int, int, const avt_csv_attr*, const int32_t*, const double*, const char*, const int32_t*, int, int,
+                       const char*, const int32_t*, int32_t* const*, uint8_t*, int);
 }
 
 struct avt_engine {
@@ -69,6 +71,39 @@ int avt_dataset_load(avt_engine* e, int64_t n, int32_t A, const int32_t* nb, con
     }
     e->cls.assign(cc, cc + n);
     return 0;
+}
+int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char delim, int32_t skip, int32_t A, const avt_csv_attr* attrs, const int32_t* ip,
+                         const double* dp, const char* cb, const int32_t* co, int32_t class_ord, int32_t n_class, const char* kb, const int32_t* ko,
+                         int64_t* n_rows, int64_t* first_row, int64_t* bad_row, int32_t* bad_reason) {
+    // the C restatement of the encode (avt_csv_attr and ora_csv_attr have the same layout)
+    if (bad_row) *bad_row = -1;
+    if (bad_reason) *bad_reason = 0;
+    const int64_t n = ora_encode_csv(text, n_bytes, delim, skip, A, attrs, ip, dp, cb, co, class_ord, n_class, kb, ko, nullptr, nullptr, 1);
+    std::vector<std::vector<int32_t>> tmp((size_t)A, std::vector<int32_t>((size_t)n));
+    std::vector<int32_t*> ptrs;
+    for (auto& v : tmp) ptrs.push_back(v.data());
+    std::vector<uint8_t> cls((size_t)n);
+    const int64_t rc = ora_encode_csv(text, n_bytes, delim, skip, A, attrs, ip, dp, cb, co, class_ord, n_class, kb, ko, ptrs.data(), cls.data(), 1);
+    if (rc < 0) {
+        if (bad_row) *bad_row = -rc - 1;
+        e->err = "avt_dataset_load_csv (mock): row " + std::to_string(-rc - 1) + " rejected";
+        return AVT_E_REFERENCE;
+    }
+    if (n_rows) *n_rows = n;
+    std::vector<int32_t> nb((size_t)A);
+    for (int a = 0; a < A; ++a) nb[(size_t)a] = attrs[a].kind == AVT_CSV_CATEGORICAL ? attrs[a].n : attrs[a].n + 1;
+    std::vector<std::vector<uint8_t>> c8((size_t)A);
+    std::vector<std::vector<uint16_t>> c16((size_t)A);
+    std::vector<const void*> cols((size_t)A);
+    for (int a = 0; a < A; ++a) {
+        if (nb[(size_t)a] > 256) { c16[(size_t)a].assign(tmp[(size_t)a].begin(), tmp[(size_t)a].end()); cols[(size_t)a] = c16[(size_t)a].data(); }
+        else { c8[(size_t)a].assign(tmp[(size_t)a].begin(), tmp[(size_t)a].end()); cols[(size_t)a] = c8[(size_t)a].data(); }
+    }
+    if (first_row) {
+        for (int k = 0; k < n_class; ++k) first_row[k] = -1;
+        for (int64_t r = 0; r < n; ++r) if (first_row[cls[(size_t)r]] < 0) first_row[cls[(size_t)r]] = r;
+    }
+    return avt_dataset_load(e, n, A, nb.data(), cols.data(), cls.data(), n_class);
 }
 int avt_forest_init(avt_engine* e, int32_t T, const uint8_t* const* weights, const uint16_t* const* node_ids) {
     e->T = T; e->nid.assign(T, {}); e->w.assign(T, {});
