@@ -6,6 +6,7 @@
 // the device (avt_dataset_load_csv) once per destination attribute with that attribute as the "class": the root
 // histogram H[bin of source attribute][class] IS the pair's contingency matrix, for all source attributes at once.
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <memory>
 
@@ -52,18 +53,101 @@ double cramer_index(const std::vector<long long>& t, int rows, int cols) {
     return pearson / (smaller - 1);
 }
 
+// ContingencyMatrix.getAggregates + rowSumAsDouble / colSumAsDouble (util/ContingencyMatrix.java:62-85, 126-140)
+struct Aggregates {
+    std::vector<double> row, col;   // sums (0 counted as 1) over the total count
+    long long total = 0;
+};
+Aggregates aggregates(const std::vector<long long>& t, int rows, int cols) {
+    Aggregates a;
+    std::vector<long long> rs((size_t)rows, 0), cs((size_t)cols, 0);
+    for (int i = 0; i < rows; ++i) {
+        for (int j = 0; j < cols; ++j) { rs[(size_t)i] += t[(size_t)i * cols + j]; a.total += t[(size_t)i * cols + j]; }
+        if (rs[(size_t)i] == 0) rs[(size_t)i] = 1;
+    }
+    for (int j = 0; j < cols; ++j) {
+        for (int i = 0; i < rows; ++i) cs[(size_t)j] += t[(size_t)i * cols + j];
+        if (cs[(size_t)j] == 0) cs[(size_t)j] = 1;
+    }
+    for (int i = 0; i < rows; ++i) a.row.push_back((double)rs[(size_t)i] / (double)a.total);
+    for (int j = 0; j < cols; ++j) a.col.push_back((double)cs[(size_t)j] / (double)a.total);
+    return a;
+}
+
+// ContingencyMatrix.concentrationCoeff (util/ContingencyMatrix.java:142-164)
+double concentration_coeff(const std::vector<long long>& t, int rows, int cols) {
+    const Aggregates a = aggregates(t, rows, cols);
+    double sum_one = 0;
+    for (int i = 0; i < rows; ++i) {
+        double sq = 0;
+        for (int j = 0; j < cols; ++j) {
+            const double elem = (double)t[(size_t)i * cols + j] / (double)a.total;
+            const double p = elem * elem;
+            sq += p;
+        }
+        sum_one += sq / a.row[(size_t)i];
+    }
+    double sum_two = 0;
+    for (int j = 0; j < cols; ++j) {
+        const double p = a.col[(size_t)j] * a.col[(size_t)j];
+        sum_two += p;
+    }
+    return (sum_one - sum_two) / (1.0 - sum_two);
+}
+
+// ContingencyMatrix.uncertaintyCoeff (util/ContingencyMatrix.java:166-187); an empty cell gives 0 * log10(0) = NaN, as there
+double uncertainty_coeff(const std::vector<long long>& t, int rows, int cols) {
+    const Aggregates a = aggregates(t, rows, cols);
+    double sum_one = 0;
+    for (int i = 0; i < rows; ++i)
+        for (int j = 0; j < cols; ++j) {
+            const double elem = (double)t[(size_t)i * cols + j] / (double)a.total;
+            const double arg = elem * a.col[(size_t)j] / a.row[(size_t)i];
+            const double term = elem * log10(arg);
+            sum_one += term;
+        }
+    double sum_two = 0;
+    for (int j = 0; j < cols; ++j) {
+        const double term = a.col[(size_t)j] * log10(a.col[(size_t)j]);
+        sum_two += term;
+    }
+    return sum_one / sum_two;
+}
+
+struct CorrelationKeys {
+    const char *schema, *source, *dest;
+    double (*stat)(const std::vector<long long>&, int, int);
+};
+
+int run_correlation(const Props& conf, const std::string& in_path, const std::string& out_path, const CorrelationKeys& K);
+
 }  // namespace
 
 int run_cramer_correlation(const Props& conf, const std::string& in_path, const std::string& out_path) {
+    return run_correlation(conf, in_path, out_path, CorrelationKeys{"crc.feature.schema.file.path", "crc.source.attributes", "crc.dest.attributes", cramer_index});
+}
+
+// org.avenir.explore.HeterogeneityReductionCorrelation: CategoricalCorrelation's mapper (explore/CategoricalCorrelation.java:66-150,
+// the same pair bookkeeping, `cac.*` keys -- `cac.second.set..attributes` with two dots is the reference's spelling) and a reducer
+// that prints the concentration ("gini") or the uncertainty coefficient (explore/HeterogeneityReductionCorrelation.java:71-88).
+int run_heterogeneity_reduction_correlation(const Props& conf, const std::string& in_path, const std::string& out_path) {
+    const bool gini = conf.get("hrc.heterogeneity.algorithm", "gini") == "gini";
+    return run_correlation(conf, in_path, out_path,
+                           CorrelationKeys{"cac.feature.schema.file.path", "cac.first.set.attributes", "cac.second.set..attributes", gini ? concentration_coeff : uncertainty_coeff});
+}
+
+namespace {
+
+int run_correlation(const Props& conf, const std::string& in_path, const std::string& out_path, const CorrelationKeys& K) {
     const std::string delim = conf.get("field.delim.regex", ",");
     const std::string delim_out = conf.get("field.delim.out", ",");
-    if (!conf.has("crc.feature.schema.file.path")) throw ReferenceError("NullPointerException: crc.feature.schema.file.path is not set");
-    const Schema schema = Schema::load(conf.get("crc.feature.schema.file.path"));
-    const std::vector<int> src = int_list(conf, "crc.source.attributes"), dst = int_list(conf, "crc.dest.attributes");
+    if (!conf.has(K.schema)) throw ReferenceError(std::string("NullPointerException: ") + K.schema + " is not set");
+    const Schema schema = Schema::load(conf.get(K.schema));
+    const std::vector<int> src = int_list(conf, K.source), dst = int_list(conf, K.dest);
     for (int s : src)
         for (int d : dst)
             if (s == d)
-                throw Unsupported("crc.source.attributes and crc.dest.attributes overlap: the reference's mapper then walks its pair list out of step "
+                throw Unsupported("the source and destination attribute sets overlap: the reference's mapper then walks its pair list out of step "
                                   "(explore/CramerCorrelation.java:170-180) and mis-assigns or overruns the matrices; not reproduced");
     if (delim.size() != 1) throw Unsupported("field.delim.regex must be a single literal character for the device encoder");
     std::vector<const Field*> sf, df;
@@ -81,7 +165,7 @@ int run_cramer_correlation(const Props& conf, const std::string& in_path, const 
     for (size_t i = 0; i < by_ord.size(); ++i) by_ord[i] = i;
     std::sort(by_ord.begin(), by_ord.end(), [&](size_t a, size_t b) { return sf[a]->ordinal < sf[b]->ordinal; });
     for (size_t i = 1; i < by_ord.size(); ++i)
-        if (sf[by_ord[i]]->ordinal == sf[by_ord[i - 1]]->ordinal) throw Unsupported("crc.source.attributes lists an attribute twice");
+        if (sf[by_ord[i]]->ordinal == sf[by_ord[i - 1]]->ordinal) throw Unsupported("the source attribute set lists an attribute twice");
     std::vector<avt_csv_attr> attrs;
     std::string cat_bytes;
     std::vector<int32_t> cat_off, bin_off{0};
@@ -137,7 +221,7 @@ int run_cramer_correlation(const Props& conf, const std::string& in_path, const 
             std::vector<long long> t((size_t)R * C);
             for (int i = 0; i < R; ++i)
                 for (int j = 0; j < C; ++j) t[(size_t)i * C + j] = H[((size_t)bin_off[k] + i) * C + j];
-            out.push_back(Pair{S.ordinal, D.ordinal, S.name + delim_out + D.name + delim_out + java_double_to_string(cramer_index(t, R, C))});
+            out.push_back(Pair{S.ordinal, D.ordinal, S.name + delim_out + D.name + delim_out + java_double_to_string(K.stat(t, R, C))});
         }
     }
     // one reducer: keys arrive sorted, Tuple (src, dst) compares element by element
@@ -147,5 +231,7 @@ int run_cramer_correlation(const Props& conf, const std::string& in_path, const 
     write_output_lines(out_path, out_lines);
     return 0;
 }
+
+}  // namespace
 
 }  // namespace avt_host

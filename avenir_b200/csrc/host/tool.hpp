@@ -18,6 +18,9 @@ int run_model_predictor(const Props& conf, const std::string& in_path, const std
 // org.avenir.explore.CramerCorrelation.run(args)  (explore/CramerCorrelation.java:56-81)
 int run_cramer_correlation(const Props& conf, const std::string& in_path, const std::string& out_path);
 
+// org.avenir.explore.HeterogeneityReductionCorrelation.run(args)  (explore/HeterogeneityReductionCorrelation.java:40-65)
+int run_heterogeneity_reduction_correlation(const Props& conf, const std::string& in_path, const std::string& out_path);
+
 // Input "path" as Hadoop takes it: a file, or a directory whose regular files (not starting with
 // '_' or '.') are read in name order.
 std::vector<std::string> read_input_lines(const std::string& path);

@@ -54,6 +54,10 @@ class CramerCorrelation(_Tool):
     java_class = "org.avenir.explore.CramerCorrelation"
 
 
+class HeterogeneityReductionCorrelation(_Tool):
+    java_class = "org.avenir.explore.HeterogeneityReductionCorrelation"
+
+
 def main(argv: List[str] | None = None) -> int:
     argv = list(sys.argv[1:] if argv is None else argv)
     if not argv:

@@ -101,3 +101,56 @@ def test_reference_failures(lib, tmp_path):
     assert rc == 1 and "crc.dest.attributes" in err
     rc, err, _, _, _ = run_both(lib, str(tmp_path / "e"), schema, lines, {"crc.source.attributes": "1", "crc.dest.attributes": "9"})
     assert rc == 1 and "NullPointerException" in err
+
+
+HRC = "org.avenir.explore.HeterogeneityReductionCorrelation"
+
+
+def run_hrc(lib, d, schema, lines, conf):
+    os.makedirs(d, exist_ok=True)
+    sp = os.path.join(d, "schema.json")
+    json.dump(schema, open(sp, "w"))
+    conf = dict(conf, **{"cac.feature.schema.file.path": sp})
+    pp = os.path.join(d, "hrc.properties")
+    with open(pp, "w") as f:
+        for k, v in conf.items():
+            f.write(f"{k}={v}\n")
+    data = os.path.join(d, "in.txt")
+    open(data, "w").write("\n".join(lines) + "\n")
+    rc, err = helpers.tool_run(lib, HRC, [f"-Dconf.path={pp}", data, os.path.join(d, "out")])
+    got = open(os.path.join(d, "out", "part-r-00000")).read().splitlines() if rc == 0 else None
+    return rc, err, got, literal.load_properties(pp), literal.FeatureSchema(schema)
+
+
+def test_heterogeneity_reduction_correlation(lib, tmp_path):
+    """Same contingency matrices, concentration ("gini") and uncertainty coefficient; the reference's key with two dots."""
+    schema = hangup_schema()
+    lines = synth.call_hangup_csv(4000)
+    keys = {"cac.first.set.attributes": "1,3", "cac.second.set..attributes": "4,6"}
+    rc, err, got, conf, fs = run_hrc(lib, str(tmp_path / "g"), schema, lines, keys)
+    assert rc == 0, err
+    assert got == crc_literal.heterogeneity_reduction_correlation(lines, conf, fs) and len(got) == 4
+    assert all(0.0 <= float(ln.rsplit(",", 1)[1]) < 1.0 for ln in got)
+    rc, err, got, conf, fs = run_hrc(lib, str(tmp_path / "u"), schema, lines, dict(keys, **{"hrc.heterogeneity.algorithm": "uncertainty"}))
+    assert rc == 0, err
+    want = crc_literal.heterogeneity_reduction_correlation(lines, conf, fs)
+    assert got == want
+    # residence callers never have issue "cable"/... combinations missing?  whichever cells are empty give NaN, the dense pairs a number
+    assert any(ln.endswith("NaN") for ln in got) or all(float(ln.rsplit(",", 1)[1]) == float(ln.rsplit(",", 1)[1]) for ln in got)
+    rc, err, _, _, _ = run_hrc(lib, str(tmp_path / "m"), schema, lines, {"cac.first.set.attributes": "1"})
+    assert rc == 1 and "cac.second.set..attributes" in err
+
+
+def test_uncertainty_coefficient_with_an_empty_cell_is_nan(lib, tmp_path):
+    schema = {"fields": [{"name": "a", "ordinal": 0, "dataType": "categorical", "feature": True, "cardinality": ["p", "q"]},
+                         {"name": "b", "ordinal": 1, "dataType": "categorical", "cardinality": ["x", "y"]}]}
+    dense = ["p,x", "p,y", "q,x", "q,y", "q,y"]
+    rc, err, got, conf, fs = run_hrc(lib, str(tmp_path / "d"), schema, dense, {"cac.first.set.attributes": "0", "cac.second.set..attributes": "1",
+                                                                             "hrc.heterogeneity.algorithm": "uncertainty"})
+    assert rc == 0, err
+    assert got == crc_literal.heterogeneity_reduction_correlation(dense, conf, fs) and not got[0].endswith("NaN")
+    sparse = ["p,x", "p,x", "q,y"]
+    rc, err, got, conf, fs = run_hrc(lib, str(tmp_path / "s"), schema, sparse, {"cac.first.set.attributes": "0", "cac.second.set..attributes": "1",
+                                                                              "hrc.heterogeneity.algorithm": "uncertainty"})
+    assert rc == 0, err
+    assert got == crc_literal.heterogeneity_reduction_correlation(sparse, conf, fs) == ["a,b,NaN"]
