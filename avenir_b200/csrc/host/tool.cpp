@@ -45,13 +45,22 @@ extern "C" int avt_tool_run(const char* tool, int argc, const char* const* argv,
             if (kv.first == "conf.path") conf.load(kv.second);
         for (auto& kv : overrides)
             if (kv.first != "conf.path") conf.set(kv.first, kv.second);
+        if (ends_with(name, "SplitGenerator")) {
+            // tree/SplitGenerator.java:39-54: ClassPartitionGenerator whose paths come from the project layout instead of the arguments
+            const std::string base = conf.get("project.base.path");
+            if (trim(base).empty()) throw ReferenceError("IllegalStateException: base path not defined");
+            const std::string split_path = conf.get("split.path");
+            const std::string in = trim(split_path).empty() ? base + "/split=root/data" : base + "/split=root/data/" + split_path;
+            const size_t cut = in.find_last_of('/');
+            return run_class_partition_generator(conf, in, in.substr(0, cut) + "/splits");   // Utility.getSiblingPath(inPath, "splits")
+        }
         if (positional.size() < 2) throw std::runtime_error("usage: <tool> -Dconf.path=<file.properties> [-Dkey=value ...] <inPath> <outPath>");
         if (ends_with(name, "DecisionTreeBuilder")) return run_decision_tree_builder(conf, positional[0], positional[1]);
         if (ends_with(name, "ClassPartitionGenerator")) return run_class_partition_generator(conf, positional[0], positional[1]);
         if (ends_with(name, "ModelPredictor")) return run_model_predictor(conf, positional[0], positional[1]);
         if (ends_with(name, "CramerCorrelation")) return run_cramer_correlation(conf, positional[0], positional[1]);
         if (ends_with(name, "HeterogeneityReductionCorrelation")) return run_heterogeneity_reduction_correlation(conf, positional[0], positional[1]);
-        throw std::runtime_error("unknown tool '" + name + "' (DecisionTreeBuilder | ClassPartitionGenerator | ModelPredictor | CramerCorrelation | HeterogeneityReductionCorrelation)");
+        throw std::runtime_error("unknown tool '" + name + "' (DecisionTreeBuilder | ClassPartitionGenerator | ModelPredictor | SplitGenerator | CramerCorrelation | HeterogeneityReductionCorrelation)");
     } catch (const ReferenceError& e) {
         set_err(errbuf, errlen, std::string("reference failure reproduced: ") + e.what());
     } catch (const Unsupported& e) {

@@ -54,6 +54,10 @@ class CramerCorrelation(_Tool):
     java_class = "org.avenir.explore.CramerCorrelation"
 
 
+class SplitGenerator(_Tool):
+    java_class = "org.avenir.tree.SplitGenerator"
+
+
 class HeterogeneityReductionCorrelation(_Tool):
     java_class = "org.avenir.explore.HeterogeneityReductionCorrelation"
 

@@ -250,3 +250,27 @@ def test_random_among_top_follows_the_seeded_stream(hostmock, tmp_path, seed):
                          "dtb.sub.sampling.buffer.size": "300"})
     got, want = run_dtb_both(hostmock, str(tmp_path), synth.call_hangup_csv(900), schema, conf, 4)
     assert got == want
+
+
+def test_split_generator_is_cpg_on_the_project_layout(hostmock, tmp_path):
+    """tree/SplitGenerator.java:39-54: input <base>/split=root/data[/<split.path>], output its sibling `splits`;
+    no positional arguments."""
+    base = str(tmp_path / "proj")
+    rows = cpg_rows(500)
+    sp = str(tmp_path / "schema.json")
+    json.dump(cpg_schema(), open(sp, "w"))
+    conf = {"cpg.feature.schema.file.path": sp, "cpg.split.attributes": "1,2", "cpg.split.algorithm": "giniIndex", "cpg.parent.info": "0.9",
+            "project.base.path": base}
+    want = literal.cpg_run(rows, conf, literal.FeatureSchema(cpg_schema()))
+    for split_path, data_dir, out_dir in (("", base + "/split=root/data", base + "/split=root/splits"),
+                                          ("split=3/segment=1/data", base + "/split=root/data/split=3/segment=1/data", base + "/split=root/data/split=3/segment=1/splits")):
+        os.makedirs(data_dir, exist_ok=True)
+        open(os.path.join(data_dir, "part-00000"), "w").write("\n".join(rows) + "\n")
+        pp = str(tmp_path / "sg.properties")
+        _props(pp, dict(conf, **({"split.path": split_path} if split_path else {})))
+        rc, err = helpers.tool_run(hostmock, "org.avenir.tree.SplitGenerator", [f"-Dconf.path={pp}"])
+        assert rc == 0, err
+        assert open(os.path.join(out_dir, "part-r-00000")).read().splitlines() == want
+    _props(str(tmp_path / "bad.properties"), {k: v for k, v in conf.items() if k != "project.base.path"})
+    rc, err = helpers.tool_run(hostmock, "org.avenir.tree.SplitGenerator", [f"-Dconf.path={tmp_path}/bad.properties"])
+    assert rc == 1 and "base path not defined" in err
