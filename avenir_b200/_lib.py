@@ -12,6 +12,7 @@ AVT_NODE_NONE = 0xFFFF
 AVT_MAX_CLASSES = 16
 AVT_MAX_SEG = 8
 CRIT_GINI, CRIT_ENTROPY, CRIT_HELLINGER, CRIT_CLASS_CONF = 0, 1, 2, 3
+SAMPLE_WITH_REPLACE, SAMPLE_WITHOUT_REPLACE = 1, 2
 SPLIT_NUMERIC, SPLIT_LUT = 0, 1
 
 
@@ -57,7 +58,7 @@ class Stats(C.Structure):
                 ("last_hist_variant", C.c_int32), ("last_hist_replicas", C.c_int32),
                 ("last_hist_grid", C.c_int32), ("last_hist_block", C.c_int32), ("last_hist_smem", C.c_int32),
                 ("reserved0", C.c_int32), ("last_csv_h2d_ms", C.c_double), ("last_csv_index_ms", C.c_double),
-                ("last_csv_encode_ms", C.c_double), ("last_grow_ms", C.c_double)]
+                ("last_csv_encode_ms", C.c_double), ("last_grow_ms", C.c_double), ("sample_ms", C.c_double)]
 
 
 # every symbol include/avenir_tree.h declares: name -> (restype, argtypes)
@@ -71,6 +72,8 @@ SIGNATURES = {
                                       C.c_int32, C.c_int32, _P, _P, C.POINTER(C.c_int64), _P, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "avt_dataset_fetch_column": (C.c_int, [_P, C.c_int32, _P]),
     "avt_forest_init": (C.c_int, [_P, C.c_int32, C.POINTER(_P), C.POINTER(_P)]),
+    "avt_forest_init_sampled": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64, C.c_int64]),
+    "avt_forest_weights": (C.c_int, [_P, C.c_int32, _P]),
     "avt_split_table_set": (C.c_int, [_P, C.c_int32, C.POINTER(Split), C.POINTER(C.c_int32), C.c_int32, _P, C.c_int64]),
     "avt_level_histogram": (C.c_int, [_P, C.POINTER(C.c_int32), _P]),
     "avt_level_scan": (C.c_int, [_P, C.c_int32, _P, _P, C.POINTER(NodeBest)]),

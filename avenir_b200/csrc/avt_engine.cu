@@ -72,6 +72,7 @@ struct avt_engine {
     DevBuf<uint16_t> d_nid, d_nid2;
     uint16_t* nid_cur = nullptr;  // buffer holding the current node ids (d_nid or d_nid2)
     DevBuf<uint8_t> d_w, d_has_w;
+    std::vector<uint8_t> h_has_w;
     // frontier
     std::vector<int> node_base;
     int NF = 0;
@@ -722,8 +723,105 @@ int avt_forest_init(avt_engine* e, int32_t n_trees, const uint8_t* const* weight
             if (has_w[t]) CUDA_TRY(e, cudaMemcpyAsync(e->d_w.p + (size_t)t * e->Npad, weights[t], (size_t)e->N, cudaMemcpyHostToDevice, e->stream));
     }
     if (int rc = upload(e, e->d_has_w, has_w.data(), (size_t)n_trees)) return rc;
+    e->h_has_w = has_w;
     if (int rc = timer_close(e, ts)) return rc;
     e->hist_valid = e->scan_valid = false;
+    return sync_and_resolve(e);
+}
+
+int avt_forest_init_sampled(avt_engine* e, int32_t n_trees, int32_t mode, int64_t seed, int32_t param, int64_t total_rows, int64_t row0) {
+    if (!e) return AVT_E_INVALID;
+    if (e->N == 0) return fail(e, AVT_E_STATE, "avt_forest_init_sampled: no data set loaded");
+    if (n_trees < 1) return fail(e, AVT_E_INVALID, "avt_forest_init_sampled: n_trees %d < 1", n_trees);
+    if (mode != AVT_SAMPLE_WITH_REPLACE && mode != AVT_SAMPLE_WITHOUT_REPLACE) return fail(e, AVT_E_INVALID, "avt_forest_init_sampled: mode %d", mode);
+    if (param < 1) return fail(e, AVT_E_INVALID, "avt_forest_init_sampled: %s %d < 1", mode == AVT_SAMPLE_WITH_REPLACE ? "batch size" : "sampling rate", param);
+    if (row0 < 0 || total_rows < row0 + e->N) return fail(e, AVT_E_INVALID, "avt_forest_init_sampled: rows [%lld, %lld) are not inside a file of %lld rows", (long long)row0, (long long)(row0 + e->N), (long long)total_rows);
+    if (total_rows >= (1LL << 46)) return fail(e, AVT_E_INVALID, "avt_forest_init_sampled: more rows than the 48-bit stream has draws");
+    if (int rc = use_device(e)) return rc;
+    e->T = n_trees;
+    e->any_w = true;
+    std::vector<uint8_t> has_w(n_trees, 1);
+    TimerSlot ts;
+    if (int rc = timer_open(e, &e->stats.sample_ms, &ts)) return rc;
+    CUDA_TRY(e, e->d_nid.ensure((size_t)n_trees * e->Npad));
+    CUDA_TRY(e, e->d_w.ensure((size_t)n_trees * e->Npad));
+    CUDA_TRY(e, e->d_err.ensure(1));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_err.p, 0, sizeof(int32_t), e->stream));
+    e->nid_cur = e->d_nid.p;
+    if (e->Npad == e->N) {
+        CUDA_TRY(e, cudaMemsetAsync(e->d_nid.p, 0, (size_t)n_trees * e->Npad * 2, e->stream));
+    } else {
+        CUDA_TRY(e, cudaMemsetAsync(e->d_nid.p, 0xFF, (size_t)n_trees * e->Npad * 2, e->stream));
+        for (int t = 0; t < n_trees; ++t) CUDA_TRY(e, cudaMemsetAsync(e->d_nid.p + (size_t)t * e->Npad, 0, (size_t)e->N * 2, e->stream));
+    }
+    CUDA_TRY(e, cudaMemsetAsync(e->d_w.p, 0, (size_t)n_trees * e->Npad, e->stream));
+    BagArgs ba{};
+    ba.w = e->d_w.p;
+    ba.Npad = e->Npad;
+    ba.total_rows = total_rows;
+    ba.row0 = row0;
+    ba.n_local = e->N;
+    ba.seed = seed;
+    ba.batch = param;
+    ba.err = e->d_err.p;
+    if (mode == AVT_SAMPLE_WITH_REPLACE) {
+        ba.first_batch = row0 / param;
+        const long long last_batch = (row0 + e->N - 1) / param;
+        const long long n_batches = last_batch - ba.first_batch + 1;
+        if (n_batches > 0x7FFFFFFFLL) return fail(e, AVT_E_INVALID, "avt_forest_init_sampled: too many batches");
+        const size_t smem = (size_t)param * sizeof(uint32_t);
+        if (smem <= kMaxDynSmem) {
+            CUDA_TRY(e, cudaFuncSetAttribute(bagging_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+            // grid.y is limited to 65535 trees
+            for (int t0 = 0; t0 < n_trees; t0 += 65535) {
+                BagArgs b2 = ba;
+                b2.w = ba.w + (size_t)t0 * e->Npad;
+                b2.seed = seed + t0;
+                bagging_kernel<<<dim3((unsigned)n_batches, (unsigned)std::min(65535, n_trees - t0)), 512, smem, e->stream>>>(b2);
+            }
+        } else {
+            const unsigned slices = (unsigned)std::min<long long>(1024, ((long long)param + 256 * 64 - 1) / (256 * 64));
+            for (int t0 = 0; t0 < n_trees; t0 += 65535) {
+                BagArgs b2 = ba;
+                b2.w = ba.w + (size_t)t0 * e->Npad;
+                b2.seed = seed + t0;
+                bagging_global_kernel<<<dim3((unsigned)n_batches, (unsigned)std::min(65535, n_trees - t0), slices), 256, 0, e->stream>>>(b2);
+            }
+        }
+    } else {
+        const int rpt = 64;
+        const long long threads = (e->N + rpt - 1) / rpt;
+        for (int t0 = 0; t0 < n_trees; t0 += 65535) {
+            BagArgs b2 = ba;
+            b2.w = ba.w + (size_t)t0 * e->Npad;
+            b2.seed = seed + t0;
+            bernoulli_kernel<<<dim3((unsigned)((threads + 255) / 256), (unsigned)std::min(65535, n_trees - t0)), 256, 0, e->stream>>>(b2, param, rpt);
+        }
+    }
+    CUDA_TRY(e, cudaGetLastError());
+    if (int rc = upload(e, e->d_has_w, has_w.data(), (size_t)n_trees)) return rc;
+    e->h_has_w = has_w;
+    int32_t err = 0;
+    CUDA_TRY(e, cudaMemcpyAsync(&err, e->d_err.p, sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+    if (int rc = timer_close(e, ts)) return rc;
+    e->hist_valid = e->scan_valid = false;
+    if (int rc = sync_and_resolve(e)) return rc;
+    if (err) {
+        e->T = 0;
+        return fail(e, AVT_E_INVALID, "avt_forest_init_sampled: a bootstrap multiplicity exceeds 255");
+    }
+    return AVT_OK;
+}
+
+int avt_forest_weights(avt_engine* e, int32_t tree, uint8_t* out) {
+    if (!e) return AVT_E_INVALID;
+    if (tree < 0 || tree >= e->T || !out) return fail(e, AVT_E_INVALID, "avt_forest_weights: tree %d out of range", tree);
+    if (int rc = use_device(e)) return rc;
+    if (!e->any_w || !e->h_has_w[(size_t)tree]) {
+        memset(out, 1, (size_t)e->N);
+        return AVT_OK;
+    }
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->d_w.p + (size_t)tree * e->Npad, (size_t)e->N, cudaMemcpyDeviceToHost, e->stream));
     return sync_and_resolve(e);
 }
 

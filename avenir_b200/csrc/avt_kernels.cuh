@@ -717,3 +717,4 @@ __global__ void __launch_bounds__(256) repartition_fast_kernel(const RepartFastA
 #include "avt_csv.cuh"
 #include "avt_predict.cuh"
 #include "avt_persistent.cuh"
+#include "avt_bagging.cuh"

@@ -214,6 +214,18 @@ class Engine:
         self._check(self.lib.avt_forest_init(self.h, n_trees, wp, npp))
         self.n_trees = n_trees
 
+    def forest_init_sampled(self, n_trees: int, mode: int, seed: int, param: int, total_rows: Optional[int] = None, row0: int = 0):
+        """Trees whose first-pass sub-sampling is generated on the device (avt_forest_init_sampled): mode
+        _lib.SAMPLE_WITH_REPLACE (param = bas.batch.size) or _lib.SAMPLE_WITHOUT_REPLACE (param = rate in percent)."""
+        total = self.n_rows if total_rows is None else int(total_rows)
+        self._check(self.lib.avt_forest_init_sampled(self.h, n_trees, mode, seed, param, total, row0))
+        self.n_trees = n_trees
+
+    def weights(self, tree: int) -> np.ndarray:
+        out = np.empty(self.n_rows, dtype=np.uint8)
+        self._check(self.lib.avt_forest_weights(self.h, tree, _ptr(out)))
+        return out
+
     def set_splits(self, t: SplitTable):
         n = len(t)
         arr = (Split * max(n, 1))()

@@ -103,6 +103,7 @@ typedef struct avt_stats {
     double last_csv_h2d_ms, last_csv_index_ms, last_csv_encode_ms; /* last avt_dataset_load_csv: text upload, line index, per-row encode */
     double last_grow_ms; /* device time of the last avt_grow_levels call: CUDA events on the library's stream around everything
                           * the call enqueued, result copies included (host-side argument handling excluded) */
+    double sample_ms;    /* accumulated device time of avt_forest_init_sampled (multiplicity generation + node-id reset) */
 } avt_stats;
 
 /* ---- engine ------------------------------------------------------------------------------- */
@@ -174,6 +175,25 @@ int avt_dataset_fetch_column(avt_engine* e, int32_t attr, void* out);
  * (AVT_NODE_NONE = dropped), as recovered from a path-tagged input file (:268-292). */
 int avt_forest_init(avt_engine* e, int32_t n_trees, const uint8_t* const* weights,
                     const uint16_t* const* node_ids);
+
+/* Starts `n_trees` trees whose first-pass sub-sampling is done ON THE DEVICE, for the rows loaded on this engine,
+ * which are rows [row0, row0 + n_rows) of a file of `total_rows` rows (row0 = 0, total_rows = n_rows on one GPU; a
+ * rank of a row-sharded job passes its shard's position, so that every shard count yields the same forest).
+ * Tree t draws from a java.util.Random(seed + t) stream in file order (the reference's Math.random() is unseeded,
+ * the seed is this library's addition).
+ *   AVT_SAMPLE_WITH_REPLACE     param = batch size: per batch of `param` rows (the tail batch is shorter) m draws
+ *                               (int)(nextDouble() * m); a row's multiplicity = draws that hit it.  This is
+ *                               explore/BaggingSampler.java:101-122 (emitBatch) and the intended buffer bootstrap of
+ *                               tree/DecisionTreeBuilder.java:214-229.  Fails if one exceeds 255.
+ *   AVT_SAMPLE_WITHOUT_REPLACE  param = dtb.sub.sampling.rate: row kept (multiplicity 1) when
+ *                               (int)(nextDouble() * 100) < param (tree/DecisionTreeBuilder.java:230-235).
+ * Every row starts in node 0.  Same result as avt_forest_init with host-generated multiplicities. */
+#define AVT_SAMPLE_WITH_REPLACE 1
+#define AVT_SAMPLE_WITHOUT_REPLACE 2
+int avt_forest_init_sampled(avt_engine* e, int32_t n_trees, int32_t mode, int64_t seed, int32_t param,
+                            int64_t total_rows, int64_t row0);
+/* Copies back tree t's multiplicities (uint8[n_rows]; all 1 for a tree started without any). */
+int avt_forest_weights(avt_engine* e, int32_t tree, uint8_t* out);
 
 /* Installs the candidate-split table shared by all nodes. */
 int avt_split_table_set(avt_engine* e, int32_t n_splits, const avt_split* splits,

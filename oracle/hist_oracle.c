@@ -629,3 +629,38 @@ int64_t ora_encode_csv(const char* text, int64_t n_bytes, char delim, int skip, 
     free(jobs); free(th);
     return bad >= 0 ? -(bad + 1) : rows;
 }
+
+/* ---- explore/BaggingSampler.java:101-122 (emitBatch), SURVEY App. B-3 / B-5 / E --------------------------------
+ * Bootstrap multiplicities of rows [row0, row0 + n) of a file of `total_rows` rows: rows are taken in file
+ * order in batches of `batch` (bas.batch.size, default 10 000; the tail batch is shorter); a batch of m rows
+ * emits m draws `batch.get((int)(Math.random() * m))`; the multiplicity of a row is the number of draws that
+ * hit it.  Math.random() is java.util.Random.nextDouble(): seed' = (seed * 0x5DEECE66D + 0xB) mod 2^48,
+ * next(b) = seed' >> (48 - b), nextDouble = ((next(26) << 27) + next(27)) * 2^-53.  The stream is seeded
+ * (our addition, App. B-5) with `seed` scrambled as `new Random(seed)` does.  Sequential on purpose: this is
+ * the checker of the device generator's skip-ahead.  Returns -1 when a multiplicity exceeds 255. */
+int ora_bagging_weights(int64_t seed, int32_t batch, int64_t total_rows, int64_t row0, int64_t n, uint8_t* out) {
+    const uint64_t MULT = 0x5DEECE66DULL, MASK = (1ULL << 48) - 1;
+    uint64_t s = ((uint64_t)seed ^ MULT) & MASK;
+    int64_t b0, i;
+    memset(out, 0, (size_t)n);
+    if (batch < 1) batch = 1;
+    for (b0 = 0; b0 < total_rows; b0 += batch) {
+        const int64_t m = total_rows - b0 < batch ? total_rows - b0 : batch;
+        for (i = 0; i < m; ++i) {
+            uint64_t hi, lo;
+            double d;
+            int64_t sel;
+            s = (s * MULT + 0xBULL) & MASK; hi = s >> (48 - 26);
+            s = (s * MULT + 0xBULL) & MASK; lo = s >> (48 - 27);
+            d = (double)((hi << 27) + lo) * (1.0 / 9007199254740992.0);
+            sel = (int64_t)(int32_t)(d * (double)m);
+            if (sel >= m) sel = m - 1;
+            sel += b0 - row0;
+            if (sel >= 0 && sel < n) {
+                if (out[sel] == 255) return -1;
+                ++out[sel];
+            }
+        }
+    }
+    return 0;
+}
