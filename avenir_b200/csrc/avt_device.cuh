@@ -46,6 +46,25 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
     return v;
 }
 
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// Waits until the flag word another GPU stores into this GPU's memory has reached `epoch` (wrap-safe), but never for
+// longer than kPeerWaitNs: a rank that died, returned early or skipped a call must not hang this GPU inside a kernel.
+// Returns false on timeout; the caller reports it (error word 3 -> AVT_E_COMM) and carries on with whatever is there.
+constexpr unsigned long long kPeerWaitNs = 20ull * 1000 * 1000 * 1000;
+__device__ __forceinline__ bool wait_flag_bounded(const uint32_t* flag, uint32_t epoch) {
+    if ((int32_t)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+    const unsigned long long t0 = global_timer_ns();
+    for (;;) {
+        for (int i = 0; i < 256; ++i)
+            if ((int32_t)(ld_acquire_sys(flag) - epoch) >= 0) return true;
+        if (global_timer_ns() - t0 > kPeerWaitNs) return false;
+    }
+}
+
 __device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
     asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }

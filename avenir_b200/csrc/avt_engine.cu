@@ -140,9 +140,6 @@ struct avt_engine {
     avt_stats stats{};
     int force_variant = -1;
     bool skip_h_memset = false;
-    bool persistent = false;  // AVT_PERSISTENT=1: whole level loop in one cooperative kernel.  Measured slower than the stream-ordered
-                              // loop with programmatic dependent launch (0.62 vs 0.52 ms on C2): the per-level cost is the phases'
-                              // own dependency chains, not launches, and the cooperative grid runs at 2 blocks/SM.  Kept for round 2.
     DevBuf<unsigned char> d_levels;
     DevBuf<unsigned long long> d_phase;
     // level loop control block: [0] error flag, [1] last-block ticket, [16 ...] node_base of every level; initialised by one
@@ -354,7 +351,6 @@ int avt_create(int device, avt_engine** out) {
     }
     if (const char* v = getenv("AVT_HIST_TARGET_ADDRS")) e->hist_target_addrs = std::max(1LL, atoll(v));
     if (const char* v = getenv("AVT_GROW_HOST")) e->grow_host_loop = atoi(v);
-    if (const char* v = getenv("AVT_PERSISTENT")) e->persistent = atoi(v) != 0;
     if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
     if (const char* v = getenv("AVT_SCAN_FAST")) e->scan_fast = atoi(v) != 0;
     if (const char* v = getenv("AVT_PEER_SIGNAL_SCAN")) e->peer_signal_scan = atoi(v) != 0;
@@ -489,9 +485,9 @@ int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32
     if (int rc = dataset_shape(e, n_rows, n_attrs, n_bins, n_classes, "avt_dataset_load")) return rc;
     for (int a = 0; a < n_attrs; ++a) {
         const size_t w = e->wide[a] ? 2 : 1;
-        CUDA_TRY(e, cudaMemcpyAsync(e->cols[a], columns[a], (size_t)n_rows * w, cudaMemcpyHostToDevice, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(e->cols[a], columns[a], (size_t)n_rows * w, cudaMemcpyDefault, e->stream));   // host or device source
     }
-    CUDA_TRY(e, cudaMemcpyAsync(e->d_cls.p, class_codes, (size_t)n_rows, cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_cls.p, class_codes, (size_t)n_rows, cudaMemcpyDefault, e->stream));
     if (int rc = dataset_install(e)) return rc;
     if (int rc = timer_close(e, ts)) return rc;
     return sync_and_resolve(e);
@@ -895,15 +891,7 @@ struct FusedRepart {
 // Plans and launches kernel (a) for the frontier in e->node_base (already uploaded to d_node_base).
 // With `fr` the previous level's repartition is applied on the fly (node ids ping-pong between the two
 // buffers); without it the node ids are read in place.
-// What launch_histogram would launch (persistent level loop: the pass runs inside another kernel).
-struct HistPlan {
-    HistArgs ha;
-    dim3 grid;
-    size_t smem = 0;
-    int variant = 0, sel = 0;
-};
-
-static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, const int32_t* d_node_base = nullptr, HistPlan* plan_out = nullptr) {
+static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, const int32_t* d_node_base = nullptr) {
     const size_t hwords = (size_t)e->NF * e->TB * e->C;
     if (!e->H_cur) CUDA_TRY(e, e->d_H.ensure(hwords));
     uint32_t* const Hbuf = e->H_cur ? e->H_cur : e->d_H.p;
@@ -926,10 +914,6 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
     if (fr) {
         CUDA_TRY(e, e->d_nid2.ensure((size_t)e->T * e->Npad));
         nid_out = (e->nid_cur == e->d_nid.p) ? e->d_nid2.p : e->d_nid.p;
-    }
-    if (plan_out && variant == 1) {
-        plan_out->variant = 1;
-        return AVT_OK;
     }
     if (fr && variant == 1) {
         // the global-atomics fallback has no fused form: repartition in place first
@@ -971,10 +955,8 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
 
     TimerSlot ts;
     ts.acc = nullptr;
-    if (!plan_out) {
-        if (int rc = timer_open(e, &e->stats.hist_ms, &ts)) return rc;
-        if (!e->skip_h_memset) CUDA_TRY(e, cudaMemsetAsync(Hbuf, 0, hwords * sizeof(uint32_t), e->stream));
-    }
+    if (int rc = timer_open(e, &e->stats.hist_ms, &ts)) return rc;
+    if (!e->skip_h_memset) CUDA_TRY(e, cudaMemsetAsync(Hbuf, 0, hwords * sizeof(uint32_t), e->stream));
     if (variant == 0) {
         // Replication policy: enough copies that a warp's 32 updates spread over >= kTargetAddrs distinct
         // words, but no more -- smaller histograms mean more resident blocks per SM (latency hiding).
@@ -1082,15 +1064,6 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
             e->signal_in_hist = true;
         }
         const int sel = (e->any_w ? 4 : 0) | (any_wide ? 2 : 0) | (fr ? 1 : 0);
-        if (plan_out) {
-            plan_out->ha = ha;
-            plan_out->grid = grid;
-            plan_out->smem = smem;
-            plan_out->variant = 0;
-            plan_out->sel = sel;
-            if (fr) e->nid_cur = nid_out;   // the pass will leave the node ids in the other buffer
-            return AVT_OK;
-        }
         void (*kern)(const HistArgs) = nullptr;
         switch (sel) {
             case 0: kern = hist_smem_kernel<false, false, false>; break;
@@ -1833,7 +1806,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         e->peer.lazy = false;
         ++e->peer.epoch;
         peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
-        peer_wait_kernel<<<1, 32, 0, e->stream>>>(e->peer.arena, e->peer.n, e->peer.epoch);
+        peer_wait_kernel<<<1, 32, 0, e->stream>>>(e->peer.arena, e->peer.n, e->peer.epoch, d_err_p);
         CUDA_TRY(e, cudaGetLastError());
     }
     e->hist_valid = e->scan_valid = false;
@@ -1866,6 +1839,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         const size_t true_nf = (size_t)nb_all_host[(size_t)rg.level * (T + 1) + T];
         for (size_t i = true_nf; i < rg.count; ++i) all[rg.host_at + i].level = -1;
     }
+    if (err == 3) return fail(e, AVT_E_COMM, "avt_grow_levels: another rank's histogram did not arrive within %d s (a rank died, failed or skipped this call); the results of this call are invalid", (int)(kPeerWaitNs / 1000000000ull));
     if (err == 2) return fail(e, AVT_E_CUDA, "avt_grow_levels: a scan block waited too long for its predecessors (look-back planning)");
     if (err) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
     if (last_level >= 0)
@@ -1880,232 +1854,6 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
     return AVT_OK;
 }
 
-// Persistent form of the device-driven loop: every level inside one cooperative kernel (avt_persistent.cuh).
-// Returns 1 when the configuration is outside what the persistent kernel covers (the caller then runs the
-// stream-ordered loop), 0 on success, a negative code on failure.
-static int grow_persistent_loop(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
-                                avt_grow_record* records, int64_t max_records, int64_t* n_records) {
-    const int T = e->T;
-    const bool peer_on = e->peer.active && e->peer.n > 1;
-    if (e->profiling || e->subtract || n_levels <= 0 || n_levels > 64 || (e->comm && !peer_on)) return 1;
-    int lut_w = 1, g_max = 2;
-    bool any_wide = false;
-    for (int a = 0; a < e->A; ++a) {
-        lut_w = std::max(lut_w, e->n_bins[a]);
-        any_wide = any_wide || e->wide[a];
-    }
-    for (auto& sp : e->splits) g_max = std::max(g_max, sp.n_seg);
-    // frontier bounds of every level
-    std::vector<std::vector<int32_t>> ub((size_t)n_levels, std::vector<int32_t>((size_t)T));
-    std::vector<long long> nf_ub((size_t)n_levels, 0);
-    long long nf_max = 0, nf_total = 0;
-    for (int level = 0; level < n_levels; ++level)
-        for (int t = 0; t < T; ++t) {
-            const long long v = level == 0 ? nodes_per_tree[t] : std::min<long long>((long long)ub[(size_t)level - 1][(size_t)t] * g_max, (long long)AVT_NODE_NONE - 1);
-            ub[(size_t)level][(size_t)t] = (int32_t)v;
-            nf_ub[(size_t)level] += v;
-            nf_max = std::max(nf_max, nf_ub[(size_t)level]);
-        }
-    for (auto v : nf_ub) nf_total += v;
-    if (nf_max == 0 || nf_max > kAsyncNodeLimit) return 1;
-    const size_t hw_max = (size_t)nf_max * e->TB * e->C;
-    if (peer_on && hw_max > e->peer.cap_words) return 1;
-    if (int rc = upload_order(e, class_order)) return rc;
-    const bool want_records = records != nullptr || n_records != nullptr;
-    // ---- every buffer at its final size before anything is enqueued
-    CUDA_TRY(e, e->d_next_count.ensure((size_t)T));
-    CUDA_TRY(e, e->d_err.ensure(1));
-    CUDA_TRY(e, e->d_nb_all.ensure((size_t)(n_levels + 1) * (T + 1)));
-    CUDA_TRY(e, e->d_av.ensure((size_t)nf_max * e->S));
-    CUDA_TRY(e, e->d_best.ensure((size_t)nf_max));
-    CUDA_TRY(e, e->d_best_eval.ensure((size_t)nf_max));
-    CUDA_TRY(e, e->d_node_attr.ensure((size_t)nf_max));
-    CUDA_TRY(e, e->d_lut.ensure((size_t)nf_max * lut_w));
-    if (peer_on) CUDA_TRY(e, e->d_hsum.ensure(hw_max));
-    else CUDA_TRY(e, e->d_H.ensure(hw_max));
-    if (want_records) CUDA_TRY(e, e->d_records.ensure((size_t)nf_total));
-    CUDA_TRY(e, e->d_levels.ensure((size_t)n_levels * sizeof(LevelParams)));
-    CUDA_TRY(e, cudaMemsetAsync(e->d_err.p, 0, sizeof(int32_t), e->stream));
-    auto nb_level = [&](int level) { return e->d_nb_all.p + (size_t)level * (T + 1); };
-    auto arena_H = [&](int parity) { return e->peer.arena + 64 + (size_t)parity * e->peer.cap_words; };
-    std::vector<int32_t> nb_host((size_t)T + 1, 0);
-    for (int t = 0; t < T; ++t) nb_host[(size_t)t + 1] = nb_host[(size_t)t] + nodes_per_tree[t];
-    CUDA_TRY(e, cudaMemcpyAsync(nb_level(0), nb_host.data(), ((size_t)T + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
-    // ---- launch geometry: as many blocks as can be co-resident
-    void (*kern)(const PersistArgs) = nullptr;
-    switch ((e->any_w ? 2 : 0) | (any_wide ? 1 : 0)) {
-        case 0: kern = grow_persistent_kernel<false, false>; break;
-        case 1: kern = grow_persistent_kernel<false, true>; break;
-        case 2: kern = grow_persistent_kernel<true, false>; break;
-        default: kern = grow_persistent_kernel<true, true>; break;
-    }
-    // ---- per-level plans
-    std::vector<LevelParams> lv((size_t)n_levels);
-    std::vector<size_t> rec_off((size_t)n_levels, 0);
-    size_t smem_max = 0, rec_total = 0;
-    FusedRepart fr{};
-    uint16_t* const nid_start = e->nid_cur;
-    if (peer_on && e->peer.lazy) {
-        // the stream-ordered loop left its buffers without a trailing round and this loop restarts the numbering
-        ++e->peer.epoch;
-        peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
-        peer_wait_kernel<<<1, 32, 0, e->stream>>>(e->peer.arena, e->peer.n, e->peer.epoch);
-        CUDA_TRY(e, cudaGetLastError());
-        e->peer.lazy = false;
-        e->peer.seq = 0;
-    }
-    const uint32_t epoch_start = e->peer.epoch;
-    bool ok = true;
-    for (int level = 0; level < n_levels && ok; ++level) {
-        int n_max = 0;
-        for (int t = 0; t < T; ++t) n_max = std::max(n_max, ub[(size_t)level][(size_t)t]);
-        e->NF = (int)nf_ub[(size_t)level];
-        if (level > 0) fr.prev_node_base = nb_level(level - 1);
-        e->H_cur = peer_on ? arena_H(level & 1) : e->d_H.p;
-        if (peer_on) ++e->peer.epoch;
-        e->signal_pending = peer_on;
-        HistPlan hp;
-        int rc = launch_histogram(e, n_max, level > 0 ? &fr : nullptr, nb_level(level), &hp);
-        e->H_cur = nullptr;
-        e->signal_pending = false;
-        if (rc) return rc;
-        if (hp.variant != 0 || (peer_on && !e->signal_in_hist)) { ok = false; break; }
-        LevelParams& L = lv[(size_t)level];
-        memset(&L, 0, sizeof L);
-        L.ha = hp.ha;
-        L.n_groups = (int)hp.grid.z;
-        L.repart = level > 0;
-        smem_max = std::max(smem_max, hp.smem);
-        L.Hc = peer_on ? e->d_hsum.p : e->d_H.p;
-        L.n_nodes_dev = nb_level(level) + T;
-        PlanArgs& pa = L.pa;
-        pa.best = e->d_best.p;
-        pa.best_eval = e->d_best_eval.p;
-        pa.node_base = nb_level(level);
-        pa.node_attr = e->d_node_attr.p;
-        pa.child_lut = e->d_lut.p;
-        pa.next_count = e->d_next_count.p;
-        pa.records = want_records ? e->d_records.p + rec_total : nullptr;
-        pa.err = e->d_err.p;
-        pa.next_node_base = nb_level(level + 1);
-        pa.lut_w = lut_w;
-        pa.level = level;
-        pa.n_trees = T;
-        if (peer_on) {
-            pa.peer_H = e->d_peer_H[level & 1].p;
-            pa.peer_flags = e->peer.arena;
-            pa.h_sum = e->d_hsum.p;
-            pa.peer_epoch = e->peer.epoch;
-            pa.n_ranks = e->peer.n;
-        }
-        if (level + 1 < n_levels) {
-            L.zero_next_ptr = peer_on ? arena_H((level + 1) & 1) : e->d_H.p;
-            L.zero_next_words = nf_ub[(size_t)level + 1] * e->TB * e->C;
-        }
-        rec_off[(size_t)level] = rec_total;
-        rec_total += (size_t)nf_ub[(size_t)level];
-        fr.node_attr = e->d_node_attr.p;
-        fr.child_lut = e->d_lut.p;
-        fr.lut_w = lut_w;
-        fr.prev_n_max = n_max;
-    }
-    if (!ok) {   // a level needs the global-atomics pass: undo the bookkeeping, let the stream-ordered loop run
-        e->nid_cur = nid_start;
-        e->peer.epoch = epoch_start;
-        return 1;
-    }
-    int occ = 0;
-    CUDA_TRY(e, cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem_max, 1024)));
-    CUDA_TRY(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)kern, kScanThreads, smem_max));
-    if (occ < 1) {
-        e->nid_cur = nid_start;
-        e->peer.epoch = epoch_start;
-        return 1;
-    }
-    const int n_blocks = e->sm_count * std::min(occ, 8);
-    for (int level = 0; level < n_levels; ++level) {
-        LevelParams& L = lv[(size_t)level];
-        const long long tiles = (e->N + (long long)kScanThreads * kRowsPerThread - 1) / ((long long)kScanThreads * kRowsPerThread);
-        L.n_chunks = (int)std::max<long long>(1, std::min<long long>(tiles, (long long)n_blocks / ((long long)T * L.n_groups)));
-    }
-    CUDA_TRY(e, cudaMemcpyAsync(e->d_levels.p, lv.data(), lv.size() * sizeof(LevelParams), cudaMemcpyHostToDevice, e->stream));
-    // level 0's histogram region starts cleared; later levels are cleared inside the kernel
-    CUDA_TRY(e, cudaMemsetAsync(peer_on ? arena_H(0) : e->d_H.p, 0, (size_t)nf_ub[0] * e->TB * e->C * sizeof(uint32_t), e->stream));
-    PersistArgs pg{};
-    pg.levels = reinterpret_cast<const LevelParams*>(e->d_levels.p);
-    pg.n_levels = n_levels;
-    pg.st = make_table(e);
-    pg.order = e->d_order.p;
-    pg.criterion = criterion;
-    pg.av = e->d_av.p;
-    pg.best = e->d_best.p;
-    pg.best_eval = e->d_best_eval.p;
-    pg.final_nid = e->nid_cur;
-    pg.cols = (const void* const*)e->d_colptrs.p;
-    pg.wide = e->d_wide.p;
-    pg.final_node_base = nb_level(n_levels - 1);
-    pg.node_attr = e->d_node_attr.p;
-    pg.child_lut = e->d_lut.p;
-    pg.lut_w = lut_w;
-    pg.T = T;
-    pg.N = e->N;
-    pg.Npad = e->Npad;
-    const bool stamps = getenv("AVT_PHASE_NS") != nullptr;
-    if (stamps) {
-        CUDA_TRY(e, e->d_phase.ensure((size_t)n_levels * 3 + 2));
-        pg.phase_ns = e->d_phase.p;
-    }
-    void* kargs[] = {(void*)&pg};
-    CUDA_TRY(e, cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)n_blocks), dim3(kScanThreads), kargs, smem_max, e->stream));
-    e->stats.hist_launches += n_levels;
-    e->stats.scan_launches += n_levels;
-    e->stats.repart_launches += 1;
-    e->stats.last_hist_variant = 0;
-    if (peer_on) {
-        ++e->peer.epoch;
-        peer_signal_kernel<<<1, 32, 0, e->stream>>>(e->d_remote_flags.p, e->peer.n, e->peer.epoch);
-        peer_wait_kernel<<<1, 32, 0, e->stream>>>(e->peer.arena, e->peer.n, e->peer.epoch);
-        CUDA_TRY(e, cudaGetLastError());
-    }
-    e->hist_valid = e->scan_valid = false;
-    e->NF = 0;
-    // ---- results
-    int32_t err = 0;
-    CUDA_TRY(e, cudaMemcpyAsync(&err, e->d_err.p, sizeof err, cudaMemcpyDeviceToHost, e->stream));
-    std::vector<int32_t> nb_all_host((size_t)(n_levels + 1) * (T + 1));
-    CUDA_TRY(e, cudaMemcpyAsync(nb_all_host.data(), e->d_nb_all.p, nb_all_host.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
-    std::vector<avt_grow_record> all;
-    if (want_records) {
-        all.resize(rec_total);
-        CUDA_TRY(e, cudaMemcpyAsync(all.data(), e->d_records.p, rec_total * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
-    }
-    if (int rc = sync_and_resolve(e)) return rc;
-    if (stamps) {   // developer timing: phase durations of every level
-        std::vector<unsigned long long> ns((size_t)n_levels * 3 + 2);
-        CUDA_TRY(e, cudaMemcpy(ns.data(), e->d_phase.p, ns.size() * 8, cudaMemcpyDeviceToHost));
-        fprintf(stderr, "[avt] persistent loop, grid %d x %d threads, %zu B dynamic smem\n", n_blocks, kScanThreads, smem_max);
-        for (int level = 0; level < n_levels; ++level)
-            fprintf(stderr, "[avt]   level %d: hist %.1f us, scan %.1f us, plan+clear %.1f us\n", level, (ns[1 + level * 3] - ns[level * 3]) * 1e-3,
-                    (ns[2 + level * 3] - ns[1 + level * 3]) * 1e-3, (ns[3 + level * 3] - ns[2 + level * 3]) * 1e-3);
-        fprintf(stderr, "[avt]   final repartition %.1f us, total %.1f us\n", (ns[1 + n_levels * 3] - ns[n_levels * 3]) * 1e-3, (ns[1 + n_levels * 3] - ns[0]) * 1e-3);
-    }
-    if (err) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
-    for (int t = 0; t < T; ++t) nodes_per_tree[t] = nb_all_host[(size_t)n_levels * (T + 1) + t + 1] - nb_all_host[(size_t)n_levels * (T + 1) + t];
-    int64_t nrec = 0;
-    if (want_records)
-        for (int level = 0; level < n_levels; ++level) {
-            const size_t true_nf = (size_t)nb_all_host[(size_t)level * (T + 1) + T];
-            for (size_t i = 0; i < true_nf; ++i) {
-                const avt_grow_record& r = all[rec_off[(size_t)level] + i];
-                if (r.split < 0) continue;
-                if (records && nrec < max_records) records[nrec] = r;
-                ++nrec;
-            }
-        }
-    if (n_records) *n_records = nrec;
-    return AVT_OK;
-}
-
 int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
                     avt_grow_record* records, int64_t max_records, int64_t* n_records) {
     if (!e) return AVT_E_INVALID;
@@ -2116,7 +1864,6 @@ int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const ui
     CUDA_TRY(e, cudaEventRecord(e->gev0, e->stream));
     e->gev1_recorded = false;
     int rc = 1;
-    if (e->grow_host_loop == 0 && e->persistent) rc = grow_persistent_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
     if (rc > 0) {
         if (e->grow_host_loop == 2) rc = grow_device_loop_sync(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
         else if (e->grow_host_loop) rc = grow_host_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
@@ -2434,6 +2181,8 @@ extern "C" int avt_histogram_static(int device, int64_t n_rows, int32_t n_attrs,
     if (n_classes < 1 || n_classes > AVT_MAX_CLASSES) return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: n_classes %d outside 1..%d", n_classes, AVT_MAX_CLASSES);
     if (n_nodes < 1 || n_nodes >= (int)AVT_NODE_NONE) return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: n_nodes %d outside 1..%d", n_nodes, AVT_NODE_NONE - 1);
     if (device < 0 || device >= AVT_STATIC_MAX_DEVICES) return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: device %d outside 0..%d", device, AVT_STATIC_MAX_DEVICES - 1);
+    if (n_rows > (int64_t)AVT_STATIC_SCRATCH_BYTES)   // before any size arithmetic: a huge row count must not wrap the carve below
+        return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: %lld rows cannot fit the built-in %u-byte array", (long long)n_rows, (unsigned)AVT_STATIC_SCRATCH_BYTES);
 
     // ---- carve the static array (fixed-size host bookkeeping only: nothing is allocated anywhere)
     int32_t bin_off[AVT_STATIC_MAX_ATTRS + 1], wide[AVT_STATIC_MAX_ATTRS];
@@ -2455,6 +2204,7 @@ extern "C" int avt_histogram_static(int device, int64_t n_rows, int32_t n_attrs,
     const size_t off_binoff = cur;    cur += align256((size_t)(n_attrs + 1) * sizeof(int32_t));
     const size_t off_wide = cur;      cur += align256((size_t)n_attrs * sizeof(int32_t));
     const size_t off_nb = cur;        cur += align256(2 * sizeof(int32_t));
+    const size_t off_bad = cur;       cur += align256(sizeof(int32_t));
     const size_t off_hist = cur;
     const size_t hist_bytes = (size_t)n_nodes * TB * n_classes * sizeof(uint32_t);
     cur += align256(hist_bytes);
@@ -2464,6 +2214,12 @@ extern "C" int avt_histogram_static(int device, int64_t n_rows, int32_t n_attrs,
                     "counts) but the built-in array holds %u bytes; use avt_level_histogram (which allocates) or split the rows",
                     cur, (long long)n_rows, n_attrs, n_nodes, TB, n_classes, (unsigned)AVT_STATIC_SCRATCH_BYTES);
 
+    // the caller's current device is put back on every return path
+    struct DeviceRestore {
+        int prev = -1;
+        ~DeviceRestore() { if (prev >= 0) cudaSetDevice(prev); }
+    } restore;
+    if (cudaGetDevice(&restore.prev) != cudaSuccess) restore.prev = -1;
     cudaError_t st = cudaSetDevice(device);
     if (st != cudaSuccess) return fail(nullptr, AVT_E_CUDA, "avt_histogram_static: cudaSetDevice(%d): %s", device, cudaGetErrorString(st));
     unsigned char* base = nullptr;
@@ -2502,6 +2258,7 @@ extern "C" int avt_histogram_static(int device, int64_t n_rows, int32_t n_attrs,
     STATIC_TRY(cudaMemcpy(base + off_nb, node_base, sizeof node_base, cudaMemcpyHostToDevice));
     // the counts are accumulated with atomics: whatever an earlier call left in this region must go
     STATIC_TRY(cudaMemset(base + off_hist, 0, hist_bytes));
+    STATIC_TRY(cudaMemset(base + off_bad, 0, sizeof(int32_t)));
 
     HistArgs ha{};
     ha.cols = (const void* const*)(base + off_ptrs);
@@ -2516,12 +2273,18 @@ extern "C" int avt_histogram_static(int device, int64_t n_rows, int32_t n_attrs,
     ha.C = n_classes;
     ha.TB = TB;
     ha.T = 1;
+    ha.bad = (int32_t*)(base + off_bad);   // the caller's ids and codes are unvalidated: out-of-shape rows are dropped and reported
     int sm_count = kSmCountFallback;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device);
     const long long blocks = std::min<long long>((n_rows + 255) / 256, (long long)sm_count * 8);
     hist_global_kernel<<<dim3((unsigned)blocks, 1), 256, 0, 0>>>(ha, n_attrs, (const int32_t*)(base + off_binoff), (const int32_t*)(base + off_wide));
     STATIC_TRY(cudaGetLastError());
     // synchronous copy on the same stream: waits for the kernel
+    int32_t bad = 0;
+    STATIC_TRY(cudaMemcpy(&bad, base + off_bad, sizeof bad, cudaMemcpyDeviceToHost));
+    if (bad)
+        return fail(nullptr, AVT_E_INVALID, "avt_histogram_static: the data does not fit the declared shape (a node id >= n_nodes other than AVT_NODE_NONE, "
+                    "a bin code >= n_bins[attribute] or a class code >= n_classes); nothing was written to hist_out");
     STATIC_TRY(cudaMemcpy(hist_out, base + off_hist, hist_bytes, cudaMemcpyDeviceToHost));
 #undef STATIC_TRY
     return AVT_OK;

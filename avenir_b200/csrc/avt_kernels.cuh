@@ -61,6 +61,8 @@ struct HistArgs {
     int signal_ranks;
     // bit-packed codes: when the data set has <= 4 narrow attributes whose codes fit one byte together, the pass reads that
     // one byte per row instead of one byte per attribute (pack_codes_kernel builds it when the data set is loaded)
+    int32_t* bad;            // hist_global_kernel only, nullable: rows whose node id, bin code or class code is outside the declared
+                             // shape are not counted and *bad is set to 1 (callers that stage unvalidated data: avt_histogram_static)
     const uint8_t* packed;   // [Npad] or nullptr
     uint32_t pk_shift[4];    // bit position of attribute q's code
     uint32_t pk_mask4[4];    // its mask, replicated into the four bytes of a word
@@ -368,15 +370,20 @@ __global__ void __launch_bounds__(256) hist_global_kernel(const HistArgs a, int 
         live = live && node != AVT_NODE_NONE && w != 0;
         if (live && a.skip) live = a.skip[nb + node] == 0;
         const uint32_t cl = live ? a.cls[r] : 0;
+        if (a.bad && live && (node >= (uint32_t)(a.node_base[t + 1] - nb) || cl >= (uint32_t)a.C)) {
+            *a.bad = 1;
+            live = false;
+        }
         for (int at = 0; at < n_attrs; ++at) {
             unsigned long long idx = ~0ULL - lane;  // unique dummy key for idle lanes
             if (live) {
                 uint32_t code = wide[at] ? ((const uint16_t*)a.cols[at])[r] : ((const uint8_t*)a.cols[at])[r];
-                idx = ((unsigned long long)(nb + node) * a.TB + bin_off[at] + code) * a.C + cl;
+                if (a.bad && code >= (uint32_t)(bin_off[at + 1] - bin_off[at])) *a.bad = 1;
+                else idx = ((unsigned long long)(nb + node) * a.TB + bin_off[at] + code) * a.C + cl;
             }
             const unsigned peers = __match_any_sync(0xffffffffu, idx);
             const uint32_t sum = __reduce_add_sync(peers, w);
-            if (live && (unsigned)(__ffs(peers) - 1) == lane) atomicAdd(&a.H[idx], sum);
+            if (live && idx < ~0ULL - 31 && (unsigned)(__ffs(peers) - 1) == lane) atomicAdd(&a.H[idx], sum);
         }
     }
 }
@@ -716,5 +723,4 @@ __global__ void __launch_bounds__(256) repartition_fast_kernel(const RepartFastA
 #include "avt_scan_fast.cuh"
 #include "avt_csv.cuh"
 #include "avt_predict.cuh"
-#include "avt_persistent.cuh"
 #include "avt_bagging.cuh"

@@ -59,9 +59,9 @@ __global__ void peer_signal_kernel(uint32_t* const* remote_flags, int n_ranks, u
 
 // Waits until every rank has signalled `epoch` (used once at the end of a level loop, so that no rank
 // reuses its exchange buffers while another is still reading them).
-__global__ void peer_wait_kernel(const uint32_t* flags, int n_ranks, uint32_t epoch) {
+__global__ void peer_wait_kernel(const uint32_t* flags, int n_ranks, uint32_t epoch, int32_t* err) {
     if ((int)threadIdx.x < n_ranks)
-        while ((int32_t)(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) {}
+        if (!wait_flag_bounded(flags + threadIdx.x, epoch)) *err = 3;
 }
 
 // The same with a bound on the wait (engine teardown: a rank that is gone must not hang the others).
@@ -220,7 +220,7 @@ __device__ __forceinline__ void scan_node(const uint32_t* H, const SplitTable& s
             // every rank's partial counts for this node, pulled over NVLink and summed; the ranks' frontiers are
             // identical, so node indices agree.  Wait first until all of them have finished their histogram pass.
             if ((int)threadIdx.x < plan.n_ranks)
-                while ((int32_t)(ld_acquire_sys(plan.peer_flags + threadIdx.x) - plan.peer_epoch) < 0) {}
+                if (!wait_flag_bounded(plan.peer_flags + threadIdx.x, plan.peer_epoch)) *plan.err = 3;
             __syncthreads();
             const long long words = (long long)st.TB * C, off = (long long)node * words;
             const int dp = plan.drv_parent ? plan.drv_parent[node] : -1;

@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
     if (plan.peer_H) {
         // wait until every rank has finished this level's histogram pass (which also means: its previous scan)
         if (tid < plan.n_ranks)
-            while ((int32_t)(ld_acquire_sys(plan.peer_flags + tid) - plan.peer_epoch) < 0) {}
+            if (!wait_flag_bounded(plan.peer_flags + tid, plan.peer_epoch)) *plan.err = 3;
         __syncthreads();
     }
     const int n_nodes = *n_nodes_dev;
@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
             }
             if (node < n_nodes) atomicAdd(&s_sum[w], (uint32_t)v);
         }
-        if (timeout) *plan.err = 2;
+        if (timeout) *plan.err = 3;
         __syncthreads();
         if (node < n_nodes) {
             for (int w = tid; w < words; w += blockDim.x) plan.h_sum[off + w] = s_sum[w];

@@ -151,6 +151,15 @@ class Engine:
         self.n_rows, self.n_bins, self.n_classes = n, [int(b) for b in n_bins], int(n_classes)
         self.total_bins = sum(self.n_bins)
 
+    def load_dataset_device(self, col_ptrs: Sequence[int], cls_ptr: int, n_rows: int, n_bins: Sequence[int], n_classes: int):
+        """avt_dataset_load from buffers that already sit in this engine's device memory (raw device addresses, e.g.
+        torch_tensor.data_ptr(); uint8 / uint16 codes as in load_dataset).  The library copies them."""
+        nb = (C.c_int32 * len(n_bins))(*[int(b) for b in n_bins])
+        ptrs = (C.c_void_p * len(col_ptrs))(*[int(p) for p in col_ptrs])
+        self._check(self.lib.avt_dataset_load(self.h, int(n_rows), len(col_ptrs), nb, ptrs, C.c_void_p(int(cls_ptr)), int(n_classes)))
+        self.n_rows, self.n_bins, self.n_classes = int(n_rows), [int(b) for b in n_bins], int(n_classes)
+        self.total_bins = sum(self.n_bins)
+
     def load_csv(self, text: bytes, delim: str, attrs: Sequence[tuple], class_ordinal: int, class_values: Sequence[str],
                  skip_fields: int = 0):
         """avt_dataset_load_csv: CSV text -> data set, encoded on the device.  `attrs`: (ordinal, "int", [points]) |

@@ -140,3 +140,44 @@ def binned_dataset(n: int, n_bins, n_classes: int, seed: int = DEFAULT_SEED, sta
     rnd = (uniform(seed, rows, 6) * n_classes).astype(np.int64)
     cls = np.where(flip, rnd, cls).astype(np.uint8)
     return cols, cls
+
+
+def binned_dataset_device(n: int, n_bins, n_classes: int, seed: int = DEFAULT_SEED, start: int = 0, signal_attrs: int = 4,
+                          noise: float = 0.15, device="cuda", chunk: int = 8_000_000):
+    """binned_dataset, bit for bit, generated in device memory with torch integer/fp64 tensor ops (bench.py's C3/C5
+    workloads: 100 M rows x 32 attributes would take minutes on the host and 3.3 GB of upload).  Returns
+    ([uint8 tensor per attribute], uint8 class tensor); attributes with more than 256 bins are not supported here."""
+    import torch
+    assert all(b <= 256 for b in n_bins)
+    M64 = (1 << 64) - 1
+
+    def s64(v):  # uint64 constant as the int64 with the same bits
+        v &= M64
+        return v - (1 << 64) if v >= (1 << 63) else v
+
+    def lsr(z, k):  # logical shift right of int64 bit patterns
+        return (z >> k) & ((1 << (64 - k)) - 1)
+
+    def u01(rows, draw):
+        x = rows * 1024 + s64(((seed << 40) & M64) + draw) + s64(0x9E3779B97F4A7C15)
+        z = (x ^ lsr(x, 30)) * s64(0xBF58476D1CE4E5B9)
+        z = (z ^ lsr(z, 27)) * s64(0x94D049BB133111EB)
+        z = z ^ lsr(z, 31)
+        return lsr(z, 11).to(torch.float64) * (1.0 / 9007199254740992.0)
+
+    cols = [torch.empty(n, dtype=torch.uint8, device=device) for _ in n_bins]
+    cls = torch.empty(n, dtype=torch.uint8, device=device)
+    for s in range(0, n, chunk):
+        m = min(chunk, n - s)
+        rows = torch.arange(start + s, start + s + m, dtype=torch.int64, device=device)
+        score = torch.zeros(m, dtype=torch.int64, device=device)
+        for a, b in enumerate(n_bins):
+            code = torch.clamp((u01(rows, 32 + a) * b).to(torch.int64), max=b - 1)
+            cols[a][s:s + m] = code.to(torch.uint8)
+            if a < signal_attrs:
+                score += (code * 2 >= b).to(torch.int64) * (a + 1)
+        c = score % n_classes
+        flip = u01(rows, 5) < noise
+        rnd = (u01(rows, 6) * n_classes).to(torch.int64)
+        cls[s:s + m] = torch.where(flip, rnd, c).to(torch.uint8)
+    return cols, cls

@@ -118,7 +118,9 @@ const char* avt_last_error(const avt_engine* e);
 
 /* Uploads the once-encoded columnar data set.  Replaces the per-level re-read and re-parse of the
  * text rows in BuilderMapper.pathMapHelper (tree/DecisionTreeBuilder.java:266-320).
- * columns[a] is uint8[n_rows] when n_bins[a] <= 256, else uint16[n_rows]. */
+ * columns[a] is uint8[n_rows] when n_bins[a] <= 256, else uint16[n_rows].  The column and class buffers may be
+ * host memory (pageable or page-locked) or memory of this engine's device (a caller that encodes on the GPU);
+ * they are copied, the caller keeps ownership. */
 int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins,
                      const void* const* columns, const uint8_t* class_codes, int32_t n_classes);
 
@@ -312,7 +314,11 @@ int avt_set_hist_variant(avt_engine* e, int32_t variant);
  * stream or event creation happens.  Requests whose staged inputs plus counts exceed that array, or with
  * more than 64 attributes, fail with AVT_E_INVALID (avt_last_error(NULL) states needed vs available bytes).
  * The first call on each device looks up the array's device address: make it before any stream capture.
- * Calls on one GPU share the array; overlapping calls race -- serialise them. */
+ * Calls on one GPU share the array; overlapping calls race -- serialise them.
+ * The data is checked against the declared shape on the device: a node id >= n_nodes (other than AVT_NODE_NONE),
+ * a bin code >= n_bins[a] or a class code >= n_classes fails the call with AVT_E_INVALID and leaves hist_out alone.
+ * Side effects: the copies and the kernel run on the legacy default stream (which serialises with every blocking
+ * stream of the process) and the call blocks until the counts are back; the caller's current device is restored. */
 int avt_histogram_static(int device, int64_t n_rows, int32_t n_attrs, const int32_t* n_bins,
                          const void* const* columns, const uint8_t* class_codes, int32_t n_classes,
                          const uint16_t* node_ids, int32_t n_nodes, uint32_t* hist_out);

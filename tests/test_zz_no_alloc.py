@@ -42,6 +42,21 @@ def regular_histogram(cols, cls, n_bins, n_classes, node_ids, n_nodes):
     return h
 
 
+def numpy_histogram(cols, cls, n_bins, n_classes, node_ids, n_nodes):
+    """Independent count: one numpy bincount per attribute over (node, bin, class) keys."""
+    n = len(cls)
+    nid = np.zeros(n, dtype=np.int64) if node_ids is None else np.asarray(node_ids, dtype=np.int64)
+    live = nid != AVT_NODE_NONE
+    tb = sum(n_bins)
+    out = np.zeros((n_nodes, tb, n_classes), dtype=np.uint32)
+    off = 0
+    for c, b in zip(cols, n_bins):
+        key = (nid[live] * b + np.asarray(c, dtype=np.int64)[live]) * n_classes + np.asarray(cls, dtype=np.int64)[live]
+        out[:, off:off + b, :] = np.bincount(key, minlength=n_nodes * b * n_classes).reshape(n_nodes, b, n_classes)
+        off += b
+    return out
+
+
 def test_two_calls_in_a_row_match_the_allocating_entry_point():
     from avenir_b200 import _lib
     lib = _lib.load()
@@ -55,6 +70,7 @@ def test_two_calls_in_a_row_match_the_allocating_entry_point():
     rc, got1 = static_histogram(lib, cols1, cls1, bins1, 3, nid1, 5)
     assert rc == 0, lib.avt_last_error(None).decode()
     assert np.array_equal(got1, regular_histogram(cols1, cls1, bins1, 3, nid1, 5))
+    assert np.array_equal(got1, numpy_histogram(cols1, cls1, bins1, 3, nid1, 5))   # and against a count that shares no code with either
 
     # call 2 straight after, smaller and differently shaped: nothing of call 1 may show through
     n2, bins2 = 33_333, [2, 4, 2, 10]
@@ -63,6 +79,7 @@ def test_two_calls_in_a_row_match_the_allocating_entry_point():
     assert rc == 0, lib.avt_last_error(None).decode()
     want2 = regular_histogram(cols2, cls2, bins2, 2, None, 1)
     assert np.array_equal(got2, want2)
+    assert np.array_equal(got2, numpy_histogram(cols2, cls2, bins2, 2, None, 1))
     assert int(got2.sum()) == 4 * n2            # every row counted once per attribute, no stale counts
 
     # and call 1's inputs again give call 1's answer again
@@ -82,3 +99,34 @@ def test_requests_beyond_the_built_in_array_are_refused():
     assert (out == 0xDEADBEEF).all()             # nothing was written
     rc, _ = static_histogram(lib, [np.zeros(10, dtype=np.uint8)] * 65, np.zeros(10, dtype=np.uint8), [2] * 65, 2, None, 1)
     assert rc == -1 and "limit 64" in lib.avt_last_error(None).decode()
+
+
+def test_data_outside_the_declared_shape_is_refused_and_the_device_is_left_alone():
+    """A node id >= n_nodes, a bin code >= n_bins[a] or a class code >= n_classes would index past the counts
+    (the last region of the built-in array): the call must fail, write nothing, and still work afterwards."""
+    import torch
+    from avenir_b200 import _lib
+    lib = _lib.load()
+    n, bins = 10_000, [4, 9]
+    rng = np.random.default_rng(5)
+    cols = [rng.integers(0, b, n).astype(np.uint8) for b in bins]
+    cls = rng.integers(0, 2, n).astype(np.uint8)
+    nid = rng.integers(0, 3, n).astype(np.uint16)
+    before = torch.cuda.current_device()
+    for what in ("node", "code", "class"):
+        c2, k2, n2 = [c.copy() for c in cols], cls.copy(), nid.copy()
+        if what == "node":
+            n2[777] = 3
+        elif what == "code":
+            c2[1][4242] = 9
+        else:
+            k2[99] = 2
+        rc, out = static_histogram(lib, c2, k2, bins, 2, n2, 3)
+        assert rc == -1 and "declared shape" in lib.avt_last_error(None).decode(), what
+        assert (out == 0xDEADBEEF).all()
+    # several nodes with node_ids = None: every row is in node 0, the other nodes stay empty
+    rc, out = static_histogram(lib, cols, cls, bins, 2, None, 3)
+    assert rc == 0 and np.array_equal(out, numpy_histogram(cols, cls, bins, 2, None, 3)) and not out[1:].any()
+    rc, out = static_histogram(lib, cols, cls, bins, 2, nid, 3)
+    assert rc == 0 and np.array_equal(out, numpy_histogram(cols, cls, bins, 2, nid, 3))
+    assert torch.cuda.current_device() == before
