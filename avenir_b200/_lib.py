@@ -74,6 +74,7 @@ SIGNATURES = {
     "avt_forest_init": (C.c_int, [_P, C.c_int32, C.POINTER(_P), C.POINTER(_P)]),
     "avt_forest_init_sampled": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64, C.c_int64]),
     "avt_forest_weights": (C.c_int, [_P, C.c_int32, _P]),
+    "avt_forest_reset": (C.c_int, [_P]),
     "avt_split_table_set": (C.c_int, [_P, C.c_int32, C.POINTER(Split), C.POINTER(C.c_int32), C.c_int32, _P, C.c_int64]),
     "avt_level_histogram": (C.c_int, [_P, C.POINTER(C.c_int32), _P]),
     "avt_level_scan": (C.c_int, [_P, C.c_int32, _P, _P, C.POINTER(NodeBest)]),

@@ -159,7 +159,6 @@ struct avt_engine {
     long long hist_target_addrs = 4096;  // AVT_HIST_TARGET_ADDRS
     int hist_max_bpsm = 2;               // AVT_HIST_BPSM: histogram blocks per SM.  2 x 512 threads x 64 registers fill the register file, so more
                                          // blocks only queue behind them and add flushes (measured on C2: 0.383 ms/step with 2, 0.403 with 4, 0.52 with 1)
-    int grow_host_loop = 0;              // AVT_GROW_HOST=1: host-driven level loop (3 round trips per level)
     // comm
     ncclComm_t comm = nullptr;
     int n_ranks = 1, rank = 0;
@@ -184,9 +183,10 @@ struct avt_engine {
     DevBuf<uint32_t> d_hsum, d_hsum2, d_H2, d_ticket2;
     DevBuf<uint8_t> d_skip;
     DevBuf<int32_t> d_drv_parent, d_kids;
-    bool subtract = false;             // AVT_SUBTRACT=1: sibling subtraction (count the smaller children, derive the largest); measured
-                                       // neutral on C2/C3/C5 shapes in round 1 -- the pass is not bound by update issue -- so off by default
+    int subtract_mode = -1;            // sibling subtraction: -1 automatic (on for the shapes the forest kernel takes), AVT_SUBTRACT=0/1 forces
     const uint8_t* skip_cur = nullptr; // skip marks for the pass being launched
+    int32_t* hist_err = nullptr;       // error word of the level loop that is launching the pass (nullptr: d_err)
+    int g_max_splits = 2;              // most segments of any installed split (bounds the counted nodes under sibling subtraction)
     bool ticket2_zeroed = false;
     uint32_t* H_cur = nullptr;         // histogram buffer of the pass being launched (nullptr: d_H)
     bool signal_pending = false;       // the pass being launched must signal peer.epoch to every rank
@@ -344,13 +344,18 @@ int avt_create(int device, avt_engine** out) {
         for (const void* k : kernels)
             if (st == cudaSuccess) st = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
     }
+    {
+        const void* kernels[] = {(const void*)hist_forest_kernel<false, false>, (const void*)hist_forest_kernel<false, true>,
+                                 (const void*)hist_forest_kernel<true, false>, (const void*)hist_forest_kernel<true, true>};
+        for (const void* k : kernels)
+            if (st == cudaSuccess) st = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    }
     if (st != cudaSuccess) {
         int rc = fail(nullptr, AVT_E_CUDA, "avt_create: %s", cudaGetErrorString(st));
         delete e;
         return rc;
     }
     if (const char* v = getenv("AVT_HIST_TARGET_ADDRS")) e->hist_target_addrs = std::max(1LL, atoll(v));
-    if (const char* v = getenv("AVT_GROW_HOST")) e->grow_host_loop = atoi(v);
     if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
     if (const char* v = getenv("AVT_SCAN_FAST")) e->scan_fast = atoi(v) != 0;
     if (const char* v = getenv("AVT_PEER_SIGNAL_SCAN")) e->peer_signal_scan = atoi(v) != 0;
@@ -358,7 +363,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_PEER_TRAIL")) e->peer_trailing_round = atoi(v) != 0;
     if (const char* v = getenv("AVT_LOOKBACK")) e->lookback = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
-    if (const char* v = getenv("AVT_SUBTRACT")) e->subtract = atoi(v) != 0;
+    if (const char* v = getenv("AVT_SUBTRACT")) e->subtract_mode = atoi(v) != 0 ? 1 : 0;
     if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
     *out = e;
     return AVT_OK;
@@ -809,6 +814,22 @@ int avt_forest_init_sampled(avt_engine* e, int32_t n_trees, int32_t mode, int64_
     return AVT_OK;
 }
 
+int avt_forest_reset(avt_engine* e) {
+    if (!e) return AVT_E_INVALID;
+    if (e->T == 0) return fail(e, AVT_E_STATE, "avt_forest_reset: no forest (avt_forest_init / avt_forest_init_sampled first)");
+    if (int rc = use_device(e)) return rc;
+    e->nid_cur = e->d_nid.p;
+    if (e->Npad == e->N) {
+        CUDA_TRY(e, cudaMemsetAsync(e->d_nid.p, 0, (size_t)e->T * e->Npad * 2, e->stream));
+    } else {
+        CUDA_TRY(e, cudaMemsetAsync(e->d_nid.p, 0xFF, (size_t)e->T * e->Npad * 2, e->stream));
+        for (int t = 0; t < e->T; ++t) CUDA_TRY(e, cudaMemsetAsync(e->d_nid.p + (size_t)t * e->Npad, 0, (size_t)e->N * 2, e->stream));
+    }
+    e->hist_valid = e->scan_valid = false;
+    e->NF = 0;
+    return AVT_OK;
+}
+
 int avt_forest_weights(avt_engine* e, int32_t tree, uint8_t* out) {
     if (!e) return AVT_E_INVALID;
     if (tree < 0 || tree >= e->T || !out) return fail(e, AVT_E_INVALID, "avt_forest_weights: tree %d out of range", tree);
@@ -851,6 +872,8 @@ int avt_split_table_set(avt_engine* e, int32_t n_splits, const avt_split* splits
     for (int a = prev + 1; a <= e->A; ++a) attr_first[a] = n_splits;
     e->S = n_splits;
     e->splits.assign(splits, splits + n_splits);
+    e->g_max_splits = 2;
+    for (int i = 0; i < n_splits; ++i) e->g_max_splits = std::max(e->g_max_splits, splits[i].n_seg);
     e->h_bounds.assign(bounds, bounds + std::max(n_bounds, 0));
     e->h_seg_lut.assign(seg_lut, seg_lut + std::max<int64_t>(n_lut, 0));
     if (int rc = upload(e, e->d_splits, splits, (size_t)n_splits)) return rc;
@@ -904,9 +927,25 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         any_wide = any_wide || e->wide[a];
     }
     int variant = (per_bin * max_bins <= kHistWordsBudget) ? 0 : 1;
+    // forest kernel (avt_forest.cuh): lane = attribute, so it wants enough attributes to fill a warp, uint8 codes, and room
+    // for at least one tree's counted nodes in shared memory
+    int f_slots = std::max(n_max, 1), f_G = 0;
+    size_t f_smem = 0;
+    {
+        if (e->skip_cur) f_slots = std::max(1, n_max - n_max / std::max(2, e->g_max_splits));   // one child of every expanded parent is derived, not counted
+        const size_t per_tree = (size_t)f_slots * e->C * max_bins * 128 + ((size_t)n_max + 1 + f_slots) * 2 + 1;
+        const size_t fixed = (size_t)kForestWarps * kForestRing * kForestUnitBytes + kForestWarps * 128 + 64;
+        if (!any_wide && max_bins <= 256 && per_tree + fixed <= kMaxDynSmem) {
+            f_G = (int)std::min<size_t>((size_t)e->T, (kMaxDynSmem - fixed) / per_tree);
+            f_smem = fixed + per_tree * (size_t)f_G;
+        }
+        if (f_G > 0 && e->A >= 16 && e->force_variant < 0) variant = 2;
+    }
     if (e->force_variant >= 0) {
         if (e->force_variant == 0 && variant == 1)
             return fail(e, AVT_E_INVALID, "avt_level_histogram: shared-memory variant forced but the frontier needs %lld words", per_bin * max_bins);
+        if (e->force_variant == 2 && f_G == 0)
+            return fail(e, AVT_E_INVALID, "avt_level_histogram: forest variant forced but it needs uint8 codes, <= 256 bins per attribute and one tree's counters in shared memory");
         variant = e->force_variant;
     }
     uint16_t* nid_in = e->nid_cur;
@@ -1092,6 +1131,44 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         e->stats.last_hist_grid = (int)(grid.x * grid.y * grid.z);
         e->stats.last_hist_block = kHistThreads;
         e->stats.last_hist_smem = (int)smem;
+    } else if (variant == 2) {
+        ForestArgs fa{};
+        fa.bin_off = e->d_bin_off.p;
+        fa.A = e->A;
+        fa.G = f_G;
+        fa.n_slots = f_slots;
+        fa.Bmax = max_bins;
+        fa.n_nodes_max = std::max(n_max, 1);
+        if (!e->hist_err) CUDA_TRY(e, e->d_err.ensure(1));
+        fa.err = e->hist_err ? e->hist_err : e->d_err.p;
+        const int groups = (e->T + f_G - 1) / f_G, achunks = (e->A + 31) / 32;
+        const long long n_tiles = (e->N + 31) / 32;
+        // grid.x = tree group (fastest): blocks that run together read the same rows, so the codes come out of L2 once per group
+        long long parts = std::max<long long>(1, ((long long)e->sm_count * 4 + (long long)groups * achunks - 1) / ((long long)groups * achunks));
+        long long tpp = (n_tiles + parts - 1) / parts;
+        tpp = std::max<long long>((tpp + kForestWarps - 1) / kForestWarps * kForestWarps, (long long)kForestWarps * 8);
+        parts = std::min<long long>((n_tiles + tpp - 1) / tpp, 65535);
+        tpp = (n_tiles + parts - 1) / parts;
+        fa.tiles_per_part = tpp;
+        dim3 grid((unsigned)groups, (unsigned)parts, (unsigned)achunks);
+        void (*kern)(const HistArgs, const ForestArgs) = e->any_w ? (fr ? hist_forest_kernel<true, true> : hist_forest_kernel<true, false>)
+                                                                  : (fr ? hist_forest_kernel<false, true> : hist_forest_kernel<false, false>);
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = grid;
+        cfg.blockDim = dim3(kForestThreads);
+        cfg.dynamicSmemBytes = f_smem;
+        cfg.stream = e->stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = (e->pdl && e->pdl_chain) ? 1 : 0;
+        CUDA_TRY(e, cudaLaunchKernelEx(&cfg, kern, ha, fa));
+        e->signal_in_hist = false;
+        e->stats.last_hist_replicas = f_G;
+        e->stats.last_hist_grid = (int)(grid.x * grid.y * grid.z);
+        e->stats.last_hist_block = kForestThreads;
+        e->stats.last_hist_smem = (int)f_smem;
     } else {
         long long blocks = std::min<long long>((e->N + 255) / 256, (long long)e->sm_count * 8);
         dim3 grid((unsigned)blocks, (unsigned)e->T);
@@ -1258,195 +1335,6 @@ int avt_level_repartition(avt_engine* e, const int32_t* node_attr, const uint16_
     return AVT_OK;
 }
 
-// Host-driven form of the level loop (separate kernels, three device->host round trips per level);
-// kept for A/B checks against the device-driven loop below (AVT_GROW_HOST=1).
-static int grow_host_loop(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
-                          avt_grow_record* records, int64_t max_records, int64_t* n_records) {
-    int64_t nrec = 0;
-    int lut_w = 1;
-    for (int a = 0; a < e->A; ++a) lut_w = std::max(lut_w, e->n_bins[a]);
-    std::vector<avt_node_best> best;
-    std::vector<avt_split_eval> evals;
-    std::vector<int32_t> ev_nodes, ev_splits, node_attr;
-    std::vector<uint16_t> child_lut;
-    for (int level = 0; level < n_levels; ++level) {
-        int NF = 0;
-        for (int t = 0; t < e->T; ++t) NF += nodes_per_tree[t];
-        if (NF == 0) break;
-        if (int rc = avt_level_histogram(e, nodes_per_tree, nullptr)) return rc;
-        best.resize((size_t)NF);
-        if (int rc = avt_level_scan(e, criterion, nullptr, class_order, best.data())) return rc;
-        ev_nodes.clear();
-        ev_splits.clear();
-        for (int g = 0; g < NF; ++g)
-            if (best[(size_t)g].population > 0 && best[(size_t)g].best_split >= 0) {
-                ev_nodes.push_back(g);
-                ev_splits.push_back(best[(size_t)g].best_split);
-            }
-        evals.resize(ev_nodes.size() ? ev_nodes.size() : 1);
-        if (int rc = avt_level_eval(e, criterion, class_order, (int32_t)ev_nodes.size(), ev_nodes.data(), ev_splits.data(), evals.data())) return rc;
-        node_attr.assign((size_t)NF, -1);
-        child_lut.assign((size_t)NF * lut_w, (uint16_t)AVT_NODE_NONE);
-        size_t k = 0;
-        int base = 0;
-        for (int t = 0; t < e->T; ++t) {
-            int next = 0;
-            for (int i = 0; i < nodes_per_tree[t]; ++i) {
-                const int g = base + i;
-                if (k >= ev_nodes.size() || ev_nodes[k] != g) continue;
-                const int s = ev_splits[k];
-                const avt_split_eval& ev = evals[k];
-                ++k;
-                const avt_split& sp = e->splits[(size_t)s];
-                node_attr[(size_t)g] = sp.attr;
-                avt_grow_record rec{};
-                rec.level = level; rec.tree = t; rec.node = i; rec.split = s;
-                rec.n_ties = best[(size_t)g].n_ties;
-                rec.min_av = best[(size_t)g].min_av;
-                for (int sg = 0; sg < AVT_MAX_SEG; ++sg) rec.child[sg] = -1;
-                for (int sg = 0; sg < sp.n_seg; ++sg) {
-                    int64_t pop = 0;
-                    for (int c = 0; c < e->C; ++c) pop += ev.seg_count[sg][c];
-                    rec.child_pop[sg] = pop;
-                    rec.child_stat[sg] = ev.seg_stat[sg];
-                    if (pop) {
-                        if (next >= (int)AVT_NODE_NONE - 1) return fail(e, AVT_E_INVALID, "avt_grow_levels: more than %d frontier nodes in tree %d", AVT_NODE_NONE - 1, t);
-                        rec.child[sg] = next++;
-                    }
-                }
-                const int B = e->n_bins[sp.attr];
-                for (int b = 0; b < B; ++b) {
-                    int sg;
-                    if (sp.kind == AVT_SPLIT_NUMERIC) {
-                        sg = 0;
-                        while (sg < sp.n_seg - 1 && b > e->h_bounds[(size_t)(sp.off + sg)]) ++sg;
-                    } else {
-                        sg = e->h_seg_lut[(size_t)(sp.off + b)];
-                        if (sg >= sp.n_seg) continue;
-                    }
-                    if (rec.child[sg] >= 0) child_lut[(size_t)g * lut_w + b] = (uint16_t)rec.child[sg];
-                }
-                if (records && nrec < max_records) records[nrec] = rec;
-                ++nrec;
-            }
-            base += nodes_per_tree[t];
-            nodes_per_tree[t] = next;
-        }
-        if (int rc = avt_level_repartition(e, node_attr.data(), child_lut.data(), lut_w)) return rc;
-    }
-    if (n_records) *n_records = nrec;
-    return sync_and_resolve(e);
-}
-
-// Device-driven level loop: per level ONE fused repartition+histogram pass, the scan (which also emits
-// the children of the best split) and a planning kernel that numbers the children and builds the next
-// pass's bin -> child tables on the device.  The host only reads back T frontier sizes per level.
-static int grow_device_loop_sync(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
-                            avt_grow_record* records, int64_t max_records, int64_t* n_records) {
-    int lut_w = 1;
-    for (int a = 0; a < e->A; ++a) lut_w = std::max(lut_w, e->n_bins[a]);
-    if (int rc = upload_order(e, class_order)) return rc;
-    CUDA_TRY(e, e->d_next_count.ensure((size_t)e->T));
-    CUDA_TRY(e, e->d_err.ensure(1));
-    CUDA_TRY(e, cudaMemsetAsync(e->d_err.p, 0, sizeof(int32_t), e->stream));
-    std::vector<int32_t> next((size_t)e->T);
-    std::vector<avt_grow_record> all;  // every level's records, in (level, tree, node) order
-    const bool want_records = records != nullptr || n_records != nullptr;
-    bool pending = false;  // a planned split not yet applied to the node ids
-    FusedRepart fr{};
-    for (int level = 0; level < n_levels; ++level) {
-        int n_max = 0;
-        if (int rc = set_frontier(e, nodes_per_tree, &n_max, "avt_grow_levels")) return rc;
-        if (e->NF == 0) break;
-        const int NF = e->NF;
-        // the tables of the previous level are indexed with the previous frontier's node_base
-        if (pending) {
-            CUDA_TRY(e, e->d_prev_node_base.ensure((size_t)e->T + 1));
-            CUDA_TRY(e, cudaMemcpyAsync(e->d_prev_node_base.p, e->d_node_base.p, ((size_t)e->T + 1) * sizeof(int32_t), cudaMemcpyDeviceToDevice, e->stream));
-            fr.prev_node_base = e->d_prev_node_base.p;
-        }
-        if (int rc = upload(e, e->d_node_base, e->node_base.data(), e->node_base.size())) return rc;
-        if (int rc = launch_histogram(e, n_max, pending ? &fr : nullptr)) return rc;
-        pending = false;
-        // scan + children of the best split
-        CUDA_TRY(e, e->d_av.ensure((size_t)NF * e->S));
-        CUDA_TRY(e, e->d_best.ensure((size_t)NF));
-        CUDA_TRY(e, e->d_best_eval.ensure((size_t)NF));
-        TimerSlot ts;
-        if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
-        scan_kernel<<<NF, kScanThreads, 0, e->stream>>>(e->d_H.p, make_table(e), nullptr, e->d_order.p, criterion, e->d_av.p, e->d_best.p,
-                                                        e->d_best_eval.p, nullptr, PlanArgs{});
-        CUDA_TRY(e, cudaGetLastError());
-        if (int rc = timer_close(e, ts)) return rc;
-        e->stats.scan_launches += 1;
-        e->scan_valid = true;
-        // plan: child numbering, next tables, records
-        // (node_attr / child_lut double as inputs of the NEXT histogram pass, so they must not be
-        //  overwritten before that pass has run: sizes only grow, and the pass above already consumed them)
-        CUDA_TRY(e, e->d_node_attr.ensure((size_t)NF));
-        CUDA_TRY(e, e->d_lut.ensure((size_t)NF * lut_w));
-        CUDA_TRY(e, e->d_records.ensure((size_t)NF));
-        PlanArgs pa{};
-        pa.best = e->d_best.p;
-        pa.best_eval = e->d_best_eval.p;
-        pa.node_base = e->d_node_base.p;
-        pa.node_attr = e->d_node_attr.p;
-        pa.child_lut = e->d_lut.p;
-        pa.next_count = e->d_next_count.p;
-        pa.records = want_records ? e->d_records.p : nullptr;
-        pa.err = e->d_err.p;
-        pa.lut_w = lut_w;
-        pa.level = level;
-        pa.n_trees = e->T;
-        TimerSlot tp;
-        if (int rc = timer_open(e, &e->stats.eval_ms, &tp)) return rc;
-        plan_kernel<<<1, kScanThreads, 0, e->stream>>>(pa, make_table(e));
-        CUDA_TRY(e, cudaGetLastError());
-        if (int rc = timer_close(e, tp)) return rc;
-        e->stats.eval_launches += 1;
-        if (want_records) {
-            const size_t at = all.size();
-            all.resize(at + (size_t)NF);
-            CUDA_TRY(e, cudaMemcpyAsync(all.data() + at, e->d_records.p, (size_t)NF * sizeof(avt_grow_record), cudaMemcpyDeviceToHost, e->stream));
-        }
-        CUDA_TRY(e, cudaMemcpyAsync(next.data(), e->d_next_count.p, (size_t)e->T * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
-        if (int rc = sync_and_resolve(e)) return rc;
-        for (int t = 0; t < e->T; ++t) nodes_per_tree[t] = next[(size_t)t];
-        fr.node_attr = e->d_node_attr.p;
-        fr.child_lut = e->d_lut.p;
-        fr.lut_w = lut_w;
-        fr.prev_n_max = n_max;
-        pending = true;
-    }
-    if (pending) {
-        // apply the last planned split so that the node ids match the returned frontier
-        TimerSlot tr;
-        if (int rc = timer_open(e, &e->stats.repart_ms, &tr)) return rc;
-        long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
-        dim3 grid((unsigned)blocks, (unsigned)e->T);
-        repartition_kernel<<<grid, 256, 0, e->stream>>>(e->nid_cur, (const void* const*)e->d_colptrs.p, e->d_wide.p, e->d_node_base.p,
-                                                        e->d_node_attr.p, e->d_lut.p, lut_w, e->N, e->Npad);
-        CUDA_TRY(e, cudaGetLastError());
-        if (int rc = timer_close(e, tr)) return rc;
-        e->stats.repart_launches += 1;
-        e->stats.repart_alg_bytes += (long long)e->N * e->T * 5;
-    }
-    e->hist_valid = e->scan_valid = false;
-    e->NF = 0;
-    int32_t err = 0;
-    CUDA_TRY(e, cudaMemcpyAsync(&err, e->d_err.p, sizeof err, cudaMemcpyDeviceToHost, e->stream));
-    if (int rc = sync_and_resolve(e)) return rc;
-    int64_t nrec = 0;
-    for (size_t i = 0; i < all.size(); ++i) {
-        if (all[i].split < 0) continue;
-        if (records && nrec < max_records) records[nrec] = all[i];
-        ++nrec;
-    }
-    if (err) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
-    if (n_records) *n_records = nrec;
-    return AVT_OK;
-}
-
 // Asynchronous form of the device-driven loop: nothing is read back until the last level.  The host
 // sizes every launch from an UPPER BOUND of the frontier (each node has at most max-n_seg children);
 // the kernels read the true frontier (node_base of every level lives on the device, written by the
@@ -1498,7 +1386,11 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         if (init != e->h_ctrl) CUDA_TRY(e, cudaStreamSynchronize(e->stream));   // the pageable source goes out of scope
     }
     const bool peer_on = e->peer.active && e->peer.n > 1;
-    const bool subtract = e->subtract;
+    // Sibling subtraction (count the smaller children, derive the largest as parent - siblings; exact in integers): pays off where
+    // the pass is bound by counter updates, i.e. on the shapes the forest kernel takes; AVT_SUBTRACT=0/1 overrides.
+    bool forest_shape = e->A >= 16;
+    for (int a = 0; a < e->A; ++a) forest_shape = forest_shape && !e->wide[a];
+    const bool subtract = e->subtract_mode < 0 ? forest_shape : e->subtract_mode != 0;
     const bool fast_scan = e->scan_fast && e->fast_scan_ok && !subtract;   // latency-optimised scan + planning (avt_scan_fast.cuh)
     // complete counts of a level: single GPU = the (ping-pong) histogram buffer itself; peer mode = the local sums
     auto H_level = [&](int level) { return (level & 1) ? e->d_H2.p : e->d_H.p; };
@@ -1621,7 +1513,8 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             CUDA_TRY(e, cudaMemsetAsync(e->d_skip.p, 0, (size_t)NF, e->stream));
         }
         derive_ok = true;
-        e->skip_cur = (subtract && level > 0 && planned_skip) ? e->d_skip.p : nullptr;
+        e->skip_cur = derive ? e->d_skip.p : nullptr;   // (without derivation the marks were just cleared: every node is counted)
+        e->hist_err = d_err_p;
         e->skip_h_memset = h_prezeroed;
         // programmatic dependent launch: legal when nothing but the previous scan kernel precedes this pass
         e->pdl_chain = level > 0 && h_prezeroed && !e->profiling && !(subtract && planned_skip && !derive);
@@ -1646,6 +1539,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         e->pdl_chain = false;
         e->H_cur = nullptr;
         e->skip_cur = nullptr;
+        e->hist_err = nullptr;
         e->signal_pending = false;
         if (peer_level) {
             if (!e->signal_in_hist) {
@@ -1840,6 +1734,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         for (size_t i = true_nf; i < rg.count; ++i) all[rg.host_at + i].level = -1;
     }
     if (err == 3) return fail(e, AVT_E_COMM, "avt_grow_levels: another rank's histogram did not arrive within %d s (a rank died, failed or skipped this call); the results of this call are invalid", (int)(kPeerWaitNs / 1000000000ull));
+    if (err == 4) return fail(e, AVT_E_STATE, "avt_grow_levels: a tree had more counted nodes than the histogram pass reserved slots for (internal bound violated)");
     if (err == 2) return fail(e, AVT_E_CUDA, "avt_grow_levels: a scan block waited too long for its predecessors (look-back planning)");
     if (err) return fail(e, AVT_E_INVALID, "avt_grow_levels: a tree exceeded %d frontier nodes", AVT_NODE_NONE - 1);
     if (last_level >= 0)
@@ -1863,13 +1758,7 @@ int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const ui
     if (int rc = use_device(e)) return rc;
     CUDA_TRY(e, cudaEventRecord(e->gev0, e->stream));
     e->gev1_recorded = false;
-    int rc = 1;
-    if (rc > 0) {
-        if (e->grow_host_loop == 2) rc = grow_device_loop_sync(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
-        else if (e->grow_host_loop) rc = grow_host_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
-        else rc = grow_device_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records);
-    }
-    if (rc != AVT_OK) return rc;
+    if (int rc = grow_device_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records)) return rc;
     if (!e->gev1_recorded) {   // loops that read back between levels: the stream is idle here
         CUDA_TRY(e, cudaEventRecord(e->gev1, e->stream));
         CUDA_TRY(e, cudaEventSynchronize(e->gev1));

@@ -230,6 +230,9 @@ class Engine:
         self._check(self.lib.avt_forest_init_sampled(self.h, n_trees, mode, seed, param, total, row0))
         self.n_trees = n_trees
 
+    def forest_reset(self):
+        self._check(self.lib.avt_forest_reset(self.h))
+
     def weights(self, tree: int) -> np.ndarray:
         out = np.empty(self.n_rows, dtype=np.uint8)
         self._check(self.lib.avt_forest_weights(self.h, tree, _ptr(out)))

@@ -194,6 +194,9 @@ int avt_forest_init(avt_engine* e, int32_t n_trees, const uint8_t* const* weight
 #define AVT_SAMPLE_WITHOUT_REPLACE 2
 int avt_forest_init_sampled(avt_engine* e, int32_t n_trees, int32_t mode, int64_t seed, int32_t param,
                             int64_t total_rows, int64_t row0);
+/* Puts every row of every tree back into node 0 and keeps the trees' multiplicities: the level loop can be run again
+ * on the same sample (asynchronous; ordered before the next call on this engine). */
+int avt_forest_reset(avt_engine* e);
 /* Copies back tree t's multiplicities (uint8[n_rows]; all 1 for a tree started without any). */
 int avt_forest_weights(avt_engine* e, int32_t tree, uint8_t* out);
 

@@ -177,6 +177,17 @@ class OracleEngine:
         return self.H[:, :self.n_bins[0], :].sum(axis=1).astype(np.uint32)
 
 
+def oracle_bagging(seed: int, batch: int, total: int, row0: int, n: int) -> np.ndarray:
+    """oracle/hist_oracle.c:ora_bagging_weights -- multiplicities of rows [row0, row0 + n) of a `total`-row file."""
+    lib = oracle_lib()
+    lib.ora_bagging_weights.restype = C.c_int
+    lib.ora_bagging_weights.argtypes = [C.c_int64, C.c_int32, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
+    out = np.empty(n, dtype=np.uint8)
+    if lib.ora_bagging_weights(seed, batch, total, row0, n, out.ctypes.data_as(C.c_void_p)) != 0:
+        raise ValueError("bootstrap multiplicity above 255")
+    return out
+
+
 def bits(x: float) -> int:
     import struct
     return struct.unpack("<Q", struct.pack("<d", x))[0]

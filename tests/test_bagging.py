@@ -21,13 +21,7 @@ def python_bagging(n, batch, seed):
     return w
 
 
-def oracle_bagging(seed, batch, total, row0, n):
-    lib = helpers.oracle_lib()
-    lib.ora_bagging_weights.restype = C.c_int
-    lib.ora_bagging_weights.argtypes = [C.c_int64, C.c_int32, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]
-    out = np.empty(n, dtype=np.uint8)
-    assert lib.ora_bagging_weights(seed, batch, total, row0, n, out.ctypes.data_as(C.c_void_p)) == 0
-    return out
+oracle_bagging = helpers.oracle_bagging
 
 
 def test_c_restatement_equals_java_random_model():

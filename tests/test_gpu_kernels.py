@@ -206,25 +206,20 @@ def test_api_misuse_is_reported():
         g.set_splits(t)                                  # bound outside the attribute's bins
 
 
-@pytest.mark.parametrize("host_loop", [0, 1, 2, 3, 4, 5],
-                         ids=["persistent", "host-driven", "device-sync", "device-async", "device-async-general-scan", "device-async-ticket"])
+@pytest.mark.parametrize("mode", ["fast-scan-lookback", "general-scan-unpacked", "fast-scan-ticket"])
 @pytest.mark.parametrize("criterion", [CRIT_GINI, CRIT_ENTROPY])
-def test_in_library_level_loop_equals_oracle(host_loop, criterion, monkeypatch):
-    """avt_grow_levels (device-driven: fused repartition+histogram, scan, on-device planning; and its
-    host-driven twin) against the oracle's level loop: every record and every final node id."""
-    monkeypatch.setenv("AVT_GROW_HOST", str(host_loop if host_loop < 3 else 0))
-    monkeypatch.setenv("AVT_PERSISTENT", "0" if host_loop >= 3 else "1")
-    monkeypatch.setenv("AVT_SCAN_FAST", "0" if host_loop == 4 else "1")   # 3: item-parallel scan (the table fits it), 4: general kernel
-    monkeypatch.setenv("AVT_HIST_PACK", "0" if host_loop == 4 else "1")   # 4: one byte per attribute instead of the bit-packed copy
-    monkeypatch.setenv("AVT_LOOKBACK", "0" if host_loop == 5 else "1")    # 5: the last scan block plans the level instead of look-back
+def test_in_library_level_loop_equals_oracle(mode, criterion, monkeypatch):
+    """avt_grow_levels (device-driven: fused repartition+histogram, scan, on-device planning) against the oracle's
+    level loop: every record and every final node id, through each form of the scan / planning kernels."""
+    monkeypatch.setenv("AVT_SCAN_FAST", "0" if mode == "general-scan-unpacked" else "1")   # item-parallel scan vs the general kernel
+    monkeypatch.setenv("AVT_HIST_PACK", "0" if mode == "general-scan-unpacked" else "1")   # one byte per attribute instead of the bit-packed copy
+    monkeypatch.setenv("AVT_LOOKBACK", "0" if mode == "fast-scan-ticket" else "1")         # the last scan block plans the level instead of look-back
     n = 150001
     rng = np.random.default_rng(12)
     cols, cls, n_bins, _ = synth.call_hangup_encoded(n)
     table = binary_split_table(n_bins, [True, True, True, False])
     weights = [None, rng.poisson(1.0, n).clip(0, 255).astype(np.uint8), None]
     g, o = make_pair(cols, cls, n_bins, 2, table, 3, weights, None)
-    if host_loop == 0:
-        g.set_profiling(False)     # the persistent kernel has no per-launch timing; with it on the library uses the stream-ordered loop
     (rec, nrec), frontier = g.grow(7, criterion, [1, 1, 1], max_records=4096)
     ho, fo = grow_levels(o, table, 7, criterion, n_trees=3)
     want = [(lvl, t, nd, s, pops, av, ties) for lvl, level in enumerate(ho) for (t, nd, s, pops, av, ties) in level]
