@@ -13,6 +13,7 @@ AVT_MAX_CLASSES = 16
 AVT_MAX_SEG = 8
 CRIT_GINI, CRIT_ENTROPY, CRIT_HELLINGER, CRIT_CLASS_CONF = 0, 1, 2, 3
 SAMPLE_WITH_REPLACE, SAMPLE_WITHOUT_REPLACE = 1, 2
+ATTRS_ALL, ATTRS_NOT_USED_YET = 0, 1
 SPLIT_NUMERIC, SPLIT_LUT = 0, 1
 
 
@@ -83,6 +84,8 @@ SIGNATURES = {
     "avt_level_eval": (C.c_int, [_P, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(SplitEval)]),
     "avt_level_repartition": (C.c_int, [_P, C.POINTER(C.c_int32), _P, C.c_int32]),
     "avt_grow_levels": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.POINTER(C.c_int32), C.POINTER(GrowRecord), C.c_int64, C.POINTER(C.c_int64)]),
+    "avt_grow_levels_ex": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.c_int32, _P, C.POINTER(C.c_int32), C.POINTER(GrowRecord), C.c_int64,
+                                     C.POINTER(C.c_int64)]),
     "avt_cpg_sweep": (C.c_int, [_P, C.c_int32, C.c_int32, _P, C.POINTER(CpgStat)]),
     "avt_predict": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_int32), _P, _P, _P, C.c_int32, _P, _P]),
     "avt_forest_node_ids": (C.c_int, [_P, C.c_int32, _P]),

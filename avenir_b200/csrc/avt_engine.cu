@@ -112,6 +112,7 @@ struct avt_engine {
     DevBuf<double> d_av;
     DevBuf<avt_node_best> d_best;
     DevBuf<uint32_t> d_mask;
+    DevBuf<uint32_t> d_cand[2];    // level loop: candidate attribute sets of the current / next frontier (ping-pong by level)
     DevBuf<uint8_t> d_order;
     DevBuf<int32_t> d_pairs;
     DevBuf<avt_split_eval> d_eval;
@@ -393,7 +394,7 @@ void avt_destroy(avt_engine* e) {
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
     e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_pub.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
-    e->d_mask.release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
+    e->d_mask.release(); e->d_cand[0].release(); e->d_cand[1].release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release(); e->d_ctrl.release();
     if (e->h_ctrl) cudaFreeHost(e->h_ctrl);
     if (e->h_rec) cudaFreeHost(e->h_rec);
@@ -436,10 +437,10 @@ static int dataset_shape(avt_engine* e, int64_t n_rows, int32_t n_attrs, const i
     e->TB = e->bin_off[n_attrs];
     for (int a = 0; a < n_attrs; ++a) {
         const size_t w = e->wide[a] ? 2 : 1;
-        if (!e->cols[a]) CUDA_TRY(e, cudaMalloc(&e->cols[a], (size_t)e->Npad * w));
+        if (!e->cols[a]) CUDA_TRY(e, cudaMalloc(&e->cols[a], ((size_t)e->Npad + 32) * w));   // + one tile of slack (hist_forest_kernel reads whole 32-row tiles)
         CUDA_TRY(e, cudaMemsetAsync((char*)e->cols[a] + (size_t)n_rows * w, 0, (size_t)(e->Npad - n_rows) * w, e->stream));
     }
-    CUDA_TRY(e, e->d_cls.ensure((size_t)e->Npad));
+    CUDA_TRY(e, e->d_cls.ensure((size_t)e->Npad + 32));
     CUDA_TRY(e, cudaMemsetAsync(e->d_cls.p + n_rows, 0, (size_t)(e->Npad - n_rows), e->stream));
     if (int rc = upload(e, e->d_colptrs, e->cols.data(), (size_t)n_attrs)) return rc;
     if (int rc = upload(e, e->d_bin_off, e->bin_off.data(), (size_t)n_attrs + 1)) return rc;
@@ -708,7 +709,7 @@ int avt_forest_init(avt_engine* e, int32_t n_trees, const uint8_t* const* weight
             if (weights[t]) { has_w[t] = 1; e->any_w = true; }
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.h2d_ms, &ts)) return rc;
-    CUDA_TRY(e, e->d_nid.ensure((size_t)n_trees * e->Npad));
+    CUDA_TRY(e, e->d_nid.ensure((size_t)n_trees * e->Npad + 32));
     // 0xFFFF everywhere (covers the padding), then node 0 / caller ids for the real rows
     CUDA_TRY(e, cudaMemsetAsync(e->d_nid.p, 0xFF, (size_t)n_trees * e->Npad * 2, e->stream));
     for (int t = 0; t < n_trees; ++t) {
@@ -718,7 +719,7 @@ int avt_forest_init(avt_engine* e, int32_t n_trees, const uint8_t* const* weight
         else CUDA_TRY(e, cudaMemsetAsync(dst, 0, (size_t)e->N * 2, e->stream));
     }
     if (e->any_w) {
-        CUDA_TRY(e, e->d_w.ensure((size_t)n_trees * e->Npad));
+        CUDA_TRY(e, e->d_w.ensure((size_t)n_trees * e->Npad + 32));
         CUDA_TRY(e, cudaMemsetAsync(e->d_w.p, 0, (size_t)n_trees * e->Npad, e->stream));
         for (int t = 0; t < n_trees; ++t)
             if (has_w[t]) CUDA_TRY(e, cudaMemcpyAsync(e->d_w.p + (size_t)t * e->Npad, weights[t], (size_t)e->N, cudaMemcpyHostToDevice, e->stream));
@@ -744,8 +745,8 @@ int avt_forest_init_sampled(avt_engine* e, int32_t n_trees, int32_t mode, int64_
     std::vector<uint8_t> has_w(n_trees, 1);
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.sample_ms, &ts)) return rc;
-    CUDA_TRY(e, e->d_nid.ensure((size_t)n_trees * e->Npad));
-    CUDA_TRY(e, e->d_w.ensure((size_t)n_trees * e->Npad));
+    CUDA_TRY(e, e->d_nid.ensure((size_t)n_trees * e->Npad + 32));
+    CUDA_TRY(e, e->d_w.ensure((size_t)n_trees * e->Npad + 32));
     CUDA_TRY(e, e->d_err.ensure(1));
     CUDA_TRY(e, cudaMemsetAsync(e->d_err.p, 0, sizeof(int32_t), e->stream));
     e->nid_cur = e->d_nid.p;
@@ -933,8 +934,9 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
     size_t f_smem = 0;
     {
         if (e->skip_cur) f_slots = std::max(1, n_max - n_max / std::max(2, e->g_max_splits));   // one child of every expanded parent is derived, not counted
-        const size_t per_tree = (size_t)f_slots * e->C * max_bins * 128 + ((size_t)n_max + 1 + f_slots) * 2 + 1;
-        const size_t fixed = (size_t)kForestWarps * kForestRing * kForestUnitBytes + kForestWarps * 128 + 64;
+        const size_t n_prev = fr ? (size_t)std::max(fr->prev_n_max, 1) : 0;
+        const size_t per_tree = (size_t)f_slots * e->C * max_bins * 128 + n_prev * ((size_t)(fr ? fr->lut_w : 0) * 4 + 1) + ((size_t)n_max + 2 + f_slots) * 2 + 1;
+        const size_t fixed = (size_t)kForestWarps * kForestSub * 256 + (fr ? (size_t)kForestWarps * 1024 : 0) + 64;
         if (!any_wide && max_bins <= 256 && per_tree + fixed <= kMaxDynSmem) {
             f_G = (int)std::min<size_t>((size_t)e->T, (kMaxDynSmem - fixed) / per_tree);
             f_smem = fixed + per_tree * (size_t)f_G;
@@ -951,7 +953,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
     uint16_t* nid_in = e->nid_cur;
     uint16_t* nid_out = nullptr;
     if (fr) {
-        CUDA_TRY(e, e->d_nid2.ensure((size_t)e->T * e->Npad));
+        CUDA_TRY(e, e->d_nid2.ensure((size_t)e->T * e->Npad + 32));
         nid_out = (e->nid_cur == e->d_nid.p) ? e->d_nid2.p : e->d_nid.p;
     }
     if (fr && variant == 1) {
@@ -1139,6 +1141,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         fa.n_slots = f_slots;
         fa.Bmax = max_bins;
         fa.n_nodes_max = std::max(n_max, 1);
+        fa.n_prev_max = fr ? std::max(fr->prev_n_max, 1) : 1;
         if (!e->hist_err) CUDA_TRY(e, e->d_err.ensure(1));
         fa.err = e->hist_err ? e->hist_err : e->d_err.p;
         const int groups = (e->T + f_G - 1) / f_G, achunks = (e->A + 31) / 32;
@@ -1342,9 +1345,12 @@ int avt_level_repartition(avt_engine* e, const int32_t* node_attr, const uint16_
 // read-back so that buffers follow the real frontier.
 constexpr int kAsyncNodeLimit = 16384;
 
-static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
-                            avt_grow_record* records, int64_t max_records, int64_t* n_records) {
+static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t strategy,
+                            const uint32_t* root_cand, int32_t* nodes_per_tree, avt_grow_record* records, int64_t max_records,
+                            int64_t* n_records) {
     const int T = e->T;
+    const int mw = (e->A + 31) / 32;
+    const bool masks_on = strategy == AVT_ATTRS_NOT_USED_YET || root_cand != nullptr;   // per-node candidate attribute sets on the device
     int lut_w = 1, g_max = 2;
     for (int a = 0; a < e->A; ++a) lut_w = std::max(lut_w, e->n_bins[a]);
     for (auto& sp : e->splits) g_max = std::max(g_max, sp.n_seg);
@@ -1384,6 +1390,32 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         for (int t = 0; t <= T; ++t) init[16 + t] = nb_host[(size_t)t];
         CUDA_TRY(e, cudaMemcpyAsync(e->d_ctrl.p, init, (16 + (size_t)T + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
         if (init != e->h_ctrl) CUDA_TRY(e, cudaStreamSynchronize(e->stream));   // the pageable source goes out of scope
+    }
+    if (masks_on) {
+        // both buffers sized for the largest frontier bound any level of this call can reach (nothing reallocates mid-loop)
+        long long worst = 0, cur_bound = 0;
+        std::vector<long long> b(ub.begin(), ub.end());
+        for (int level = 0; level <= n_levels; ++level) {
+            cur_bound = 0;
+            for (int t = 0; t < T; ++t) {
+                cur_bound += b[(size_t)t];
+                b[(size_t)t] = std::min<long long>(b[(size_t)t] * g_max, (long long)AVT_NODE_NONE - 1);
+            }
+            worst = std::max(worst, cur_bound);
+        }
+        if ((size_t)worst * mw > ((size_t)1 << 28)) return fail(e, AVT_E_NOMEM, "avt_grow_levels_ex: candidate sets for up to %lld nodes do not fit", worst);
+        CUDA_TRY(e, e->d_cand[0].ensure((size_t)worst * mw));
+        CUDA_TRY(e, e->d_cand[1].ensure((size_t)worst * mw));
+        const size_t nf0 = (size_t)nb_host[(size_t)T];
+        std::vector<uint32_t> init(nf0 * mw);
+        for (size_t g = 0; g < nf0; ++g)
+            for (int w = 0; w < mw; ++w) {
+                const int bits = std::min(32, e->A - 32 * w);
+                const uint32_t all = bits >= 32 ? 0xFFFFFFFFu : ((1u << bits) - 1u);
+                init[g * mw + w] = root_cand ? (root_cand[g * mw + w] & all) : all;
+            }
+        CUDA_TRY(e, cudaMemcpyAsync(e->d_cand[0].p, init.data(), init.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, e->stream));
+        CUDA_TRY(e, cudaStreamSynchronize(e->stream));   // `init` goes out of scope
     }
     const bool peer_on = e->peer.active && e->peer.n > 1;
     // Sibling subtraction (count the smaller children, derive the largest as parent - siblings; exact in integers): pays off where
@@ -1625,7 +1657,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             const bool chain = e->pdl && !e->profiling && e->stats.last_hist_variant == 0 && (peer_level ? e->signal_in_hist : e->comm == nullptr);
             cfg.numAttrs = chain ? 1 : 0;
             if (fast_scan) {
-                FastTable ft{e->d_items.p, e->d_seg_first.p, e->d_nkids.p, e->n_items, nullptr, 0u};
+                FastTable ft{e->d_items.p, e->d_seg_first.p, e->d_nkids.p, e->n_items, masks_on ? e->d_cand[level & 1].p : nullptr, nullptr, 0u};
                 if (e->lookback && NF <= kLookbackNodes) {
                     if (e->d_pub.cap < (size_t)kLookbackNodes || e->scan_epoch >= (1u << 24) - 1) {
                         // (re)start the tags: no earlier launch may have left this value behind
@@ -1639,10 +1671,16 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
                 CUDA_TRY(e, cudaLaunchKernelEx(&cfg, scan_fast_kernel, (const uint32_t*)Hc, make_table(e), ft, (const uint8_t*)e->d_order.p, (int)criterion,
                                                (const int32_t*)(nb_level(level) + T), pa));
             } else
-            CUDA_TRY(e, cudaLaunchKernelEx(&cfg, scan_kernel, (const uint32_t*)Hc, make_table(e), (const uint32_t*)nullptr, (const uint8_t*)e->d_order.p,
+            CUDA_TRY(e, cudaLaunchKernelEx(&cfg, scan_kernel, (const uint32_t*)Hc, make_table(e), (const uint32_t*)(masks_on ? e->d_cand[level & 1].p : nullptr), (const uint8_t*)e->d_order.p,
                                            (int)criterion, e->d_av.p, e->d_best.p, e->d_best_eval.p, (const int32_t*)(nb_level(level) + T), pa));
         }
         CUDA_TRY(e, cudaGetLastError());
+        if (masks_on && level + 1 < n_levels) {
+            inherit_masks_kernel<<<(NF + 127) / 128, 128, 0, e->stream>>>(nb_level(level), nb_level(level + 1), T, e->d_node_attr.p, e->d_lut.p, lut_w,
+                                                                          e->d_cand[level & 1].p, e->d_cand[(level + 1) & 1].p, mw,
+                                                                          strategy == AVT_ATTRS_NOT_USED_YET ? 1 : 0);
+            CUDA_TRY(e, cudaGetLastError());
+        }
         if (int rc = timer_close(e, ts)) return rc;
         e->stats.scan_launches += 1;
         if (want_records) {
@@ -1751,14 +1789,21 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
 
 int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t* nodes_per_tree,
                     avt_grow_record* records, int64_t max_records, int64_t* n_records) {
+    return avt_grow_levels_ex(e, n_levels, criterion, class_order, AVT_ATTRS_ALL, nullptr, nodes_per_tree, records, max_records, n_records);
+}
+
+int avt_grow_levels_ex(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t strategy,
+                       const uint32_t* root_cand_mask, int32_t* nodes_per_tree, avt_grow_record* records, int64_t max_records,
+                       int64_t* n_records) {
     if (!e) return AVT_E_INVALID;
+    if (strategy != AVT_ATTRS_ALL && strategy != AVT_ATTRS_NOT_USED_YET) return fail(e, AVT_E_INVALID, "avt_grow_levels_ex: strategy %d", strategy);
     if (!nodes_per_tree) return fail(e, AVT_E_INVALID, "avt_grow_levels: nodes_per_tree is NULL");
     if (e->T == 0 || e->S == 0) return fail(e, AVT_E_STATE, "avt_grow_levels: needs avt_forest_init and avt_split_table_set first");
     if (criterion != AVT_CRIT_GINI && criterion != AVT_CRIT_ENTROPY) return fail(e, AVT_E_INVALID, "avt_grow_levels: criterion %d", criterion);
     if (int rc = use_device(e)) return rc;
     CUDA_TRY(e, cudaEventRecord(e->gev0, e->stream));
     e->gev1_recorded = false;
-    if (int rc = grow_device_loop(e, n_levels, criterion, class_order, nodes_per_tree, records, max_records, n_records)) return rc;
+    if (int rc = grow_device_loop(e, n_levels, criterion, class_order, strategy, root_cand_mask, nodes_per_tree, records, max_records, n_records)) return rc;
     if (!e->gev1_recorded) {   // loops that read back between levels: the stream is idle here
         CUDA_TRY(e, cudaEventRecord(e->gev1, e->stream));
         CUDA_TRY(e, cudaEventSynchronize(e->gev1));
@@ -1909,7 +1954,7 @@ int avt_reset_stats(avt_engine* e) {
 
 int avt_set_hist_variant(avt_engine* e, int32_t variant) {
     if (!e) return AVT_E_INVALID;
-    if (variant < -1 || variant > 1) return fail(e, AVT_E_INVALID, "avt_set_hist_variant: %d", variant);
+    if (variant < -1 || variant > 2) return fail(e, AVT_E_INVALID, "avt_set_hist_variant: %d", variant);
     e->force_variant = variant;
     return AVT_OK;
 }

@@ -11,8 +11,11 @@
 // wavefront -- and rows that are not counted cost no update at all (no partial warps: a row is either skipped by the
 // whole warp or updated by the whole warp).  A warp owns 32-row tiles: lane a keeps column a's 32 codes of the tile in
 // registers (pre-scaled to counter offsets) and loops over the trees resident in the block, so the codes are read once per
-// (tile, tree group) instead of once per tree; per (tile, tree) only 64 B of node ids and 32 B of multiplicities move,
-// prefetched through a per-warp cp.async ring.  The previous level's repartition is folded in as in hist_smem_kernel.
+// (tile, tree group) instead of once per tree; per (tile, tree) only 64 B of node ids and 32 B of multiplicities move.
+// Per tile the lanes first act as ROWS (phase A): each looks its row up in every resident tree -- node id, multiplicity,
+// the fused repartition through shared-memory copies of the previous level's tables, the counter slot of the new node --
+// and appends (counter base, multiplicity) of the live pairs to its row's list in shared memory; then as ATTRIBUTES
+// (phase B): row by row, entry by entry, one update each.  Bookkeeping is per lane and per pair; nothing is paid per dead pair.
 #pragma once
 // (included at the end of avt_kernels.cuh)
 
@@ -20,8 +23,7 @@ namespace avt {
 
 constexpr int kForestThreads = 512;
 constexpr int kForestWarps = kForestThreads / 32;
-constexpr int kForestRing = 8;          // (tile, tree) units in flight per warp
-constexpr int kForestUnitBytes = 96;    // 32 node ids (uint16) + 32 multiplicities (uint8)
+constexpr int kForestSub = 8;           // trees per (tile, sub-batch): one list entry per (row, tree) of the sub-batch
 
 struct ForestArgs {
     const int32_t* bin_off;   // [A+1]
@@ -30,15 +32,12 @@ struct ForestArgs {
     int n_slots;       // counter slots (counted nodes) per tree in shared memory
     int Bmax;          // bins per attribute in the shared layout (max over all attributes)
     int n_nodes_max;   // bound on a tree's frontier nodes (stride of the node -> slot tables)
+    int n_prev_max;    // fused repartition: bound on a tree's nodes in the previous frontier
     long long tiles_per_part;   // 32-row tiles per grid.y slice
     int32_t* err;      // set to 4 when a tree has more counted nodes than n_slots (host bound violated)
 };
 
-__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, bool valid) {
-    const int sz = valid ? 4 : 0;   // src-size 0: the four bytes are zero-filled
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
-}
-// explicit shared-window accesses for the hot loop (a generic pointer into dynamic shared memory compiles to LD.E/ST.E)
+// explicit shared-window accesses for the hot loops (a generic pointer into dynamic shared memory compiles to LD.E/ST.E)
 __device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
     uint16_t v;
     asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
@@ -49,23 +48,35 @@ __device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
     asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
 }
-__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint2 lds_v2(uint32_t addr) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
     return v;
 }
 __device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void sts_v2(uint32_t addr, uint32_t x, uint32_t y) {
+    asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(addr), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, const uint4& v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 
-// Shared memory of a block (dynamic):
+// Shared memory of a block (dynamic), in this order:
 //   counters   [G][n_slots][C][Bmax][32] uint32
-//   slot_of    [G][n_nodes_max + 1] uint16      node -> slot, 0xFFFF = not counted here
-//   node_of    [G][n_slots] uint16              slot -> node (flush)
-//   ring       [warps][kForestRing][96 B]       prefetched node ids + multiplicities
-//   bcast      [warps][32] uint32               per-row (counter base | multiplicity << 20), read back as broadcasts
+//   lists      [warps][kForestSub][32] uint2     phase A -> phase B: (counter base address, multiplicity) of the live (row, tree) pairs
+//   codes      [warps][32 attributes][32 rows]   (fused repartition only) the tile's codes, for "the code of the node's split attribute"
+//   lut32      [G][n_prev_max][lut_w] uint32     (fused repartition only) bin -> (slot << 16 | child node) of every previous node
+//   slot_of    [G][n_nodes_max + 1] uint16       node -> slot, 0xFFFF = not counted here
+//   node_of    [G][n_slots] uint16               slot -> node (flush)
+//   attr8      [G][n_prev_max] uint8             (fused repartition only) split attribute of every previous node, 0xFF = not expanded
 //   has_w      [G] uint8
+// Every global row buffer (columns, classes, node ids, multiplicities) is allocated with 32 rows of slack, so a tile that
+// reaches past the padded row count reads in bounds; such rows are never counted (row >= N) and never stored (row >= Npad).
 template <bool HAS_W, bool REPART>
 __global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const HistArgs a, const ForestArgs f) {
     extern __shared__ __align__(16) uint32_t fsh[];
@@ -77,15 +88,16 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const Hi
     const bool attr_ok = attr < f.A;
     const uint32_t slot_words = (uint32_t)a.C * f.Bmax * 32u;       // words of one (tree, slot)
     const uint32_t cnt_words = (uint32_t)f.G * f.n_slots * slot_words;
-    uint32_t* cnt = fsh;
-    uint16_t* slot_of = reinterpret_cast<uint16_t*>(cnt + cnt_words);
     const int so_stride = f.n_nodes_max + 1;
+    const int lut_stride = f.n_prev_max * a.lut_w;                   // words of one tree's lut32
+    uint32_t* cnt = fsh;
+    uint32_t* lists = cnt + cnt_words;
+    uint8_t* codes_s = reinterpret_cast<uint8_t*>(lists + kForestWarps * kForestSub * 64);
+    uint32_t* lut32 = reinterpret_cast<uint32_t*>(codes_s + (REPART ? kForestWarps * 1024 : 0));
+    uint16_t* slot_of = reinterpret_cast<uint16_t*>(lut32 + (REPART ? (size_t)f.G * lut_stride : 0));
     uint16_t* node_of = slot_of + (size_t)f.G * so_stride;
-    uint8_t* ring_all = reinterpret_cast<uint8_t*>(node_of + (size_t)f.G * f.n_slots);
-    ring_all = reinterpret_cast<uint8_t*>(((uintptr_t)ring_all + 15) & ~(uintptr_t)15);
-    uint8_t* ring = ring_all + (size_t)warp * kForestRing * kForestUnitBytes;
-    uint32_t* bcast = reinterpret_cast<uint32_t*>(ring_all + (size_t)kForestWarps * kForestRing * kForestUnitBytes) + warp * 32;
-    uint8_t* s_has_w = reinterpret_cast<uint8_t*>(bcast - warp * 32 + kForestWarps * 32);   // [G]
+    uint8_t* attr8 = reinterpret_cast<uint8_t*>(node_of + (size_t)f.G * f.n_slots);
+    uint8_t* s_has_w = attr8 + (REPART ? (size_t)f.G * f.n_prev_max : 0);
 
     pdl_launch_dependents();
     for (uint32_t i = threadIdx.x; i < cnt_words; i += blockDim.x) cnt[i] = 0;
@@ -102,7 +114,7 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const Hi
             const bool counted = i < n && !(a.skip && a.skip[nb + i]);
             const uint32_t m = __ballot_sync(0xffffffffu, counted);
             const int s = run + __popc(m & ((1u << lane) - 1u));
-            if (i < n && i < so_stride) slot_of[g * so_stride + i] = (counted && s < f.n_slots) ? (uint16_t)s : (uint16_t)0xFFFF;
+            if (i < n && i < so_stride && counted && s < f.n_slots) slot_of[g * so_stride + i] = (uint16_t)s;
             if (counted && s < f.n_slots) node_of[g * f.n_slots + s] = (uint16_t)i;
             run += __popc(m);
         }
@@ -110,128 +122,137 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const Hi
         for (int s = run + lane; s < f.n_slots; s += 32) node_of[g * f.n_slots + s] = 0xFFFF;
     }
     __syncthreads();
+    if (REPART) {
+        // previous frontier: bin -> (slot of the child | child), split attribute
+        for (int g = 0; g < Gb; ++g) {
+            const int pnb = a.prev_node_base[t0 + g], n_prev = min(a.prev_node_base[t0 + g + 1] - pnb, f.n_prev_max);
+            if (threadIdx.x == 0 && a.prev_node_base[t0 + g + 1] - pnb > f.n_prev_max) *f.err = 4;
+            for (int i = threadIdx.x; i < n_prev * a.lut_w; i += blockDim.x) {
+                const uint32_t child = a.child_lut[(long long)pnb * a.lut_w + i];
+                const uint32_t s = child == AVT_NODE_NONE ? 0xFFFFu : (uint32_t)slot_of[g * so_stride + min(child, (uint32_t)f.n_nodes_max)];
+                lut32[g * lut_stride + i] = (s << 16) | child;
+            }
+            for (int i = threadIdx.x; i < n_prev; i += blockDim.x) {
+                const int at = a.node_attr[pnb + i];
+                attr8[g * f.n_prev_max + i] = at < 0 ? (uint8_t)0xFF : (uint8_t)at;
+            }
+        }
+        __syncthreads();
+    }
 
-    const uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(cnt);
-    const uint32_t ring_base = (uint32_t)__cvta_generic_to_shared(ring);
-    const uint32_t bcast_base = (uint32_t)__cvta_generic_to_shared(bcast);
-    const uint32_t slot_of_base = (uint32_t)__cvta_generic_to_shared(slot_of);
-    const uint32_t has_w_base = (uint32_t)__cvta_generic_to_shared(s_has_w);
+    uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(cnt);
+    uint32_t list_base = (uint32_t)__cvta_generic_to_shared(lists) + (uint32_t)warp * kForestSub * 256u;   // [i][row] uint2
+    uint32_t codes_base = (uint32_t)__cvta_generic_to_shared(codes_s) + (uint32_t)warp * 1024u;
+    uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(lut32);
+    uint32_t slot_of_base = (uint32_t)__cvta_generic_to_shared(slot_of);
+    uint32_t attr8_base = (uint32_t)__cvta_generic_to_shared(attr8);
+    uint32_t has_w_base = (uint32_t)__cvta_generic_to_shared(s_has_w);
+    // keep the window addresses in registers: left to itself the compiler re-derives them (S2R + LDC + shifts) at every use
+    asm volatile("" : "+r"(cnt_base), "+r"(list_base), "+r"(codes_base), "+r"(lut_base), "+r"(slot_of_base), "+r"(attr8_base), "+r"(has_w_base));
     const uint8_t* col = attr_ok ? (const uint8_t*)a.cols[attr] : nullptr;
     const long long n_tiles = (a.N + 31) >> 5;
     const long long tile_lo = (long long)blockIdx.y * f.tiles_per_part;
     const long long tile_hi = min(n_tiles, tile_lo + f.tiles_per_part);
-    // this warp's tiles: tile_lo + warp, + kForestWarps, ...
-    const long long my_tiles = tile_hi > tile_lo + warp ? (tile_hi - tile_lo - warp + kForestWarps - 1) / kForestWarps : 0;
     const uint32_t class_bytes = (uint32_t)f.Bmax * 128u;          // one (slot, class): Bmax bins x 32 attributes x 4 B
     const uint32_t slot_bytes = slot_words * 4u;
     const uint32_t tree_bytes = (uint32_t)f.n_slots * slot_bytes;
+    const uint32_t l4 = 4u * lane;
+    const uint32_t l4l4 = l4 | (l4 << 16);
 
-    static_assert((kForestRing & (kForestRing - 1)) == 0, "ring size must be a power of two");
-    auto tile_of = [&](int k) { return tile_lo + warp + (long long)k * kForestWarps; };
-    // prefetch of one unit's node ids (lanes 0-15: two rows each) and multiplicities (lanes 16-23: four rows each);
-    // units are (tile k, tree g) in the order the loop below consumes them
-    int ik = 0, ig = 0;
-    uint32_t iu = 0;
-    auto issue_next = [&]() {
-        if (ik < (int)my_tiles) {
-            const long long row0 = tile_of(ik) << 5;
-            const uint32_t dst = ring_base + (iu & (kForestRing - 1)) * kForestUnitBytes;
-            if (lane < 16) {
-                const long long r = row0 + 2 * lane;
-                cp_async4(dst + 4u * lane, a.nid + (long long)(t0 + ig) * a.Npad + r, r < a.Npad);
-            } else if (HAS_W && lane < 24) {
-                const long long r = row0 + 4 * (lane - 16);
-                const bool hw = lds_u8(has_w_base + ig) != 0;
-                cp_async4(dst + 64u + 4u * (lane - 16), a.wts + (long long)(t0 + ig) * a.Npad + r, hw && r < a.Npad);
-            }
-        }
-        cp_async_commit();
-        ++iu;
-        if (++ig == Gb) { ig = 0; ++ik; }
-    };
-    auto load_codes = [&](long long tile, uint4& c0, uint4& c1, uint32_t& cl) {
-        const long long row0 = tile << 5;
-        c0 = make_uint4(0, 0, 0, 0);
-        c1 = c0;
-        if (attr_ok) {
-            c0 = ld_stream(col + row0);
-            if (row0 + 16 < a.Npad) c1 = ld_stream(col + row0 + 16);
-        }
-        cl = row0 + lane < a.N ? a.cls[row0 + lane] : 0u;
-    };
-
-    for (int d = 0; d < kForestRing - 1; ++d) issue_next();
     uint4 nc0 = make_uint4(0, 0, 0, 0), nc1 = nc0;
     uint32_t ncl = 0;
-    if (my_tiles) load_codes(tile_of(0), nc0, nc1, ncl);
-    uint32_t cu = 0;
-    for (int k = 0; k < (int)my_tiles; ++k) {
-        const long long row = (tile_of(k) << 5) + lane;
-        // new tile: codes -> counter offsets (row j of the tile: code * 128 + lane * 4, bin-major / attribute-minor, packed in
-        // pairs), then start loading the next tile's codes
+    auto load_codes = [&](long long tile) {
+        const long long row0 = tile << 5;
+        if (attr_ok) {
+            nc0 = ld_stream(col + row0);
+            nc1 = ld_stream(col + row0 + 16);
+        }
+        ncl = a.cls[row0 + lane];
+    };
+    long long tile = tile_lo + warp;
+    if (tile < tile_hi) load_codes(tile);
+    for (; tile < tile_hi; tile += kForestWarps) {
+        const long long row = (tile << 5) + lane;
+        const bool row_ok = row < a.N;
+        // ---- new tile: codes -> counter offsets (row j: code * 128 + lane * 4, bin-major / attribute-minor; two rows per register)
         uint32_t offs[16];
         {
-            const uint32_t l4 = 4u * lane;
             const uint32_t w8[8] = {nc0.x, nc0.y, nc0.z, nc0.w, nc1.x, nc1.y, nc1.z, nc1.w};
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
-                const uint32_t b0 = w8[q] & 0xFFu, b1 = (w8[q] >> 8) & 0xFFu, b2 = (w8[q] >> 16) & 0xFFu, b3 = w8[q] >> 24;
-                offs[2 * q] = (b0 * 128u + l4) | ((b1 * 128u + l4) << 16);
-                offs[2 * q + 1] = (b2 * 128u + l4) | ((b3 * 128u + l4) << 16);
+                offs[2 * q] = __byte_perm(w8[q], 0u, 0x4140u) * 128u + l4l4;       // bytes 0,1 -> halves
+                offs[2 * q + 1] = __byte_perm(w8[q], 0u, 0x4342u) * 128u + l4l4;   // bytes 2,3 -> halves
+            }
+            if (REPART) {
+                __syncwarp();   // the previous tile's readers are done
+                sts_v4(codes_base + 32u * lane, nc0);
+                sts_v4(codes_base + 32u * lane + 16u, nc1);
+                __syncwarp();
             }
         }
         const uint32_t cl = ncl;
-        if (k + 1 < (int)my_tiles) load_codes(tile_of(k + 1), nc0, nc1, ncl);
-        for (int g = 0; g < Gb; ++g, ++cu) {
-            issue_next();
-            cp_async_wait<kForestRing - 1>();   // this unit has landed (a thread's groups complete in order)
-            __syncwarp();
-            const uint32_t slot = ring_base + (cu & (kForestRing - 1)) * kForestUnitBytes;
-            uint32_t node = lds_u16(slot + 2u * lane);
-            uint32_t w = 1u;
-            if (HAS_W && lds_u8(has_w_base + g)) w = lds_u8(slot + 64u + lane);
-            if (row >= a.N) node = AVT_NODE_NONE;
-            const int t = t0 + g;
-            if (REPART) {
-                uint32_t nn = AVT_NODE_NONE;
-                if (node != AVT_NODE_NONE) {
-                    const int gi = a.prev_node_base[t] + (int)node;
-                    const int at = __ldg(a.node_attr + gi);
-                    if (at >= 0) {
-                        const uint32_t code = __ldg((const uint8_t*)a.cols[at] + row);
-                        nn = __ldg(a.child_lut + (long long)gi * a.lut_w + code);
-                    }
+        if (tile + kForestWarps < tile_hi) load_codes(tile + kForestWarps);
+        const uint16_t* nid_row = a.nid + (long long)t0 * a.Npad + row;
+        uint16_t* nid_out_row = REPART ? a.nid_out + (long long)t0 * a.Npad + row : nullptr;
+        const uint8_t* w_row = HAS_W ? a.wts + (long long)t0 * a.Npad + row : nullptr;
+        for (int g0 = 0; g0 < Gb; g0 += kForestSub) {
+            const int gn = min(kForestSub, Gb - g0);
+            // ---- phase A (lane = row): node, slot and liveness of this row in each tree of the sub-batch
+            uint32_t nid_r[kForestSub], w_r[kForestSub];
+#pragma unroll
+            for (int k = 0; k < kForestSub; ++k) {
+                nid_r[k] = AVT_NODE_NONE;
+                w_r[k] = 1u;
+                if (k < gn) {
+                    nid_r[k] = nid_row[(long long)(g0 + k) * a.Npad];
+                    if (HAS_W && lds_u8(has_w_base + g0 + k)) w_r[k] = w_row[(long long)(g0 + k) * a.Npad];
                 }
-                node = nn;
-                if (chunk == 0 && row < a.Npad) a.nid_out[(long long)t * a.Npad + row] = (uint16_t)node;
             }
-            uint32_t s = 0xFFFFu;
-            if (node != AVT_NODE_NONE && w != 0u) s = lds_u16(slot_of_base + 2u * (g * so_stride + min(node, (uint32_t)f.n_nodes_max)));
-            const bool live = s != 0xFFFFu;
-            const uint32_t m = __ballot_sync(0xffffffffu, live);
-            if (m) {
-                sts_u32(bcast_base + 4u * lane, (cnt_base + (uint32_t)g * tree_bytes + s * slot_bytes + cl * class_bytes) | (w << 20));
-                __syncwarp();
+            uint32_t cnt_live = 0;
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    if ((m >> (4 * q)) & 0xFu) {
-                        const uint4 v = lds_v4(bcast_base + 16u * q);   // same address in every lane: one broadcast
-#pragma unroll
-                        for (int r = 0; r < 4; ++r) {
-                            const int j = 4 * q + r;
-                            if ((m >> j) & 1u) {
-                                const uint32_t x = u4_word(v, r);
-                                const uint32_t off = (j & 1) ? (offs[j >> 1] >> 16) : (offs[j >> 1] & 0xFFFFu);
-                                red_shared_add((x & 0xFFFFFu) + off, HAS_W ? (x >> 20) : 1u);
+            for (int k = 0; k < kForestSub; ++k) {
+                if (k < gn) {
+                    const int g = g0 + k;
+                    uint32_t node = row_ok ? nid_r[k] : AVT_NODE_NONE;
+                    uint32_t s = 0xFFFFu;
+                    if (REPART) {
+                        uint32_t e = 0xFFFFFFFFu;
+                        if (node != AVT_NODE_NONE) {
+                            node = min(node, (uint32_t)f.n_prev_max - 1u);
+                            const uint32_t at = lds_u8(attr8_base + g * f.n_prev_max + node);
+                            if (at != 0xFFu) {
+                                const uint32_t code = lds_u8(codes_base + 32u * at + lane);
+                                e = lds_u32(lut_base + 4u * (g * lut_stride + node * a.lut_w + code));
                             }
                         }
+                        node = e & 0xFFFFu;
+                        s = e >> 16;
+                        if (chunk == 0 && row < a.Npad) nid_out_row[(long long)g * a.Npad] = (uint16_t)node;
+                    } else if (node != AVT_NODE_NONE) {
+                        s = lds_u16(slot_of_base + 2u * (g * so_stride + min(node, (uint32_t)f.n_nodes_max)));
+                    }
+                    if (s != 0xFFFFu && w_r[k] != 0u) {
+                        sts_v2(list_base + cnt_live * 256u + 8u * lane, cnt_base + (uint32_t)g * tree_bytes + s * slot_bytes + cl * class_bytes, w_r[k]);
+                        ++cnt_live;
                     }
                 }
             }
-            __syncwarp();   // bcast and the ring slot are rewritten by the next iterations
+            __syncwarp();
+            // ---- phase B (lane = attribute): one conflict-free update per live (row, tree) pair
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const uint32_t n = __shfl_sync(0xffffffffu, cnt_live, j);
+                const uint32_t off = (j & 1) ? (offs[j >> 1] >> 16) : (offs[j >> 1] & 0xFFFFu);
+#pragma unroll
+                for (uint32_t i = 0; i < (uint32_t)kForestSub; ++i) {   // a compare-and-branch chain: no loop counter, constant addresses
+                    if (i >= n) break;
+                    const uint2 x = lds_v2(list_base + i * 256u + 8u * j);   // same address in every lane: one broadcast
+                    red_shared_add(x.x + off, HAS_W ? x.y : 1u);
+                }
+            }
+            __syncwarp();   // the lists are rewritten by the next sub-batch
         }
     }
-    cp_async_wait<0>();
     __syncthreads();
     // flush: counters [g][slot][class][bin][lane] -> H[node][bin_off[attr] + bin][class]
     for (int g = 0; g < Gb; ++g) {

@@ -76,6 +76,37 @@ __device__ __forceinline__ uint32_t ldcg_u32(const uint32_t* p) { return __ldcg(
 __device__ __forceinline__ long long ldcg_i64(const int64_t* p) { return __ldcg((const long long*)p); }
 __device__ __forceinline__ double ldcg_f64(const double* p) { return __ldcg(p); }
 
+// Candidate attributes of the next frontier (getSplitAttributes, tree/DecisionTreeBuilder.java:365-381 with
+// tree/SplitManager.java:149-166 `all` and :195-232 `notUsedYet`): a child inherits its parent's candidate set, minus --
+// with remove_used -- the attribute its parent was split on (the attributes "on my path" are exactly the ones removed so
+// far).  One thread per node of the current frontier; runs behind the scan kernel that planned the level.
+__global__ void inherit_masks_kernel(const int32_t* nb_cur, const int32_t* nb_next, int n_trees, const int32_t* node_attr,
+                                     const uint16_t* child_lut, int lut_w, const uint32_t* cand_cur, uint32_t* cand_next, int mw,
+                                     int remove_used) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= nb_cur[n_trees]) return;
+    const int at = node_attr[g];
+    if (at < 0) return;
+    int lo = 0, hi = n_trees;   // last tree whose first node is <= g (empty trees share their successor's base and are skipped)
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (nb_cur[mid] <= g) lo = mid;
+        else hi = mid;
+    }
+    const int base = nb_next[lo];
+    uint32_t last = AVT_NODE_NONE;
+    for (int b = 0; b < lut_w; ++b) {
+        const uint32_t c = child_lut[(long long)g * lut_w + b];
+        if (c == AVT_NODE_NONE || c == last) continue;
+        last = c;
+        for (int w = 0; w < mw; ++w) {
+            uint32_t m = cand_cur[(long long)g * mw + w];
+            if (remove_used && w == (at >> 5)) m &= ~(1u << (at & 31));
+            cand_next[(long long)(base + (int)c) * mw + w] = m;
+        }
+    }
+}
+
 // Plans one tree with the whole block (blockDim.x = kScanThreads).
 __device__ void plan_tree(const PlanArgs& p, const SplitTable& st, int t, int next_base, int* warp_tot, int* running) {
     const int nb = p.node_base[t], n = p.node_base[t + 1] - nb;

@@ -28,6 +28,7 @@ struct FastTable {
     int n_items;
     // look-back planning (frontier bound <= kLookbackNodes): every node's block publishes its child count tagged with this
     // launch's epoch and reads the counts of the nodes before it, so no block has to wait for the whole grid
+    const uint32_t* cand;      // [NF] candidate attributes of every node (one word: the table has <= 8 attributes), nullptr = all
     uint32_t* pub;             // [kLookbackNodes], nullptr = the last block plans the level (ticket)
     uint32_t epoch;            // 1 .. 2^24-1, different from the tags any earlier launch left in `pub`
 };
@@ -301,7 +302,8 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
                 }
             }
             const double av = __ddiv_rn(weighted, (double)total);
-            if (av == av) best = ScanBest{av, tid, 1};   // NaN never wins
+            const bool cand = ft.cand == nullptr || ((ft.cand[node] >> s_splits[tid].attr) & 1u);
+            if (av == av && cand) best = ScanBest{av, tid, 1};   // NaN never wins
         }
 #pragma unroll
         for (int d = 16; d; d >>= 1) {

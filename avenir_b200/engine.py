@@ -288,13 +288,15 @@ class Engine:
         self._check(self.lib.avt_level_repartition(self.h, na, _ptr(lut), lut.shape[1]))
 
     def grow(self, n_levels: int, criterion: int, nodes_per_tree: Sequence[int], class_order: Optional[Sequence[int]] = None,
-             max_records: int = 0):
-        """avt_grow_levels: the level loop inside the library.  Returns (records, final nodes_per_tree)."""
+             max_records: int = 0, strategy: int = _lib.ATTRS_ALL, root_cand_mask: Optional[np.ndarray] = None):
+        """avt_grow_levels_ex: the level loop inside the library, candidate attributes per `strategy`
+        (_lib.ATTRS_ALL | _lib.ATTRS_NOT_USED_YET).  Returns (records, final nodes_per_tree)."""
         npt = (C.c_int32 * len(nodes_per_tree))(*[int(x) for x in nodes_per_tree])
         rec = (_lib.GrowRecord * max_records)() if max_records else None
         n = C.c_int64(0)
         o = None if class_order is None else np.ascontiguousarray(class_order, dtype=np.uint8)
-        self._check(self.lib.avt_grow_levels(self.h, n_levels, criterion, _ptr(o), npt, rec, max_records, C.byref(n)))
+        m = None if root_cand_mask is None else np.ascontiguousarray(root_cand_mask, dtype=np.uint32)
+        self._check(self.lib.avt_grow_levels_ex(self.h, n_levels, criterion, _ptr(o), strategy, _ptr(m), npt, rec, max_records, C.byref(n)))
         return (rec, int(n.value)), list(npt)
 
     def cpg_sweep(self, node: int, criterion: int, class_order: Optional[Sequence[int]] = None):
@@ -364,7 +366,8 @@ def comm_unique_id() -> bytes:
 
 
 def grow_levels(eng, table: SplitTable, n_levels: int, criterion: int, n_trees: int = 1,
-                class_order: Optional[Sequence[int]] = None, record: bool = True):
+                class_order: Optional[Sequence[int]] = None, record: bool = True, strategy: int = _lib.ATTRS_ALL,
+                root_cand_mask: Optional[np.ndarray] = None):
     """The per-level driver loop (what resource/detr.sh:34-54 does by hand, one Hadoop job per level):
     histogram -> scan -> children statistics -> repartition, `n_levels` times, for all trees at once.
     Ties resolve to the lowest table index (the tool layer, not this loop, replays the reference's
@@ -373,12 +376,19 @@ def grow_levels(eng, table: SplitTable, n_levels: int, criterion: int, n_trees: 
     lut_w = max(eng.n_bins)
     frontier = [1] * n_trees
     history = []
+    n_attrs = len(eng.n_bins)
+    mw = (n_attrs + 31) // 32
+    masks = None   # candidate attribute sets of the frontier nodes (getSplitAttributes, tree/DecisionTreeBuilder.java:365-381)
+    if strategy != _lib.ATTRS_ALL or root_cand_mask is not None:
+        full = np.array([(1 << min(32, n_attrs - 32 * w)) - 1 for w in range(mw)], dtype=np.uint32)
+        masks = np.tile(full, (n_trees, 1)) if root_cand_mask is None else (np.asarray(root_cand_mask, dtype=np.uint32).reshape(n_trees, mw) & full)
     for _ in range(n_levels):
         nf = sum(frontier)
         if nf == 0:
             break
         eng.histogram(frontier)
-        best = eng.scan(criterion, None, class_order)
+        best = eng.scan(criterion, masks, class_order)
+        next_masks = []
         nodes = [g for g in range(nf) if best[g].population > 0 and best[g].best_split >= 0]
         splits = [best[g].best_split for g in nodes]
         evals = eng.eval(criterion, nodes, splits, class_order)
@@ -406,6 +416,11 @@ def grow_levels(eng, table: SplitTable, n_levels: int, criterion: int, n_trees: 
                         child_of_seg[sg] = nxt
                         nxt += 1
                         pops.append(n)
+                        if masks is not None:
+                            m = masks[g].copy()
+                            if strategy == _lib.ATTRS_NOT_USED_YET:
+                                m[a >> 5] &= np.uint32(~(1 << (a & 31)) & 0xFFFFFFFF)
+                            next_masks.append(m)
                 for b in range(eng.n_bins[a]):
                     sg = table.segment_of_bin(s, b)
                     if sg in child_of_seg:
@@ -414,6 +429,8 @@ def grow_levels(eng, table: SplitTable, n_levels: int, criterion: int, n_trees: 
                     level.append((t, g - base[t], s, pops, best[g].min_av, best[g].n_ties))
             new_frontier[t] = nxt
         eng.repartition(node_attr, child_lut)
+        if masks is not None:
+            masks = np.array(next_masks, dtype=np.uint32).reshape(len(next_masks), mw)
         frontier = new_frontier
         history.append(level)
     return history, frontier

@@ -96,7 +96,7 @@ typedef struct avt_stats {
     int64_t hist_launches, scan_launches, eval_launches, repart_launches, comm_calls;
     int64_t hist_alg_bytes; /* algorithmic bytes of all histogram passes so far */
     int64_t repart_alg_bytes;
-    int32_t last_hist_variant; /* 0 shared-memory privatised, 1 global atomics (match_any) */
+    int32_t last_hist_variant; /* 0 shared-memory privatised (lane = row), 1 global atomics (match_any), 2 forest kernel (lane = attribute) */
     int32_t last_hist_replicas;
     int32_t last_hist_grid, last_hist_block, last_hist_smem;
     int32_t reserved0;
@@ -266,6 +266,21 @@ int avt_grow_levels(avt_engine* e, int32_t n_levels, int32_t criterion, const ui
                     int32_t* nodes_per_tree, avt_grow_record* records, int64_t max_records,
                     int64_t* n_records);
 
+/* avt_grow_levels with the reference's candidate-attribute strategy applied on the device (getSplitAttributes,
+ * tree/DecisionTreeBuilder.java:365-381).  Every frontier node carries a candidate set of ceil(n_attrs/32) words:
+ *   AVT_ATTRS_ALL           a child inherits its parent's set unchanged (SplitManager.getAllAttributes, tree/SplitManager.java:149-166;
+ *                           with root_cand_mask = the dtb.custom.base.attributes subset);
+ *   AVT_ATTRS_NOT_USED_YET  the reference's default, dtb.split.attribute.selection.strategy=notUsedYet: a child's set is its
+ *                           parent's minus the attribute the parent was split on, i.e. the attributes not on its path
+ *                           (SplitManager.getRemainingAttributes, tree/SplitManager.java:195-232).
+ * root_cand_mask (nullable = every attribute) gives the sets of the nodes the call starts from, [sum nodes_per_tree][words].
+ * A node whose set holds no attribute with a split is not expanded (the reference's mapper emits nothing for it). */
+#define AVT_ATTRS_ALL 0
+#define AVT_ATTRS_NOT_USED_YET 1
+int avt_grow_levels_ex(avt_engine* e, int32_t n_levels, int32_t criterion, const uint8_t* class_order, int32_t strategy,
+                       const uint32_t* root_cand_mask, int32_t* nodes_per_tree, avt_grow_record* records,
+                       int64_t max_records, int64_t* n_records);
+
 /* ClassPartitionGenerator sweep over every split of the installed table for the rows of frontier
  * node `node` (use 0 after avt_forest_init(1, NULL, NULL) for "all rows") of the last histogram.
  * Replaces PartitionGeneratorMapper.map + Combiner + Reducer (explore/ClassPartitionGenerator.java:
@@ -302,7 +317,8 @@ int avt_reset_stats(avt_engine* e);
 /* Turns the per-launch CUDA-event timing behind avt_stats on (default) or off (no event records between
  * the launches of a level loop). */
 int avt_set_profiling(avt_engine* e, int32_t on);
-/* Forces a histogram variant (-1 auto, 0 shared-memory, 1 global atomics) -- for tests/profiling. */
+/* Forces a histogram variant (-1 auto, 0 shared-memory by rows, 1 global atomics, 2 forest kernel: shared-memory by
+ * attributes) -- for tests/profiling. */
 int avt_set_hist_variant(avt_engine* e, int32_t variant);
 
 /* Allocation-free histogram.  NO COUNTERPART IN THE REFERENCE (and none in its Java object seams): it exists

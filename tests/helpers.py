@@ -188,6 +188,16 @@ def oracle_bagging(seed: int, batch: int, total: int, row0: int, n: int) -> np.n
     return out
 
 
+def unordered_model(level_json: dict):
+    """A DecisionPathList as an order-free value: the reference-held sample (resource/dec_tree_rules.json) lists its
+    paths in an order the current code's HashMap logic does not reproduce, so list order is NOT pinned by anything the
+    reference ships; paths of binary splits are disjoint, so prediction does not depend on it.  Model equality that
+    a reader of the reference can rely on is therefore this comparison; the exact-order one is between our two restatements."""
+    paths = sorted(json.dumps(p, sort_keys=True) for p in level_json.get("decisionPaths", []))
+    rest = {k: v for k, v in level_json.items() if k != "decisionPaths"}
+    return json.dumps(rest, sort_keys=True), paths
+
+
 def bits(x: float) -> int:
     import struct
     return struct.unpack("<Q", struct.pack("<d", x))[0]

@@ -1,7 +1,8 @@
 """Product host layer (C++: encoding, split ids, HashMap-order replay, stopping flags, JSON, CPG lines)
-against the literal restatement of the reference (oracle/literal.py).  The kernel layer is replaced at
-link time by the CPU mock (tests/mock), so these run without a GPU; tests/test_gpu_tool.py repeats the
-comparison through the real libavenir_tree.so."""
+against the literal restatement of the reference (oracle/literal.py).  Every case runs twice: with the
+kernel layer replaced at link time by the CPU mock (tests/mock; no GPU needed) and -- marked gpu -- through
+the real libavenir_tree.so, so that randomAmongTop, minInfoGain / minPopulation, withReplace / withoutReplace
+sampling, random schemas with double attributes and the reference-failure table all go through the CUDA path."""
 import json
 import os
 import random
@@ -14,6 +15,15 @@ from tests import helpers
 
 DTB = "org.avenir.tree.DecisionTreeBuilder"
 CPG = "org.avenir.explore.ClassPartitionGenerator"
+
+
+@pytest.fixture(params=["mock", pytest.param("gpu", marks=pytest.mark.gpu)])
+def hostmock(request):
+    """The library the tools are run through: host layer + CPU mock of the kernels, or the product itself."""
+    if request.param == "mock":
+        return helpers.hostmock_lib()
+    from avenir_b200 import _lib
+    return _lib.load()
 
 
 def _props(path, d):
@@ -43,6 +53,9 @@ def run_dtb_both(lib, tmp, lines, schema_dict, conf, expansions, tool_run=helper
         return None, None
     assert rc == 0, err
     got = [json.load(open(os.path.join(tmp, f"dec.json.level{k}"))) for k in range(len(want))]
+    # order-free model equality first (the contract a user of the reference can rely on), the callers then assert the
+    # exact, order-sensitive one (agreement of the two restatements of the HashMap orders)
+    assert [helpers.unordered_model(g) for g in got] == [helpers.unordered_model(w) for w in want]
     return got, want
 
 
@@ -151,6 +164,20 @@ def test_bagging_weights_follow_seeded_sampler(hostmock, tmp_path):
                          "dtb.split.attribute.selection.strategy": "all", "avt.random.seed": "0"})
     got, want = run_dtb_both(hostmock, str(tmp_path), lines, schema, conf, 3)
     assert got[0]["decisionPaths"][0]["population"] == 900
+    assert got == want
+
+
+@pytest.mark.parametrize("rate,seed", [(60, 0), (25, 7)])
+def test_sampling_without_replace_follows_seeded_sampler(hostmock, tmp_path, rate, seed):
+    """withoutReplace = one Bernoulli(rate %) draw per row, `(int)(Math.random() * 100) < rate`
+    (tree/DecisionTreeBuilder.java:230-235), from the seeded java.util.Random stream."""
+    schema = json.load(open(os.path.join(helpers.SCHEMA_DIR, "schemas.json")))["call_hangup.json"]
+    lines = synth.call_hangup_csv(1200)
+    conf = dict(BASE, **{"dtb.sub.sampling.strategy": "withoutReplace", "dtb.sub.sampling.rate": str(rate),
+                         "dtb.split.attribute.selection.strategy": "notUsedYet", "avt.random.seed": str(seed)})
+    got, want = run_dtb_both(hostmock, str(tmp_path), lines, schema, conf, 3)
+    pop = got[0]["decisionPaths"][0]["population"]
+    assert 0 < pop < 1200 and abs(pop - 12 * rate) < 150
     assert got == want
 
 

@@ -1,0 +1,11 @@
+set -x
+mkdir -p gpurun_out/r2
+timeout 1200 python -m pytest tests/test_gpu_forest.py tests/test_gpu_strategy.py tests/test_gpu_configs.py tests/test_gpu_subtract.py tests/test_gpu_kernels.py -m gpu -x -q 2>&1 | tail -12 > gpurun_out/r2/gputest_v2.txt
+cat gpurun_out/r2/gputest_v2.txt
+C3_ROWS=10000000 C3_TREES=16 timeout 600 python tools/config_probe.py c3 > gpurun_out/r2/c3_probe_v2.txt 2>&1
+cat gpurun_out/r2/c3_probe_v2.txt
+timeout 900 python bench.py --rows 10000000 --trees 16 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r2/bench_c3_small_v2.json 2> gpurun_out/r2/bench_c3_small_v2.err
+tail -c 1500 gpurun_out/r2/bench_c3_small_v2.json; tail -5 gpurun_out/r2/bench_c3_small_v2.err
+timeout 1500 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r2/bench_c3_full_v2.json 2> gpurun_out/r2/bench_c3_full_v2.err
+tail -c 1500 gpurun_out/r2/bench_c3_full_v2.json; tail -5 gpurun_out/r2/bench_c3_full_v2.err
+C3_ROWS=10000000 C3_TREES=16 timeout 900 ncu --set full --import-source on --clock-control none -k regex:hist_forest -c 6 -o gpurun_out/r2/c3_forest_v2 python tools/config_probe.py c3 > gpurun_out/r2/c3_ncu_v2.log 2>&1
