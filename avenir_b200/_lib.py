@@ -14,7 +14,7 @@ AVT_MAX_SEG = 8
 CRIT_GINI, CRIT_ENTROPY, CRIT_HELLINGER, CRIT_CLASS_CONF = 0, 1, 2, 3
 SAMPLE_WITH_REPLACE, SAMPLE_WITHOUT_REPLACE = 1, 2
 ATTRS_ALL, ATTRS_NOT_USED_YET = 0, 1
-SPLIT_NUMERIC, SPLIT_LUT = 0, 1
+SPLIT_NUMERIC, SPLIT_LUT, SPLIT_RANGES = 0, 1, 2
 
 
 class Split(C.Structure):

@@ -100,6 +100,11 @@ struct avt_engine {
     // all attributes' codes in one byte per row (narrow schemas; see HistArgs::packed)
     DevBuf<uint8_t> d_packed;
     bool packed_ok = false;
+    // rotated row-major copy of the codes for hist_rot_kernel (forest shapes: >= 16 uint8 attributes), [chunks][rowrot_rows][32]
+    DevBuf<uint8_t> d_rowrot;
+    long long rowrot_rows = 0;
+    bool rowrot_ok = false;
+    bool forest_rot = true;   // AVT_FOREST_ROT=0: the list-based hist_forest_kernel instead of hist_rot_kernel (A/B measurements)
     uint32_t pk_shift[4] = {0, 0, 0, 0}, pk_mask4[4] = {0, 0, 0, 0};
     // item-parallel scan (avt_scan_fast.cuh): (split, segment) items, first item of every split, per-node child counts
     DevBuf<uint32_t> d_items;
@@ -347,7 +352,11 @@ int avt_create(int device, avt_engine** out) {
     }
     {
         const void* kernels[] = {(const void*)hist_forest_kernel<false, false>, (const void*)hist_forest_kernel<false, true>,
-                                 (const void*)hist_forest_kernel<true, false>, (const void*)hist_forest_kernel<true, true>};
+                                 (const void*)hist_forest_kernel<true, false>, (const void*)hist_forest_kernel<true, true>,
+                                 (const void*)hist_rot_kernel<false, false>, (const void*)hist_rot_kernel<false, true>,
+                                 (const void*)hist_rot_kernel<true, false>, (const void*)hist_rot_kernel<true, true>,
+                                 (const void*)hist_joint_kernel<false, false>, (const void*)hist_joint_kernel<false, true>,
+                                 (const void*)hist_joint_kernel<true, false>, (const void*)hist_joint_kernel<true, true>};
         for (const void* k : kernels)
             if (st == cudaSuccess) st = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
     }
@@ -364,6 +373,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_PEER_TRAIL")) e->peer_trailing_round = atoi(v) != 0;
     if (const char* v = getenv("AVT_LOOKBACK")) e->lookback = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
+    if (const char* v = getenv("AVT_FOREST_ROT")) e->forest_rot = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract_mode = atoi(v) != 0 ? 1 : 0;
     if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
     *out = e;
@@ -393,7 +403,7 @@ void avt_destroy(avt_engine* e) {
     e->d_nid.release(); e->d_levels.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
-    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_pub.release(); e->d_packed.release(); e->d_av.release(); e->d_best.release();
+    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_pub.release(); e->d_packed.release(); e->d_rowrot.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_cand[0].release(); e->d_cand[1].release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release(); e->d_ctrl.release();
     if (e->h_ctrl) cudaFreeHost(e->h_ctrl);
@@ -470,6 +480,20 @@ static int dataset_install(avt_engine* e) {
             pack_codes_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, e->stream>>>((const void* const*)e->d_colptrs.p, n_attrs,
                                                                                       make_uint4(e->pk_shift[0], e->pk_shift[1], e->pk_shift[2], e->pk_shift[3]), e->Npad, e->d_packed.p);
             CUDA_TRY(e, cudaGetLastError());
+        }
+    }
+    {
+        bool shape = n_attrs >= 16;
+        for (int a = 0; a < n_attrs && shape; ++a) shape = !e->wide[a];
+        e->rowrot_ok = false;
+        if (shape) {
+            const int chunks = (n_attrs + 31) / 32;
+            e->rowrot_rows = e->Npad + 32;
+            CUDA_TRY(e, e->d_rowrot.ensure((size_t)chunks * e->rowrot_rows * 32));
+            rowrot_kernel<<<dim3((unsigned)((e->rowrot_rows + 255) / 256), (unsigned)chunks), 256, 0, e->stream>>>((const void* const*)e->d_colptrs.p, n_attrs, e->N,
+                                                                                                               e->rowrot_rows, e->d_rowrot.p);
+            CUDA_TRY(e, cudaGetLastError());
+            e->rowrot_ok = true;
         }
     }
     e->T = 0;
@@ -862,6 +886,12 @@ int avt_split_table_set(avt_engine* e, int32_t n_splits, const avt_split* splits
                 int b = bounds[sp.off + j];
                 if (b < -1 || b >= e->n_bins[sp.attr]) return fail(e, AVT_E_INVALID, "split %d: bound %d outside the attribute's bins", s, b);
             }
+        } else if (sp.kind == AVT_SPLIT_RANGES) {
+            if (sp.off < 0 || sp.off + 2 * sp.n_seg > n_bounds) return fail(e, AVT_E_INVALID, "split %d: ranges out of range", s);
+            for (int j = 0; j < sp.n_seg; ++j) {
+                const int lo = bounds[sp.off + 2 * j], hi = bounds[sp.off + 2 * j + 1];
+                if (lo < 0 || hi >= e->n_bins[sp.attr]) return fail(e, AVT_E_INVALID, "split %d: range [%d, %d] outside the attribute's bins", s, lo, hi);
+            }
         } else if (sp.kind == AVT_SPLIT_LUT) {
             if (sp.off < 0 || (int64_t)sp.off + e->n_bins[sp.attr] > n_lut) return fail(e, AVT_E_INVALID, "split %d: segment table out of range", s);
         } else {
@@ -890,7 +920,7 @@ int avt_split_table_set(avt_engine* e, int32_t n_splits, const avt_split* splits
             seg_first[(size_t)s] = (int32_t)items.size();
             for (int j = 0; j < splits[s].n_seg; ++j) items.push_back(((uint32_t)s << 4) | (uint32_t)j);
             const int B = e->n_bins[splits[s].attr];
-            ok = ok && (long long)B * e->C <= kFastWordsPerAttr && (splits[s].kind == AVT_SPLIT_NUMERIC || B <= 64);
+            ok = ok && (long long)B * e->C <= kFastWordsPerAttr && (splits[s].kind == AVT_SPLIT_NUMERIC || (splits[s].kind == AVT_SPLIT_LUT && B <= 64));
         }
         seg_first[(size_t)n_splits] = (int32_t)items.size();
         ok = ok && items.size() <= (size_t)kFastItems && items.size() * (size_t)e->C <= (size_t)kFastCntWords;
@@ -932,18 +962,39 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
     // for at least one tree's counted nodes in shared memory
     int f_slots = std::max(n_max, 1), f_G = 0;
     size_t f_smem = 0;
+    bool f_rot = false;
     {
         if (e->skip_cur) f_slots = std::max(1, n_max - n_max / std::max(2, e->g_max_splits));   // one child of every expanded parent is derived, not counted
         const size_t n_prev = fr ? (size_t)std::max(fr->prev_n_max, 1) : 0;
         const size_t per_tree = (size_t)f_slots * e->C * max_bins * 128 + n_prev * ((size_t)(fr ? fr->lut_w : 0) * 4 + 1) + ((size_t)n_max + 2 + f_slots) * 2 + 1;
         const size_t fixed = (size_t)kForestWarps * kForestSub * 256 + (fr ? (size_t)kForestWarps * 1024 : 0) + 64;
-        if (!any_wide && max_bins <= 256 && per_tree + fixed <= kMaxDynSmem) {
-            f_G = (int)std::min<size_t>((size_t)e->T, (kMaxDynSmem - fixed) / per_tree);
-            f_smem = fixed + per_tree * (size_t)f_G;
+        f_rot = e->forest_rot && e->rowrot_ok;
+        const size_t fixed_rot = (size_t)f_slots * 0 + (size_t)e->C * max_bins * 128 /* phantom slot */ + (fr ? (size_t)kForestWarps * 1024 : 0) + 64;
+        const size_t fx = f_rot ? fixed_rot : fixed;
+        if (!any_wide && max_bins <= 256 && per_tree + fx <= kMaxDynSmem) {
+            f_G = (int)std::min<size_t>((size_t)e->T, (kMaxDynSmem - fx) / per_tree);
+            f_smem = fx + per_tree * (size_t)f_G;
         }
-        if (f_G > 0 && e->A >= 16 && e->force_variant < 0) variant = 2;
+        // hist_rot_kernel takes every forest-shaped level whose counted nodes fit; the list-based kernel (AVT_FOREST_ROT=0) only pays
+        // with >= 4 trees resident (measured on the C3 shape, profiles/)
+        if (f_G >= (f_rot ? 1 : 4) && e->A >= 16 && e->force_variant < 0 && variant == 0) variant = 2;
+    }
+    // joint-code kernel (avt_joint.cuh): the data set has a packed copy (<= 4 narrow attributes in one byte) and one block can hold
+    // the frontier's joint counters; it has no form for skip marks and does not signal peers itself
+    int j_J = 0;
+    size_t j_smem = 0;
+    if (e->packed_ok && !e->skip_cur && (!e->signal_pending || (e->peer_signal_scan && e->scan_will_signal))) {
+        int maxv = 0;
+        for (int a = 0; a < e->A; ++a) maxv += (e->n_bins[a] - 1) << e->pk_shift[a];
+        j_J = maxv + 1;
+        const size_t n_prev = fr ? (size_t)std::max(fr->prev_n_max, 1) : 0;
+        j_smem = ((size_t)std::max(n_max, 1) + 1) * j_J * e->C * 4 + (fr ? (n_prev + 1) * j_J * 2 : 0) + 16;
+        if (j_smem > kMaxDynSmem) j_J = 0;
+        else if (e->force_variant < 0 && variant == 0) variant = 3;
     }
     if (e->force_variant >= 0) {
+        if (e->force_variant == 3 && j_J == 0)
+            return fail(e, AVT_E_INVALID, "avt_level_histogram: joint-code variant forced but it needs a packed data set (<= 4 narrow attributes) and the frontier's joint counters in shared memory");
         if (e->force_variant == 0 && variant == 1)
             return fail(e, AVT_E_INVALID, "avt_level_histogram: shared-memory variant forced but the frontier needs %lld words", per_bin * max_bins);
         if (e->force_variant == 2 && f_G == 0)
@@ -1133,6 +1184,42 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         e->stats.last_hist_grid = (int)(grid.x * grid.y * grid.z);
         e->stats.last_hist_block = kHistThreads;
         e->stats.last_hist_smem = (int)smem;
+    } else if (variant == 3) {
+        JointArgs ja{};
+        ja.bin_off = e->d_bin_off.p;
+        ja.A = e->A;
+        ja.J = j_J;
+        ja.n_prev_max = fr ? std::max(fr->prev_n_max, 1) : 1;
+        ja.zero_words = (std::max(n_max, 1) + 1) * j_J * e->C;
+        for (int q = 0; q < 4; ++q) {
+            ja.shift[q] = e->pk_shift[q];
+            ja.mask[q] = e->pk_mask4[q] & 0xFFu;
+        }
+        ha.packed = e->d_packed.p;
+        // the per-block table build and flush grow with the frontier: deep levels run one block per SM
+        const int bpsm = n_max > 32 ? 1 : (int)std::min<size_t>((size_t)e->hist_max_bpsm, std::max<size_t>(1, (kMaxDynSmem + 1024) / (j_smem + 1024)));
+        long long chunks = std::max<long long>(1, (long long)e->sm_count * bpsm / e->T);
+        const long long tiles = (e->N + (long long)kJointThreads * kRowsPerThread - 1) / ((long long)kJointThreads * kRowsPerThread);
+        chunks = std::min(std::min(chunks, tiles), 65535LL);
+        dim3 grid((unsigned)e->T, (unsigned)chunks);
+        void (*kern)(const HistArgs, const JointArgs) = e->any_w ? (fr ? hist_joint_kernel<true, true> : hist_joint_kernel<true, false>)
+                                                                 : (fr ? hist_joint_kernel<false, true> : hist_joint_kernel<false, false>);
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = grid;
+        cfg.blockDim = dim3(kJointThreads);
+        cfg.dynamicSmemBytes = j_smem;
+        cfg.stream = e->stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = (e->pdl && e->pdl_chain) ? 1 : 0;
+        CUDA_TRY(e, cudaLaunchKernelEx(&cfg, kern, ha, ja));
+        e->signal_in_hist = e->signal_pending;   // (only reached when the scan kernel behind this pass signals the peers)
+        e->stats.last_hist_replicas = 1;
+        e->stats.last_hist_grid = (int)(grid.x * grid.y);
+        e->stats.last_hist_block = kJointThreads;
+        e->stats.last_hist_smem = (int)j_smem;
     } else if (variant == 2) {
         ForestArgs fa{};
         fa.bin_off = e->d_bin_off.p;
@@ -1154,8 +1241,12 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         tpp = (n_tiles + parts - 1) / parts;
         fa.tiles_per_part = tpp;
         dim3 grid((unsigned)groups, (unsigned)parts, (unsigned)achunks);
+        fa.rowrot = e->d_rowrot.p;
+        fa.rowrot_rows = e->rowrot_rows;
         void (*kern)(const HistArgs, const ForestArgs) = e->any_w ? (fr ? hist_forest_kernel<true, true> : hist_forest_kernel<true, false>)
                                                                   : (fr ? hist_forest_kernel<false, true> : hist_forest_kernel<false, false>);
+        if (f_rot)
+            kern = e->any_w ? (fr ? hist_rot_kernel<true, true> : hist_rot_kernel<true, false>) : (fr ? hist_rot_kernel<false, true> : hist_rot_kernel<false, false>);
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = grid;
         cfg.blockDim = dim3(kForestThreads);
@@ -1566,7 +1657,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         e->scan_will_signal = false;
         // small levels: push form of the exchange (no flags at all); needs the item-parallel scan kernel behind a shared-memory pass
         const bool push_level = peer_level && push_ok;
-        const bool scan_signals = peer_level && !push_level && e->peer_signal_scan && e->stats.last_hist_variant == 0;
+        const bool scan_signals = peer_level && !push_level && e->peer_signal_scan && (e->stats.last_hist_variant == 0 || e->stats.last_hist_variant == 3);
         e->skip_h_memset = false;
         e->pdl_chain = false;
         e->H_cur = nullptr;
@@ -1654,7 +1745,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             attr[0].val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = attr;
             // directly behind the histogram kernel unless an NCCL all-reduce or a signalling launch sits between
-            const bool chain = e->pdl && !e->profiling && e->stats.last_hist_variant == 0 && (peer_level ? e->signal_in_hist : e->comm == nullptr);
+            const bool chain = e->pdl && !e->profiling && (e->stats.last_hist_variant == 0 || e->stats.last_hist_variant == 3) && (peer_level ? e->signal_in_hist : e->comm == nullptr);
             cfg.numAttrs = chain ? 1 : 0;
             if (fast_scan) {
                 FastTable ft{e->d_items.p, e->d_seg_first.p, e->d_nkids.p, e->n_items, masks_on ? e->d_cand[level & 1].p : nullptr, nullptr, 0u};
@@ -1797,6 +1888,10 @@ int avt_grow_levels_ex(avt_engine* e, int32_t n_levels, int32_t criterion, const
                        int64_t* n_records) {
     if (!e) return AVT_E_INVALID;
     if (strategy != AVT_ATTRS_ALL && strategy != AVT_ATTRS_NOT_USED_YET) return fail(e, AVT_E_INVALID, "avt_grow_levels_ex: strategy %d", strategy);
+    for (auto& sp : e->splits)
+        if (sp.kind == AVT_SPLIT_RANGES)
+            return fail(e, AVT_E_INVALID, "avt_grow_levels: the split table has AVT_SPLIT_RANGES splits (segments may overlap, a row can have several children); "
+                                          "drive such tables level by level (avt_level_histogram / scan / eval / repartition)");
     if (!nodes_per_tree) return fail(e, AVT_E_INVALID, "avt_grow_levels: nodes_per_tree is NULL");
     if (e->T == 0 || e->S == 0) return fail(e, AVT_E_STATE, "avt_grow_levels: needs avt_forest_init and avt_split_table_set first");
     if (criterion != AVT_CRIT_GINI && criterion != AVT_CRIT_ENTROPY) return fail(e, AVT_E_INVALID, "avt_grow_levels: criterion %d", criterion);
@@ -1954,7 +2049,7 @@ int avt_reset_stats(avt_engine* e) {
 
 int avt_set_hist_variant(avt_engine* e, int32_t variant) {
     if (!e) return AVT_E_INVALID;
-    if (variant < -1 || variant > 2) return fail(e, AVT_E_INVALID, "avt_set_hist_variant: %d", variant);
+    if (variant < -1 || variant > 3) return fail(e, AVT_E_INVALID, "avt_set_hist_variant: %d", variant);
     e->force_variant = variant;
     return AVT_OK;
 }

@@ -35,6 +35,8 @@ struct ForestArgs {
     int n_prev_max;    // fused repartition: bound on a tree's nodes in the previous frontier
     long long tiles_per_part;   // 32-row tiles per grid.y slice
     int32_t* err;      // set to 4 when a tree has more counted nodes than n_slots (host bound violated)
+    const uint8_t* rowrot;      // hist_rot_kernel: rotated row-major copy of the codes, [chunks][rowrot_rows][32]
+    long long rowrot_rows;      // rows per chunk in `rowrot` (padded row count + one tile of slack)
 };
 
 // explicit shared-window accesses for the hot loops (a generic pointer into dynamic shared memory compiles to LD.E/ST.E)
@@ -56,6 +58,19 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
 __device__ __forceinline__ uint2 lds_v2(uint32_t addr) {
     uint2 v;
     asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+    return v;
+}
+// update executed only where `n > i` (a predicate, not a branch: the loads around it stay in flight)
+template <int I>
+__device__ __forceinline__ void red_shared_add_gt(uint32_t addr, uint32_t v, uint32_t n) {
+    asm volatile("{\n .reg .pred p;\n setp.gt.u32 p, %2, %3;\n @p red.shared.add.u32 [%0], %1;\n}" ::"r"(addr), "r"(v), "r"(n), "n"(I) : "memory");
+}
+__device__ __forceinline__ void red_shared_add_bit(uint32_t addr, uint32_t v, uint32_t mask, uint32_t bit) {
+    asm volatile("{\n .reg .pred p;\n .reg .b32 t;\n and.b32 t, %2, %3;\n setp.ne.u32 p, t, 0;\n @p red.shared.add.u32 [%0], %1;\n}" ::"r"(addr), "r"(v), "r"(mask), "r"(bit) : "memory");
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
     return v;
 }
 __device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
@@ -208,7 +223,10 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const Hi
                     if (HAS_W && lds_u8(has_w_base + g0 + k)) w_r[k] = w_row[(long long)(g0 + k) * a.Npad];
                 }
             }
-            uint32_t cnt_live = 0;
+            // few trees (deep levels, one or two trees resident): entries stay at [tree][row] and a ballot says which rows are
+            // live -- nothing is paid per row and tree; several trees: each row compacts its live entries at [0..n)[row]
+            const bool compact = gn > 2;
+            uint32_t cnt_live = 0, live_bits = 0;
 #pragma unroll
             for (int k = 0; k < kForestSub; ++k) {
                 if (k < gn) {
@@ -221,7 +239,9 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const Hi
                             node = min(node, (uint32_t)f.n_prev_max - 1u);
                             const uint32_t at = lds_u8(attr8_base + g * f.n_prev_max + node);
                             if (at != 0xFFu) {
-                                const uint32_t code = lds_u8(codes_base + 32u * at + lane);
+                                // the tile in shared memory holds this block's 32 attributes; another chunk's column is read from global memory
+                                const uint32_t code = (at >> 5) == (uint32_t)chunk ? lds_u8(codes_base + 32u * (at & 31u) + lane)
+                                                                                   : (uint32_t)__ldg((const uint8_t*)a.cols[at] + row);
                                 e = lds_u32(lut_base + 4u * (g * lut_stride + node * a.lut_w + code));
                             }
                         }
@@ -232,22 +252,49 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const Hi
                         s = lds_u16(slot_of_base + 2u * (g * so_stride + min(node, (uint32_t)f.n_nodes_max)));
                     }
                     if (s != 0xFFFFu && w_r[k] != 0u) {
-                        sts_v2(list_base + cnt_live * 256u + 8u * lane, cnt_base + (uint32_t)g * tree_bytes + s * slot_bytes + cl * class_bytes, w_r[k]);
+                        sts_v2(list_base + (compact ? cnt_live : (uint32_t)k) * 256u + 8u * lane,
+                               cnt_base + (uint32_t)g * tree_bytes + s * slot_bytes + cl * class_bytes, w_r[k]);
                         ++cnt_live;
+                        live_bits |= 1u << k;
                     }
                 }
             }
             __syncwarp();
             // ---- phase B (lane = attribute): one conflict-free update per live (row, tree) pair
+            if (compact) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const uint32_t n = __shfl_sync(0xffffffffu, cnt_live, j);
-                const uint32_t off = (j & 1) ? (offs[j >> 1] >> 16) : (offs[j >> 1] & 0xFFFFu);
+                for (int j = 0; j < 32; ++j) {
+                    const uint32_t n = __shfl_sync(0xffffffffu, cnt_live, j);
+                    const uint32_t off = (j & 1) ? (offs[j >> 1] >> 16) : (offs[j >> 1] & 0xFFFFu);
+                    // the first four entries are loaded unconditionally (same address in every lane: broadcasts that overlap each
+                    // other) and applied under a predicate; longer lists continue with a compare-and-branch chain
+                    const uint2 x0 = lds_v2(list_base + 0u * 256u + 8u * j), x1 = lds_v2(list_base + 1u * 256u + 8u * j);
+                    const uint2 x2 = lds_v2(list_base + 2u * 256u + 8u * j), x3 = lds_v2(list_base + 3u * 256u + 8u * j);
+                    red_shared_add_gt<0>(x0.x + off, HAS_W ? x0.y : 1u, n);
+                    red_shared_add_gt<1>(x1.x + off, HAS_W ? x1.y : 1u, n);
+                    red_shared_add_gt<2>(x2.x + off, HAS_W ? x2.y : 1u, n);
+                    red_shared_add_gt<3>(x3.x + off, HAS_W ? x3.y : 1u, n);
 #pragma unroll
-                for (uint32_t i = 0; i < (uint32_t)kForestSub; ++i) {   // a compare-and-branch chain: no loop counter, constant addresses
-                    if (i >= n) break;
-                    const uint2 x = lds_v2(list_base + i * 256u + 8u * j);   // same address in every lane: one broadcast
-                    red_shared_add(x.x + off, HAS_W ? x.y : 1u);
+                    for (uint32_t i = 4; i < (uint32_t)kForestSub; ++i) {
+                        if (i >= n) break;
+                        const uint2 x = lds_v2(list_base + i * 256u + 8u * j);
+                        red_shared_add(x.x + off, HAS_W ? x.y : 1u);
+                    }
+                }
+            } else {
+                for (int k = 0; k < gn; ++k) {
+                    const uint32_t m = __ballot_sync(0xffffffffu, (live_bits >> k) & 1u);
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        if ((m >> (4 * q)) & 0xFu) {
+                            const uint4 v0 = lds_v4(list_base + (uint32_t)k * 256u + 32u * q), v1 = lds_v4(list_base + (uint32_t)k * 256u + 32u * q + 16u);
+                            const uint32_t o0 = offs[2 * q] & 0xFFFFu, o1 = offs[2 * q] >> 16, o2 = offs[2 * q + 1] & 0xFFFFu, o3 = offs[2 * q + 1] >> 16;
+                            red_shared_add_bit(v0.x + o0, HAS_W ? v0.y : 1u, m, 1u << (4 * q));
+                            red_shared_add_bit(v0.z + o1, HAS_W ? v0.w : 1u, m, 2u << (4 * q));
+                            red_shared_add_bit(v1.x + o2, HAS_W ? v1.y : 1u, m, 4u << (4 * q));
+                            red_shared_add_bit(v1.z + o3, HAS_W ? v1.w : 1u, m, 8u << (4 * q));
+                        }
+                    }
                 }
             }
             __syncwarp();   // the lists are rewritten by the next sub-batch
@@ -269,6 +316,212 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const Hi
             const int s = (int)(sc / (uint32_t)a.C);
             const int at = chunk * 32 + la;
             if (at >= f.A) continue;   // lanes without an attribute counted into their own (unused) column
+            const int node = node_of[g * f.n_slots + s];
+            const int b0 = f.bin_off[at];
+            if (node == 0xFFFF || bin >= f.bin_off[at + 1] - b0) continue;
+            atomicAdd(a.H + ((long long)(nb + node) * a.TB + b0 + bin) * a.C + c, v);
+        }
+    }
+}
+
+
+// ----------------------------------------------------------------------------------------------------------------------
+// hist_rot_kernel: lane = ROW, attributes visited in a lane-rotated order.
+//
+// Same counters as hist_forest_kernel ([tree][slot][class][bin][attribute(32)]: the bank of a counter is its attribute),
+// but every lane owns one row of the warp's 32-row tile and, at step p of the 32-step update loop, counts attribute
+// (p + lane) mod 32 of its row: at every step the 32 lanes touch 32 different attributes, i.e. 32 different banks -- each
+// ATOMS is one conflict-free wavefront with all lanes active, three instructions per counter update, nothing shuffled or
+// broadcast.  For that a lane must find "attribute (p + lane) mod 32 of my row" at a compile-time byte position p of its
+// registers: the data set keeps a second, row-major copy of the codes in which row r's 32 bytes are rotated by r mod 32
+// (rowrot_kernel, built once when the data set is installed), so one 32-byte load per row and tile gives exactly that.
+// The tile's codes stay in registers (pre-scaled to counter offsets) across the loop over the block's resident trees; per
+// (row, tree) only the node id, the multiplicity, the fused repartition (shared-memory tables) and the slot lookup remain.
+// Rows that are not counted (outside the frontier, multiplicity 0, node derived by sibling subtraction) update a phantom
+// slot: a partially active ATOMS is much slower than a full one on sm_100a (tools/microbench/atoms_bench.cu).
+// Shared memory: counters [G * n_slots + 1 phantom][C][Bmax][32], tile copies [warps][32 rows][32 B] (fused repartition),
+// then lut32 / slot_of / node_of / attr8 / has_w as in hist_forest_kernel.
+__global__ void rowrot_kernel(const void* const* cols, int A, long long N, long long rows_alloc, uint8_t* out) {
+    const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int chunk = blockIdx.y;
+    if (r >= rows_alloc) return;
+    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (r < N) {
+        const int rot = (int)(r & 31);
+#pragma unroll 4
+        for (int p = 0; p < 32; ++p) {
+            const int a = chunk * 32 + ((p + rot) & 31);
+            const uint32_t code = a < A ? ((const uint8_t*)cols[a])[r] : 0u;
+            w[p >> 2] |= code << (8 * (p & 3));
+        }
+    }
+    uint4* dst = reinterpret_cast<uint4*>(out + ((long long)chunk * rows_alloc + r) * 32);
+    dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+}
+
+template <bool HAS_W, bool REPART>
+__global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistArgs a, const ForestArgs f) {
+    extern __shared__ __align__(16) uint32_t fsh[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t0 = blockIdx.x * f.G;
+    const int Gb = min(f.G, a.T - t0);
+    const int chunk = blockIdx.z;
+    const uint32_t slot_words = (uint32_t)a.C * f.Bmax * 32u;
+    const uint32_t cnt_words = ((uint32_t)f.G * f.n_slots + 1u) * slot_words;    // + the phantom slot
+    const int so_stride = f.n_nodes_max + 1;
+    const int lut_stride = f.n_prev_max * a.lut_w;
+    uint32_t* cnt = fsh;
+    uint8_t* codes_s = reinterpret_cast<uint8_t*>(cnt + cnt_words);
+    uint32_t* lut32 = reinterpret_cast<uint32_t*>(codes_s + (REPART ? kForestWarps * 1024 : 0));
+    uint16_t* slot_of = reinterpret_cast<uint16_t*>(lut32 + (REPART ? (size_t)f.G * lut_stride : 0));
+    uint16_t* node_of = slot_of + (size_t)f.G * so_stride;
+    uint8_t* attr8 = reinterpret_cast<uint8_t*>(node_of + (size_t)f.G * f.n_slots);
+    uint8_t* s_has_w = attr8 + (REPART ? (size_t)f.G * f.n_prev_max : 0);
+
+    pdl_launch_dependents();
+    for (uint32_t i = threadIdx.x; i < cnt_words; i += blockDim.x) cnt[i] = 0;
+    pdl_wait();
+    for (int g = warp; g < Gb; g += kForestWarps) {
+        const int nb = a.node_base[t0 + g], n = a.node_base[t0 + g + 1] - nb;
+        for (int i = lane; i < so_stride; i += 32) slot_of[g * so_stride + i] = 0xFFFF;
+        if (lane == 0) s_has_w[g] = HAS_W && a.has_w[t0 + g] ? 1 : 0;
+        __syncwarp();
+        int run = 0;
+        for (int i0 = 0; i0 < n; i0 += 32) {
+            const int i = i0 + lane;
+            const bool counted = i < n && !(a.skip && a.skip[nb + i]);
+            const uint32_t m = __ballot_sync(0xffffffffu, counted);
+            const int s = run + __popc(m & ((1u << lane) - 1u));
+            if (i < n && i < so_stride && counted && s < f.n_slots) slot_of[g * so_stride + i] = (uint16_t)s;
+            if (counted && s < f.n_slots) node_of[g * f.n_slots + s] = (uint16_t)i;
+            run += __popc(m);
+        }
+        if (lane == 0 && (run > f.n_slots || n > f.n_nodes_max)) *f.err = 4;
+        for (int s = run + lane; s < f.n_slots; s += 32) node_of[g * f.n_slots + s] = 0xFFFF;
+    }
+    __syncthreads();
+    if (REPART) {
+        for (int g = 0; g < Gb; ++g) {
+            const int pnb = a.prev_node_base[t0 + g], n_prev = min(a.prev_node_base[t0 + g + 1] - pnb, f.n_prev_max);
+            if (threadIdx.x == 0 && a.prev_node_base[t0 + g + 1] - pnb > f.n_prev_max) *f.err = 4;
+            for (int i = threadIdx.x; i < n_prev * a.lut_w; i += blockDim.x) {
+                const uint32_t child = a.child_lut[(long long)pnb * a.lut_w + i];
+                const uint32_t s = child == AVT_NODE_NONE ? 0xFFFFu : (uint32_t)slot_of[g * so_stride + min(child, (uint32_t)f.n_nodes_max)];
+                lut32[g * lut_stride + i] = (s << 16) | child;
+            }
+            for (int i = threadIdx.x; i < n_prev; i += blockDim.x) {
+                const int at = a.node_attr[pnb + i];
+                attr8[g * f.n_prev_max + i] = at < 0 ? (uint8_t)0xFF : (uint8_t)at;
+            }
+        }
+        __syncthreads();
+    }
+    uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(cnt);
+    uint32_t codes_base = (uint32_t)__cvta_generic_to_shared(codes_s) + (uint32_t)warp * 1024u + 32u * lane;   // this lane's row
+    uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(lut32);
+    uint32_t slot_of_base = (uint32_t)__cvta_generic_to_shared(slot_of);
+    uint32_t attr8_base = (uint32_t)__cvta_generic_to_shared(attr8);
+    uint32_t has_w_base = (uint32_t)__cvta_generic_to_shared(s_has_w);
+    asm volatile("" : "+r"(cnt_base), "+r"(codes_base), "+r"(lut_base), "+r"(slot_of_base), "+r"(attr8_base), "+r"(has_w_base));
+    const uint32_t class_bytes = (uint32_t)f.Bmax * 128u;
+    const uint32_t slot_bytes = slot_words * 4u;
+    const uint32_t tree_bytes = (uint32_t)f.n_slots * slot_bytes;
+    const uint32_t phantom = cnt_base + (uint32_t)f.G * tree_bytes;   // class 0 of the phantom slot: any bin, own column
+    const long long n_tiles = (a.N + 31) >> 5;
+    const long long tile_lo = (long long)blockIdx.y * f.tiles_per_part;
+    const long long tile_hi = min(n_tiles, tile_lo + f.tiles_per_part);
+    const uint8_t* rr = f.rowrot + (long long)chunk * f.rowrot_rows * 32;
+    // column (= attribute within the chunk) this lane counts at step p, as a byte offset: 4 * ((p + lane) & 31), two per word
+    uint32_t colw[16];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) colw[q] = (4u * ((2u * q + lane) & 31u)) | ((4u * ((2u * q + 1u + lane) & 31u)) << 16);
+
+    uint4 nc0 = make_uint4(0, 0, 0, 0), nc1 = nc0;
+    uint32_t ncl = 0;
+    auto load_row = [&](long long tile) {
+        const long long row = (tile << 5) + lane;
+        const uint4* src = reinterpret_cast<const uint4*>(rr + row * 32);
+        nc0 = __ldg(src);
+        nc1 = __ldg(src + 1);
+        ncl = a.cls[row];
+    };
+    long long tile = tile_lo + warp;
+    if (tile < tile_hi) load_row(tile);
+    for (; tile < tile_hi; tile += kForestWarps) {
+        const long long row = (tile << 5) + lane;
+        const bool row_ok = row < a.N;
+        uint32_t offs[16];   // step p: code * 128 + column offset, two steps per register
+        {
+            const uint32_t w8[8] = {nc0.x, nc0.y, nc0.z, nc0.w, nc1.x, nc1.y, nc1.z, nc1.w};
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                offs[2 * q] = __byte_perm(w8[q], 0u, 0x4140u) * 128u + colw[2 * q];
+                offs[2 * q + 1] = __byte_perm(w8[q], 0u, 0x4342u) * 128u + colw[2 * q + 1];
+            }
+            if (REPART) {
+                sts_v4(codes_base, nc0);          // own row, own 32 bytes: no other lane reads or writes them
+                sts_v4(codes_base + 16u, nc1);
+            }
+        }
+        const uint32_t cl = ncl;
+        if (tile + kForestWarps < tile_hi) load_row(tile + kForestWarps);
+        const uint16_t* nid_row = a.nid + (long long)t0 * a.Npad + row;
+        uint16_t* nid_out_row = REPART ? a.nid_out + (long long)t0 * a.Npad + row : nullptr;
+        const uint8_t* w_row = HAS_W ? a.wts + (long long)t0 * a.Npad + row : nullptr;
+        uint32_t nid_next = nid_row[0], w_next = 1u;
+        if (HAS_W && lds_u8(has_w_base)) w_next = w_row[0];
+        for (int g = 0; g < Gb; ++g) {
+            uint32_t node = row_ok ? nid_next : AVT_NODE_NONE;
+            const uint32_t w = w_next;
+            if (g + 1 < Gb) {   // next tree's node id and multiplicity while this tree's updates issue
+                nid_next = nid_row[(long long)(g + 1) * a.Npad];
+                w_next = 1u;
+                if (HAS_W && lds_u8(has_w_base + g + 1)) w_next = w_row[(long long)(g + 1) * a.Npad];
+            }
+            uint32_t s = 0xFFFFu;
+            if (REPART) {
+                uint32_t e = 0xFFFFFFFFu;
+                if (node != AVT_NODE_NONE) {
+                    node = min(node, (uint32_t)f.n_prev_max - 1u);
+                    const uint32_t at = lds_u8(attr8_base + g * f.n_prev_max + node);
+                    if (at != 0xFFu) {
+                        // byte position of attribute `at` in this row's rotated copy; another chunk's column comes from global memory
+                        const uint32_t code = (at >> 5) == (uint32_t)chunk ? lds_u8(codes_base + ((at - (uint32_t)lane) & 31u))
+                                                                           : (uint32_t)__ldg((const uint8_t*)a.cols[at] + row);
+                        e = lds_u32(lut_base + 4u * (g * lut_stride + node * a.lut_w + code));
+                    }
+                }
+                node = e & 0xFFFFu;
+                s = e >> 16;
+                if (chunk == 0 && row < a.Npad) nid_out_row[(long long)g * a.Npad] = (uint16_t)node;
+            } else if (node != AVT_NODE_NONE) {
+                s = lds_u16(slot_of_base + 2u * (g * so_stride + min(node, (uint32_t)f.n_nodes_max)));
+            }
+            const bool live = s != 0xFFFFu && w != 0u;
+            const uint32_t hb = live ? cnt_base + (uint32_t)g * tree_bytes + s * slot_bytes + cl * class_bytes : phantom;
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                red_shared_add(hb + (offs[q] & 0xFFFFu), HAS_W ? w : 1u);
+                red_shared_add(hb + (offs[q] >> 16), HAS_W ? w : 1u);
+            }
+        }
+    }
+    __syncthreads();
+    for (int g = 0; g < Gb; ++g) {
+        const int nb = a.node_base[t0 + g];
+        const uint32_t per_tree = (uint32_t)f.n_slots * slot_words;
+        for (uint32_t i = threadIdx.x; i < per_tree; i += blockDim.x) {
+            const uint32_t v = cnt[(uint32_t)g * per_tree + i];
+            if (!v) continue;
+            const int la = (int)(i & 31u);
+            const uint32_t rest = i >> 5;
+            const int bin = (int)(rest % (uint32_t)f.Bmax);
+            const uint32_t sc = rest / (uint32_t)f.Bmax;
+            const int c = (int)(sc % (uint32_t)a.C);
+            const int s = (int)(sc / (uint32_t)a.C);
+            const int at = chunk * 32 + la;
+            if (at >= f.A) continue;
             const int node = node_of[g * f.n_slots + s];
             const int b0 = f.bin_off[at];
             if (node == 0xFFFF || bin >= f.bin_off[at + 1] - b0) continue;

@@ -430,6 +430,15 @@ __device__ __forceinline__ void segment_counts(const SplitTable& st, const avt_s
             for (int b = lo + 1; b <= hi; ++b)
                 for (int c = 0; c < C; ++c) cnt[c] += Hn[b * C + c];
         }
+    } else if (sp.kind == AVT_SPLIT_RANGES) {
+        const int lo = st.bounds[sp.off + 2 * j], hi = min(st.bounds[sp.off + 2 * j + 1], B - 1);
+        if (hi < lo) return;
+        if (P) {
+            for (int c = 0; c < C; ++c) cnt[c] = P[hi * C + c] - (lo > 0 ? P[(lo - 1) * C + c] : 0u);
+        } else {
+            for (int b = lo; b <= hi; ++b)
+                for (int c = 0; c < C; ++c) cnt[c] += Hn[b * C + c];
+        }
     } else {
         const uint8_t* lut = st.seg_lut + sp.off;
         for (int b = 0; b < B; ++b) {
@@ -722,6 +731,7 @@ __global__ void __launch_bounds__(256) repartition_fast_kernel(const RepartFastA
 
 #include "avt_scan_fast.cuh"
 #include "avt_forest.cuh"
+#include "avt_joint.cuh"
 #include "avt_csv.cuh"
 #include "avt_predict.cuh"
 #include "avt_bagging.cuh"

@@ -294,6 +294,11 @@ struct Node {
     std::vector<std::string> tagged;  // key items as the reducer sees them: "$root", "3:2 le 20", ...
     DecPath path;                     // its entry in the current decision-path list
     std::vector<int> cand;            // candidate attribute columns (indices into attrs_)
+    // Where the node's rows live on the device.  An engine "tree" is a LAYER: one node id per row.  With binary splits a
+    // reference tree is one layer.  The predicates of a multi-way numeric split overlap (`le p_last` has no lower bound,
+    // SURVEY App. B-1), so a row can sit in several frontier nodes at once: children whose bins overlap a sibling's are
+    // given a layer of their own (same rows and multiplicities, node ids of their own).
+    int layer = 0, id = 0;
 };
 
 struct Tree {
@@ -325,6 +330,8 @@ class DtbJob {
     std::vector<std::vector<uint16_t>> col16_;
     std::vector<uint8_t> cls_;
     std::vector<Tree> trees_;
+    std::vector<int> layer_tree_;    // device layer (engine tree) -> reference tree
+    bool multiway_ = false;          // some candidate split has more than two predicates
     std::unique_ptr<Engine> eng_;
     JavaRandom rng_{0};
     int pass_ = 0;  // passes written so far (0 = root pass)
@@ -433,6 +440,8 @@ private:
         for (int o : base) attrs_.push_back(dtb_attr_splits(schema_.by_ordinal(o)));
         if (attrs_.empty()) throw ReferenceError("no candidate attributes in the schema");
         table_ = flatten_splits(attrs_);
+        for (auto& as : attrs_)
+            for (auto& h : as.splits) multiway_ = multiway_ || h.n_seg > 2;
         class_ord_ = schema_.class_field().ordinal;
         int rec_len = conf_.get_int("dtb.rec.len", -1);
         if (rec_len > 0)
@@ -521,8 +530,11 @@ private:
             if (!tr.weights.empty()) wptr[(size_t)t] = tr.weights.data();
             Node root;
             root.tagged = {kRoot};
+            root.layer = t;
             tr.frontier.push_back(root);
         }
+        layer_tree_.resize((size_t)num_trees_);
+        for (int t = 0; t < num_trees_; ++t) layer_tree_[(size_t)t] = t;
         eng_->check(avt_forest_init(eng_->raw(), num_trees_, wptr.data(), nullptr));
     }
 
@@ -534,7 +546,11 @@ private:
         Tree& tr = trees_[0];
         tr.rng = JavaRandom(seed_);
         tr.frontier.resize(dec_in.size());
-        for (size_t i = 0; i < dec_in.size(); ++i) tr.frontier[i].path = dec_in[i];
+        for (size_t i = 0; i < dec_in.size(); ++i) {
+            tr.frontier[i].path = dec_in[i];
+            tr.frontier[i].id = (int)i;   // one layer: every input line carries one path, hence one node
+        }
+        layer_tree_.assign(1, 0);
         if (dec_in.size() >= AVT_NODE_NONE) throw Unsupported("more than 65534 frontier nodes");
         std::vector<uint16_t> nid(rows_.size(), (uint16_t)AVT_NODE_NONE);
         JStrMap<int> cache;  // validDecPaths
@@ -572,9 +588,11 @@ private:
         eng_->check(avt_forest_init(eng_->raw(), 1, nullptr, &np));
     }
 
+    // frontier nodes of every device layer (node ids inside a layer are 0..n-1)
     std::vector<int32_t> nodes_per_tree() const {
-        std::vector<int32_t> v;
-        for (auto& t : trees_) v.push_back((int32_t)t.frontier.size());
+        std::vector<int32_t> v(layer_tree_.size(), 0);
+        for (auto& t : trees_)
+            for (auto& nd : t.frontier) v[(size_t)nd.layer] = std::max(v[(size_t)nd.layer], (int32_t)nd.id + 1);
         return v;
     }
 
@@ -654,8 +672,8 @@ private:
                     bool any = false;
                     for (int c = 0; c < C; ++c) any = any || hist[(size_t)(bin_off[(size_t)a] + b) * C + c] != 0;
                     if (!any) continue;
-                    int sg = split_segment_of_bin(as, h, b);
-                    if (sg >= 0) present[(size_t)sg] = 1;
+                    for (int sg = 0; sg < h.n_seg; ++sg)
+                        if (split_bin_in_segment(as, h, b, sg)) present[(size_t)sg] = 1;
                 }
                 for (int sg = 0; sg < h.n_seg; ++sg)
                     if (present[(size_t)sg]) keys.push_back({std::to_string(split_id) + ":" + h.pred_str[(size_t)sg], table_.attr_first[(size_t)a] + (int)k, sg});
@@ -688,14 +706,54 @@ private:
         return o;
     }
 
+    // Every tag chain under which the reference's reducer sees this node's rows.  With multi-way splits the same predicate
+    // string occurs in several candidate splits of an attribute (`5 le 60` in [60], [60,120], [60,180], ...), the next
+    // mapper matches rows by their id-STRIPPED path (tree/DecisionTreeBuilder.java:274-292), so rows written under rejected
+    // splits survive with their own split ids: identical rows, different keys.  They change nothing in
+    // the statistics (infoContentBySplit overwrites equal entries, :652-665) but they are keys of `decPaths`, whose size and
+    // iteration order decide the order of the emitted list.  With binary splits every predicate string belongs to one split.
+    std::vector<std::vector<std::string>> tag_variants(const Node& nd) const {
+        std::vector<std::vector<std::string>> out{{}};
+        Node prefix;
+        for (size_t k = 0; k < nd.tagged.size(); ++k) {
+            const std::string& item = nd.tagged[k];
+            std::vector<std::string> alts;
+            if (item == kRoot || !multiway_) {
+                alts.push_back(item);
+            } else {
+                const std::string pred = strip_id(item);
+                int split_id = 0;
+                for (int a : candidates(prefix))
+                    for (auto& h : attrs_[(size_t)a].splits) {
+                        ++split_id;
+                        for (auto& ps : h.pred_str)
+                            if (ps == pred) { alts.push_back(std::to_string(split_id) + ":" + pred); break; }
+                    }
+                if (alts.empty()) alts.push_back(item);
+            }
+            std::vector<std::vector<std::string>> next;
+            for (auto& pre : out)
+                for (auto& alt : alts) {
+                    next.push_back(pre);
+                    next.back().push_back(alt);
+                }
+            if (next.size() > 200000) throw Unsupported("more than 200000 duplicate decision paths (multi-way splits, SURVEY App. B-2)");
+            out.swap(next);
+            prefix.tagged.push_back(item);
+        }
+        return out;
+    }
+
     // Parent iteration order of decPathsInfoContentBySplit.keySet() (tree/DecisionTreeBuilder.java:
     // 512, 640-650): parents enter `decPaths` in reducer key order (Tuple order, element-wise),
     // are re-inserted id-stripped in decPaths.keySet() order, then iterated.
     std::vector<int> parent_order(const Tree& tr, const std::vector<int>& live) const {
-        std::vector<int> sorted = live;
-        std::sort(sorted.begin(), sorted.end(), [&](int x, int y) { return tr.frontier[(size_t)x].tagged < tr.frontier[(size_t)y].tagged; });
+        std::vector<std::pair<std::vector<std::string>, int>> keys;
+        for (int i : live)
+            for (auto& v : tag_variants(tr.frontier[(size_t)i])) keys.emplace_back(v, i);
+        std::stable_sort(keys.begin(), keys.end(), [](const auto& x, const auto& y) { return x.first < y.first; });
         JStrMap<int> dec_paths;
-        for (int i : sorted) dec_paths.put(join_str(tr.frontier[(size_t)i].tagged, path_delim_), i);
+        for (auto& kv : keys) dec_paths.put(join_str(kv.first, path_delim_), kv.second);
         JStrMap<int> by_split;
         dec_paths.for_each([&](const std::string&, int& i) {
             std::vector<std::string> st;
@@ -720,20 +778,21 @@ private:
         const int C = (int)classes_.names.size();
         const int A = (int)attrs_.size();
         const int mw = (A + 31) / 32;
-        auto npt = nodes_per_tree();
-        std::vector<int> base((size_t)num_trees_ + 1, 0);
-        for (int t = 0; t < num_trees_; ++t) base[(size_t)t + 1] = base[(size_t)t] + npt[(size_t)t];
-        const int NF = base[(size_t)num_trees_];
+        auto npl = nodes_per_tree();                       // per device layer
+        const int n_layers = (int)npl.size();
+        std::vector<int> base((size_t)n_layers + 1, 0);
+        for (int l = 0; l < n_layers; ++l) base[(size_t)l + 1] = base[(size_t)l] + npl[(size_t)l];
+        const int NF = base[(size_t)n_layers];
+        auto gidx = [&](const Node& nd) { return base[(size_t)nd.layer] + nd.id; };
         lists.assign((size_t)num_trees_, {});
         list_null.assign((size_t)num_trees_, true);
         if (NF == 0) return false;
-        eng_->check(avt_level_histogram(eng_->raw(), npt.data(), nullptr));
+        eng_->check(avt_level_histogram(eng_->raw(), npl.data(), nullptr));
         std::vector<uint32_t> mask((size_t)NF * mw, 0);
         for (int t = 0; t < num_trees_; ++t)
-            for (size_t i = 0; i < trees_[(size_t)t].frontier.size(); ++i) {
-                Node& nd = trees_[(size_t)t].frontier[i];
+            for (Node& nd : trees_[(size_t)t].frontier) {
                 nd.cand = candidates(nd);
-                for (int a : nd.cand) mask[(size_t)(base[(size_t)t] + (int)i) * mw + (a >> 5)] |= 1u << (a & 31);
+                for (int a : nd.cand) mask[(size_t)gidx(nd) * mw + (a >> 5)] |= 1u << (a & 31);
             }
         std::vector<avt_node_best> best((size_t)NF);
         eng_->check(avt_level_scan(eng_->raw(), criterion(), mask.data(), classes_.order.data(), best.data()));
@@ -750,14 +809,47 @@ private:
             orders[(size_t)g] = java_order(nd, hist);
             have_order[(size_t)g] = 1;
         };
+        // av of every candidate split of node g, exactly as the reference sums it.  Two-predicate splits: the device value
+        // (two terms commute).  More predicates: the weighted sum runs in predInfoContent.keySet() order and the terms do not
+        // commute in floating point, so the per-predicate statistics come from the device and the sum is redone here.
+        auto node_av = [&](int g, const Node& nd) {
+            eng_->check(avt_level_fetch_av(eng_->raw(), g, av.data()));
+            if (!multiway_) return;
+            need_order(g, nd);
+            std::vector<int32_t> nodes, splits;
+            for (int a : nd.cand)
+                for (size_t k = 0; k < attrs_[(size_t)a].splits.size(); ++k)
+                    if (attrs_[(size_t)a].splits[k].n_seg > 2) { nodes.push_back(g); splits.push_back(table_.attr_first[(size_t)a] + (int)k); }
+            if (nodes.empty()) return;
+            std::vector<avt_split_eval> ev(nodes.size());
+            eng_->check(avt_level_eval(eng_->raw(), criterion(), classes_.order.data(), (int32_t)nodes.size(), nodes.data(), splits.data(), ev.data()));
+            for (size_t k = 0; k < splits.size(); ++k) {
+                const int ti = splits[k];
+                double weighted = 0.0;
+                long long total = 0;
+                for (int sg : orders[(size_t)g].seg_order_by_split[(size_t)ti]) {
+                    long long n = 0;
+                    for (int c = 0; c < C; ++c) n += ev[k].seg_count[sg][c];
+                    weighted += ev[k].seg_stat[sg] * (double)n;
+                    total += n;
+                }
+                av[(size_t)ti] = weighted / (double)total;
+            }
+        };
         for (int t = 0; t < num_trees_; ++t)
-            for (size_t i = 0; i < trees_[(size_t)t].frontier.size(); ++i) {
-                const int g = base[(size_t)t] + (int)i;
-                const Node& nd = trees_[(size_t)t].frontier[i];
+            for (const Node& nd : trees_[(size_t)t].frontier) {
+                const int g = gidx(nd);
                 const avt_node_best& b = best[(size_t)g];
                 if (b.population == 0 || b.best_split < 0) continue;  // no rows or no candidate split: nothing is emitted for this parent
                 chosen[(size_t)g] = b.best_split;
-                if (split_sel_ == "best" && b.n_ties > 1) {
+                if (split_sel_ != "best") continue;
+                if (multiway_) {
+                    // strict `<` from 1000000 over splitInfoContent.keySet() (tree/DecisionTreeBuilder.java:549-559)
+                    node_av(g, nd);
+                    double mn = 1000000.0;
+                    for (int ti : orders[(size_t)g].split_order)
+                        if (av[(size_t)ti] < mn) { mn = av[(size_t)ti]; chosen[(size_t)g] = ti; }
+                } else if (b.n_ties > 1) {
                     need_order(g, nd);
                     eng_->check(avt_level_fetch_av(eng_->raw(), g, av.data()));
                     for (int ti : orders[(size_t)g].split_order)
@@ -772,11 +864,12 @@ private:
                 Tree& tr = trees_[(size_t)t];
                 std::vector<int> live;
                 for (size_t i = 0; i < tr.frontier.size(); ++i)
-                    if (chosen[(size_t)(base[(size_t)t] + (int)i)] >= 0) live.push_back((int)i);
+                    if (chosen[(size_t)gidx(tr.frontier[i])] >= 0) live.push_back((int)i);
                 for (int i : parent_order(tr, live)) {
-                    const int g = base[(size_t)t] + i;
-                    need_order(g, tr.frontier[(size_t)i]);
-                    eng_->check(avt_level_fetch_av(eng_->raw(), g, av.data()));
+                    const Node& nd = tr.frontier[(size_t)i];
+                    const int g = gidx(nd);
+                    need_order(g, nd);
+                    node_av(g, nd);
                     std::map<double, int> ranked;
                     for (int ti : orders[(size_t)g].split_order) ranked[av[(size_t)ti]] = ti;
                     std::vector<int> top;
@@ -801,17 +894,21 @@ private:
         for (auto& as : attrs_) lut_w = std::max(lut_w, as.n_bins);
         std::vector<int32_t> node_attr((size_t)NF, -1);
         std::vector<uint16_t> child_lut((size_t)NF * lut_w, (uint16_t)AVT_NODE_NONE);
+        std::vector<int> next_id((size_t)n_layers, 0);   // next free node id of every existing layer
+        struct Spawn { int layer, parent_layer, parent_id, attr, lo, hi; };
+        std::vector<Spawn> spawns;                        // children that overlap a sibling: a layer of their own
+        std::vector<int> new_layer_tree = layer_tree_;
         bool any = false;
         for (int t = 0; t < num_trees_; ++t) {
             Tree& tr = trees_[(size_t)t];
             std::vector<int> live;
             for (size_t i = 0; i < tr.frontier.size(); ++i)
-                if (chosen[(size_t)(base[(size_t)t] + (int)i)] >= 0) live.push_back((int)i);
+                if (chosen[(size_t)gidx(tr.frontier[i])] >= 0) live.push_back((int)i);
             std::vector<Node> next;
             std::vector<DecPath>& out_list = lists[(size_t)t];
             for (int i : parent_order(tr, live)) {
-                const int g = base[(size_t)t] + i;
                 const Node& nd = tr.frontier[(size_t)i];
+                const int g = gidx(nd);
                 const int ti = chosen[(size_t)g];
                 const avt_split& ds = table_.splits[(size_t)ti];
                 const AttrSplits& as = attrs_[(size_t)ds.attr];
@@ -842,6 +939,18 @@ private:
                     need_order(g, nd);
                     segs = orders[(size_t)g].seg_order_by_split[(size_t)ti];
                 }
+                // which children stay in the parent's layer: greedily, in predicate order, those whose bins are still free
+                std::vector<char> bin_taken((size_t)as.n_bins, 0);
+                std::vector<char> in_parent_layer((size_t)hs.n_seg, 0);
+                for (int sg = 0; sg < hs.n_seg; ++sg) {
+                    if (!seg_n[(size_t)sg]) continue;
+                    bool free = true;
+                    for (int b = 0; b < as.n_bins && free; ++b) free = !(split_bin_in_segment(as, hs, b, sg) && bin_taken[(size_t)b]);
+                    if (!free) continue;
+                    in_parent_layer[(size_t)sg] = 1;
+                    for (int b = 0; b < as.n_bins; ++b)
+                        if (split_bin_in_segment(as, hs, b, sg)) bin_taken[(size_t)b] = 1;
+                }
                 // parent predicates (tree/DecisionPathList.java:454-472)
                 std::vector<PathPred> parent_preds;
                 for (auto& it : nd.tagged) {
@@ -866,10 +975,21 @@ private:
                     ch.tagged = nd.tagged;
                     ch.tagged.push_back(std::to_string(split_id) + ":" + hs.pred_str[(size_t)sg]);
                     ch.path = d;
-                    if (next.size() >= AVT_NODE_NONE - 1) throw Unsupported("more than 65534 frontier nodes in one tree");
-                    const uint16_t child_id = (uint16_t)next.size();
-                    for (int b = 0; b < as.n_bins; ++b)
-                        if (split_segment_of_bin(as, hs, b) == sg) child_lut[(size_t)g * lut_w + b] = child_id;
+                    if (in_parent_layer[(size_t)sg]) {
+                        ch.layer = nd.layer;
+                        ch.id = next_id[(size_t)nd.layer]++;
+                        if (ch.id >= (int)AVT_NODE_NONE - 1) throw Unsupported("more than 65534 frontier nodes in one tree");
+                        for (int b = 0; b < as.n_bins; ++b)
+                            if (split_bin_in_segment(as, hs, b, sg)) child_lut[(size_t)g * lut_w + b] = (uint16_t)ch.id;
+                    } else {
+                        ch.layer = (int)new_layer_tree.size();
+                        ch.id = 0;
+                        new_layer_tree.push_back(t);
+                        int lo = as.n_bins, hi = -1;
+                        for (int b = 0; b < as.n_bins; ++b)
+                            if (split_bin_in_segment(as, hs, b, sg)) { lo = std::min(lo, b); hi = std::max(hi, b); }
+                        spawns.push_back({ch.layer, nd.layer, nd.id, ds.attr, lo, hi});
+                    }
                     next.push_back(ch);
                     out_list.push_back(d);
                 }
@@ -878,7 +998,43 @@ private:
             any = any || !next.empty();
             tr.frontier.swap(next);
         }
+        // rows of the spawned children: members of the parent node (ids BEFORE the repartition) whose bin is in the child's range
+        std::vector<std::vector<uint16_t>> spawn_nid;
+        if (!spawns.empty()) {
+            std::map<int, std::vector<uint16_t>> parent_nid;
+            for (auto& sp : spawns)
+                if (!parent_nid.count(sp.parent_layer)) {
+                    auto& v = parent_nid[sp.parent_layer];
+                    v.resize(rows_.size());
+                    eng_->check(avt_forest_node_ids(eng_->raw(), sp.parent_layer, v.data()));
+                }
+            for (auto& sp : spawns) {
+                const auto& pn = parent_nid[sp.parent_layer];
+                std::vector<uint16_t> v(rows_.size(), (uint16_t)AVT_NODE_NONE);
+                const bool wide = attrs_[(size_t)sp.attr].n_bins > 256;
+                for (size_t r = 0; r < rows_.size(); ++r) {
+                    if (pn[r] != (uint16_t)sp.parent_id) continue;
+                    const int b = wide ? col16_[(size_t)sp.attr][r] : col8_[(size_t)sp.attr][r];
+                    if (b >= sp.lo && b <= sp.hi) v[r] = 0;
+                }
+                spawn_nid.push_back(std::move(v));
+            }
+        }
         eng_->check(avt_level_repartition(eng_->raw(), node_attr.data(), child_lut.data(), lut_w));
+        if (!spawns.empty()) {
+            // the forest grows by the new layers: existing layers keep their (repartitioned) node ids
+            std::vector<std::vector<uint16_t>> old_nid((size_t)n_layers, std::vector<uint16_t>(rows_.size()));
+            for (int l = 0; l < n_layers; ++l) eng_->check(avt_forest_node_ids(eng_->raw(), l, old_nid[(size_t)l].data()));
+            layer_tree_ = new_layer_tree;
+            std::vector<const uint16_t*> np;
+            std::vector<const uint8_t*> wp;
+            for (int l = 0; l < (int)layer_tree_.size(); ++l) {
+                np.push_back(l < n_layers ? old_nid[(size_t)l].data() : spawn_nid[(size_t)(l - n_layers)].data());
+                const Tree& tr = trees_[(size_t)layer_tree_[(size_t)l]];
+                wp.push_back(tr.weights.empty() ? nullptr : tr.weights.data());
+            }
+            eng_->check(avt_forest_init(eng_->raw(), (int32_t)layer_tree_.size(), wp.data(), np.data()));
+        }
         return any;
     }
 
@@ -925,16 +1081,28 @@ private:
     // pass's mapper would keep, tree/DecisionTreeBuilder.java:279-292), in
     // reducer key order.
     void write_level_data() {
-        std::vector<uint16_t> nid(rows_.size());
+        std::vector<std::vector<uint16_t>> nid(layer_tree_.size());
         for (int t = 0; t < num_trees_; ++t) {
             const Tree& tr = trees_[(size_t)t];
-            eng_->check(avt_forest_node_ids(eng_->raw(), t, nid.data()));
             std::vector<int> order(tr.frontier.size());
             for (size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
             std::sort(order.begin(), order.end(), [&](int x, int y) { return tr.frontier[(size_t)x].tagged < tr.frontier[(size_t)y].tagged; });
+            // rows of every frontier node: its layer's node ids
+            std::map<std::pair<int, int>, int> node_of;   // (layer, id) -> index in the frontier
+            for (size_t i = 0; i < tr.frontier.size(); ++i) node_of[{tr.frontier[i].layer, tr.frontier[i].id}] = (int)i;
             std::vector<std::vector<size_t>> rows_of(tr.frontier.size());
-            for (size_t r = 0; r < rows_.size(); ++r)
-                if (nid[r] != AVT_NODE_NONE && nid[r] < tr.frontier.size()) rows_of[nid[r]].push_back(r);
+            for (size_t l = 0; l < layer_tree_.size(); ++l) {
+                if (layer_tree_[l] != t) continue;
+                nid[l].resize(rows_.size());
+                eng_->check(avt_forest_node_ids(eng_->raw(), (int32_t)l, nid[l].data()));
+                for (size_t r = 0; r < rows_.size(); ++r) {
+                    if (nid[l][r] == AVT_NODE_NONE) continue;
+                    auto it = node_of.find({(int)l, (int)nid[l][r]});
+                    if (it != node_of.end()) rows_of[(size_t)it->second].push_back(r);
+                }
+                nid[l].clear();
+                nid[l].shrink_to_fit();
+            }
             std::vector<std::string> out;
             for (int i : order) {
                 const std::string key = join_str(tr.frontier[(size_t)i].tagged, path_delim_);

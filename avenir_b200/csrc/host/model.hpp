@@ -3,6 +3,7 @@
 // device layout.  Stand-ins for chombo's FeatureSchema/FeatureField/Utility follow SURVEY App. D.
 #pragma once
 #include <algorithm>
+#include <functional>
 #include <cstdint>
 #include <fstream>
 #include <map>
@@ -159,6 +160,8 @@ struct Schema {
 struct HostSplit {
     int n_seg = 2;
     std::vector<int> bounds;                       // numeric: inclusive upper bin of segments 0..n_seg-2
+    std::vector<std::pair<int, int>> ranges;       // DecisionTreeBuilder multi-way numeric (maxSplit > 2): inclusive bin range of every
+                                                   // predicate; ranges may overlap (tree/SplitManager.java:635-694)
     std::vector<uint8_t> lut;                      // categorical: segment of each bin
     std::vector<std::string> pred_str;             // DecisionTreeBuilder: predicate string per segment
     std::string key;                               // ClassPartitionGenerator: split key
@@ -254,6 +257,53 @@ inline std::vector<uint8_t> groups_to_lut(const Field& f, const CatSplit& groups
     return lut;
 }
 
+// createIntPartitions / createDoublePartitions + createIntAttrPredicates / createDoubleAttrPredicates
+// (tree/SplitManager.java:288-330, 366-399, 635-694): every increasing tuple of up to `max_points` grid points in DFS order
+// ([p0], [p0,p1], ..., [p1], ...), and its predicates.  One point: `le p`, `gt p`.  Several points, int: `le p0`,
+// `le p_i p_{i-1}` (lower bound p_{i-1}) for the middle points, then `le p_last` WITHOUT a lower bound, `gt p_last`; double: the
+// four-argument DoublePredicate constructor never stores the other bound (:840-843), so every `le` is unbounded and prints
+// without it.  Bins: value <= p_k  <=>  bin <= k.
+inline void numeric_split_lists(AttrSplits& as, const std::string& ord, const std::vector<std::string>& pts, int max_points, bool dbl) {
+    const int K = (int)pts.size(), B = K + 1;
+    std::vector<int> cur;
+    std::function<void(int)> rec = [&](int first) {
+        for (int k = first; k < K; ++k) {
+            cur.push_back(k);
+            HostSplit h;
+            for (int i : cur) h.points.push_back(pts[(size_t)i]);
+            const int m = (int)cur.size();
+            if (m == 1) {
+                h.n_seg = 2;
+                h.bounds = {k};
+                h.pred_str = {ord + " le " + pts[(size_t)k], ord + " gt " + pts[(size_t)k]};
+            } else {
+                h.n_seg = m + 1;
+                for (int i = 0; i < m; ++i) {
+                    const int pi = cur[(size_t)i];
+                    if (i == m - 1) {
+                        h.pred_str.push_back(ord + " le " + pts[(size_t)pi]);
+                        h.ranges.emplace_back(0, pi);
+                        h.pred_str.push_back(ord + " gt " + pts[(size_t)pi]);
+                        h.ranges.emplace_back(pi + 1, B - 1);
+                    } else if (i == 0) {
+                        h.pred_str.push_back(ord + " le " + pts[(size_t)pi]);
+                        h.ranges.emplace_back(0, pi);
+                    } else {
+                        // int: `attr le p_i p_{i-1}`; double: otherBound is never stored, so neither evaluate() nor toString() sees it
+                        h.pred_str.push_back(dbl ? ord + " le " + pts[(size_t)pi] : ord + " le " + pts[(size_t)pi] + " " + pts[(size_t)cur[(size_t)i - 1]]);
+                        h.ranges.emplace_back(dbl ? 0 : cur[(size_t)i - 1] + 1, pi);
+                    }
+                }
+            }
+            as.splits.push_back(h);
+            if (as.splits.size() > 4000000) throw Unsupported("numeric split enumeration exceeds 4M candidates");
+            if (m < max_points) rec(k + 1);
+            cur.pop_back();
+        }
+    };
+    rec(0);
+}
+
 // DecisionTreeBuilder candidate splits of one attribute (tree/SplitManager.java:256-445, 635-694).
 inline AttrSplits dtb_attr_splits(const Field& f) {
     AttrSplits as;
@@ -263,9 +313,7 @@ inline AttrSplits dtb_attr_splits(const Field& f) {
     if (f.is_int() || f.is_double()) {
         as.numeric = true;
         as.dbl = f.is_double();
-        if (f.max_split > 2)
-            throw Unsupported("attribute " + ord + ": maxSplit " + std::to_string(f.max_split) +
-                              " > 2 (multi-way numeric splits have overlapping predicates in the reference, SURVEY App. B-1/B-2; not implemented)");
+        if (f.max_split - 1 > AVT_MAX_SEG - 2) throw Unsupported("attribute " + ord + ": maxSplit above " + std::to_string(AVT_MAX_SEG - 1));
         double itv = f.split_scan_interval;
         if (java_int_cast((f.max - f.min) / itv) == 0) itv = (f.max - f.min) / 2;
         if (f.is_int()) {
@@ -277,15 +325,10 @@ inline AttrSplits dtb_attr_splits(const Field& f) {
                 sp = nx;
                 if (as.int_points.size() > 65534) throw Unsupported("attribute " + ord + ": more than 65534 split points");
             }
-            for (size_t k = 0; k < as.int_points.size(); ++k) {
-                HostSplit h;
-                h.bounds = {(int)k};
-                std::string p = std::to_string(as.int_points[k]);
-                h.points = {p};
-                h.pred_str = {ord + " le " + p, ord + " gt " + p};
-                as.splits.push_back(h);
-            }
             as.n_bins = (int)as.int_points.size() + 1;
+            std::vector<std::string> pts;
+            for (long long v : as.int_points) pts.push_back(std::to_string(v));
+            numeric_split_lists(as, ord, pts, std::max(f.max_split, 2) - 1, false);
         } else {
             double sp = f.min + itv;
             while (sp < f.max) {
@@ -295,20 +338,13 @@ inline AttrSplits dtb_attr_splits(const Field& f) {
                 sp = nx;
                 if (as.dbl_points.size() > 65534) throw Unsupported("attribute " + ord + ": more than 65534 split points");
             }
-            for (size_t k = 0; k < as.dbl_points.size(); ++k) {
-                HostSplit h;
-                h.bounds = {(int)k};
-                std::string p = java_double_to_string(as.dbl_points[k]);
-                h.points = {p};
-                h.pred_str = {ord + " le " + p, ord + " gt " + p};
-                as.splits.push_back(h);
-            }
             as.n_bins = (int)as.dbl_points.size() + 1;
+            std::vector<std::string> pts;
+            for (double v : as.dbl_points) pts.push_back(java_double_to_string(v));
+            numeric_split_lists(as, ord, pts, std::max(f.max_split, 2) - 1, true);
         }
     } else if (f.is_categorical()) {
-        if (f.max_split > 2)
-            throw Unsupported("attribute " + ord + ": maxSplit " + std::to_string(f.max_split) +
-                              " > 2 (identical predicate strings recur across splits and duplicate rows in the reference, SURVEY App. B-2; not implemented)");
+        if (f.max_split > AVT_MAX_SEG) throw Unsupported("attribute " + ord + ": maxSplit above " + std::to_string(AVT_MAX_SEG));
         if (f.cardinality.empty()) throw ReferenceError("attribute " + ord + ": categorical attribute without cardinality");
         as.n_bins = (int)f.cardinality.size();
         for (int gr = 2; gr <= f.max_split; ++gr) {
@@ -458,7 +494,11 @@ inline DeviceSplitTable flatten_splits(const std::vector<AttrSplits>& attrs) {
             avt_split s;
             s.attr = (int)a;
             s.n_seg = h.n_seg;
-            if (attrs[a].numeric) {
+            if (!h.ranges.empty()) {
+                s.kind = AVT_SPLIT_RANGES;
+                s.off = (int)t.bounds.size();
+                for (auto& r : h.ranges) { t.bounds.push_back(r.first); t.bounds.push_back(r.second); }
+            } else if (attrs[a].numeric) {
                 s.kind = AVT_SPLIT_NUMERIC;
                 s.off = (int)t.bounds.size();
                 for (int b : h.bounds) t.bounds.push_back(b);
@@ -474,14 +514,27 @@ inline DeviceSplitTable flatten_splits(const std::vector<AttrSplits>& attrs) {
     return t;
 }
 
-// segment a bin falls in for a host split (mirror of the device rule)
+// does the bin fall in segment `sg` of the split (segments of a multi-way numeric split may overlap)
+inline bool split_bin_in_segment(const AttrSplits& as, const HostSplit& h, int bin, int sg);
+
+// segment a bin falls in for a host split (mirror of the device rule); for overlapping ranges: the first one
 inline int split_segment_of_bin(const AttrSplits& as, const HostSplit& h, int bin) {
+    if (!h.ranges.empty()) {
+        for (int sg = 0; sg < (int)h.ranges.size(); ++sg)
+            if (bin >= h.ranges[(size_t)sg].first && bin <= h.ranges[(size_t)sg].second) return sg;
+        return -1;
+    }
     if (as.numeric) {
         int j = 0;
         while (j < (int)h.bounds.size() && bin > h.bounds[(size_t)j]) ++j;
         return j;
     }
     return h.lut[(size_t)bin] == 0xFF ? -1 : h.lut[(size_t)bin];
+}
+
+inline bool split_bin_in_segment(const AttrSplits& as, const HostSplit& h, int bin, int sg) {
+    if (!h.ranges.empty()) return bin >= h.ranges[(size_t)sg].first && bin <= h.ranges[(size_t)sg].second;
+    return split_segment_of_bin(as, h, bin) == sg;
 }
 
 }  // namespace avt_host

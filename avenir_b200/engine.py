@@ -9,7 +9,7 @@ from typing import List, Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import (AVT_MAX_CLASSES, AVT_MAX_SEG, AVT_NODE_NONE, CRIT_ENTROPY, CRIT_GINI, SPLIT_LUT, SPLIT_NUMERIC,
+from ._lib import (AVT_MAX_CLASSES, AVT_MAX_SEG, AVT_NODE_NONE, CRIT_ENTROPY, CRIT_GINI, SPLIT_LUT, SPLIT_NUMERIC, SPLIT_RANGES,
                    CpgStat, NodeBest, Split, SplitEval, Stats)
 
 
@@ -50,6 +50,13 @@ class SplitTable:
         self.attr.append(attr); self.kind.append(SPLIT_LUT)
         self.n_seg.append(max(2, (max(seg_of_bin) + 1) if n_seg is None else n_seg))
         self.off.append(len(self.lut)); self.lut.extend(int(s) for s in seg_of_bin)
+
+    def add_ranges(self, attr: int, ranges: Sequence[Sequence[int]]):
+        """Segments as inclusive bin ranges (lo, hi) that may overlap (the reference's multi-way numeric predicates)."""
+        self.attr.append(attr); self.kind.append(SPLIT_RANGES); self.n_seg.append(len(ranges))
+        self.off.append(len(self.bounds))
+        for lo, hi in ranges:
+            self.bounds.extend([int(lo), int(hi)])
 
     def __len__(self):
         return len(self.attr)
@@ -244,7 +251,7 @@ class Engine:
         for i in range(n):
             arr[i] = Split(t.attr[i], t.kind[i], t.n_seg[i], t.off[i])
         b = np.asarray(t.bounds if t.bounds else [0], dtype=np.int32)
-        l = np.asarray(t.lut if t.lut else [0], dtype=np.uint8)
+        l = np.asarray(t.lut if len(t.lut) else [0], dtype=np.uint8)
         self._check(self.lib.avt_split_table_set(self.h, n, arr, b.ctypes.data_as(C.POINTER(C.c_int32)), len(t.bounds), _ptr(l), len(t.lut)))
         self.n_splits = n
 

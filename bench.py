@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- split-evaluation throughput of the tree-building hot path (BASELINE.json metric).
 
-    python bench.py [--workload c3|c2] [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--workload c3|c2|c5|c4|c1] [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
                     [--rows R] [--trees T] [--levels L] [--no-verify] [--no-cpu-baseline]
 
 Headline workload (default, the configuration BASELINE.json's metric and north_star's targets are quoted on): C3 --
@@ -13,7 +13,8 @@ histograms are summed over NVLink (peer memory inside the scan kernel when they 
 all-reduce).  Columns are generated in device memory (counter-based splitmix64, avenir_b200/synth.py) -- nothing of this
 size is built on the host.  A "step" grows the whole forest once: 6 x (fused repartition + histogram -> gini scan/arg-min
 + children statistics + level planning), all trees of a level in one launch.  `--workload c2` is the round-1 line (call_hangup tree,
-10 M rows per GPU, entropy, 8 expansions, weak scaling).
+10 M rows per GPU, entropy, 8 expansions, weak scaling); `--workload c5|c4|c1` are the other BASELINE.json configs as one-GPU lines
+(bench_extra.py: wide 512-attribute schema, ClassPartitionGenerator sweep, the tutorial through the reference-named tool).
 
   verify  (default on) BEFORE the timed region the parity subset of SURVEY 8(d) -- 5 trees over the first 1 M rows, same knobs,
           sharded over the same ranks through the same exchange -- is grown and compared with the C oracle on every rank:
@@ -308,7 +309,7 @@ def run_c2(args):
             "gpu_launches": int((st.hist_launches + st.scan_launches + st.eval_launches + st.repart_launches) * args.steps // prof_steps),
             "e2e": {"value": world * N * L / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(sum(c.nbytes for c in cols_p) + cls_p.nbytes), "d2h_bytes_per_step": int(nid.nbytes)},
-            "roofline": {"bound": "hbm", "kernel": "hist_smem_kernel" if st.last_hist_variant == 0 else "hist_global_kernel",
+            "roofline": {"bound": "hbm", "kernel": {0: "hist_smem_kernel", 1: "hist_global_kernel", 2: "hist_forest_kernel", 3: "hist_joint_kernel"}.get(st.last_hist_variant, "?"),
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                          "frac_of_spec_8000": achieved / 8000.0, "traffic": traffic,
                          "alg_bytes_per_launch": alg_bytes_per_launch, "ms_per_launch": hist_ms_per_launch,
@@ -579,7 +580,7 @@ def run_c3(args):
             "e2e": {"value": N_total * L * T / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(sum(c.nbytes for c in cols_p) + cls_p.nbytes),
                     "d2h_bytes_per_step": int(nrec * C.sizeof(_lib.GrowRecord))},
-            "roofline": {"bound": "hbm", "kernel": {0: "hist_smem_kernel", 1: "hist_global_kernel", 2: "hist_forest_kernel"}.get(st.last_hist_variant, "?"),
+            "roofline": {"bound": "hbm", "kernel": {0: "hist_smem_kernel", 1: "hist_global_kernel", 2: "hist_forest_kernel", 3: "hist_joint_kernel"}.get(st.last_hist_variant, "?"),
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                          "frac_of_spec_8000": achieved / 8000.0, "traffic": traffic, "traffic_source": traffic_src,
                          "alg_bytes_per_launch": alg_bytes_per_launch, "ms_per_launch": hist_ms_per_launch,
@@ -605,7 +606,7 @@ def run_c3(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--workload", default="c3", choices=["c3", "c2"])
+    ap.add_argument("--workload", default="c3", choices=["c3", "c2", "c5", "c4", "c1"])
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
@@ -618,6 +619,14 @@ def main():
     args = ap.parse_args()
     if args.workload == "c2":
         return run_c2(args)
+    if args.workload in ("c5", "c4", "c1"):
+        # secondary lines (one GPU): bench_extra.py
+        if int(os.environ.get("WORLD_SIZE", "1")) > 1 or args.impl == "reference":
+            raise SystemExit(f"bench.py --workload {args.workload} is a one-GPU line of our arm only; the scaling runs and the reference arm use c3 (default) or c2")
+        import bench_extra
+        line = getattr(bench_extra, "run_" + args.workload)(args, ClockSampler, measured_peak)
+        print(json.dumps(line))
+        return 0
     return run_c3(args)
 
 

@@ -53,6 +53,9 @@ extern "C" {
 
 #define AVT_SPLIT_NUMERIC 0 /* segments are contiguous bin ranges given by upper bounds */
 #define AVT_SPLIT_LUT 1     /* segments given by a per-bin uint8 segment table */
+#define AVT_SPLIT_RANGES 2  /* segments are inclusive bin ranges [lo, hi] that MAY OVERLAP: the reference's multi-way numeric
+                               splits (maxSplit > 2), whose last `le` predicate has no lower bound (tree/SplitManager.java:635-661)
+                               and whose double twins drop every lower bound (:668-694, 840-843); SURVEY App. B-1 */
 
 typedef struct avt_engine avt_engine;
 
@@ -65,7 +68,10 @@ typedef struct avt_split {
     int32_t kind;  /* AVT_SPLIT_NUMERIC | AVT_SPLIT_LUT */
     int32_t n_seg; /* number of segments, 2..AVT_MAX_SEG */
     int32_t off;   /* NUMERIC: index into `bounds` of n_seg-1 inclusive upper bin bounds;
-                      LUT:     index into `seg_lut` of n_bins[attr] segment ids */
+                      LUT:     index into `seg_lut` of n_bins[attr] segment ids;
+                      RANGES:  index into `bounds` of n_seg (lo, hi) pairs, hi < lo = empty segment.  Scan, eval and the
+                               CPG sweep count a row once per segment it falls in; avt_grow_levels rejects tables with
+                               RANGES splits (a row can have several children: the caller places them) */
 } avt_split;
 
 /* Result of the fused impurity scan for one frontier node. */
@@ -96,7 +102,7 @@ typedef struct avt_stats {
     int64_t hist_launches, scan_launches, eval_launches, repart_launches, comm_calls;
     int64_t hist_alg_bytes; /* algorithmic bytes of all histogram passes so far */
     int64_t repart_alg_bytes;
-    int32_t last_hist_variant; /* 0 shared-memory privatised (lane = row), 1 global atomics (match_any), 2 forest kernel (lane = attribute) */
+    int32_t last_hist_variant; /* 0 shared-memory privatised (lane = row), 1 global atomics (match_any), 2 forest kernel (lane = attribute), 3 joint-code kernel (packed narrow schemas) */
     int32_t last_hist_replicas;
     int32_t last_hist_grid, last_hist_block, last_hist_smem;
     int32_t reserved0;
@@ -318,7 +324,7 @@ int avt_reset_stats(avt_engine* e);
  * the launches of a level loop). */
 int avt_set_profiling(avt_engine* e, int32_t on);
 /* Forces a histogram variant (-1 auto, 0 shared-memory by rows, 1 global atomics, 2 forest kernel: shared-memory by
- * attributes) -- for tests/profiling. */
+ * attributes, 3 joint-code kernel for packed narrow schemas) -- for tests/profiling. */
 int avt_set_hist_variant(avt_engine* e, int32_t variant);
 
 /* Allocation-free histogram.  NO COUNTERPART IN THE REFERENCE (and none in its Java object seams): it exists

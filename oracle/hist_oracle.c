@@ -237,6 +237,13 @@ static void seg_counts(const ora_split* sp, int j, int B, int C, const int32_t* 
         int hi = j == sp->n_seg - 1 ? B - 1 : bounds[sp->off + j];
         for (b = lo + 1; b <= hi; ++b)
             for (c = 0; c < C; ++c) cnt[c] += Hn[b * C + c];
+    } else if (sp->kind == 2) {
+        /* multi-way numeric predicates as inclusive bin ranges that may overlap: `le p_last` has no lower bound
+         * (tree/SplitManager.java:644-658), the double twins never have one (:677-689, 840-843) */
+        int lo = bounds[sp->off + 2 * j], hi = bounds[sp->off + 2 * j + 1];
+        if (hi > B - 1) hi = B - 1;
+        for (b = lo; b <= hi; ++b)
+            for (c = 0; c < C; ++c) cnt[c] += Hn[b * C + c];
     } else {
         /* categorical: bins whose value is in group j (tree/SplitManager.java:928-937) */
         for (b = 0; b < B; ++b)

@@ -115,7 +115,7 @@ class OracleEngine:
         for i in range(n):
             self.splits[i] = Split(t.attr[i], t.kind[i], t.n_seg[i], t.off[i])
         self.bounds = np.asarray(t.bounds if t.bounds else [0], dtype=np.int32)
-        self.lut = np.asarray(t.lut if t.lut else [0], dtype=np.uint8)
+        self.lut = np.asarray(t.lut if len(t.lut) else [0], dtype=np.uint8)
         self.n_splits = n
 
     def histogram(self, nodes_per_tree, fetch=False):

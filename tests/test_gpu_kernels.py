@@ -30,7 +30,7 @@ def random_node_ids(rng, n, n_nodes, p_none=0.1):
 
 
 @pytest.mark.parametrize("n", [1, 15, 16, 17, 8191, 8193, 100003])
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, 3])
 def test_histogram_ragged_sizes(n, variant):
     rng = np.random.default_rng(n)
     n_bins = [2, 4, 2, 10]
@@ -61,6 +61,24 @@ def test_histogram_forest_weights_wide_codes(variant):
     hg = g.histogram([3, 1, 6], fetch=True)
     ho = o.histogram([3, 1, 6], fetch=True)
     assert np.array_equal(hg, ho)
+
+
+@pytest.mark.parametrize("n_bins,n_classes", [([2, 4, 2, 10], 2), ([3, 5, 7], 3), ([200], 4), ([2, 2, 2, 2], 2), ([16, 9], 5)])
+def test_joint_code_histogram_forest_and_weights(n_bins, n_classes):
+    """hist_joint_kernel (one counter space per node indexed by the packed byte, marginals at flush): several trees, one of them
+    unweighted, many nodes, rows outside the frontier, schemas whose highest field is not a power of two."""
+    n = 70_019
+    rng = np.random.default_rng(len(n_bins) * 100 + n_classes)
+    cols, cls = synth.binned_dataset(n, n_bins, n_classes, seed=21)
+    table = binary_split_table(n_bins, [False] * len(n_bins))
+    weights = [rng.poisson(1.0, n).clip(0, 255).astype(np.uint8), None, rng.poisson(1.0, n).clip(0, 255).astype(np.uint8)]
+    nids = [random_node_ids(rng, n, k) for k in (7, 1, 20)]
+    g, o = make_pair(cols, cls, n_bins, n_classes, table, 3, weights, nids)
+    g.set_hist_variant(3)
+    hg = g.histogram([7, 1, 20], fetch=True)
+    assert g.stats().last_hist_variant == 3
+    assert np.array_equal(hg, o.histogram([7, 1, 20], fetch=True))
+    g.close()
 
 
 def test_histogram_many_nodes_uses_fewer_replicas_then_global():

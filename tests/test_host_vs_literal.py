@@ -84,6 +84,71 @@ def test_stopping_strategies_and_support(hostmock, tmp_path, stop, key, val):
     assert any(p["stopped"] for p in got[-1]["decisionPaths"]) and any(not p["stopped"] for p in got[-1]["decisionPaths"])
 
 
+def multiway_schema(int_max_split=3, cat_max_split=2, interval=120):
+    d = json.load(open(os.path.join(helpers.SCHEMA_DIR, "schemas.json")))["call_hangup.json"]
+    d = json.loads(json.dumps(d))
+    for f in d["fields"]:
+        if f.get("ordinal") == 5:
+            f["maxSplit"] = int_max_split
+            f["splitScanInterval"] = interval
+        if f.get("ordinal") == 3:
+            f["maxSplit"] = cat_max_split
+    return d
+
+
+@pytest.mark.parametrize("n,levels,strategy,alg,ims,cms,itv", [
+    (700, 2, "all", "giniIndex", 3, 2, 120),          # int attribute with 1- and 2-point splits: `le p_last` overlaps `le p0`
+    (500, 3, "notUsedYet", "entropy", 3, 3, 120),     # + 3-group categorical partitions (predicate strings recur across splits)
+    (400, 3, "all", "entropy", 4, 2, 150),            # up to 3 points: a middle predicate with both bounds
+    (300, 2, "all", "giniIndex", 2, 3, 60),           # categorical multi-way only
+])
+def test_multiway_splits_equal_literal(hostmock, tmp_path, n, levels, strategy, alg, ims, cms, itv):
+    """maxSplit > 2 (App. B-1/B-2): overlapping numeric predicates (a row sits in several children),
+    predicate strings shared by several candidate splits, weighted sums in HashMap order -- every level's list equals
+    the literal restatement, which emits one record per (row, split, true predicate) like the reference."""
+    schema = multiway_schema(ims, cms, itv)
+    conf = dict(BASE, **{"dtb.split.attribute.selection.strategy": strategy, "dtb.split.algorithm": alg, "dtb.max.depth.limit": "3"})
+    got, want = run_dtb_both(hostmock, str(tmp_path), synth.call_hangup_csv(n), schema, conf, levels)
+    assert got == want
+    assert any(len(p["predicates"]) > 1 and any(q["otherBoundInt"] is not None or q["predicateStr"].count(" ") == 2 for q in p["predicates"][1:])
+               for lvl in got[1:] for p in lvl["decisionPaths"])
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_selected_multiway_splits_put_rows_in_several_children(hostmock, tmp_path, seed):
+    """randomAmongTop over the five best splits picks multi-way ones: `5 le 360` and `5 le 480` are siblings and share rows
+    (device layers), three-group categorical partitions; the next levels grow from those children."""
+    schema = multiway_schema(3, 3, 120)
+    conf = dict(BASE, **{"dtb.split.attribute.selection.strategy": "all", "dtb.split.algorithm": "giniIndex", "dtb.max.depth.limit": "3",
+                         "dtb.split.select.strategy": "randomAmongTop", "dtb.top.split.count": "5", "avt.random.seed": str(seed)})
+    got, want = run_dtb_both(hostmock, str(tmp_path), synth.call_hangup_csv(500), schema, conf, 3)
+    assert got == want
+    if seed == 3:   # 27 rows with hold <= 360 are also among the 100 with hold <= 480
+        pops = {";".join(q["predicateStr"] for q in p["predicates"][1:]): p["population"] for p in got[2]["decisionPaths"]}
+        assert pops["3 in internet;5 le 360"] + pops["3 in internet;5 gt 480"] < 151 < sum(v for k, v in pops.items() if k.startswith("3 in internet"))
+
+
+def test_multiway_double_attribute_every_le_is_unbounded(hostmock, tmp_path):
+    """DoublePredicate's four-argument constructor never stores the other bound (tree/SplitManager.java:840-843): every
+    `le` of a multi-point double split is cumulative and prints without the bound."""
+    rng = random.Random(77)
+    fields = [{"name": "id", "ordinal": 0, "id": True, "dataType": "string"},
+              {"name": "x", "ordinal": 1, "dataType": "double", "feature": True, "min": 0.0, "max": 1.0, "splitScanInterval": 0.2, "maxSplit": 4},
+              {"name": "k", "ordinal": 2, "dataType": "categorical", "feature": True, "maxSplit": 2, "cardinality": ["p", "q", "r"]},
+              {"name": "cls", "ordinal": 3, "dataType": "categorical"}]
+    rows = []
+    for i in range(400):
+        x = round(rng.random(), 3)
+        k = rng.choice("pqr")
+        c = "Y" if (0.25 < x < 0.7) != (rng.random() < 0.2) else "N"
+        rows.append(f"r{i},{x!r},{k},{c}")
+    for sel, seed in (("best", 0), ("randomAmongTop", 4), ("randomAmongTop", 9)):
+        conf = dict(BASE, **{"dtb.split.attribute.selection.strategy": "all", "dtb.split.algorithm": "entropy", "dtb.max.depth.limit": "3",
+                             "dtb.split.select.strategy": sel, "dtb.top.split.count": "6", "avt.random.seed": str(seed)})
+        got, want = run_dtb_both(hostmock, str(tmp_path / f"{sel}{seed}"), rows, {"fields": fields}, conf, 2)
+        assert got == want
+
+
 def random_schema_and_rows(rng, n_rows):
     """Small random schema: categorical attrs (2..5 levels), int attrs and a double attr, 2..4 classes."""
     fields = [{"name": "id", "ordinal": 0, "id": True, "dataType": "string"}]
