@@ -104,7 +104,6 @@ struct avt_engine {
     DevBuf<uint8_t> d_rowrot;
     long long rowrot_rows = 0;
     bool rowrot_ok = false;
-    bool forest_rot = true;   // AVT_FOREST_ROT=0: the list-based hist_forest_kernel instead of hist_rot_kernel (A/B measurements)
     uint32_t pk_shift[4] = {0, 0, 0, 0}, pk_mask4[4] = {0, 0, 0, 0};
     // item-parallel scan (avt_scan_fast.cuh): (split, segment) items, first item of every split, per-node child counts
     DevBuf<uint32_t> d_items;
@@ -117,6 +116,7 @@ struct avt_engine {
     DevBuf<double> d_av;
     DevBuf<avt_node_best> d_best;
     DevBuf<uint32_t> d_mask;
+    DevBuf<uint16_t> d_lut2;       // level loop: packed byte -> child rows (joint-code histogram kernel)
     DevBuf<uint32_t> d_cand[2];    // level loop: candidate attribute sets of the current / next frontier (ping-pong by level)
     DevBuf<uint8_t> d_order;
     DevBuf<int32_t> d_pairs;
@@ -156,6 +156,7 @@ struct avt_engine {
     uint8_t order_cached[AVT_MAX_CLASSES];
     int order_cached_n = -1;        // classes covered by order_cached (-1: nothing uploaded yet)
     bool hist_pack = true;    // AVT_HIST_PACK=0: never use the bit-packed copy of the codes
+    bool hist_joint = true;   // AVT_HIST_JOINT=0: hist_smem_kernel instead of the joint-code kernel on packed schemas (A/B measurements)
     bool lookback = true;     // AVT_LOOKBACK=0: the last scan block plans the level (ticket) even for small frontiers
     bool peer_trailing_round = false;   // AVT_PEER_TRAIL=1: end every level loop with a round of flags over all ranks
     bool scan_fast = true;    // AVT_SCAN_FAST=0: always the general scan kernel in the level loop
@@ -351,9 +352,7 @@ int avt_create(int device, avt_engine** out) {
             if (st == cudaSuccess) st = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
     }
     {
-        const void* kernels[] = {(const void*)hist_forest_kernel<false, false>, (const void*)hist_forest_kernel<false, true>,
-                                 (const void*)hist_forest_kernel<true, false>, (const void*)hist_forest_kernel<true, true>,
-                                 (const void*)hist_rot_kernel<false, false>, (const void*)hist_rot_kernel<false, true>,
+        const void* kernels[] = {(const void*)hist_rot_kernel<false, false>, (const void*)hist_rot_kernel<false, true>,
                                  (const void*)hist_rot_kernel<true, false>, (const void*)hist_rot_kernel<true, true>,
                                  (const void*)hist_joint_kernel<false, false>, (const void*)hist_joint_kernel<false, true>,
                                  (const void*)hist_joint_kernel<true, false>, (const void*)hist_joint_kernel<true, true>};
@@ -373,7 +372,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_PEER_TRAIL")) e->peer_trailing_round = atoi(v) != 0;
     if (const char* v = getenv("AVT_LOOKBACK")) e->lookback = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
-    if (const char* v = getenv("AVT_FOREST_ROT")) e->forest_rot = atoi(v) != 0;
+    if (const char* v = getenv("AVT_HIST_JOINT")) e->hist_joint = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract_mode = atoi(v) != 0 ? 1 : 0;
     if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
     *out = e;
@@ -404,7 +403,7 @@ void avt_destroy(avt_engine* e) {
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
     e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_pub.release(); e->d_packed.release(); e->d_rowrot.release(); e->d_av.release(); e->d_best.release();
-    e->d_mask.release(); e->d_cand[0].release(); e->d_cand[1].release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
+    e->d_mask.release(); e->d_lut2.release(); e->d_cand[0].release(); e->d_cand[1].release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release(); e->d_ctrl.release();
     if (e->h_ctrl) cudaFreeHost(e->h_ctrl);
     if (e->h_rec) cudaFreeHost(e->h_rec);
@@ -447,7 +446,7 @@ static int dataset_shape(avt_engine* e, int64_t n_rows, int32_t n_attrs, const i
     e->TB = e->bin_off[n_attrs];
     for (int a = 0; a < n_attrs; ++a) {
         const size_t w = e->wide[a] ? 2 : 1;
-        if (!e->cols[a]) CUDA_TRY(e, cudaMalloc(&e->cols[a], ((size_t)e->Npad + 32) * w));   // + one tile of slack (hist_forest_kernel reads whole 32-row tiles)
+        if (!e->cols[a]) CUDA_TRY(e, cudaMalloc(&e->cols[a], ((size_t)e->Npad + 32) * w));   // + one tile of slack (hist_rot_kernel reads whole 32-row tiles)
         CUDA_TRY(e, cudaMemsetAsync((char*)e->cols[a] + (size_t)n_rows * w, 0, (size_t)(e->Npad - n_rows) * w, e->stream));
     }
     CUDA_TRY(e, e->d_cls.ensure((size_t)e->Npad + 32));
@@ -940,6 +939,7 @@ struct FusedRepart {
     const uint16_t* child_lut;
     int lut_w;
     int prev_n_max;  // bound on the previous frontier's nodes per tree (sizes the shared-memory copy of the tables)
+    const uint16_t* lut2;  // packed byte -> child rows of the previous frontier written by its scan kernel (nullptr: none)
 };
 
 // Plans and launches kernel (a) for the frontier in e->node_base (already uploaded to d_node_base).
@@ -958,32 +958,26 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         any_wide = any_wide || e->wide[a];
     }
     int variant = (per_bin * max_bins <= kHistWordsBudget) ? 0 : 1;
-    // forest kernel (avt_forest.cuh): lane = attribute, so it wants enough attributes to fill a warp, uint8 codes, and room
-    // for at least one tree's counted nodes in shared memory
+    // forest kernel (avt_forest.cuh: hist_rot_kernel): wants the rotated row-major copy of the codes (built for data sets with >= 16
+    // uint8 attributes) and room for at least one tree's counted nodes in shared memory
     int f_slots = std::max(n_max, 1), f_G = 0;
     size_t f_smem = 0;
-    bool f_rot = false;
     {
         if (e->skip_cur) f_slots = std::max(1, n_max - n_max / std::max(2, e->g_max_splits));   // one child of every expanded parent is derived, not counted
         const size_t n_prev = fr ? (size_t)std::max(fr->prev_n_max, 1) : 0;
-        const size_t per_tree = (size_t)f_slots * e->C * max_bins * 128 + n_prev * ((size_t)(fr ? fr->lut_w : 0) * 4 + 1) + ((size_t)n_max + 2 + f_slots) * 2 + 1;
-        const size_t fixed = (size_t)kForestWarps * kForestSub * 256 + (fr ? (size_t)kForestWarps * 1024 : 0) + 64;
-        f_rot = e->forest_rot && e->rowrot_ok;
-        const size_t fixed_rot = (size_t)f_slots * 0 + (size_t)e->C * max_bins * 128 /* phantom slot */ + (fr ? (size_t)kForestWarps * 1024 : 0) + 64;
-        const size_t fx = f_rot ? fixed_rot : fixed;
-        if (!any_wide && max_bins <= 256 && per_tree + fx <= kMaxDynSmem) {
-            f_G = (int)std::min<size_t>((size_t)e->T, (kMaxDynSmem - fx) / per_tree);
-            f_smem = fx + per_tree * (size_t)f_G;
+        const size_t per_tree = (size_t)f_slots * e->C * max_bins * 128 + n_prev * ((size_t)(fr ? fr->lut_w : 0) * 4 + 2) + ((size_t)n_max + 2 + f_slots) * 2 + 1;
+        const size_t fixed = (size_t)e->C * max_bins * 128 /* phantom slot */ + (fr ? (size_t)kForestWarps * 1024 : 0) + 64;
+        if (e->rowrot_ok && max_bins <= 256 && per_tree + fixed <= kMaxDynSmem) {
+            f_G = (int)std::min<size_t>((size_t)e->T, (kMaxDynSmem - fixed) / per_tree);
+            f_smem = fixed + per_tree * (size_t)f_G;
         }
-        // hist_rot_kernel takes every forest-shaped level whose counted nodes fit; the list-based kernel (AVT_FOREST_ROT=0) only pays
-        // with >= 4 trees resident (measured on the C3 shape, profiles/)
-        if (f_G >= (f_rot ? 1 : 4) && e->A >= 16 && e->force_variant < 0 && variant == 0) variant = 2;
+        if (f_G >= 1 && e->force_variant < 0 && variant == 0) variant = 2;
     }
     // joint-code kernel (avt_joint.cuh): the data set has a packed copy (<= 4 narrow attributes in one byte) and one block can hold
     // the frontier's joint counters; it has no form for skip marks and does not signal peers itself
     int j_J = 0;
     size_t j_smem = 0;
-    if (e->packed_ok && !e->skip_cur && (!e->signal_pending || (e->peer_signal_scan && e->scan_will_signal))) {
+    if (e->packed_ok && e->hist_joint && !e->skip_cur && (!e->signal_pending || (e->peer_signal_scan && e->scan_will_signal))) {
         int maxv = 0;
         for (int a = 0; a < e->A; ++a) maxv += (e->n_bins[a] - 1) << e->pk_shift[a];
         j_J = maxv + 1;
@@ -998,7 +992,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         if (e->force_variant == 0 && variant == 1)
             return fail(e, AVT_E_INVALID, "avt_level_histogram: shared-memory variant forced but the frontier needs %lld words", per_bin * max_bins);
         if (e->force_variant == 2 && f_G == 0)
-            return fail(e, AVT_E_INVALID, "avt_level_histogram: forest variant forced but it needs uint8 codes, <= 256 bins per attribute and one tree's counters in shared memory");
+            return fail(e, AVT_E_INVALID, "avt_level_histogram: forest variant forced but it needs >= 16 attributes, uint8 codes and one tree's counters in shared memory");
         variant = e->force_variant;
     }
     uint16_t* nid_in = e->nid_cur;
@@ -1191,6 +1185,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         ja.J = j_J;
         ja.n_prev_max = fr ? std::max(fr->prev_n_max, 1) : 1;
         ja.zero_words = (std::max(n_max, 1) + 1) * j_J * e->C;
+        ja.lut2_g = fr ? fr->lut2 : nullptr;
         for (int q = 0; q < 4; ++q) {
             ja.shift[q] = e->pk_shift[q];
             ja.mask[q] = e->pk_mask4[q] & 0xFFu;
@@ -1243,10 +1238,8 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         dim3 grid((unsigned)groups, (unsigned)parts, (unsigned)achunks);
         fa.rowrot = e->d_rowrot.p;
         fa.rowrot_rows = e->rowrot_rows;
-        void (*kern)(const HistArgs, const ForestArgs) = e->any_w ? (fr ? hist_forest_kernel<true, true> : hist_forest_kernel<true, false>)
-                                                                  : (fr ? hist_forest_kernel<false, true> : hist_forest_kernel<false, false>);
-        if (f_rot)
-            kern = e->any_w ? (fr ? hist_rot_kernel<true, true> : hist_rot_kernel<true, false>) : (fr ? hist_rot_kernel<false, true> : hist_rot_kernel<false, false>);
+        void (*kern)(const HistArgs, const ForestArgs) = e->any_w ? (fr ? hist_rot_kernel<true, true> : hist_rot_kernel<true, false>)
+                                                                  : (fr ? hist_rot_kernel<false, true> : hist_rot_kernel<false, false>);
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = grid;
         cfg.blockDim = dim3(kForestThreads);
@@ -1733,6 +1726,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             planned_skip = next_plannable;
         }
         prev_peer = peer_level;
+        bool lut2_written = false;
         TimerSlot ts;
         if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
         {
@@ -1758,6 +1752,22 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
                     }
                     ft.pub = e->d_pub.p;
                     ft.epoch = ++e->scan_epoch;
+                    if (e->packed_ok && level + 1 < n_levels) {
+                        // the next pass may be the joint-code kernel: have the node blocks expand their rows to packed bytes
+                        int maxv = 0;
+                        for (int a = 0; a < e->A; ++a) maxv += (e->n_bins[a] - 1) << e->pk_shift[a];
+                        const size_t need = (size_t)kLookbackNodes * (maxv + 1);
+                        if (e->d_lut2.cap < need) {
+                            // (the table is written by this launch and read by the next pass: a reallocation here can only
+                            // happen before the first scan that uses it)
+                            if (int rc = sync_and_resolve(e)) return rc;
+                            CUDA_TRY(e, e->d_lut2.ensure(need));
+                        }
+                        pa.lut2 = e->d_lut2.p;
+                        pa.lut2_J = maxv + 1;
+                        for (int q = 0; q < 4; ++q) { pa.pk_shift[q] = e->pk_shift[q]; pa.pk_mask[q] = e->pk_mask4[q] & 0xFFu; }
+                        lut2_written = true;
+                    }
                 }
                 CUDA_TRY(e, cudaLaunchKernelEx(&cfg, scan_fast_kernel, (const uint32_t*)Hc, make_table(e), ft, (const uint8_t*)e->d_order.p, (int)criterion,
                                                (const int32_t*)(nb_level(level) + T), pa));
@@ -1782,6 +1792,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         fr.child_lut = e->d_lut.p;
         fr.lut_w = lut_w;
         fr.prev_n_max = n_max;
+        fr.lut2 = lut2_written ? e->d_lut2.p : nullptr;
         pending = true;
         last_level = level;
         for (int t = 0; t < T; ++t) ub[(size_t)t] = (int)std::min<long long>((long long)ub[(size_t)t] * g_max, (long long)AVT_NODE_NONE - 1);

@@ -1,21 +1,13 @@
-// Kernel (a) for bagged forests and wide schemas: hist_forest_kernel.
+// Kernel (a) for bagged forests and wide schemas: hist_rot_kernel (+ rowrot_kernel, which builds its input layout).
 //
 // Why a second histogram kernel: on forest shapes (C3: 100 trees x 32 attributes) hist_smem_kernel is bound by the
-// shared-memory pipe, not by HBM -- ncu shows l1tex at 99 % with 3.5-3.9 wavefronts per ATOMS (32 lanes = 32 rows hitting
-// random bins collide on banks), every tree re-reads all bin codes, and rows with multiplicity 0 (37 % of a bootstrap
-// sample) or in nodes derived by sibling subtraction still issue their updates (a partially active ATOMS runs at a
-// fraction of the full-warp rate on sm_100a, so predicating them away is slower still; tools/microbench/atoms_bench.cu).
-//
-// Here one warp instruction updates ONE row: lane = attribute, and the block's private counters are laid out
-// [tree][slot][class][bin][attribute(32)], so the bank of an update is its lane -- every ATOMS is a single conflict-free
-// wavefront -- and rows that are not counted cost no update at all (no partial warps: a row is either skipped by the
-// whole warp or updated by the whole warp).  A warp owns 32-row tiles: lane a keeps column a's 32 codes of the tile in
-// registers (pre-scaled to counter offsets) and loops over the trees resident in the block, so the codes are read once per
-// (tile, tree group) instead of once per tree; per (tile, tree) only 64 B of node ids and 32 B of multiplicities move.
-// Per tile the lanes first act as ROWS (phase A): each looks its row up in every resident tree -- node id, multiplicity,
-// the fused repartition through shared-memory copies of the previous level's tables, the counter slot of the new node --
-// and appends (counter base, multiplicity) of the live pairs to its row's list in shared memory; then as ATTRIBUTES
-// (phase B): row by row, entry by entry, one update each.  Bookkeeping is per lane and per pair; nothing is paid per dead pair.
+// shared-memory pipe, not by HBM -- ncu (profiles/hist_c3_r02_baseline_ncu.txt) shows l1tex at 99 % with 3.5-3.9 wavefronts
+// per ATOMS (32 lanes = 32 rows hitting random bins collide on banks) -- and every tree re-reads and re-unpacks all bin codes.
+// A first redesign with lane = attribute (one row per warp instruction, rows that are not counted skipped by whole warps,
+// live (row, tree) pairs handed from a per-lane "row" phase to a per-lane "attribute" phase through shared-memory lists) was
+// conflict-free too but spent 190-290 warp instructions per (32-row tile, tree) on bookkeeping and ran at 1.6 ms (16 trees
+// resident) to 8.5 ms (1 tree resident) per 10 M rows x 16 trees, against 2.3-2.6 ms for hist_smem_kernel; measured and
+// dropped (profiles/README.md).  hist_rot_kernel below needs 1.4-2.0 ms at every depth.
 #pragma once
 // (included at the end of avt_kernels.cuh)
 
@@ -23,7 +15,6 @@ namespace avt {
 
 constexpr int kForestThreads = 512;
 constexpr int kForestWarps = kForestThreads / 32;
-constexpr int kForestSub = 8;           // trees per (tile, sub-batch): one list entry per (row, tree) of the sub-batch
 
 struct ForestArgs {
     const int32_t* bin_off;   // [A+1]
@@ -55,281 +46,15 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
 }
-__device__ __forceinline__ uint2 lds_v2(uint32_t addr) {
-    uint2 v;
-    asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
-    return v;
-}
-// update executed only where `n > i` (a predicate, not a branch: the loads around it stay in flight)
-template <int I>
-__device__ __forceinline__ void red_shared_add_gt(uint32_t addr, uint32_t v, uint32_t n) {
-    asm volatile("{\n .reg .pred p;\n setp.gt.u32 p, %2, %3;\n @p red.shared.add.u32 [%0], %1;\n}" ::"r"(addr), "r"(v), "r"(n), "n"(I) : "memory");
-}
-__device__ __forceinline__ void red_shared_add_bit(uint32_t addr, uint32_t v, uint32_t mask, uint32_t bit) {
-    asm volatile("{\n .reg .pred p;\n .reg .b32 t;\n and.b32 t, %2, %3;\n setp.ne.u32 p, t, 0;\n @p red.shared.add.u32 [%0], %1;\n}" ::"r"(addr), "r"(v), "r"(mask), "r"(bit) : "memory");
-}
-__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
-    return v;
-}
-__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
-__device__ __forceinline__ void sts_v2(uint32_t addr, uint32_t x, uint32_t y) {
-    asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(addr), "r"(x), "r"(y) : "memory");
-}
 __device__ __forceinline__ void sts_v4(uint32_t addr, const uint4& v) {
     asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
-// Shared memory of a block (dynamic), in this order:
-//   counters   [G][n_slots][C][Bmax][32] uint32
-//   lists      [warps][kForestSub][32] uint2     phase A -> phase B: (counter base address, multiplicity) of the live (row, tree) pairs
-//   codes      [warps][32 attributes][32 rows]   (fused repartition only) the tile's codes, for "the code of the node's split attribute"
-//   lut32      [G][n_prev_max][lut_w] uint32     (fused repartition only) bin -> (slot << 16 | child node) of every previous node
-//   slot_of    [G][n_nodes_max + 1] uint16       node -> slot, 0xFFFF = not counted here
-//   node_of    [G][n_slots] uint16               slot -> node (flush)
-//   attr8      [G][n_prev_max] uint8             (fused repartition only) split attribute of every previous node, 0xFF = not expanded
-//   has_w      [G] uint8
-// Every global row buffer (columns, classes, node ids, multiplicities) is allocated with 32 rows of slack, so a tile that
-// reaches past the padded row count reads in bounds; such rows are never counted (row >= N) and never stored (row >= Npad).
-template <bool HAS_W, bool REPART>
-__global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const HistArgs a, const ForestArgs f) {
-    extern __shared__ __align__(16) uint32_t fsh[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int t0 = blockIdx.x * f.G;
-    const int Gb = min(f.G, a.T - t0);
-    const int chunk = blockIdx.z;                 // attributes [32 * chunk, 32 * chunk + 32)
-    const int attr = chunk * 32 + lane;
-    const bool attr_ok = attr < f.A;
-    const uint32_t slot_words = (uint32_t)a.C * f.Bmax * 32u;       // words of one (tree, slot)
-    const uint32_t cnt_words = (uint32_t)f.G * f.n_slots * slot_words;
-    const int so_stride = f.n_nodes_max + 1;
-    const int lut_stride = f.n_prev_max * a.lut_w;                   // words of one tree's lut32
-    uint32_t* cnt = fsh;
-    uint32_t* lists = cnt + cnt_words;
-    uint8_t* codes_s = reinterpret_cast<uint8_t*>(lists + kForestWarps * kForestSub * 64);
-    uint32_t* lut32 = reinterpret_cast<uint32_t*>(codes_s + (REPART ? kForestWarps * 1024 : 0));
-    uint16_t* slot_of = reinterpret_cast<uint16_t*>(lut32 + (REPART ? (size_t)f.G * lut_stride : 0));
-    uint16_t* node_of = slot_of + (size_t)f.G * so_stride;
-    uint8_t* attr8 = reinterpret_cast<uint8_t*>(node_of + (size_t)f.G * f.n_slots);
-    uint8_t* s_has_w = attr8 + (REPART ? (size_t)f.G * f.n_prev_max : 0);
-
-    pdl_launch_dependents();
-    for (uint32_t i = threadIdx.x; i < cnt_words; i += blockDim.x) cnt[i] = 0;
-    pdl_wait();   // node_base, skip marks, repartition tables and node ids come from the previous launches
-    // node -> slot tables: the counted (not derived) nodes of each resident tree, numbered in node order
-    for (int g = warp; g < Gb; g += kForestWarps) {
-        const int nb = a.node_base[t0 + g], n = a.node_base[t0 + g + 1] - nb;
-        for (int i = lane; i < so_stride; i += 32) slot_of[g * so_stride + i] = 0xFFFF;
-        if (lane == 0) s_has_w[g] = HAS_W && a.has_w[t0 + g] ? 1 : 0;
-        __syncwarp();
-        int run = 0;
-        for (int i0 = 0; i0 < n; i0 += 32) {
-            const int i = i0 + lane;
-            const bool counted = i < n && !(a.skip && a.skip[nb + i]);
-            const uint32_t m = __ballot_sync(0xffffffffu, counted);
-            const int s = run + __popc(m & ((1u << lane) - 1u));
-            if (i < n && i < so_stride && counted && s < f.n_slots) slot_of[g * so_stride + i] = (uint16_t)s;
-            if (counted && s < f.n_slots) node_of[g * f.n_slots + s] = (uint16_t)i;
-            run += __popc(m);
-        }
-        if (lane == 0 && (run > f.n_slots || n > f.n_nodes_max)) *f.err = 4;
-        for (int s = run + lane; s < f.n_slots; s += 32) node_of[g * f.n_slots + s] = 0xFFFF;
-    }
-    __syncthreads();
-    if (REPART) {
-        // previous frontier: bin -> (slot of the child | child), split attribute
-        for (int g = 0; g < Gb; ++g) {
-            const int pnb = a.prev_node_base[t0 + g], n_prev = min(a.prev_node_base[t0 + g + 1] - pnb, f.n_prev_max);
-            if (threadIdx.x == 0 && a.prev_node_base[t0 + g + 1] - pnb > f.n_prev_max) *f.err = 4;
-            for (int i = threadIdx.x; i < n_prev * a.lut_w; i += blockDim.x) {
-                const uint32_t child = a.child_lut[(long long)pnb * a.lut_w + i];
-                const uint32_t s = child == AVT_NODE_NONE ? 0xFFFFu : (uint32_t)slot_of[g * so_stride + min(child, (uint32_t)f.n_nodes_max)];
-                lut32[g * lut_stride + i] = (s << 16) | child;
-            }
-            for (int i = threadIdx.x; i < n_prev; i += blockDim.x) {
-                const int at = a.node_attr[pnb + i];
-                attr8[g * f.n_prev_max + i] = at < 0 ? (uint8_t)0xFF : (uint8_t)at;
-            }
-        }
-        __syncthreads();
-    }
-
-    uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(cnt);
-    uint32_t list_base = (uint32_t)__cvta_generic_to_shared(lists) + (uint32_t)warp * kForestSub * 256u;   // [i][row] uint2
-    uint32_t codes_base = (uint32_t)__cvta_generic_to_shared(codes_s) + (uint32_t)warp * 1024u;
-    uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(lut32);
-    uint32_t slot_of_base = (uint32_t)__cvta_generic_to_shared(slot_of);
-    uint32_t attr8_base = (uint32_t)__cvta_generic_to_shared(attr8);
-    uint32_t has_w_base = (uint32_t)__cvta_generic_to_shared(s_has_w);
-    // keep the window addresses in registers: left to itself the compiler re-derives them (S2R + LDC + shifts) at every use
-    asm volatile("" : "+r"(cnt_base), "+r"(list_base), "+r"(codes_base), "+r"(lut_base), "+r"(slot_of_base), "+r"(attr8_base), "+r"(has_w_base));
-    const uint8_t* col = attr_ok ? (const uint8_t*)a.cols[attr] : nullptr;
-    const long long n_tiles = (a.N + 31) >> 5;
-    const long long tile_lo = (long long)blockIdx.y * f.tiles_per_part;
-    const long long tile_hi = min(n_tiles, tile_lo + f.tiles_per_part);
-    const uint32_t class_bytes = (uint32_t)f.Bmax * 128u;          // one (slot, class): Bmax bins x 32 attributes x 4 B
-    const uint32_t slot_bytes = slot_words * 4u;
-    const uint32_t tree_bytes = (uint32_t)f.n_slots * slot_bytes;
-    const uint32_t l4 = 4u * lane;
-    const uint32_t l4l4 = l4 | (l4 << 16);
-
-    uint4 nc0 = make_uint4(0, 0, 0, 0), nc1 = nc0;
-    uint32_t ncl = 0;
-    auto load_codes = [&](long long tile) {
-        const long long row0 = tile << 5;
-        if (attr_ok) {
-            nc0 = ld_stream(col + row0);
-            nc1 = ld_stream(col + row0 + 16);
-        }
-        ncl = a.cls[row0 + lane];
-    };
-    long long tile = tile_lo + warp;
-    if (tile < tile_hi) load_codes(tile);
-    for (; tile < tile_hi; tile += kForestWarps) {
-        const long long row = (tile << 5) + lane;
-        const bool row_ok = row < a.N;
-        // ---- new tile: codes -> counter offsets (row j: code * 128 + lane * 4, bin-major / attribute-minor; two rows per register)
-        uint32_t offs[16];
-        {
-            const uint32_t w8[8] = {nc0.x, nc0.y, nc0.z, nc0.w, nc1.x, nc1.y, nc1.z, nc1.w};
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                offs[2 * q] = __byte_perm(w8[q], 0u, 0x4140u) * 128u + l4l4;       // bytes 0,1 -> halves
-                offs[2 * q + 1] = __byte_perm(w8[q], 0u, 0x4342u) * 128u + l4l4;   // bytes 2,3 -> halves
-            }
-            if (REPART) {
-                __syncwarp();   // the previous tile's readers are done
-                sts_v4(codes_base + 32u * lane, nc0);
-                sts_v4(codes_base + 32u * lane + 16u, nc1);
-                __syncwarp();
-            }
-        }
-        const uint32_t cl = ncl;
-        if (tile + kForestWarps < tile_hi) load_codes(tile + kForestWarps);
-        const uint16_t* nid_row = a.nid + (long long)t0 * a.Npad + row;
-        uint16_t* nid_out_row = REPART ? a.nid_out + (long long)t0 * a.Npad + row : nullptr;
-        const uint8_t* w_row = HAS_W ? a.wts + (long long)t0 * a.Npad + row : nullptr;
-        for (int g0 = 0; g0 < Gb; g0 += kForestSub) {
-            const int gn = min(kForestSub, Gb - g0);
-            // ---- phase A (lane = row): node, slot and liveness of this row in each tree of the sub-batch
-            uint32_t nid_r[kForestSub], w_r[kForestSub];
-#pragma unroll
-            for (int k = 0; k < kForestSub; ++k) {
-                nid_r[k] = AVT_NODE_NONE;
-                w_r[k] = 1u;
-                if (k < gn) {
-                    nid_r[k] = nid_row[(long long)(g0 + k) * a.Npad];
-                    if (HAS_W && lds_u8(has_w_base + g0 + k)) w_r[k] = w_row[(long long)(g0 + k) * a.Npad];
-                }
-            }
-            // few trees (deep levels, one or two trees resident): entries stay at [tree][row] and a ballot says which rows are
-            // live -- nothing is paid per row and tree; several trees: each row compacts its live entries at [0..n)[row]
-            const bool compact = gn > 2;
-            uint32_t cnt_live = 0, live_bits = 0;
-#pragma unroll
-            for (int k = 0; k < kForestSub; ++k) {
-                if (k < gn) {
-                    const int g = g0 + k;
-                    uint32_t node = row_ok ? nid_r[k] : AVT_NODE_NONE;
-                    uint32_t s = 0xFFFFu;
-                    if (REPART) {
-                        uint32_t e = 0xFFFFFFFFu;
-                        if (node != AVT_NODE_NONE) {
-                            node = min(node, (uint32_t)f.n_prev_max - 1u);
-                            const uint32_t at = lds_u8(attr8_base + g * f.n_prev_max + node);
-                            if (at != 0xFFu) {
-                                // the tile in shared memory holds this block's 32 attributes; another chunk's column is read from global memory
-                                const uint32_t code = (at >> 5) == (uint32_t)chunk ? lds_u8(codes_base + 32u * (at & 31u) + lane)
-                                                                                   : (uint32_t)__ldg((const uint8_t*)a.cols[at] + row);
-                                e = lds_u32(lut_base + 4u * (g * lut_stride + node * a.lut_w + code));
-                            }
-                        }
-                        node = e & 0xFFFFu;
-                        s = e >> 16;
-                        if (chunk == 0 && row < a.Npad) nid_out_row[(long long)g * a.Npad] = (uint16_t)node;
-                    } else if (node != AVT_NODE_NONE) {
-                        s = lds_u16(slot_of_base + 2u * (g * so_stride + min(node, (uint32_t)f.n_nodes_max)));
-                    }
-                    if (s != 0xFFFFu && w_r[k] != 0u) {
-                        sts_v2(list_base + (compact ? cnt_live : (uint32_t)k) * 256u + 8u * lane,
-                               cnt_base + (uint32_t)g * tree_bytes + s * slot_bytes + cl * class_bytes, w_r[k]);
-                        ++cnt_live;
-                        live_bits |= 1u << k;
-                    }
-                }
-            }
-            __syncwarp();
-            // ---- phase B (lane = attribute): one conflict-free update per live (row, tree) pair
-            if (compact) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const uint32_t n = __shfl_sync(0xffffffffu, cnt_live, j);
-                    const uint32_t off = (j & 1) ? (offs[j >> 1] >> 16) : (offs[j >> 1] & 0xFFFFu);
-                    // the first four entries are loaded unconditionally (same address in every lane: broadcasts that overlap each
-                    // other) and applied under a predicate; longer lists continue with a compare-and-branch chain
-                    const uint2 x0 = lds_v2(list_base + 0u * 256u + 8u * j), x1 = lds_v2(list_base + 1u * 256u + 8u * j);
-                    const uint2 x2 = lds_v2(list_base + 2u * 256u + 8u * j), x3 = lds_v2(list_base + 3u * 256u + 8u * j);
-                    red_shared_add_gt<0>(x0.x + off, HAS_W ? x0.y : 1u, n);
-                    red_shared_add_gt<1>(x1.x + off, HAS_W ? x1.y : 1u, n);
-                    red_shared_add_gt<2>(x2.x + off, HAS_W ? x2.y : 1u, n);
-                    red_shared_add_gt<3>(x3.x + off, HAS_W ? x3.y : 1u, n);
-#pragma unroll
-                    for (uint32_t i = 4; i < (uint32_t)kForestSub; ++i) {
-                        if (i >= n) break;
-                        const uint2 x = lds_v2(list_base + i * 256u + 8u * j);
-                        red_shared_add(x.x + off, HAS_W ? x.y : 1u);
-                    }
-                }
-            } else {
-                for (int k = 0; k < gn; ++k) {
-                    const uint32_t m = __ballot_sync(0xffffffffu, (live_bits >> k) & 1u);
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) {
-                        if ((m >> (4 * q)) & 0xFu) {
-                            const uint4 v0 = lds_v4(list_base + (uint32_t)k * 256u + 32u * q), v1 = lds_v4(list_base + (uint32_t)k * 256u + 32u * q + 16u);
-                            const uint32_t o0 = offs[2 * q] & 0xFFFFu, o1 = offs[2 * q] >> 16, o2 = offs[2 * q + 1] & 0xFFFFu, o3 = offs[2 * q + 1] >> 16;
-                            red_shared_add_bit(v0.x + o0, HAS_W ? v0.y : 1u, m, 1u << (4 * q));
-                            red_shared_add_bit(v0.z + o1, HAS_W ? v0.w : 1u, m, 2u << (4 * q));
-                            red_shared_add_bit(v1.x + o2, HAS_W ? v1.y : 1u, m, 4u << (4 * q));
-                            red_shared_add_bit(v1.z + o3, HAS_W ? v1.w : 1u, m, 8u << (4 * q));
-                        }
-                    }
-                }
-            }
-            __syncwarp();   // the lists are rewritten by the next sub-batch
-        }
-    }
-    __syncthreads();
-    // flush: counters [g][slot][class][bin][lane] -> H[node][bin_off[attr] + bin][class]
-    for (int g = 0; g < Gb; ++g) {
-        const int nb = a.node_base[t0 + g];
-        const uint32_t per_tree = (uint32_t)f.n_slots * slot_words;
-        for (uint32_t i = threadIdx.x; i < per_tree; i += blockDim.x) {
-            const uint32_t v = cnt[(uint32_t)g * per_tree + i];
-            if (!v) continue;
-            const int la = (int)(i & 31u);
-            const uint32_t rest = i >> 5;
-            const int bin = (int)(rest % (uint32_t)f.Bmax);
-            const uint32_t sc = rest / (uint32_t)f.Bmax;
-            const int c = (int)(sc % (uint32_t)a.C);
-            const int s = (int)(sc / (uint32_t)a.C);
-            const int at = chunk * 32 + la;
-            if (at >= f.A) continue;   // lanes without an attribute counted into their own (unused) column
-            const int node = node_of[g * f.n_slots + s];
-            const int b0 = f.bin_off[at];
-            if (node == 0xFFFF || bin >= f.bin_off[at + 1] - b0) continue;
-            atomicAdd(a.H + ((long long)(nb + node) * a.TB + b0 + bin) * a.C + c, v);
-        }
-    }
-}
-
-
 // ----------------------------------------------------------------------------------------------------------------------
 // hist_rot_kernel: lane = ROW, attributes visited in a lane-rotated order.
 //
-// Same counters as hist_forest_kernel ([tree][slot][class][bin][attribute(32)]: the bank of a counter is its attribute),
-// but every lane owns one row of the warp's 32-row tile and, at step p of the 32-step update loop, counts attribute
+// The block's private counters are laid out [tree][slot][class][bin][attribute(32)]: the bank of a counter is its attribute.
+// Every lane owns one row of the warp's 32-row tile and, at step p of the 32-step update loop, counts attribute
 // (p + lane) mod 32 of its row: at every step the 32 lanes touch 32 different attributes, i.e. 32 different banks -- each
 // ATOMS is one conflict-free wavefront with all lanes active, three instructions per counter update, nothing shuffled or
 // broadcast.  For that a lane must find "attribute (p + lane) mod 32 of my row" at a compile-time byte position p of its
@@ -340,7 +65,10 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_forest_kernel(const Hi
 // Rows that are not counted (outside the frontier, multiplicity 0, node derived by sibling subtraction) update a phantom
 // slot: a partially active ATOMS is much slower than a full one on sm_100a (tools/microbench/atoms_bench.cu).
 // Shared memory: counters [G * n_slots + 1 phantom][C][Bmax][32], tile copies [warps][32 rows][32 B] (fused repartition),
-// then lut32 / slot_of / node_of / attr8 / has_w as in hist_forest_kernel.
+// then lut32 [G][n_prev_max][lut_w] (bin -> slot << 16 | child of every previous node), slot_of [G][n_nodes_max + 1] (node -> slot,
+// 0xFFFF = not counted), node_of [G][n_slots], attr16 [G][n_prev_max] (split attribute, 0xFFFF = not expanded), has_w [G].
+// Every global row buffer (columns, classes, node ids, multiplicities, the rotated copy) is allocated with 32 rows of slack, so
+// a tile that reaches past the padded row count reads in bounds; such rows are never counted and never stored.
 __global__ void rowrot_kernel(const void* const* cols, int A, long long N, long long rows_alloc, uint8_t* out) {
     const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const int chunk = blockIdx.y;
@@ -376,8 +104,8 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
     uint32_t* lut32 = reinterpret_cast<uint32_t*>(codes_s + (REPART ? kForestWarps * 1024 : 0));
     uint16_t* slot_of = reinterpret_cast<uint16_t*>(lut32 + (REPART ? (size_t)f.G * lut_stride : 0));
     uint16_t* node_of = slot_of + (size_t)f.G * so_stride;
-    uint8_t* attr8 = reinterpret_cast<uint8_t*>(node_of + (size_t)f.G * f.n_slots);
-    uint8_t* s_has_w = attr8 + (REPART ? (size_t)f.G * f.n_prev_max : 0);
+    uint16_t* attr16 = node_of + (size_t)f.G * f.n_slots;   // split attribute of every previous node, 0xFFFF = not expanded
+    uint8_t* s_has_w = reinterpret_cast<uint8_t*>(attr16 + (REPART ? (size_t)f.G * f.n_prev_max : 0));
 
     pdl_launch_dependents();
     for (uint32_t i = threadIdx.x; i < cnt_words; i += blockDim.x) cnt[i] = 0;
@@ -412,7 +140,7 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
             }
             for (int i = threadIdx.x; i < n_prev; i += blockDim.x) {
                 const int at = a.node_attr[pnb + i];
-                attr8[g * f.n_prev_max + i] = at < 0 ? (uint8_t)0xFF : (uint8_t)at;
+                attr16[g * f.n_prev_max + i] = at < 0 ? (uint16_t)0xFFFF : (uint16_t)at;
             }
         }
         __syncthreads();
@@ -421,9 +149,9 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
     uint32_t codes_base = (uint32_t)__cvta_generic_to_shared(codes_s) + (uint32_t)warp * 1024u + 32u * lane;   // this lane's row
     uint32_t lut_base = (uint32_t)__cvta_generic_to_shared(lut32);
     uint32_t slot_of_base = (uint32_t)__cvta_generic_to_shared(slot_of);
-    uint32_t attr8_base = (uint32_t)__cvta_generic_to_shared(attr8);
+    uint32_t attr16_base = (uint32_t)__cvta_generic_to_shared(attr16);
     uint32_t has_w_base = (uint32_t)__cvta_generic_to_shared(s_has_w);
-    asm volatile("" : "+r"(cnt_base), "+r"(codes_base), "+r"(lut_base), "+r"(slot_of_base), "+r"(attr8_base), "+r"(has_w_base));
+    asm volatile("" : "+r"(cnt_base), "+r"(codes_base), "+r"(lut_base), "+r"(slot_of_base), "+r"(attr16_base), "+r"(has_w_base));
     const uint32_t class_bytes = (uint32_t)f.Bmax * 128u;
     const uint32_t slot_bytes = slot_words * 4u;
     const uint32_t tree_bytes = (uint32_t)f.n_slots * slot_bytes;
@@ -469,23 +197,31 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
         const uint16_t* nid_row = a.nid + (long long)t0 * a.Npad + row;
         uint16_t* nid_out_row = REPART ? a.nid_out + (long long)t0 * a.Npad + row : nullptr;
         const uint8_t* w_row = HAS_W ? a.wts + (long long)t0 * a.Npad + row : nullptr;
-        uint32_t nid_next = nid_row[0], w_next = 1u;
-        if (HAS_W && lds_u8(has_w_base)) w_next = w_row[0];
-        for (int g = 0; g < Gb; ++g) {
-            uint32_t node = row_ok ? nid_next : AVT_NODE_NONE;
-            const uint32_t w = w_next;
-            if (g + 1 < Gb) {   // next tree's node id and multiplicity while this tree's updates issue
-                nid_next = nid_row[(long long)(g + 1) * a.Npad];
-                w_next = 1u;
-                if (HAS_W && lds_u8(has_w_base + g + 1)) w_next = w_row[(long long)(g + 1) * a.Npad];
+        // node id and multiplicity of this row in the next two trees are in flight while a tree's updates issue
+        auto fetch = [&](int g, uint32_t& n, uint32_t& w) {
+            n = AVT_NODE_NONE;
+            w = 1u;
+            if (g < Gb) {
+                n = nid_row[(long long)g * a.Npad];
+                if (HAS_W && lds_u8(has_w_base + g)) w = w_row[(long long)g * a.Npad];
             }
+        };
+        uint32_t n0, w0, n1, w1;
+        fetch(0, n0, w0);
+        fetch(1, n1, w1);
+        for (int g = 0; g < Gb; ++g) {
+            uint32_t node = row_ok ? n0 : AVT_NODE_NONE;
+            const uint32_t w = w0;
+            n0 = n1;
+            w0 = w1;
+            fetch(g + 2, n1, w1);
             uint32_t s = 0xFFFFu;
             if (REPART) {
                 uint32_t e = 0xFFFFFFFFu;
                 if (node != AVT_NODE_NONE) {
                     node = min(node, (uint32_t)f.n_prev_max - 1u);
-                    const uint32_t at = lds_u8(attr8_base + g * f.n_prev_max + node);
-                    if (at != 0xFFu) {
+                    const uint32_t at = lds_u16(attr16_base + 2u * (g * f.n_prev_max + node));
+                    if (at != 0xFFFFu) {
                         // byte position of attribute `at` in this row's rotated copy; another chunk's column comes from global memory
                         const uint32_t code = (at >> 5) == (uint32_t)chunk ? lds_u8(codes_base + ((at - (uint32_t)lane) & 31u))
                                                                            : (uint32_t)__ldg((const uint8_t*)a.cols[at] + row);

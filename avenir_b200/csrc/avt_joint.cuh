@@ -21,6 +21,8 @@ struct JointArgs {
     int n_prev_max;    // fused repartition: bound on a tree's nodes in the previous frontier (sizes the table)
     int zero_words;    // counter words the block may clear before it waits for the previous launch
     uint32_t shift[4], mask[4];   // field of attribute q in the packed byte
+    const uint16_t* lut2_g;       // fused repartition: packed byte -> child rows of the previous frontier, written by the scan kernel
+                                  // ([NF_prev][J]); nullptr = derive them here from node_attr / child_lut
 };
 
 // Dynamic shared memory: counters [n_nodes + 1][J][C] uint32 (node n_nodes swallows the rows that are not counted), then --
@@ -42,14 +44,19 @@ __global__ void __launch_bounds__(kJointThreads) hist_joint_kernel(const HistArg
     if (REPART) {
         const int pnb = a.prev_node_base[t];
         n_prev = min(a.prev_node_base[t + 1] - pnb, ja.n_prev_max);
-        for (int i = threadIdx.x; i < (n_prev + 1) * J; i += blockDim.x) {
-            const int p = i / J, v = i - p * J;
-            uint16_t child = (uint16_t)AVT_NODE_NONE;
-            if (p < n_prev) {
-                const int at = a.node_attr[pnb + p];
-                if (at >= 0) child = a.child_lut[(long long)(pnb + p) * a.lut_w + ((v >> ja.shift[at]) & ja.mask[at])];
+        if (ja.lut2_g) {
+            const uint16_t* src = ja.lut2_g + (long long)pnb * J;
+            for (int i = threadIdx.x; i < (n_prev + 1) * J; i += blockDim.x) lut2[i] = i < n_prev * J ? src[i] : (uint16_t)AVT_NODE_NONE;
+        } else {
+            for (int i = threadIdx.x; i < (n_prev + 1) * J; i += blockDim.x) {
+                const int p = i / J, v = i - p * J;
+                uint16_t child = (uint16_t)AVT_NODE_NONE;
+                if (p < n_prev) {
+                    const int at = a.node_attr[pnb + p];
+                    if (at >= 0) child = a.child_lut[(long long)(pnb + p) * a.lut_w + ((v >> ja.shift[at]) & ja.mask[at])];
+                }
+                lut2[i] = child;
             }
-            lut2[i] = child;
         }
     }
     __syncthreads();

@@ -39,6 +39,11 @@ struct PlanArgs {
                                     // block, right after the wait for the histogram pass) instead of the pass's last block
     // sibling subtraction: the most populous child of every split is NOT counted by the next histogram pass; its
     // counts are derived as parent - (other children), exact in integers, by that child's scan block
+    // joint-code histogram kernel (packed narrow schemas): the node's block also expands its bin -> child row into a
+    // packed-byte -> child row, so the next histogram pass copies its repartition table instead of deriving it
+    uint16_t* lut2;             // [NF][lut2_J] (nullptr: not wanted)
+    int lut2_J;
+    uint32_t pk_shift[4], pk_mask[4];
     uint8_t* next_skip;         // [NF_next] 1 = derived (nullptr: subtraction off)
     int32_t* next_parent;       // [NF_next] global index (this frontier) of a derived node's parent, else -1
     int32_t* kids;              // [NF][kMaxSeg] global index (next frontier) of each segment's child, -1 = none

@@ -423,6 +423,13 @@ __global__ void __launch_bounds__(kScanThreads) scan_fast_kernel(const uint32_t*
             }
         }
     }
+    if (lookback && plan.lut2 && node < n_nodes) {   // (look-back mode: the child ids in the row are final)
+        __syncthreads();   // warp 0 has written the node's split attribute and bin -> child row
+        const int at = plan.node_attr[node];
+        const uint16_t* lut = plan.child_lut + (long long)node * plan.lut_w;
+        for (int v = tid; v < plan.lut2_J; v += blockDim.x)
+            plan.lut2[(long long)node * plan.lut2_J + v] = at >= 0 ? lut[(v >> plan.pk_shift[at]) & plan.pk_mask[at]] : (uint16_t)AVT_NODE_NONE;
+    }
     if (lookback) {
         // an empty frontier has no block that owns the next level's node_base: block 0 writes it (all zero)
         if (blockIdx.x == 0 && n_nodes == 0)

@@ -5,6 +5,12 @@
 // e_log.c algorithm; evaluating that algorithm with one IEEE rounding per operation (this file is
 // compiled with -fmad=false, and uses no FMA intrinsics) gives bit-identical results on the GPU,
 // on the host and in the CPU oracle.
+//
+// The algorithm and its constants are those of fdlibm's e_log.c (a third-party source that is not part of the reference
+// tree), whose notice is preserved here:
+//   Copyright (C) 1993 by Sun Microsystems, Inc. All rights reserved.
+//   Developed at SunSoft, a Sun Microsystems, Inc. business.
+//   Permission to use, copy, modify, and distribute this software is freely granted, provided that this notice is preserved.
 #pragma once
 #include <stdint.h>
 #include <string.h>

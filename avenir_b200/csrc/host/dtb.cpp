@@ -18,6 +18,7 @@
 //   avt.device           (0)  CUDA device ordinal
 #include <dirent.h>
 #include <sys/stat.h>
+#include <unistd.h>
 
 #include <algorithm>
 #include <cstdio>
@@ -110,9 +111,11 @@ static void write_text(const std::string& path, const std::string& text) {
     fclose(f);
 }
 
-void write_output_lines(const std::string& out_dir, const std::vector<std::string>& lines) {
+void write_output_lines(const std::string& out_dir, const std::vector<std::string>& lines, int part) {
     mkdirs(out_dir);
-    std::string path = out_dir + "/part-r-00000";
+    char name[32];
+    snprintf(name, sizeof name, "/part-r-%05d", part);
+    std::string path = out_dir + name;
     FILE* f = fopen(path.c_str(), "wb");
     if (!f) throw std::runtime_error("cannot write " + path);
     for (auto& l : lines) {
@@ -331,6 +334,15 @@ class DtbJob {
     std::vector<uint8_t> cls_;
     std::vector<Tree> trees_;
     std::vector<int> layer_tree_;    // device layer (engine tree) -> reference tree
+    // Row sharding over several GPUs (avt.num.ranks > 1; one process per GPU, launched like the ranks of any multi-GPU job):
+    // every rank reads the whole input, so class codes, bootstrap samples and every host-side decision are identical, but
+    // uploads and partitions only rows [lo_, hi_); the per-level histograms are summed over the ranks inside
+    // avt_level_histogram (avt_comm_init_rank: NCCL over NVLink).  Rank 0 writes the decision-path lists, every rank its
+    // own part-r-<rank> of the level data.  This is the reference's shuffle between BuilderMapper and BuilderReducer
+    // (tree/DecisionTreeBuilder.java:80-93) with the mappers' rows living on different GPUs.
+    int n_ranks_ = 1, rank_ = 0;
+    size_t lo_ = 0, hi_ = 0;
+    size_t n_local() const { return hi_ - lo_; }
     bool multiway_ = false;          // some candidate split has more than two predicates
     std::unique_ptr<Engine> eng_;
     JavaRandom rng_{0};
@@ -352,7 +364,11 @@ public:
             for (auto& pj : arr->arr) dec_in.push_back(path_from_json(pj));
         }
         encode(lines, tree_available, row_tagged);
+        lo_ = rows_.size() * (size_t)rank_ / (size_t)n_ranks_;
+        hi_ = rows_.size() * (size_t)(rank_ + 1) / (size_t)n_ranks_;
+        if (hi_ == lo_) throw Unsupported("rank " + std::to_string(rank_) + " of " + std::to_string(n_ranks_) + " has no rows");
         eng_.reset(new Engine(device_));
+        if (n_ranks_ > 1) join_ranks();
         upload();
         int levels_left = num_levels_;
         if (!tree_available) {
@@ -387,6 +403,9 @@ private:
 
     void read_conf() {
         debug_ = conf_.get_bool("debug.on", false);
+        n_ranks_ = conf_.get_int("avt.num.ranks", 1);
+        rank_ = conf_.get_int("avt.rank", 0);
+        if (n_ranks_ < 1 || rank_ < 0 || rank_ >= n_ranks_) throw Unsupported("avt.rank " + std::to_string(rank_) + " outside 0.." + std::to_string(n_ranks_ - 1));
         delim_regex_ = conf_.get("field.delim.regex", ",");
         delim_out_ = conf_.get("field.delim.out", ",");
         path_delim_ = conf_.get("dtb.dec.path.delim", ";");
@@ -488,14 +507,43 @@ private:
         classes_.finish();
     }
 
+    // NCCL rendezvous through a file both ranks can see (avt.comm.id.file, default <decision file out>.ncclid): rank 0 creates the
+    // 128-byte id and publishes it with an atomic rename, the others poll for it.  Any launcher that starts one process per GPU
+    // with avt.rank / avt.num.ranks set (torchrun, mpirun, a shell loop) works; nothing else is exchanged on the host side.
+    void join_ranks() {
+        std::string path = conf_.get("avt.comm.id.file", conf_.get("dtb.decision.file.path.out", "avt") + ".ncclid");
+        unsigned char id[128];
+        if (rank_ == 0) {
+            eng_->check(avt_comm_unique_id(id));
+            const std::string tmp = path + ".tmp";
+            FILE* f = fopen(tmp.c_str(), "wb");
+            if (!f || fwrite(id, 1, sizeof id, f) != sizeof id) throw std::runtime_error("cannot write " + tmp);
+            fclose(f);
+            if (rename(tmp.c_str(), path.c_str()) != 0) throw std::runtime_error("cannot publish " + path);
+        } else {
+            bool ok = false;
+            for (int tries = 0; tries < 1200 && !ok; ++tries) {   // up to two minutes
+                FILE* f = fopen(path.c_str(), "rb");
+                if (f) {
+                    ok = fread(id, 1, sizeof id, f) == sizeof id;
+                    fclose(f);
+                }
+                if (!ok) usleep(100000);
+            }
+            if (!ok) throw std::runtime_error("rank " + std::to_string(rank_) + ": no communicator id at " + path + " after 120 s");
+        }
+        eng_->check(avt_comm_init_rank(eng_->raw(), n_ranks_, rank_, id));
+        if (rank_ == 0 && conf_.get_bool("avt.comm.id.cleanup", false)) remove(path.c_str());
+    }
+
     void upload() {
         std::vector<int32_t> nb;
         std::vector<const void*> cols;
         for (size_t a = 0; a < attrs_.size(); ++a) {
             nb.push_back(attrs_[a].n_bins);
-            cols.push_back(attrs_[a].n_bins > 256 ? (const void*)col16_[a].data() : (const void*)col8_[a].data());
+            cols.push_back(attrs_[a].n_bins > 256 ? (const void*)(col16_[a].data() + lo_) : (const void*)(col8_[a].data() + lo_));
         }
-        eng_->check(avt_dataset_load(eng_->raw(), (int64_t)rows_.size(), (int32_t)attrs_.size(), nb.data(), cols.data(), cls_.data(), (int32_t)classes_.names.size()));
+        eng_->check(avt_dataset_load(eng_->raw(), (int64_t)n_local(), (int32_t)attrs_.size(), nb.data(), cols.data(), cls_.data() + lo_, (int32_t)classes_.names.size()));
         eng_->check(avt_split_table_set(eng_->raw(), (int32_t)table_.splits.size(), table_.splits.data(), table_.bounds.data(), (int32_t)table_.bounds.size(),
                                         table_.lut.data(), (int64_t)table_.lut.size()));
     }
@@ -527,7 +575,7 @@ private:
                 for (size_t r = 0; r < n; ++r)
                     if (java_int_cast(rng.next_double() * 100) < sampling_rate_) tr.weights[r] = 1;
             }
-            if (!tr.weights.empty()) wptr[(size_t)t] = tr.weights.data();
+            if (!tr.weights.empty()) wptr[(size_t)t] = tr.weights.data() + lo_;
             Node root;
             root.tagged = {kRoot};
             root.layer = t;
@@ -584,7 +632,7 @@ private:
                 if (tr.frontier[(size_t)node].tagged.empty()) tr.frontier[(size_t)node].tagged = row_tagged[r];
             }
         }
-        const uint16_t* np = nid.data();
+        const uint16_t* np = nid.data() + lo_;
         eng_->check(avt_forest_init(eng_->raw(), 1, nullptr, &np));
     }
 
@@ -1005,16 +1053,16 @@ private:
             for (auto& sp : spawns)
                 if (!parent_nid.count(sp.parent_layer)) {
                     auto& v = parent_nid[sp.parent_layer];
-                    v.resize(rows_.size());
+                    v.resize(n_local());
                     eng_->check(avt_forest_node_ids(eng_->raw(), sp.parent_layer, v.data()));
                 }
             for (auto& sp : spawns) {
                 const auto& pn = parent_nid[sp.parent_layer];
-                std::vector<uint16_t> v(rows_.size(), (uint16_t)AVT_NODE_NONE);
+                std::vector<uint16_t> v(n_local(), (uint16_t)AVT_NODE_NONE);
                 const bool wide = attrs_[(size_t)sp.attr].n_bins > 256;
-                for (size_t r = 0; r < rows_.size(); ++r) {
+                for (size_t r = 0; r < n_local(); ++r) {
                     if (pn[r] != (uint16_t)sp.parent_id) continue;
-                    const int b = wide ? col16_[(size_t)sp.attr][r] : col8_[(size_t)sp.attr][r];
+                    const int b = wide ? col16_[(size_t)sp.attr][lo_ + r] : col8_[(size_t)sp.attr][lo_ + r];
                     if (b >= sp.lo && b <= sp.hi) v[r] = 0;
                 }
                 spawn_nid.push_back(std::move(v));
@@ -1023,7 +1071,7 @@ private:
         eng_->check(avt_level_repartition(eng_->raw(), node_attr.data(), child_lut.data(), lut_w));
         if (!spawns.empty()) {
             // the forest grows by the new layers: existing layers keep their (repartitioned) node ids
-            std::vector<std::vector<uint16_t>> old_nid((size_t)n_layers, std::vector<uint16_t>(rows_.size()));
+            std::vector<std::vector<uint16_t>> old_nid((size_t)n_layers, std::vector<uint16_t>(n_local()));
             for (int l = 0; l < n_layers; ++l) eng_->check(avt_forest_node_ids(eng_->raw(), l, old_nid[(size_t)l].data()));
             layer_tree_ = new_layer_tree;
             std::vector<const uint16_t*> np;
@@ -1031,7 +1079,7 @@ private:
             for (int l = 0; l < (int)layer_tree_.size(); ++l) {
                 np.push_back(l < n_layers ? old_nid[(size_t)l].data() : spawn_nid[(size_t)(l - n_layers)].data());
                 const Tree& tr = trees_[(size_t)layer_tree_[(size_t)l]];
-                wp.push_back(tr.weights.empty() ? nullptr : tr.weights.data());
+                wp.push_back(tr.weights.empty() ? nullptr : tr.weights.data() + lo_);
             }
             eng_->check(avt_forest_init(eng_->raw(), (int32_t)layer_tree_.size(), wp.data(), np.data()));
         }
@@ -1052,6 +1100,11 @@ private:
     // writeDecisioList (tree/DecisionTreeBuilder.java:713-725)
     void write_lists(const std::vector<std::vector<DecPath>>& lists, const std::vector<bool>* is_null = nullptr) {
         for (int t = 0; t < num_trees_; ++t) {
+            if (rank_ != 0) {   // every rank holds the same lists; one writes them
+                const bool null_list = is_null && (*is_null)[(size_t)t];
+                if (null_list && total_population_ > 0) throw ReferenceError("NullPointerException in DecisionPathList.withTotalPopulation: no decision path was generated");
+                continue;
+            }
             const bool null_list = is_null && (*is_null)[(size_t)t];
             if (null_list && total_population_ > 0) throw ReferenceError("NullPointerException in DecisionPathList.withTotalPopulation: no decision path was generated");
             const std::string text = path_list_json(null_list ? nullptr : &lists[(size_t)t]) + "\n";
@@ -1069,11 +1122,11 @@ private:
         for (int t = 0; t < num_trees_; ++t) {
             std::vector<std::string> out;
             const Tree& tr = trees_[(size_t)t];
-            for (size_t r = 0; r < rows_.size(); ++r) {
+            for (size_t r = lo_; r < hi_; ++r) {
                 int w = tr.weights.empty() ? 1 : tr.weights[r];
                 for (int k = 0; k < w; ++k) out.push_back(std::string(kRoot) + delim_out_ + rows_[r]);
             }
-            write_output_lines(data_dir(t), out);
+            write_output_lines(data_dir(t), out, rank_);
         }
     }
 
@@ -1093,9 +1146,9 @@ private:
             std::vector<std::vector<size_t>> rows_of(tr.frontier.size());
             for (size_t l = 0; l < layer_tree_.size(); ++l) {
                 if (layer_tree_[l] != t) continue;
-                nid[l].resize(rows_.size());
+                nid[l].resize(n_local());
                 eng_->check(avt_forest_node_ids(eng_->raw(), (int32_t)l, nid[l].data()));
-                for (size_t r = 0; r < rows_.size(); ++r) {
+                for (size_t r = 0; r < n_local(); ++r) {
                     if (nid[l][r] == AVT_NODE_NONE) continue;
                     auto it = node_of.find({(int)l, (int)nid[l][r]});
                     if (it != node_of.end()) rows_of[(size_t)it->second].push_back(r);
@@ -1106,12 +1159,12 @@ private:
             std::vector<std::string> out;
             for (int i : order) {
                 const std::string key = join_str(tr.frontier[(size_t)i].tagged, path_delim_);
-                for (size_t r : rows_of[(size_t)i]) {
-                    int w = tr.weights.empty() ? 1 : tr.weights[r];
-                    for (int k = 0; k < w; ++k) out.push_back(key + delim_out_ + rows_[r]);
+                for (size_t r : rows_of[(size_t)i]) {   // r is local to the shard
+                    int w = tr.weights.empty() ? 1 : tr.weights[lo_ + r];
+                    for (int k = 0; k < w; ++k) out.push_back(key + delim_out_ + rows_[lo_ + r]);
                 }
             }
-            write_output_lines(data_dir(t), out);
+            write_output_lines(data_dir(t), out, rank_);
         }
     }
 };

@@ -24,7 +24,7 @@ int run_heterogeneity_reduction_correlation(const Props& conf, const std::string
 // Input "path" as Hadoop takes it: a file, or a directory whose regular files (not starting with
 // '_' or '.') are read in name order.
 std::vector<std::string> read_input_lines(const std::string& path);
-void write_output_lines(const std::string& out_dir, const std::vector<std::string>& lines);
+void write_output_lines(const std::string& out_dir, const std::vector<std::string>& lines, int part = 0);
 
 // RAII wrapper over the kernel-level C-ABI; every failure becomes an exception carrying
 // avt_last_error().
