@@ -156,15 +156,17 @@ struct avt_engine {
     uint8_t order_cached[AVT_MAX_CLASSES];
     int order_cached_n = -1;        // classes covered by order_cached (-1: nothing uploaded yet)
     bool hist_pack = true;    // AVT_HIST_PACK=0: never use the bit-packed copy of the codes
-    bool hist_joint = true;   // AVT_HIST_JOINT=0: hist_smem_kernel instead of the joint-code kernel on packed schemas (A/B measurements)
+    bool hist_joint = false;  // the joint-code kernel (avt_joint.cuh) is chosen only when forced (avt_set_hist_variant(3)) or with AVT_HIST_JOINT=1:
+                              // its launches are shorter than hist_smem_kernel's (ncu: 193 vs 219 us over the 8 levels of C2) but the level
+                              // loop as a whole measured slower with it on the same box (0.312 vs 0.290 ms per step), see profiles/README.md
     bool lookback = true;     // AVT_LOOKBACK=0: the last scan block plans the level (ticket) even for small frontiers
-    bool peer_trailing_round = false;   // AVT_PEER_TRAIL=1: end every level loop with a round of flags over all ranks
+    bool peer_trailing_round = false;   // (round-1 experiment, kept off) end every level loop with a round of flags over all ranks
     bool scan_fast = true;    // AVT_SCAN_FAST=0: always the general scan kernel in the level loop
     bool pdl = true;          // AVT_PDL=0: plain stream launches in the level loop
     bool pdl_chain = false;   // the launch being issued directly follows a kernel of the level loop (no memset/copy between)
     bool profiling = true;  // CUDA-event timing of every launch (avt_set_profiling)
-    long long hist_target_addrs = 4096;  // AVT_HIST_TARGET_ADDRS
-    int hist_max_bpsm = 2;               // AVT_HIST_BPSM: histogram blocks per SM.  2 x 512 threads x 64 registers fill the register file, so more
+    long long hist_target_addrs = 4096;  // replication target of hist_smem_kernel: distinct words a warp's updates spread over
+    int hist_max_bpsm = 2;               // histogram blocks per SM.  2 x 512 threads x 64 registers fill the register file, so more
                                          // blocks only queue behind them and add flushes (measured on C2: 0.383 ms/step with 2, 0.403 with 4, 0.52 with 1)
     // comm
     ncclComm_t comm = nullptr;
@@ -198,7 +200,7 @@ struct avt_engine {
     uint32_t* H_cur = nullptr;         // histogram buffer of the pass being launched (nullptr: d_H)
     bool signal_pending = false;       // the pass being launched must signal peer.epoch to every rank
     bool peer_push = true;             // AVT_PEER_PUSH=0: always the pull form of the peer exchange
-    bool peer_signal_scan = true;      // AVT_PEER_SIGNAL_SCAN=0: the histogram pass's last block signals (fence + election in every block)
+    bool peer_signal_scan = true;      // the scan kernel's first block signals the peers (false: the histogram pass's last block does -- fence + election in every block, 4.5 us per level slower)
     bool scan_will_signal = false;     // set by the stream-ordered level loop around its launch_histogram call
     bool signal_in_hist = false;       // ... and did so from inside the histogram kernel
 };
@@ -364,17 +366,13 @@ int avt_create(int device, avt_engine** out) {
         delete e;
         return rc;
     }
-    if (const char* v = getenv("AVT_HIST_TARGET_ADDRS")) e->hist_target_addrs = std::max(1LL, atoll(v));
     if (const char* v = getenv("AVT_PDL")) e->pdl = atoi(v) != 0;
     if (const char* v = getenv("AVT_SCAN_FAST")) e->scan_fast = atoi(v) != 0;
-    if (const char* v = getenv("AVT_PEER_SIGNAL_SCAN")) e->peer_signal_scan = atoi(v) != 0;
     if (const char* v = getenv("AVT_PEER_PUSH")) e->peer_push = atoi(v) != 0;
-    if (const char* v = getenv("AVT_PEER_TRAIL")) e->peer_trailing_round = atoi(v) != 0;
     if (const char* v = getenv("AVT_LOOKBACK")) e->lookback = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_JOINT")) e->hist_joint = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract_mode = atoi(v) != 0 ? 1 : 0;
-    if (const char* v = getenv("AVT_HIST_BPSM")) e->hist_max_bpsm = std::min(4, std::max(1, atoi(v)));
     *out = e;
     return AVT_OK;
 }
@@ -977,7 +975,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
     // the frontier's joint counters; it has no form for skip marks and does not signal peers itself
     int j_J = 0;
     size_t j_smem = 0;
-    if (e->packed_ok && e->hist_joint && !e->skip_cur && (!e->signal_pending || (e->peer_signal_scan && e->scan_will_signal))) {
+    if (e->packed_ok && (e->hist_joint || e->force_variant == 3) && !e->skip_cur && (!e->signal_pending || (e->peer_signal_scan && e->scan_will_signal))) {
         int maxv = 0;
         for (int a = 0; a < e->A; ++a) maxv += (e->n_bins[a] - 1) << e->pk_shift[a];
         j_J = maxv + 1;
@@ -1621,9 +1619,10 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             }
         }
         if (pending) fr.prev_node_base = nb_level(level - 1);
-        // derivation needs this level's skip marks (from the previous planning) AND the previous level's complete
-        // counts in the same mode (single GPU <-> peer switches and reallocations lose them)
-        const bool derive = subtract && level > 0 && planned_skip && derive_ok && prev_peer == peer_level;
+        // derivation needs this level's skip marks (from the previous planning) AND the previous level's complete counts
+        // (reallocations lose them); the previous level may have been exchanged the other way (peer memory for small levels,
+        // NCCL for large ones): its complete counts are read from wherever that mode left them
+        const bool derive = subtract && level > 0 && planned_skip && derive_ok;
         if (subtract && level > 0 && planned_skip && !derive) {
             // the rows of "derived" nodes must be counted after all: clear the marks
             CUDA_TRY(e, cudaMemsetAsync(e->d_skip.p, 0, (size_t)NF, e->stream));
@@ -1720,7 +1719,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             if (derive) {
                 pa.drv_parent = e->d_drv_parent.p;
                 pa.prev_kids = e->d_kids.p;
-                pa.H_prev = peer_level ? hsum_level(level - 1) : H_level(level - 1);
+                pa.H_prev = prev_peer ? hsum_level(level - 1) : H_level(level - 1);
             }
             pa.H_mut = Hc;
             planned_skip = next_plannable;
@@ -1752,7 +1751,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
                     }
                     ft.pub = e->d_pub.p;
                     ft.epoch = ++e->scan_epoch;
-                    if (e->packed_ok && level + 1 < n_levels) {
+                    if (e->packed_ok && (e->hist_joint || e->force_variant == 3) && level + 1 < n_levels) {
                         // the next pass may be the joint-code kernel: have the node blocks expand their rows to packed bytes
                         int maxv = 0;
                         for (int a = 0; a < e->A; ++a) maxv += (e->n_bins[a] - 1) << e->pk_shift[a];

@@ -22,6 +22,15 @@
  *   - class codes uint8[n_rows];
  *   - per tree: node id uint16[n_rows] (AVT_NODE_NONE = row not in any frontier node) and an
  *     optional bootstrap multiplicity uint8[n_rows].
+ *
+ * Developer switches (environment variables read once by avt_create; they select between equivalent code paths for
+ * tests and A/B measurements and never change results; every rank of a multi-GPU job must run with the same values --
+ * ranks that disagree on the exchange form fail with AVT_E_COMM after the bounded wait instead of hanging):
+ *   AVT_SCAN_FAST=0   general scan kernel instead of the item-parallel one      AVT_LOOKBACK=0  ticket instead of look-back planning
+ *   AVT_HIST_PACK=0   one byte per attribute instead of the bit-packed codes      AVT_HIST_JOINT=1 joint-code histogram kernel on packed schemas
+ *   AVT_SUBTRACT=0|1  sibling subtraction off / on (default: on for >= 16 uint8 attributes)
+ *   AVT_PDL=0         plain stream launches instead of programmatic dependent launch
+ *   AVT_PEER_PUSH=0   pull form of the NVLink peer exchange                        AVT_PEER_OFF=1  avt_peer_import is ignored (NCCL only)
  */
 #ifndef AVENIR_TREE_H
 #define AVENIR_TREE_H

@@ -224,7 +224,7 @@ def test_api_misuse_is_reported():
         g.set_splits(t)                                  # bound outside the attribute's bins
 
 
-@pytest.mark.parametrize("mode", ["fast-scan-lookback", "general-scan-unpacked", "fast-scan-ticket"])
+@pytest.mark.parametrize("mode", ["fast-scan-lookback", "general-scan-unpacked", "fast-scan-ticket", "joint-code-histogram"])
 @pytest.mark.parametrize("criterion", [CRIT_GINI, CRIT_ENTROPY])
 def test_in_library_level_loop_equals_oracle(mode, criterion, monkeypatch):
     """avt_grow_levels (device-driven: fused repartition+histogram, scan, on-device planning) against the oracle's
@@ -238,6 +238,8 @@ def test_in_library_level_loop_equals_oracle(mode, criterion, monkeypatch):
     table = binary_split_table(n_bins, [True, True, True, False])
     weights = [None, rng.poisson(1.0, n).clip(0, 255).astype(np.uint8), None]
     g, o = make_pair(cols, cls, n_bins, 2, table, 3, weights, None)
+    if mode == "joint-code-histogram":
+        g.set_hist_variant(3)      # hist_joint_kernel at every level, its repartition table written by the scan kernel
     (rec, nrec), frontier = g.grow(7, criterion, [1, 1, 1], max_records=4096)
     ho, fo = grow_levels(o, table, 7, criterion, n_trees=3)
     want = [(lvl, t, nd, s, pops, av, ties) for lvl, level in enumerate(ho) for (t, nd, s, pops, av, ties) in level]
