@@ -72,6 +72,7 @@ SIGNATURES = {
     "avt_dataset_load_csv": (C.c_int, [_P, _P, C.c_int64, C.c_char, C.c_int32, C.c_int32, C.POINTER(CsvAttr), _P, _P, _P, _P,
                                       C.c_int32, C.c_int32, _P, _P, C.POINTER(C.c_int64), _P, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "avt_dataset_fetch_column": (C.c_int, [_P, C.c_int32, _P]),
+    "avt_rows_partition": (C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, C.c_int64, _P, _P]),
     "avt_forest_init": (C.c_int, [_P, C.c_int32, C.POINTER(_P), C.POINTER(_P)]),
     "avt_forest_init_sampled": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64, C.c_int64]),
     "avt_forest_weights": (C.c_int, [_P, C.c_int32, _P]),

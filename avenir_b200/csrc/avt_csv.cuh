@@ -14,6 +14,7 @@ namespace avt {
 
 constexpr int kCsvChunk = 128;          // bytes per thread of the line-indexing kernels
 constexpr int kCsvMaxFields = 1024;     // highest field index + 1 that may be referenced
+constexpr int kCsvNoClassField = -(1 << 20);   // CsvArgs::class_field of rows without a class field: no field index reaches it
 constexpr int kCsvSlowCap = 65536;      // values left to the host's strtod per call
 constexpr int kCsvStageBytes = 24 * 1024;   // text span of one block of rows staged in shared memory (longer spans: read in place)
 
@@ -203,6 +204,10 @@ __global__ void __launch_bounds__(128) csv_encode_kernel(const CsvArgs a) {
     int n_eff = 0;                  // (index of the last non-empty field + 1), in the same numbering
     int fail_attr = -1, fail_reason = 0;
     int class_state = 0;            // 0 not seen, 1 ok, 2 unknown value
+    if (a.class_field == kCsvNoClassField) {   // no class field: one class, code 0
+        a.cls[r] = 0;
+        class_state = 1;
+    }
     int s = 0;
     for (int i = 0; i <= len; ++i) {
         if (i < len && row[i] != a.delim) continue;
@@ -298,6 +303,50 @@ __global__ void csv_patch_kernel(const CsvPatch* patches, int n, void* const* co
     const CsvPatch p = patches[i];
     if (wide[p.attr]) ((uint16_t*)cols[p.attr])[p.row] = (uint16_t)p.bin;
     else ((uint8_t*)cols[p.attr])[p.row] = (uint8_t)p.bin;
+}
+
+// ---- rows of the encoded text, physically partitioned (avt_rows_partition; tree/DataPartitioner.java:325-352) ------------------
+// A row's segment is a table look-up on one attribute's bin code; the segment's output is its rows in input order, each
+// followed by '\n' (a '\r' in front of the source's line terminator is dropped, as LineRecordReader does).  Three small
+// kernels per call + one exclusive prefix sum and one copy kernel per segment; all of it streams at HBM rate.
+__global__ void rows_len_kernel(const char* text, const long long* line_start, long long n_rows, int32_t* len) {
+    const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_rows) return;
+    const long long s = line_start[r];
+    long long l = line_start[r + 1] - 1 - s;
+    if (l > 0 && text[s + l - 1] == '\r') --l;
+    len[r] = (int32_t)l + 1;   // content + the '\n' written behind it
+}
+
+template <typename CodeT>
+__global__ void rows_mask_kernel(const CodeT* codes, const uint16_t* seg_of_bin, const int32_t* len, long long n_rows, int seg, long long* masked,
+                                 unsigned long long* seg_rows) {
+    const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool mine = r < n_rows && seg_of_bin[codes[r]] == (uint16_t)seg;
+    if (r < n_rows) masked[r] = mine ? (long long)len[r] : 0LL;
+    const int c = __syncthreads_count(mine);
+    if (threadIdx.x == 0 && c) atomicAdd(seg_rows + seg, (unsigned long long)c);
+}
+
+// base[seg + 1] = base[seg] + bytes of segment `seg`
+template <typename CodeT>
+__global__ void rows_base_kernel(const CodeT* codes, const uint16_t* seg_of_bin, const int32_t* len, long long n_rows, int seg, const long long* off, long long* base) {
+    const long long last = n_rows - 1;
+    base[seg + 1] = base[seg] + off[last] + (seg_of_bin[codes[last]] == (uint16_t)seg ? (long long)len[last] : 0LL);
+}
+
+// one warp per row: coalesced byte copy of the row to its place in the segment
+template <typename CodeT>
+__global__ void __launch_bounds__(256) rows_copy_kernel(const char* text, const long long* line_start, const CodeT* codes, const uint16_t* seg_of_bin,
+                                                        const int32_t* len, long long n_rows, int seg, const long long* off, const long long* base, char* out) {
+    const long long r = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (r >= n_rows || seg_of_bin[codes[r]] != (uint16_t)seg) return;
+    const char* src = text + line_start[r];
+    char* dst = out + base[seg] + off[r];
+    const int l = len[r] - 1;
+    for (int i = lane; i < l; i += 32) dst[i] = src[i];
+    if (lane == 0) dst[l] = '\n';
 }
 
 }  // namespace avt

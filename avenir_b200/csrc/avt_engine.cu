@@ -97,6 +97,13 @@ struct avt_engine {
     DevBuf<unsigned long long> d_csv_first;
     DevBuf<long long> d_csv_lines, d_csv_ll;
     DevBuf<uint8_t> d_csv_tmp, d_csv_tables;
+    int rot_pf = 4;   // hist_rot_kernel: L2 prefetch distance in trees (AVT_ROT_PF)
+    long long csv_rows = 0, csv_bytes = 0;   // rows / bytes of the text the installed data set was encoded from (0: not from text)
+    // avt_rows_partition scratch: row lengths, per-segment offsets, segment bases and row counts, bin -> segment table, output text
+    DevBuf<int32_t> d_part_len;
+    DevBuf<long long> d_part_off, d_part_base;
+    DevBuf<uint16_t> d_part_lut;
+    DevBuf<char> d_part_out;
     // all attributes' codes in one byte per row (narrow schemas; see HistArgs::packed)
     DevBuf<uint8_t> d_packed;
     bool packed_ok = false;
@@ -373,6 +380,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_HIST_PACK")) e->hist_pack = atoi(v) != 0;
     if (const char* v = getenv("AVT_HIST_JOINT")) e->hist_joint = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract_mode = atoi(v) != 0 ? 1 : 0;
+    if (const char* v = getenv("AVT_ROT_PF")) e->rot_pf = std::max(0, std::min(64, atoi(v)));
     *out = e;
     return AVT_OK;
 }
@@ -400,7 +408,7 @@ void avt_destroy(avt_engine* e) {
     e->d_nid.release(); e->d_levels.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
-    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_pub.release(); e->d_packed.release(); e->d_rowrot.release(); e->d_av.release(); e->d_best.release();
+    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_part_len.release(); e->d_part_off.release(); e->d_part_base.release(); e->d_part_lut.release(); e->d_part_out.release(); e->d_pub.release(); e->d_packed.release(); e->d_rowrot.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_lut2.release(); e->d_cand[0].release(); e->d_cand[1].release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release(); e->d_ctrl.release();
     if (e->h_ctrl) cudaFreeHost(e->h_ctrl);
@@ -509,6 +517,7 @@ int avt_dataset_load(avt_engine* e, int64_t n_rows, int32_t n_attrs, const int32
     if (int rc = use_device(e)) return rc;
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.h2d_ms, &ts)) return rc;
+    e->csv_rows = 0;
     if (int rc = dataset_shape(e, n_rows, n_attrs, n_bins, n_classes, "avt_dataset_load")) return rc;
     for (int a = 0; a < n_attrs; ++a) {
         const size_t w = e->wide[a] ? 2 : 1;
@@ -529,13 +538,21 @@ int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char 
     if (!e) return AVT_E_INVALID;
     if (bad_row) *bad_row = -1;
     if (bad_reason) *bad_reason = 0;
+    const bool no_class = class_ordinal == -1;   // rows without a class field (DataPartitioner): one class, every row has code 0
+    static const int32_t kNoClassOffsets[2] = {0, 0};
+    if (no_class) {
+        if (n_class_values != 1) return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: class_ordinal -1 (no class field) needs n_class_values == 1");
+        class_bytes = "";
+        class_offsets = kNoClassOffsets;
+    }
     if (!text || n_bytes <= 0 || n_attrs <= 0 || !attrs || n_class_values < 1 || !class_bytes || !class_offsets || skip_fields < 0)
         return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: empty text or NULL argument");
     if (delim == '\n' || delim == '\r') return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: the field delimiter cannot be a line terminator");
-    if (class_ordinal < 0 || class_ordinal >= kCsvMaxFields) return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: class ordinal %d outside 0..%d", class_ordinal, kCsvMaxFields - 1);
+    if (class_ordinal < -1 || class_ordinal >= kCsvMaxFields) return fail(e, AVT_E_INVALID, "avt_dataset_load_csv: class ordinal %d outside -1..%d", class_ordinal, kCsvMaxFields - 1);
+    e->csv_rows = 0;   // the text of an earlier call is gone from here on (avt_rows_partition)
     // ---- tables: attribute of every field, grids, value lists with their byte-sorted permutations
     std::vector<int32_t> n_bins((size_t)n_attrs);
-    int n_int = 0, n_dbl = 0, n_cat = 0, max_ord = class_ordinal;
+    int n_int = 0, n_dbl = 0, n_cat = 0, max_ord = std::max(class_ordinal, 0);
     for (int a = 0; a < n_attrs; ++a) {
         const avt_csv_attr& A = attrs[a];
         if (A.ordinal < 0 || A.ordinal >= kCsvMaxFields || (a && A.ordinal <= attrs[a - 1].ordinal) || A.ordinal == class_ordinal)
@@ -636,7 +653,7 @@ int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char 
     ca.attrs = (const avt_csv_attr*)(tb + o_attrs); ca.field_attr = (const int16_t*)(tb + o_fa); ca.n_fields_used = (int)field_attr.size();
     ca.int_points = (const int32_t*)(tb + o_ip); ca.dbl_points = (const double*)(tb + o_dp);
     ca.cat_bytes = (const char*)(tb + o_cb); ca.cat_offsets = (const int32_t*)(tb + o_co); ca.cat_sorted = (const int32_t*)(tb + o_cs);
-    ca.class_field = class_ordinal; ca.n_class_values = n_class_values;
+    ca.class_field = no_class ? kCsvNoClassField : class_ordinal; ca.n_class_values = n_class_values;
     ca.class_bytes = (const char*)(tb + o_kb); ca.class_offsets = (const int32_t*)(tb + o_klo); ca.class_sorted = (const int32_t*)(tb + o_kls);
     ca.cols = (void* const*)e->d_colptrs.p; ca.wide = e->d_wide.p; ca.cls = e->d_cls.p;
     ca.class_first_row = e->d_csv_ll.p;
@@ -700,8 +717,10 @@ int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char 
         return fail(e, AVT_E_REFERENCE, "avt_dataset_load_csv: row %lld: %s", row, what[reason >= 1 && reason <= 5 ? reason : 0]);
     }
     if (class_first_row)
-        for (int k = 0; k < n_class_values; ++k) class_first_row[k] = back[(size_t)k] == 0x7fffffffffffffffLL ? -1 : back[(size_t)k];
+        for (int k = 0; k < n_class_values; ++k) class_first_row[k] = no_class ? 0 : back[(size_t)k] == 0x7fffffffffffffffLL ? -1 : back[(size_t)k];
     if (int rc = dataset_install(e)) return rc;
+    e->csv_rows = n_rows;   // d_csv_text / d_csv_lines stay valid for avt_rows_partition until the next data set is loaded
+    e->csv_bytes = n_bytes;
     if (int rc = timer_close(e, ts)) return rc;
     return sync_and_resolve(e);
 }
@@ -713,6 +732,69 @@ int avt_dataset_fetch_column(avt_engine* e, int32_t attr, void* out) {
     if (int rc = use_device(e)) return rc;
     if (attr < 0) CUDA_TRY(e, cudaMemcpyAsync(out, e->d_cls.p, (size_t)e->N, cudaMemcpyDeviceToHost, e->stream));
     else CUDA_TRY(e, cudaMemcpyAsync(out, e->cols[(size_t)attr], (size_t)e->N * (e->wide[(size_t)attr] ? 2 : 1), cudaMemcpyDeviceToHost, e->stream));
+    return sync_and_resolve(e);
+}
+
+}  // extern "C"
+
+template <typename CodeT>
+static int rows_partition_device(avt_engine* e, const CodeT* codes, int n_segments) {
+    const long long N = e->N;
+    const unsigned gb = (unsigned)((N + 255) / 256);
+    long long* base = e->d_part_base.p;
+    unsigned long long* seg_rows = reinterpret_cast<unsigned long long*>(base + n_segments + 1);
+    rows_len_kernel<<<gb, 256, 0, e->stream>>>(e->d_csv_text.p, e->d_csv_lines.p, N, e->d_part_len.p);
+    CUDA_TRY(e, cudaGetLastError());
+    size_t tmp_bytes = 0;
+    CUDA_TRY(e, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, e->d_part_off.p, e->d_part_off.p, (int)N, e->stream));
+    CUDA_TRY(e, e->d_csv_tmp.ensure(tmp_bytes));
+    for (int s = 0; s < n_segments; ++s) {
+        rows_mask_kernel<CodeT><<<gb, 256, 0, e->stream>>>(codes, e->d_part_lut.p, e->d_part_len.p, N, s, e->d_part_off.p, seg_rows);
+        CUDA_TRY(e, cub::DeviceScan::ExclusiveSum(e->d_csv_tmp.p, tmp_bytes, e->d_part_off.p, e->d_part_off.p, (int)N, e->stream));
+        rows_base_kernel<CodeT><<<1, 1, 0, e->stream>>>(codes, e->d_part_lut.p, e->d_part_len.p, N, s, e->d_part_off.p, base);
+        rows_copy_kernel<CodeT><<<(unsigned)((N * 32 + 255) / 256), 256, 0, e->stream>>>(e->d_csv_text.p, e->d_csv_lines.p, codes, e->d_part_lut.p, e->d_part_len.p, N, s,
+                                                                                          e->d_part_off.p, base, e->d_part_out.p);
+        CUDA_TRY(e, cudaGetLastError());
+    }
+    return AVT_OK;
+}
+
+extern "C" {
+
+int avt_rows_partition(avt_engine* e, int32_t attr, const uint16_t* segment_of_bin, int32_t n_segments, char* out_text, int64_t out_capacity,
+                       int64_t* segment_bytes, int64_t* segment_rows) {
+    if (!e) return AVT_E_INVALID;
+    if (e->N == 0 || e->csv_rows != e->N)
+        return fail(e, AVT_E_STATE, "avt_rows_partition: the installed data set was not encoded from text (avt_dataset_load_csv keeps the text on the device)");
+    if (attr < 0 || attr >= e->A || !segment_of_bin || n_segments < 1 || n_segments > 4096 || !segment_bytes)
+        return fail(e, AVT_E_INVALID, "avt_rows_partition: attribute %d / %d segments out of range, or NULL argument", attr, n_segments);
+    if (e->N >= (1LL << 31)) return fail(e, AVT_E_INVALID, "avt_rows_partition: more than 2^31 - 1 rows");
+    const int nb = e->n_bins[(size_t)attr];
+    for (int b = 0; b < nb; ++b)
+        if (segment_of_bin[b] != AVT_NODE_NONE && segment_of_bin[b] >= n_segments)
+            return fail(e, AVT_E_INVALID, "avt_rows_partition: bin %d maps to segment %d of %d", b, (int)segment_of_bin[b], n_segments);
+    if (int rc = use_device(e)) return rc;
+    CUDA_TRY(e, e->d_part_len.ensure((size_t)e->N));
+    CUDA_TRY(e, e->d_part_off.ensure((size_t)e->N));
+    CUDA_TRY(e, e->d_part_base.ensure(2 * (size_t)n_segments + 1));
+    CUDA_TRY(e, e->d_part_lut.ensure((size_t)nb));
+    CUDA_TRY(e, e->d_part_out.ensure((size_t)e->csv_bytes + 1));   // no row grows: its terminator becomes one '\n'; an open last row gains one
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_part_lut.p, segment_of_bin, (size_t)nb * sizeof(uint16_t), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_part_base.p, 0, (2 * (size_t)n_segments + 1) * sizeof(long long), e->stream));
+    if (int rc = e->wide[(size_t)attr] ? rows_partition_device<uint16_t>(e, (const uint16_t*)e->cols[(size_t)attr], n_segments)
+                                       : rows_partition_device<uint8_t>(e, (const uint8_t*)e->cols[(size_t)attr], n_segments))
+        return rc;
+    std::vector<long long> back(2 * (size_t)n_segments + 1);
+    CUDA_TRY(e, cudaMemcpyAsync(back.data(), e->d_part_base.p, back.size() * sizeof(long long), cudaMemcpyDeviceToHost, e->stream));
+    if (int rc = sync_and_resolve(e)) return rc;
+    for (int s = 0; s < n_segments; ++s) {
+        segment_bytes[s] = back[(size_t)s + 1] - back[(size_t)s];
+        if (segment_rows) segment_rows[s] = back[(size_t)n_segments + 1 + s];
+    }
+    const long long total = back[(size_t)n_segments];
+    if (!out_text) return AVT_OK;   // sizes only
+    if (out_capacity < total) return fail(e, AVT_E_INVALID, "avt_rows_partition: the segments hold %lld bytes, the output buffer %lld", total, (long long)out_capacity);
+    if (total) CUDA_TRY(e, cudaMemcpyAsync(out_text, e->d_part_out.p, (size_t)total, cudaMemcpyDeviceToHost, e->stream));
     return sync_and_resolve(e);
 }
 
@@ -1235,6 +1317,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         fa.tiles_per_part = tpp;
         dim3 grid((unsigned)groups, (unsigned)parts, (unsigned)achunks);
         fa.rowrot = e->d_rowrot.p;
+        fa.pf = e->rot_pf;
         fa.rowrot_rows = e->rowrot_rows;
         void (*kern)(const HistArgs, const ForestArgs) = e->any_w ? (fr ? hist_rot_kernel<true, true> : hist_rot_kernel<true, false>)
                                                                   : (fr ? hist_rot_kernel<false, true> : hist_rot_kernel<false, false>);

@@ -28,6 +28,7 @@ struct ForestArgs {
     int32_t* err;      // set to 4 when a tree has more counted nodes than n_slots (host bound violated)
     const uint8_t* rowrot;      // hist_rot_kernel: rotated row-major copy of the codes, [chunks][rowrot_rows][32]
     long long rowrot_rows;      // rows per chunk in `rowrot` (padded row count + one tile of slack)
+    int pf;            // node ids / multiplicities are pulled into L2 this many trees ahead of their use (0 = off)
 };
 
 // explicit shared-window accesses for the hot loops (a generic pointer into dynamic shared memory compiles to LD.E/ST.E)
@@ -46,6 +47,7 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
 }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void sts_v4(uint32_t addr, const uint4& v) {
     asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
@@ -174,6 +176,7 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
         nc1 = __ldg(src + 1);
         ncl = a.cls[row];
     };
+    const int pf_tiles = f.pf > 0 ? (f.pf + Gb - 1) / max(Gb, 1) : 0;
     long long tile = tile_lo + warp;
     if (tile < tile_hi) load_row(tile);
     for (; tile < tile_hi; tile += kForestWarps) {
@@ -206,6 +209,20 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
                 if (HAS_W && lds_u8(has_w_base + g)) w = w_row[(long long)g * a.Npad];
             }
         };
+        // L2 prefetch of the 64 + 32 bytes a (tile, tree) pair reads: `pf` trees ahead inside this tile, and the first trees of
+        // the tile this warp visits `pf_tiles` rounds from now (the two-tree register prefetch covers one DRAM latency at best;
+        // measured on C3 at 20 M rows x 100 trees: 140.7 -> 125.0 ms per step with pf = 4, the same with 8 and 16)
+        if (f.pf > 0 && (lane & 15) == 0) {   // lanes 0 and 16: the two 32-byte sectors of a tile's node ids
+            const long long ft = tile + (long long)pf_tiles * kForestWarps;
+            if (ft < tile_hi) {
+                const long long frow = (ft << 5) + lane;
+                const int ng = min(f.pf, Gb);
+                for (int g = 0; g < ng; ++g) {
+                    prefetch_l2(a.nid + (long long)(t0 + g) * a.Npad + frow);
+                    if (HAS_W && lane == 0) prefetch_l2(a.wts + (long long)(t0 + g) * a.Npad + frow);
+                }
+            }
+        }
         uint32_t n0, w0, n1, w1;
         fetch(0, n0, w0);
         fetch(1, n1, w1);
@@ -215,6 +232,10 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
             n0 = n1;
             w0 = w1;
             fetch(g + 2, n1, w1);
+            if (f.pf > 0 && (lane & 15) == 0 && g + f.pf < Gb) {
+                prefetch_l2(nid_row + (long long)(g + f.pf) * a.Npad);
+                if (HAS_W && lane == 0) prefetch_l2(w_row + (long long)(g + f.pf) * a.Npad);
+            }
             uint32_t s = 0xFFFFu;
             if (REPART) {
                 uint32_t e = 0xFFFFFFFFu;

@@ -54,13 +54,14 @@ extern "C" int avt_tool_run(const char* tool, int argc, const char* const* argv,
             const size_t cut = in.find_last_of('/');
             return run_class_partition_generator(conf, in, in.substr(0, cut) + "/splits");   // Utility.getSiblingPath(inPath, "splits")
         }
+        if (ends_with(name, "DataPartitioner")) return run_data_partitioner(conf);   // paths come from dap.project.base.path / dap.split.path
         if (positional.size() < 2) throw std::runtime_error("usage: <tool> -Dconf.path=<file.properties> [-Dkey=value ...] <inPath> <outPath>");
         if (ends_with(name, "DecisionTreeBuilder")) return run_decision_tree_builder(conf, positional[0], positional[1]);
         if (ends_with(name, "ClassPartitionGenerator")) return run_class_partition_generator(conf, positional[0], positional[1]);
         if (ends_with(name, "ModelPredictor")) return run_model_predictor(conf, positional[0], positional[1]);
         if (ends_with(name, "CramerCorrelation")) return run_cramer_correlation(conf, positional[0], positional[1]);
         if (ends_with(name, "HeterogeneityReductionCorrelation")) return run_heterogeneity_reduction_correlation(conf, positional[0], positional[1]);
-        throw std::runtime_error("unknown tool '" + name + "' (DecisionTreeBuilder | ClassPartitionGenerator | ModelPredictor | SplitGenerator | CramerCorrelation | HeterogeneityReductionCorrelation)");
+        throw std::runtime_error("unknown tool '" + name + "' (DecisionTreeBuilder | ClassPartitionGenerator | ModelPredictor | SplitGenerator | DataPartitioner | CramerCorrelation | HeterogeneityReductionCorrelation)");
     } catch (const ReferenceError& e) {
         set_err(errbuf, errlen, std::string("reference failure reproduced: ") + e.what());
     } catch (const Unsupported& e) {

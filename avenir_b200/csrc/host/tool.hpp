@@ -21,6 +21,9 @@ int run_cramer_correlation(const Props& conf, const std::string& in_path, const 
 // org.avenir.explore.HeterogeneityReductionCorrelation.run(args)  (explore/HeterogeneityReductionCorrelation.java:40-65)
 int run_heterogeneity_reduction_correlation(const Props& conf, const std::string& in_path, const std::string& out_path);
 
+// org.avenir.tree.DataPartitioner.run(args)  (tree/DataPartitioner.java:59-105); takes no path arguments
+int run_data_partitioner(const Props& conf);
+
 // Input "path" as Hadoop takes it: a file, or a directory whose regular files (not starting with
 // '_' or '.') are read in name order.
 std::vector<std::string> read_input_lines(const std::string& path);

@@ -171,7 +171,10 @@ class Engine:
                  skip_fields: int = 0):
         """avt_dataset_load_csv: CSV text -> data set, encoded on the device.  `attrs`: (ordinal, "int", [points]) |
         (ordinal, "double", [points]) | (ordinal, "categorical", [values]), ordinals increasing.  Returns
-        (n_rows, first row of every class value or -1).  A row the reference would throw on raises CsvRowError."""
+        (n_rows, first row of every class value or -1).  A row the reference would throw on raises CsvRowError.
+        class_ordinal = -1 (rows without a class field): class_values is ignored, every row gets class code 0."""
+        if class_ordinal < 0:
+            class_values = [""]
         spec = (_lib.CsvAttr * len(attrs))()
         ints, dbls, cat_bytes, cat_off, n_bins = [], [], b"", [], []
         for i, (ordinal, kind, vals) in enumerate(attrs):
@@ -210,6 +213,22 @@ class Engine:
         self.n_rows, self.n_bins, self.n_classes = int(n_rows.value), n_bins, len(class_values)
         self.total_bins = sum(n_bins)
         return self.n_rows, [int(x) for x in first]
+
+    def rows_partition(self, attr: int, segment_of_bin: Sequence[int], n_segments: int):
+        """avt_rows_partition: the rows of the text last given to load_csv, scattered on the device into `n_segments` byte
+        strings by segment_of_bin[bin code of `attr`] (AVT_NODE_NONE drops the row); returns ([bytes per segment], [rows])."""
+        lut = np.asarray(segment_of_bin, dtype=np.uint16)
+        seg_bytes = np.zeros(n_segments, dtype=np.int64)
+        seg_rows = np.zeros(n_segments, dtype=np.int64)
+        self._check(self.lib.avt_rows_partition(self.h, attr, _ptr(lut), n_segments, None, 0, _ptr(seg_bytes), _ptr(seg_rows)))
+        total = int(seg_bytes.sum())
+        out = np.empty(max(total, 1), dtype=np.uint8)
+        self._check(self.lib.avt_rows_partition(self.h, attr, _ptr(lut), n_segments, _ptr(out), total, _ptr(seg_bytes), _ptr(seg_rows)))
+        parts, at = [], 0
+        for b in seg_bytes:
+            parts.append(out[at:at + int(b)].tobytes())
+            at += int(b)
+        return parts, [int(r) for r in seg_rows]
 
     def fetch_column(self, attr: int) -> np.ndarray:
         """The installed data set's codes of one attribute (-1: class codes)."""

@@ -62,6 +62,11 @@ class HeterogeneityReductionCorrelation(_Tool):
     java_class = "org.avenir.explore.HeterogeneityReductionCorrelation"
 
 
+class DataPartitioner(_Tool):
+    """tree/DataPartitioner.java:59-105; takes its paths from dap.project.base.path / dap.split.path, not from arguments."""
+    java_class = "org.avenir.tree.DataPartitioner"
+
+
 def main(argv: List[str] | None = None) -> int:
     argv = list(sys.argv[1:] if argv is None else argv)
     if not argv:

@@ -166,7 +166,9 @@ typedef struct avt_csv_attr {
  *   skip_fields    leading fields that are not part of the record (1 for rows tagged with their path)
  *   attrs          n_attrs attributes, ordinals strictly increasing; numeric grids in int_points / dbl_points
  *                  (ascending), categorical values as bytes cat_bytes[cat_offsets[off+k] .. cat_offsets[off+k+1])
- *   class values   n_class_values strings, class_bytes[class_offsets[k] .. class_offsets[k+1]); class code = k
+ *   class values   n_class_values strings, class_bytes[class_offsets[k] .. class_offsets[k+1]); class code = k.
+ *                  class_ordinal == -1: the rows carry no class field (tree/DataPartitioner.java's input); pass
+ *                  n_class_values = 1, class_bytes / class_offsets may be NULL, every row gets class code 0
  *   class_first_row (nullable) [n_class_values]: first row each class value occurs in, -1 = never (lets the
  *                  caller rebuild the first-seen order the reference's HashMap insertion depends on)
  * On a row the reference would throw on, returns AVT_E_REFERENCE with *bad_row = the first such row and
@@ -183,6 +185,21 @@ int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char 
 /* Copies the installed data set's codes back: column `attr` (uint8 or uint16 per row, as in avt_dataset_load;
  * attr == -1: the class codes).  For tests and for callers that keep a host copy. */
 int avt_dataset_fetch_column(avt_engine* e, int32_t attr, void* out);
+
+/* Physically partitions the ROWS OF THE TEXT the installed data set was encoded from (the last avt_dataset_load_csv on this
+ * engine; the text and its line index stay on the device) by one attribute.  Replaces DataPartitioner's job
+ * (tree/DataPartitioner.java:325-352): PartitionerMapper keys every row with AttributeSplitHandler.Split.getSegmentIndex of
+ * its attribute value (util/AttributeSplitHandler.java:146-153, 190-204), the shuffle groups the rows by that key and
+ * PartitionerReducer writes them out unchanged, one part file per reducer.
+ *   attr             installed attribute (index into the attrs of avt_dataset_load_csv)
+ *   segment_of_bin   [n_bins of attr] segment of every bin code, AVT_NODE_NONE = rows of this bin are dropped
+ *   out_text         host buffer: the rows of segment 0 in input order, then segment 1, ...; every row is followed by
+ *                    '\n' (TextOutputFormat), a '\r' before the source's line terminator is not part of the row
+ *                    (LineRecordReader).  NULL: only the sizes are computed
+ *   segment_bytes    [n_segments] bytes of each segment in out_text;  segment_rows (nullable) [n_segments] its rows
+ * Fails with AVT_E_INVALID when out_capacity is smaller than the sum of segment_bytes (which are filled in). */
+int avt_rows_partition(avt_engine* e, int32_t attr, const uint16_t* segment_of_bin, int32_t n_segments,
+                       char* out_text, int64_t out_capacity, int64_t* segment_bytes, int64_t* segment_rows);
 
 /* Starts `n_trees` trees over the loaded rows.  weights == NULL or weights[t] == NULL means
  * multiplicity 1 for every row (dtb.sub.sampling.strategy=none); otherwise weights[t][r] is the

@@ -68,6 +68,8 @@ def encode_row(line: str, delim: str, attrs: Sequence[tuple], class_ordinal: int
             if raw not in vals:
                 return None, None, BAD_CATEGORY
             bins.append(list(vals).index(raw))
+    if class_ordinal < 0:      # rows without a class field (tree/DataPartitioner.java's input): one class, code 0
+        return bins, 0, 0
     if class_ordinal + skip_fields >= len(items):
         return None, None, BAD_SHORT_ROW
     c = items[class_ordinal + skip_fields]

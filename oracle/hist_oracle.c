@@ -569,7 +569,9 @@ static int encode_one(const csv_job* j, const char* row, int len, int64_t r) {
         }
         j->out_cols[a][r] = bin;
     }
-    {
+    if (j->class_ord < 0) { /* rows without a class field (tree/DataPartitioner.java's input): one class, code 0 */
+        j->out_cls[r] = 0;
+    } else {
         const int f = j->class_ord + j->skip;
         int c;
         if (f >= nf) return 0;

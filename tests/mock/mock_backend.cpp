@@ -47,6 +47,7 @@ struct avt_engine {
     std::vector<int32_t> bounds;
     std::vector<uint8_t> lut;
     std::vector<double> av;
+    std::string csv_text;   // text of the last avt_dataset_load_csv (empty: the data set did not come from text)
     avt_stats stats{};
 };
 
@@ -70,6 +71,30 @@ int avt_dataset_load(avt_engine* e, int64_t n, int32_t A, const int32_t* nb, con
         else { e->col8[a].assign((const uint8_t*)columns[a], (const uint8_t*)columns[a] + n); e->cols[a] = e->col8[a].data(); }
     }
     e->cls.assign(cc, cc + n);
+    e->csv_text.clear();
+    return 0;
+}
+int avt_rows_partition(avt_engine* e, int32_t attr, const uint16_t* seg_of_bin, int32_t n_seg, char* out, int64_t cap, int64_t* seg_bytes, int64_t* seg_rows) {
+    // plain restatement: rows in input order per segment, '\r' before the terminator dropped, every row ends in '\n'
+    if (e->csv_text.empty()) { e->err = "avt_rows_partition (mock): no text"; return AVT_E_STATE; }
+    std::vector<std::string> seg((size_t)n_seg);
+    std::vector<int64_t> rows((size_t)n_seg, 0);
+    size_t pos = 0;
+    for (int64_t r = 0; r < e->N; ++r) {
+        size_t nl = e->csv_text.find('\n', pos);
+        if (nl == std::string::npos) nl = e->csv_text.size();
+        size_t end = nl;
+        if (end > pos && e->csv_text[end - 1] == '\r') --end;
+        const unsigned code = e->n_bins[attr] > 256 ? e->col16[attr][(size_t)r] : e->col8[attr][(size_t)r];
+        const uint16_t s = seg_of_bin[code];
+        if (s != AVT_NODE_NONE) { seg[s].append(e->csv_text, pos, end - pos); seg[s] += '\n'; ++rows[s]; }
+        pos = nl + 1;
+    }
+    int64_t total = 0;
+    for (int s = 0; s < n_seg; ++s) { seg_bytes[s] = (int64_t)seg[(size_t)s].size(); if (seg_rows) seg_rows[s] = rows[(size_t)s]; total += seg_bytes[s]; }
+    if (!out) return 0;
+    if (cap < total) { e->err = "avt_rows_partition (mock): output buffer too small"; return AVT_E_INVALID; }
+    for (int s = 0; s < n_seg; ++s) { memcpy(out, seg[(size_t)s].data(), seg[(size_t)s].size()); out += seg[(size_t)s].size(); }
     return 0;
 }
 int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char delim, int32_t skip, int32_t A, const avt_csv_attr* attrs, const int32_t* ip,
@@ -103,7 +128,9 @@ int avt_dataset_load_csv(avt_engine* e, const char* text, int64_t n_bytes, char 
         for (int k = 0; k < n_class; ++k) first_row[k] = -1;
         for (int64_t r = 0; r < n; ++r) if (first_row[cls[(size_t)r]] < 0) first_row[cls[(size_t)r]] = r;
     }
-    return avt_dataset_load(e, n, A, nb.data(), cols.data(), cls.data(), n_class);
+    const int rc2 = avt_dataset_load(e, n, A, nb.data(), cols.data(), cls.data(), n_class);
+    e->csv_text.assign(text, (size_t)n_bytes);
+    return rc2;
 }
 int avt_forest_init(avt_engine* e, int32_t T, const uint8_t* const* weights, const uint16_t* const* node_ids) {
     e->T = T; e->nid.assign(T, {}); e->w.assign(T, {});

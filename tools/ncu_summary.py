@@ -18,6 +18,9 @@ def main(path, note=""):
     hi = [i for i, r in enumerate(rows) if r and r[0] == "ID"][0]
     hdr = rows[hi]
     idx = {h: i for i, h in enumerate(hdr)}
+    units = rows[hi + 1]
+    # ncu picks the unit per column (ns/us/ms, byte/Kbyte/Mbyte/Gbyte): bring durations to ns and sizes to bytes first
+    UNIT = {"ns": 1.0, "us": 1e3, "usecond": 1e3, "ms": 1e6, "msecond": 1e6, "s": 1e9, "second": 1e9, "byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
     if note:
         print(note)
     print("kernel | " + " | ".join(n for _, n, _ in COLS))
@@ -28,7 +31,7 @@ def main(path, note=""):
         for key, _, sc in COLS:
             v = r[idx[key]] if key in idx else ""
             try:
-                v = float(v.replace(",", "")) * sc
+                v = float(v.replace(",", "")) * sc * (UNIT.get(units[idx[key]], 1.0) if key in idx and idx[key] < len(units) else 1.0)
                 v = f"{v:.2f}" if sc != 1 or v != int(v) else f"{int(v)}"
             except ValueError:
                 pass
