@@ -16,6 +16,7 @@
 //   avt.forest.num.trees (1)  bagged trees built together, one launch per level for all of them
 //   avt.random.seed      (0)  seed of the java.util.Random stream that replaces Math.random()
 //   avt.device           (0)  CUDA device ordinal
+//   avt.encode      (device)  device: the first pass hands the rows' text to avt_dataset_load_csv; host: the C++ encoder below
 #include <dirent.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -332,6 +333,7 @@ class DtbJob {
     std::vector<std::vector<uint8_t>> col8_;
     std::vector<std::vector<uint16_t>> col16_;
     std::vector<uint8_t> cls_;
+    bool device_encode_ = false;   // the rows are encoded by avt_dataset_load_csv (first pass over untagged rows); the host keeps the text only
     std::vector<Tree> trees_;
     std::vector<int> layer_tree_;    // device layer (engine tree) -> reference tree
     // Row sharding over several GPUs (avt.num.ranks > 1; one process per GPU, launched like the ranks of any multi-GPU job):
@@ -363,7 +365,12 @@ public:
             if (!arr || arr->kind != Json::Arr) throw ReferenceError("NullPointerException: decision path list has no decisionPaths");
             for (auto& pj : arr->arr) dec_in.push_back(path_from_json(pj));
         }
-        encode(lines, tree_available, row_tagged);
+        // Encoding (avt.encode = device | host, default device): the first pass over untagged rows hands the text to the device
+        // encoder after one light host pass that only collects the class values in first-seen order -- the
+        // schemas do not list them (call_hangup.json's class field has no cardinality) and the reference's HashMap order
+        // depends on it.  Tagged rows (passes that resume from a tree file) need their path strings on the host anyway.
+        device_encode_ = conf_.get("avt.encode", "device") == "device" && !tree_available && class_pass_for_device_encode(lines);
+        if (!device_encode_) encode(lines, tree_available, row_tagged);
         lo_ = rows_.size() * (size_t)rank_ / (size_t)n_ranks_;
         hi_ = rows_.size() * (size_t)(rank_ + 1) / (size_t)n_ranks_;
         if (hi_ == lo_) throw Unsupported("rank " + std::to_string(rank_) + " of " + std::to_string(n_ranks_) + " has no rows");
@@ -507,6 +514,111 @@ private:
         classes_.finish();
     }
 
+    // Device encoding is possible when the delimiter is one literal byte and the attributes come in field order.  Collects the
+    // class values (first-seen order) by walking every row up to its class field only; returns false -- the caller then runs the
+    // host encoder, which also raises the reference's exception for the row -- on anything the two encoders could treat differently.
+    bool class_pass_for_device_encode(const std::vector<std::string>& lines) {
+        if (lines.empty() || delim_regex_.size() != 1) return false;
+        int prev = -1;
+        for (auto& as : attrs_) {
+            if (as.ordinal <= prev || as.ordinal == class_ord_ || as.ordinal >= 1024) return false;
+            prev = as.ordinal;
+            for (long long p : as.int_points)
+                if (p < -2147483647LL - 1 || p > 2147483647LL) return false;
+        }
+        if (class_ord_ < 0 || class_ord_ >= 1024) return false;
+        const char d = delim_regex_[0];
+        ClassTable found;
+        for (auto& ln : lines) {
+            size_t pos = 0;
+            for (int f = 0; f < class_ord_; ++f) {
+                const size_t q = ln.find(d, pos);
+                if (q == std::string::npos) return false;   // short row: the host encoder decides which exception comes first
+                pos = q + 1;
+            }
+            size_t end = ln.find(d, pos);
+            if (end == std::string::npos) end = ln.size();
+            if (end == pos || ln.find('\n') != std::string::npos) return false;   // empty class value: String.split(regex, -1) keeps it, the device encoder's split does not
+            try {
+                found.code_of(ln.substr(pos, end - pos));
+            } catch (const Unsupported&) {
+                return false;
+            }
+        }
+        classes_ = found;
+        classes_.finish();
+        rows_ = lines;
+        return true;
+    }
+
+    void upload_text() {
+        std::string text;
+        size_t bytes = 0;
+        for (size_t r = lo_; r < hi_; ++r) bytes += rows_[r].size() + 1;
+        text.reserve(bytes);
+        for (size_t r = lo_; r < hi_; ++r) {
+            text += rows_[r];
+            text += '\n';
+        }
+        std::vector<avt_csv_attr> spec;
+        std::vector<int32_t> ip, cat_off, cls_off;
+        std::vector<double> dp;
+        std::string cat_bytes, cls_bytes;
+        for (auto& as : attrs_) {
+            if (as.numeric && !as.dbl) {
+                spec.push_back(avt_csv_attr{as.ordinal, AVT_CSV_INT, (int32_t)as.int_points.size(), (int32_t)ip.size()});
+                for (long long p : as.int_points) ip.push_back((int32_t)p);
+            } else if (as.numeric) {
+                spec.push_back(avt_csv_attr{as.ordinal, AVT_CSV_DOUBLE, (int32_t)as.dbl_points.size(), (int32_t)dp.size()});
+                dp.insert(dp.end(), as.dbl_points.begin(), as.dbl_points.end());
+            } else {
+                spec.push_back(avt_csv_attr{as.ordinal, AVT_CSV_CATEGORICAL, (int32_t)as.field->cardinality.size(), (int32_t)cat_off.size()});
+                for (auto& v : as.field->cardinality) {
+                    cat_off.push_back((int32_t)cat_bytes.size());
+                    cat_bytes += v;
+                }
+            }
+        }
+        cat_off.push_back((int32_t)cat_bytes.size());
+        for (auto& v : classes_.names) {
+            cls_off.push_back((int32_t)cls_bytes.size());
+            cls_bytes += v;
+        }
+        cls_off.push_back((int32_t)cls_bytes.size());
+        int64_t n_rows = 0, bad_row = -1;
+        int32_t bad_reason = 0;
+        const int rc = avt_dataset_load_csv(eng_->raw(), text.data(), (int64_t)text.size(), delim_regex_[0], 0, (int32_t)spec.size(), spec.data(), ip.data(), dp.data(),
+                                            cat_bytes.data(), cat_off.data(), class_ord_, (int32_t)classes_.names.size(), cls_bytes.data(), cls_off.data(), &n_rows,
+                                            nullptr, &bad_row, &bad_reason);
+        if (rc == AVT_E_REFERENCE && bad_row >= 0) {
+            // a row the reference throws on: the host encoder walks the rows in order and raises that exception with its message
+            std::vector<std::vector<std::string>> unused;
+            std::vector<std::string> lines = rows_;
+            encode(lines, false, unused);
+            throw std::runtime_error("the device encoder rejected row " + std::to_string(lo_ + (size_t)bad_row) + " but the host encoder accepts it");
+        }
+        eng_->check(rc);
+        if ((size_t)n_rows != n_local()) throw std::runtime_error("the device encoder saw " + std::to_string(n_rows) + " rows, the host " + std::to_string(n_local()));
+    }
+
+    // bin codes of one attribute for this rank's rows on the host (multi-way spawns): fetched from the device when it did the encoding
+    void need_host_column(size_t a) {
+        if (!device_encode_) return;
+        if (col8_.size() != attrs_.size()) {
+            col8_.assign(attrs_.size(), {});
+            col16_.assign(attrs_.size(), {});
+        }
+        const bool wide = attrs_[a].n_bins > 256;
+        if (wide ? !col16_[a].empty() : !col8_[a].empty()) return;
+        if (wide) {
+            col16_[a].assign(rows_.size(), 0);
+            eng_->check(avt_dataset_fetch_column(eng_->raw(), (int32_t)a, col16_[a].data() + lo_));
+        } else {
+            col8_[a].assign(rows_.size(), 0);
+            eng_->check(avt_dataset_fetch_column(eng_->raw(), (int32_t)a, col8_[a].data() + lo_));
+        }
+    }
+
     // NCCL rendezvous through a file both ranks can see (avt.comm.id.file, default <decision file out>.ncclid): rank 0 creates the
     // 128-byte id and publishes it with an atomic rename, the others poll for it.  Any launcher that starts one process per GPU
     // with avt.rank / avt.num.ranks set (torchrun, mpirun, a shell loop) works; nothing else is exchanged on the host side.
@@ -537,13 +649,17 @@ private:
     }
 
     void upload() {
-        std::vector<int32_t> nb;
-        std::vector<const void*> cols;
-        for (size_t a = 0; a < attrs_.size(); ++a) {
-            nb.push_back(attrs_[a].n_bins);
-            cols.push_back(attrs_[a].n_bins > 256 ? (const void*)(col16_[a].data() + lo_) : (const void*)(col8_[a].data() + lo_));
+        if (device_encode_) {
+            upload_text();
+        } else {
+            std::vector<int32_t> nb;
+            std::vector<const void*> cols;
+            for (size_t a = 0; a < attrs_.size(); ++a) {
+                nb.push_back(attrs_[a].n_bins);
+                cols.push_back(attrs_[a].n_bins > 256 ? (const void*)(col16_[a].data() + lo_) : (const void*)(col8_[a].data() + lo_));
+            }
+            eng_->check(avt_dataset_load(eng_->raw(), (int64_t)n_local(), (int32_t)attrs_.size(), nb.data(), cols.data(), cls_.data() + lo_, (int32_t)classes_.names.size()));
         }
-        eng_->check(avt_dataset_load(eng_->raw(), (int64_t)n_local(), (int32_t)attrs_.size(), nb.data(), cols.data(), cls_.data() + lo_, (int32_t)classes_.names.size()));
         eng_->check(avt_split_table_set(eng_->raw(), (int32_t)table_.splits.size(), table_.splits.data(), table_.bounds.data(), (int32_t)table_.bounds.size(),
                                         table_.lut.data(), (int64_t)table_.lut.size()));
     }
@@ -1060,6 +1176,7 @@ private:
                 const auto& pn = parent_nid[sp.parent_layer];
                 std::vector<uint16_t> v(n_local(), (uint16_t)AVT_NODE_NONE);
                 const bool wide = attrs_[(size_t)sp.attr].n_bins > 256;
+                need_host_column((size_t)sp.attr);
                 for (size_t r = 0; r < n_local(); ++r) {
                     if (pn[r] != (uint16_t)sp.parent_id) continue;
                     const int b = wide ? col16_[(size_t)sp.attr][lo_ + r] : col8_[(size_t)sp.attr][lo_ + r];

@@ -74,6 +74,12 @@ int avt_dataset_load(avt_engine* e, int64_t n, int32_t A, const int32_t* nb, con
     e->csv_text.clear();
     return 0;
 }
+int avt_dataset_fetch_column(avt_engine* e, int32_t attr, void* out) {
+    if (attr < 0) memcpy(out, e->cls.data(), (size_t)e->N);
+    else if (e->n_bins[attr] > 256) memcpy(out, e->col16[attr].data(), (size_t)e->N * 2);
+    else memcpy(out, e->col8[attr].data(), (size_t)e->N);
+    return 0;
+}
 int avt_rows_partition(avt_engine* e, int32_t attr, const uint16_t* seg_of_bin, int32_t n_seg, char* out, int64_t cap, int64_t* seg_bytes, int64_t* seg_rows) {
     // plain restatement: rows in input order per segment, '\r' before the terminator dropped, every row ends in '\n'
     if (e->csv_text.empty()) { e->err = "avt_rows_partition (mock): no text"; return AVT_E_STATE; }

@@ -366,3 +366,31 @@ def test_split_generator_is_cpg_on_the_project_layout(hostmock, tmp_path):
     _props(str(tmp_path / "bad.properties"), {k: v for k, v in conf.items() if k != "project.base.path"})
     rc, err = helpers.tool_run(hostmock, "org.avenir.tree.SplitGenerator", [f"-Dconf.path={tmp_path}/bad.properties"])
     assert rc == 1 and "base path not defined" in err
+
+
+def test_device_and_host_encoders_give_the_same_job_output(hostmock, tmp_path):
+    """avt.encode=device (default: the rows' text goes to avt_dataset_load_csv) and avt.encode=host (the C++ encoder) must
+    write byte-identical model files and part files, also on a schema with double attributes and multi-way splits."""
+    rng = random.Random(21)
+    schema, lines = random_schema_and_rows(rng, 900)
+    outs = {}
+    for mode in ("device", "host"):
+        d = os.path.join(str(tmp_path), mode)
+        os.makedirs(d)
+        sp = os.path.join(d, "schema.json")
+        json.dump(schema, open(sp, "w"))
+        data = os.path.join(d, "in.txt")
+        open(data, "w").write("\n".join(lines) + "\n")
+        pp = os.path.join(d, "job.properties")
+        _props(pp, {"dtb.feature.schema.file.path": sp, "dtb.decision.file.path.out": os.path.join(d, "dec.json"), "dtb.split.algorithm": "giniIndex",
+                    "dtb.path.stopping.strategy": "maxDepth", "dtb.max.depth.limit": "4", "dtb.split.attribute.selection.strategy": "notUsedYet",
+                    "dtb.sub.sampling.strategy": "none"})
+        rc, err = helpers.tool_run(hostmock, DTB, [f"-Dconf.path={pp}", "-Davt.dtb.num.levels=3", f"-Davt.encode={mode}", data, os.path.join(d, "out")])
+        assert rc == 0, err
+        files = {}
+        for root, _, names in os.walk(d):
+            for n in names:
+                if n.startswith("dec.json") or n.startswith("part-r-"):
+                    files[os.path.relpath(os.path.join(root, n), d)] = open(os.path.join(root, n)).read().replace(d, "")
+        outs[mode] = files
+    assert outs["device"] == outs["host"] and any(k.startswith("dec.json.level") for k in outs["device"])
