@@ -3,6 +3,7 @@
 // a CUDA device and fails with AVT_E_CUDA when there is none.
 #include <cuda_runtime.h>
 #include <nccl.h>
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include <algorithm>
@@ -98,6 +99,12 @@ struct avt_engine {
     DevBuf<long long> d_csv_lines, d_csv_ll;
     DevBuf<uint8_t> d_csv_tmp, d_csv_tables;
     int rot_pf = 4;   // hist_rot_kernel: L2 prefetch distance in trees (AVT_ROT_PF)
+    // hist_sorted_kernel (avt_sorted.cuh): 0 off, 1 instead of the global-atomics fallback, 2 whenever hist_rot_kernel does not fit (AVT_HIST_SORTED)
+    int hist_sorted = 2;
+    DevBuf<uint16_t> d_skeys;
+    DevBuf<uint32_t> d_siota, d_sperm;
+    DevBuf<uint8_t> d_scls, d_sw, d_stmp;
+    long long siota_rows = 0;
     long long csv_rows = 0, csv_bytes = 0;   // rows / bytes of the text the installed data set was encoded from (0: not from text)
     // avt_rows_partition scratch: row lengths, per-segment offsets, segment bases and row counts, bin -> segment table, output text
     DevBuf<int32_t> d_part_len;
@@ -381,6 +388,7 @@ int avt_create(int device, avt_engine** out) {
     if (const char* v = getenv("AVT_HIST_JOINT")) e->hist_joint = atoi(v) != 0;
     if (const char* v = getenv("AVT_SUBTRACT")) e->subtract_mode = atoi(v) != 0 ? 1 : 0;
     if (const char* v = getenv("AVT_ROT_PF")) e->rot_pf = std::max(0, std::min(64, atoi(v)));
+    if (const char* v = getenv("AVT_HIST_SORTED")) e->hist_sorted = std::max(0, std::min(2, atoi(v)));
     *out = e;
     return AVT_OK;
 }
@@ -408,7 +416,7 @@ void avt_destroy(avt_engine* e) {
     e->d_nid.release(); e->d_levels.release(); e->d_nid2.release(); e->d_nb_all.release(); e->d_ticket.release(); e->d_prev_node_base.release(); e->d_next_count.release(); e->d_err.release(); e->d_best_eval.release(); e->d_records.release(); e->d_w.release(); e->d_has_w.release(); e->d_node_base.release();
     e->d_pmask.release(); e->d_pmoff.release(); e->d_pint.release(); e->d_ppoff.release(); e->d_pcls.release(); e->d_pout.release(); e->d_pw.release();
     e->d_H.release(); e->d_grp.release(); e->d_splits.release(); e->d_bounds.release();
-    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_part_len.release(); e->d_part_off.release(); e->d_part_base.release(); e->d_part_lut.release(); e->d_part_out.release(); e->d_pub.release(); e->d_packed.release(); e->d_rowrot.release(); e->d_av.release(); e->d_best.release();
+    e->d_attr_first.release(); e->d_seg_lut.release(); e->d_items.release(); e->d_seg_first.release(); e->d_nkids.release(); e->d_csv_text.release(); e->d_csv_counts.release(); e->d_csv_first.release(); e->d_csv_lines.release(); e->d_csv_ll.release(); e->d_csv_tmp.release(); e->d_csv_tables.release(); e->d_part_len.release(); e->d_part_off.release(); e->d_part_base.release(); e->d_part_lut.release(); e->d_part_out.release(); e->d_skeys.release(); e->d_siota.release(); e->d_sperm.release(); e->d_scls.release(); e->d_sw.release(); e->d_stmp.release(); e->d_pub.release(); e->d_packed.release(); e->d_rowrot.release(); e->d_av.release(); e->d_best.release();
     e->d_mask.release(); e->d_lut2.release(); e->d_cand[0].release(); e->d_cand[1].release(); e->d_order.release(); e->d_pairs.release(); e->d_eval.release();
     e->d_cpg.release(); e->d_ccnt.release(); e->d_node_attr.release(); e->d_lut.release(); e->d_ctrl.release();
     if (e->h_ctrl) cudaFreeHost(e->h_ctrl);
@@ -1053,6 +1061,15 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         }
         if (f_G >= 1 && e->force_variant < 0 && variant == 0) variant = 2;
     }
+    // sorted-rows kernel (avt_sorted.cuh): one tree, the rotated copy, a frontier whose counters hist_rot_kernel cannot hold
+    int s_S = 0;
+    {
+        const size_t per_node = (size_t)e->C * max_bins * 128;
+        const bool usable = e->T == 1 && e->rowrot_ok && max_bins <= 256 && e->N < (1LL << 31) && per_node * 2 <= kMaxDynSmem && !e->signal_pending;
+        if (usable) s_S = (int)std::min<size_t>(std::min<size_t>(kMaxDynSmem / 2 / per_node, 8), (size_t)std::max(n_max, 1));
+        if (s_S >= 1 && ((e->force_variant < 0 && f_G == 0 && (e->hist_sorted == 2 || (e->hist_sorted == 1 && variant == 1))) || e->force_variant == 4)) variant = 4;
+        else s_S = 0;
+    }
     // joint-code kernel (avt_joint.cuh): the data set has a packed copy (<= 4 narrow attributes in one byte) and one block can hold
     // the frontier's joint counters; it has no form for skip marks and does not signal peers itself
     int j_J = 0;
@@ -1071,6 +1088,8 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
             return fail(e, AVT_E_INVALID, "avt_level_histogram: joint-code variant forced but it needs a packed data set (<= 4 narrow attributes) and the frontier's joint counters in shared memory");
         if (e->force_variant == 0 && variant == 1)
             return fail(e, AVT_E_INVALID, "avt_level_histogram: shared-memory variant forced but the frontier needs %lld words", per_bin * max_bins);
+        if (e->force_variant == 4 && s_S == 0)
+            return fail(e, AVT_E_INVALID, "avt_level_histogram: sorted-rows variant forced but it needs one tree, >= 16 uint8 attributes and two nodes' counters in shared memory");
         if (e->force_variant == 2 && f_G == 0)
             return fail(e, AVT_E_INVALID, "avt_level_histogram: forest variant forced but it needs >= 16 attributes, uint8 codes and one tree's counters in shared memory");
         variant = e->force_variant;
@@ -1081,8 +1100,8 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         CUDA_TRY(e, e->d_nid2.ensure((size_t)e->T * e->Npad + 32));
         nid_out = (e->nid_cur == e->d_nid.p) ? e->d_nid2.p : e->d_nid.p;
     }
-    if (fr && variant == 1) {
-        // the global-atomics fallback has no fused form: repartition in place first
+    if (fr && (variant == 1 || variant == 4)) {
+        // the global-atomics fallback and the sorted-rows kernel have no fused form: repartition in place first
         TimerSlot tr;
         if (int rc = timer_open(e, &e->stats.repart_ms, &tr)) return rc;
         long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
@@ -1337,6 +1356,49 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         e->stats.last_hist_grid = (int)(grid.x * grid.y * grid.z);
         e->stats.last_hist_block = kForestThreads;
         e->stats.last_hist_smem = (int)f_smem;
+    } else if (variant == 4) {
+        // node-contiguous row order: radix sort of (node id, row) pairs, class / multiplicity copies in that order, then spans
+        const long long N = e->N;
+        CUDA_TRY(e, e->d_skeys.ensure((size_t)N));
+        CUDA_TRY(e, e->d_sperm.ensure((size_t)N));
+        CUDA_TRY(e, e->d_scls.ensure((size_t)N));
+        if (e->any_w) CUDA_TRY(e, e->d_sw.ensure((size_t)N));
+        const unsigned gb = (unsigned)((N + 255) / 256);
+        if (e->siota_rows != N) {
+            CUDA_TRY(e, e->d_siota.ensure((size_t)N));
+            iota_kernel<<<gb, 256, 0, e->stream>>>(e->d_siota.p, N);
+            e->siota_rows = N;
+        }
+        size_t tmp_bytes = 0;
+        CUDA_TRY(e, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (const uint16_t*)nid_in, e->d_skeys.p, (const uint32_t*)e->d_siota.p, e->d_sperm.p, (int)N, 0, 16, e->stream));
+        CUDA_TRY(e, e->d_stmp.ensure(tmp_bytes));
+        CUDA_TRY(e, cub::DeviceRadixSort::SortPairs(e->d_stmp.p, tmp_bytes, (const uint16_t*)nid_in, e->d_skeys.p, (const uint32_t*)e->d_siota.p, e->d_sperm.p, (int)N, 0, 16, e->stream));
+        sorted_gather_kernel<<<gb, 256, 0, e->stream>>>(e->d_sperm.p, e->d_cls.p, e->any_w ? e->d_w.p : nullptr, N, e->d_scls.p, e->d_sw.p);
+        SortedArgs sa{};
+        sa.keys = e->d_skeys.p; sa.perm = e->d_sperm.p; sa.cls_s = e->d_scls.p; sa.w_s = e->d_sw.p;
+        sa.rowrot = e->d_rowrot.p; sa.rowrot_rows = e->rowrot_rows;
+        sa.bin_off = e->d_bin_off.p; sa.skip = e->skip_cur; sa.H = Hbuf;
+        sa.N = N; sa.A = e->A; sa.Bmax = max_bins; sa.S = s_S; sa.TB = e->TB; sa.C = e->C;
+        const int achunks = (e->A + 31) / 32;
+        const size_t smem = (size_t)s_S * e->C * max_bins * 128;
+        const int bpsm = (int)std::max<size_t>(1, std::min<size_t>(4, kMaxDynSmem / std::max<size_t>(smem, 1)));
+        // spans: about four waves of blocks over all chunks, at least 2048 positions each
+        long long spans = std::max<long long>(1, ((long long)e->sm_count * bpsm * 4 + achunks - 1) / achunks);
+        sa.span = std::max<long long>(2048, (N + spans - 1) / spans);
+        sa.span = (sa.span + 31) / 32 * 32;
+        spans = (N + sa.span - 1) / sa.span;
+        dim3 grid((unsigned)spans, (unsigned)achunks);
+        if (e->any_w) {
+            CUDA_TRY(e, cudaFuncSetAttribute(hist_sorted_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+            hist_sorted_kernel<true><<<grid, kSortedThreads, smem, e->stream>>>(sa);
+        } else {
+            CUDA_TRY(e, cudaFuncSetAttribute(hist_sorted_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+            hist_sorted_kernel<false><<<grid, kSortedThreads, smem, e->stream>>>(sa);
+        }
+        e->stats.last_hist_replicas = s_S;
+        e->stats.last_hist_grid = (int)(grid.x * grid.y);
+        e->stats.last_hist_block = kSortedThreads;
+        e->stats.last_hist_smem = (int)smem;
     } else {
         long long blocks = std::min<long long>((e->N + 255) / 256, (long long)e->sm_count * 8);
         dim3 grid((unsigned)blocks, (unsigned)e->T);
@@ -1904,6 +1966,14 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             const long long tiles = (e->N + 256 * kRowsPerThread - 1) / (256 * kRowsPerThread);
             dim3 grid((unsigned)std::min<long long>(tiles, std::max<long long>(1, (long long)e->sm_count * 8 / T)), (unsigned)T);
             repartition_fast_kernel<<<grid, 256, tbl, e->stream>>>(ra);
+        } else if (e->rowrot_ok && e->A <= 32 && T >= 4) {
+            // forests over one 32-attribute chunk: codes once per row from the rotated copy, loop over all trees (avt_forest.cuh)
+            const long long n_tiles = (e->N + 31) / 32;
+            long long parts = std::min<long long>((long long)e->sm_count * 4, std::max<long long>(1, n_tiles / (kForestWarps * 4)));
+            const long long tpp = ((n_tiles + parts - 1) / parts + kForestWarps - 1) / kForestWarps * kForestWarps;
+            parts = (n_tiles + tpp - 1) / tpp;
+            repartition_rot_kernel<<<(unsigned)parts, kForestThreads, 0, e->stream>>>(e->nid_cur, e->d_rowrot.p, nb_level(last_level), e->d_node_attr.p, e->d_lut.p, lut_w, T,
+                                                                                       e->N, e->Npad, tpp);
         } else {
             long long blocks = std::min<long long>((e->N + 256 * 8 - 1) / (256 * 8), (long long)e->sm_count * 8);
             dim3 grid((unsigned)blocks, (unsigned)T);
@@ -2142,7 +2212,7 @@ int avt_reset_stats(avt_engine* e) {
 
 int avt_set_hist_variant(avt_engine* e, int32_t variant) {
     if (!e) return AVT_E_INVALID;
-    if (variant < -1 || variant > 3) return fail(e, AVT_E_INVALID, "avt_set_hist_variant: %d", variant);
+    if (variant < -1 || variant > 4) return fail(e, AVT_E_INVALID, "avt_set_hist_variant: %d", variant);
     e->force_variant = variant;
     return AVT_OK;
 }

@@ -287,4 +287,42 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
     }
 }
 
+// ----------------------------------------------------------------------------------------------------------------------
+// repartition_rot_kernel: the stand-alone repartition (kernel (c), last level of avt_grow_levels) for forests over <= 32
+// uint8 attributes.  repartition_kernel gathers one code byte per (row, tree) from the column of that tree's split attribute:
+// a 32-byte sector per byte, 320 GB of sectors for C3's 10^10 pairs (39 ms per call, 6 % of the step).  Here lane = row, the
+// row's 32 codes come once from the rotated row-major copy (one sector per row, parked in shared memory) and the loop runs
+// over ALL trees: per (row, tree) only the node id is read and written.  grid.x row parts, 512 threads.
+__global__ void __launch_bounds__(kForestThreads) repartition_rot_kernel(uint16_t* nid_all, const uint8_t* rowrot, const int32_t* node_base,
+                                                                          const int32_t* node_attr, const uint16_t* child_lut, int lut_w, int T,
+                                                                          long long N, long long Npad, long long tiles_per_part) {
+    __shared__ __align__(16) uint8_t codes_s[kForestWarps * 1024];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t codes_base = (uint32_t)__cvta_generic_to_shared(codes_s) + (uint32_t)warp * 1024u + 32u * lane;
+    const long long n_tiles = (N + 31) >> 5;
+    const long long tile_lo = (long long)blockIdx.x * tiles_per_part, tile_hi = min(n_tiles, tile_lo + tiles_per_part);
+    for (long long tile = tile_lo + warp; tile < tile_hi; tile += kForestWarps) {
+        const long long row = (tile << 5) + lane;
+        const uint4* src = reinterpret_cast<const uint4*>(rowrot + row * 32);
+        sts_v4(codes_base, __ldg(src));            // own row, own 32 bytes: no other lane touches them
+        sts_v4(codes_base + 16u, __ldg(src + 1));
+        uint16_t* nid = nid_all + row;
+        if ((lane & 15) == 0)
+            for (int t = 0; t < min(T, 8); ++t) prefetch_l2(nid + (long long)t * Npad);
+        uint32_t next = row < Npad ? nid[0] : AVT_NODE_NONE;
+        for (int t = 0; t < T; ++t) {
+            const uint32_t old = next;
+            if (t + 1 < T && row < Npad) next = nid[(long long)(t + 1) * Npad];
+            if ((lane & 15) == 0 && t + 8 < T) prefetch_l2(nid + (long long)(t + 8) * Npad);
+            uint32_t nw = AVT_NODE_NONE;
+            if (old != AVT_NODE_NONE && row < N) {
+                const int g = node_base[t] + (int)old;
+                const int at = node_attr[g];
+                if (at >= 0) nw = child_lut[(long long)g * lut_w + lds_u8(codes_base + (((uint32_t)at - (uint32_t)lane) & 31u))];
+            }
+            if (row < Npad) nid[(long long)t * Npad] = (uint16_t)nw;
+        }
+    }
+}
+
 }  // namespace avt

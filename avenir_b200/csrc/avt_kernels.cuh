@@ -732,6 +732,7 @@ __global__ void __launch_bounds__(256) repartition_fast_kernel(const RepartFastA
 #include "avt_scan_fast.cuh"
 #include "avt_forest.cuh"
 #include "avt_joint.cuh"
+#include "avt_sorted.cuh"
 #include "avt_csv.cuh"
 #include "avt_predict.cuh"
 #include "avt_bagging.cuh"

@@ -309,7 +309,7 @@ def run_c2(args):
             "gpu_launches": int((st.hist_launches + st.scan_launches + st.eval_launches + st.repart_launches) * args.steps // prof_steps),
             "e2e": {"value": world * N * L / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(sum(c.nbytes for c in cols_p) + cls_p.nbytes), "d2h_bytes_per_step": int(nid.nbytes)},
-            "roofline": {"bound": "hbm", "kernel": {0: "hist_smem_kernel", 1: "hist_global_kernel", 2: "hist_rot_kernel", 3: "hist_joint_kernel"}.get(st.last_hist_variant, "?"),
+            "roofline": {"bound": "hbm", "kernel": {0: "hist_smem_kernel", 1: "hist_global_kernel", 2: "hist_rot_kernel", 3: "hist_joint_kernel", 4: "hist_sorted_kernel"}.get(st.last_hist_variant, "?"),
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                          "frac_of_spec_8000": achieved / 8000.0, "traffic": traffic,
                          "alg_bytes_per_launch": alg_bytes_per_launch, "ms_per_launch": hist_ms_per_launch,
@@ -580,7 +580,7 @@ def run_c3(args):
             "e2e": {"value": N_total * L * T / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(sum(c.nbytes for c in cols_p) + cls_p.nbytes),
                     "d2h_bytes_per_step": int(nrec * C.sizeof(_lib.GrowRecord))},
-            "roofline": {"bound": "hbm", "kernel": {0: "hist_smem_kernel", 1: "hist_global_kernel", 2: "hist_rot_kernel", 3: "hist_joint_kernel"}.get(st.last_hist_variant, "?"),
+            "roofline": {"bound": "hbm", "kernel": {0: "hist_smem_kernel", 1: "hist_global_kernel", 2: "hist_rot_kernel", 3: "hist_joint_kernel", 4: "hist_sorted_kernel"}.get(st.last_hist_variant, "?"),
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                          "frac_of_spec_8000": achieved / 8000.0, "traffic": traffic, "traffic_source": traffic_src,
                          "alg_bytes_per_launch": alg_bytes_per_launch, "ms_per_launch": hist_ms_per_launch,

@@ -26,7 +26,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 
 
 def _kernel_name(v):
-    return {0: "hist_smem_kernel", 1: "hist_global_kernel", 2: "hist_rot_kernel", 3: "hist_joint_kernel"}.get(v, "?")
+    return {0: "hist_smem_kernel", 1: "hist_global_kernel", 2: "hist_rot_kernel", 3: "hist_joint_kernel", 4: "hist_sorted_kernel"}.get(v, "?")
 
 
 def _roofline(st, peak, peak_src, traffic_file):

@@ -30,6 +30,8 @@
  *   AVT_HIST_PACK=0   one byte per attribute instead of the bit-packed codes      AVT_HIST_JOINT=1 joint-code histogram kernel on packed schemas
  *   AVT_SUBTRACT=0|1  sibling subtraction off / on (default: on for >= 16 uint8 attributes)
  *   AVT_PDL=0         plain stream launches instead of programmatic dependent launch
+ *   AVT_ROT_PF=n      forest kernel: node ids / multiplicities prefetched into L2 n trees ahead (default 4, 0 = off)
+ *   AVT_HIST_SORTED=0|1|2  sorted-rows kernel off / only in place of the global-atomics fallback / whenever the forest kernel does not fit (default 2)
  *   AVT_PEER_PUSH=0   pull form of the NVLink peer exchange                        AVT_PEER_OFF=1  avt_peer_import is ignored (NCCL only)
  */
 #ifndef AVENIR_TREE_H
@@ -111,7 +113,7 @@ typedef struct avt_stats {
     int64_t hist_launches, scan_launches, eval_launches, repart_launches, comm_calls;
     int64_t hist_alg_bytes; /* algorithmic bytes of all histogram passes so far */
     int64_t repart_alg_bytes;
-    int32_t last_hist_variant; /* 0 shared-memory privatised (lane = row), 1 global atomics (match_any), 2 forest kernel (lane = attribute), 3 joint-code kernel (packed narrow schemas) */
+    int32_t last_hist_variant; /* 0 shared-memory privatised (lane = row), 1 global atomics (match_any), 2 forest kernel (hist_rot_kernel), 3 joint-code kernel (packed narrow schemas), 4 sorted-rows kernel (one tree, deep levels) */
     int32_t last_hist_replicas;
     int32_t last_hist_grid, last_hist_block, last_hist_smem;
     int32_t reserved0;
@@ -349,8 +351,8 @@ int avt_reset_stats(avt_engine* e);
 /* Turns the per-launch CUDA-event timing behind avt_stats on (default) or off (no event records between
  * the launches of a level loop). */
 int avt_set_profiling(avt_engine* e, int32_t on);
-/* Forces a histogram variant (-1 auto, 0 shared-memory by rows, 1 global atomics, 2 forest kernel: shared-memory by
- * attributes, 3 joint-code kernel for packed narrow schemas) -- for tests/profiling. */
+/* Forces a histogram variant (-1 auto, 0 shared-memory by rows, 1 global atomics, 2 forest kernel over the rotated row-major
+ * copy, 3 joint-code kernel for packed narrow schemas, 4 sorted-rows kernel for one tree) -- for tests/profiling. */
 int avt_set_hist_variant(avt_engine* e, int32_t variant);
 
 /* Allocation-free histogram.  NO COUNTERPART IN THE REFERENCE (and none in its Java object seams): it exists

@@ -62,7 +62,8 @@ def test_c3_forest_shape():
 
 def test_c5_wide_shape():
     """C5: 512 int attributes x 64 bins (63 splits each = 32 256 candidates), gini, deep tree: the frontier
-    outgrows shared memory and the pass falls back to warp-aggregated global atomics."""
+    outgrows shared memory: hist_rot_kernel at the shallow levels, then rows in node-contiguous order (hist_sorted_kernel);
+    the same loop with that kernel switched off falls back to hist_smem_kernel / warp-aggregated global atomics."""
     n = 60_000
     n_bins = [64] * 512
     cols, cls = synth.binned_dataset(n, n_bins, 2, seed=55, signal_attrs=16)
@@ -75,7 +76,22 @@ def test_c5_wide_shape():
         e.set_splits(table)
     frontier = compare_level_loops(g, o, table, 10, CRIT_GINI, 1)
     assert frontier[0] > 400                  # beyond (200 KB / 64 bins / 2 classes / 4 B) nodes
-    assert g.stats().last_hist_variant == 1
+    assert g.stats().last_hist_variant == 4
+
+
+def test_c5_wide_shape_global_fallback(monkeypatch):
+    monkeypatch.setenv("AVT_HIST_SORTED", "0")
+    n = 40_000
+    n_bins = [64] * 512
+    cols, cls = synth.binned_dataset(n, n_bins, 2, seed=56, signal_attrs=16)
+    table = binary_split_table(n_bins, [False] * 512)
+    g, o = Engine(0), helpers.OracleEngine(threads=8)
+    for e in (g, o):
+        e.load_dataset(cols, cls, n_bins, 2)
+        e.forest_init(1)
+        e.set_splits(table)
+    frontier = compare_level_loops(g, o, table, 10, CRIT_GINI, 1)
+    assert frontier[0] > 400 and g.stats().last_hist_variant == 1
 
 
 @pytest.mark.parametrize("criterion", [CRIT_GINI, CRIT_ENTROPY])

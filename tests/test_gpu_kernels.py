@@ -81,6 +81,26 @@ def test_joint_code_histogram_forest_and_weights(n_bins, n_classes):
     g.close()
 
 
+@pytest.mark.parametrize("weights", [False, True])
+@pytest.mark.parametrize("n,nodes", [(1, 1), (33, 5), (70_001, 700), (200_000, 3000)])
+def test_histogram_sorted_rows_variant(n, nodes, weights):
+    """hist_sorted_kernel (variant 4): one tree, 40 attributes of mixed widths (two 32-attribute chunks), rows outside the
+    frontier, empty nodes, frontiers far beyond a block's shared memory, multiplicities incl. 0."""
+    rng = np.random.default_rng(n + nodes)
+    n_bins = [16] * 20 + [64] * 12 + [3] * 8
+    cols, cls = synth.binned_dataset(n, n_bins, 3, seed=9)
+    table = binary_split_table(n_bins, [False] * 32 + [True] * 8)
+    nid = random_node_ids(rng, n, nodes, 0.2)
+    nid[nid == 3] = 4 if nodes > 4 else nid[nid == 3]        # node 3 stays empty when the frontier is large enough
+    w = [rng.poisson(1.0, n).clip(0, 255).astype(np.uint8)] if weights else None
+    g, o = make_pair(cols, cls, n_bins, 3, table, 1, w, [nid])
+    g.set_hist_variant(4)
+    hg = g.histogram([nodes], fetch=True)
+    assert g.stats().last_hist_variant == 4
+    assert np.array_equal(hg, o.histogram([nodes], fetch=True))
+    g.close()
+
+
 def test_histogram_many_nodes_uses_fewer_replicas_then_global():
     n = 200000
     rng = np.random.default_rng(5)
