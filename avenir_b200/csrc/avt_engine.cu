@@ -2085,7 +2085,7 @@ int avt_cpg_sweep(avt_engine* e, int32_t node, int32_t criterion, const uint8_t*
     CUDA_TRY(e, e->d_cpg.ensure((size_t)e->S));
     TimerSlot ts;
     if (int rc = timer_open(e, &e->stats.scan_ms, &ts)) return rc;
-    cpg_kernel<<<(e->S + 63) / 64, 64, 0, e->stream>>>(e->d_H.p, make_table(e), node, e->d_order.p, criterion, e->d_cpg.p);
+    cpg_kernel<<<(e->S + kCpgWarps - 1) / kCpgWarps, kCpgWarps * 32, 0, e->stream>>>(e->d_H.p, make_table(e), node, e->d_order.p, criterion, e->d_cpg.p);
     CUDA_TRY(e, cudaGetLastError());
     if (int rc = timer_close(e, ts)) return rc;
     e->stats.scan_launches += 1;

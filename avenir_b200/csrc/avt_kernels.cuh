@@ -551,28 +551,14 @@ __global__ void class_counts_kernel(const uint32_t* H, int n_nodes, int TB, int 
 // util/AttributeSplitStat.java:153-170 (split info), 191-218 (gini/entropy), 240-282 (Hellinger),
 // 298-336 + 452-471 (class-confidence ratio).  Segments iterate in ascending index (HashMap<Integer>
 // order for < 16 segments); segments without rows do not exist.
-__global__ void cpg_kernel(const uint32_t* H, SplitTable st, int node, const uint8_t* order, int criterion,
-                           avt_cpg_stat* out) {
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= st.S) return;
-    const avt_split sp = st.splits[s];
+// The statistics of one split from its segments' class counts (r.seg_count filled in): split information, then the criterion.
+__device__ __noinline__ void cpg_statistics(const SplitTable& st, const avt_split& sp, const uint8_t* order, int criterion, avt_cpg_stat& r) {
     const int C = st.C;
-    const int B = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
-    const uint32_t* Hn = H + ((long long)node * st.TB + st.bin_off[sp.attr]) * C;
-    avt_cpg_stat r;
     uint32_t segn[kMaxSeg];
     uint32_t total = 0;
-    for (int j = 0; j < kMaxSeg; ++j) {
-        segn[j] = 0;
-        for (int c = 0; c < kMaxC; ++c) r.seg_count[j][c] = 0;
-    }
+    for (int j = 0; j < kMaxSeg; ++j) segn[j] = 0;
     for (int j = 0; j < sp.n_seg; ++j) {
-        uint32_t cnt[kMaxC];
-        segment_counts(st, sp, j, B, nullptr, Hn, cnt);
-        for (int c = 0; c < C; ++c) {
-            r.seg_count[j][c] = cnt[c];
-            segn[j] += cnt[c];
-        }
+        for (int c = 0; c < C; ++c) segn[j] += r.seg_count[j][c];
         total += segn[j];
     }
     const double log2v = 0.6931471805599453;
@@ -636,8 +622,65 @@ __global__ void cpg_kernel(const uint32_t* H, SplitTable st, int node, const uin
         stat = __ddiv_rn(sum, tot);
     }
     r.stat = stat;
-    out[s] = r;
 }
+
+// One WARP per split: the lanes stride over the attribute's bins to take the segments' class counts (coalesced reads of the
+// per-bin segment table and of H; a split over a 1 000-level categorical is 1 000 bins x n_seg passes -- one thread per split
+// spent 18 ms per sweep on C4's 81 860 splits), lane 0 then does the fp64 statistics in exactly the scalar order, and the
+// 528-byte result goes out with coalesced stores.
+constexpr int kCpgWarps = 8;
+__global__ void __launch_bounds__(kCpgWarps * 32) cpg_kernel(const uint32_t* H, SplitTable st, int node, const uint8_t* order, int criterion,
+                                                             avt_cpg_stat* out) {
+    __shared__ avt_cpg_stat s_r[kCpgWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int s = blockIdx.x * kCpgWarps + warp;
+    if (s >= st.S) return;   // whole warps leave; no block-wide barrier below
+    const avt_split sp = st.splits[s];
+    const int C = st.C;
+    const int B = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
+    const uint32_t* Hn = H + ((long long)node * st.TB + st.bin_off[sp.attr]) * C;
+    avt_cpg_stat& r = s_r[warp];
+    {
+        uint32_t* rc = &r.seg_count[0][0];
+        for (int i = lane; i < kMaxSeg * kMaxC; i += 32) rc[i] = 0;
+    }
+    __syncwarp();
+    for (int j = 0; j < sp.n_seg; ++j) {
+        uint32_t cnt[kMaxC];
+        for (int c = 0; c < kMaxC; ++c) cnt[c] = 0;
+        int lo = 0, hi = -1;           // bins [lo, hi] of the segment (numeric / ranges); the table decides for the rest
+        const uint8_t* lut = nullptr;
+        if (sp.kind == AVT_SPLIT_NUMERIC) {
+            lo = (j == 0) ? 0 : st.bounds[sp.off + j - 1] + 1;
+            hi = (j == sp.n_seg - 1) ? B - 1 : st.bounds[sp.off + j];
+            if (hi < 0 || hi < lo) { lo = 0; hi = -1; }
+        } else if (sp.kind == AVT_SPLIT_RANGES) {
+            lo = st.bounds[sp.off + 2 * j];
+            hi = min(st.bounds[sp.off + 2 * j + 1], B - 1);
+        } else {
+            lut = st.seg_lut + sp.off;
+            lo = 0;
+            hi = B - 1;
+        }
+        for (int b = lo + lane; b <= hi; b += 32) {
+            if (lut && lut[b] != j) continue;
+            for (int c = 0; c < C; ++c) cnt[c] += Hn[b * C + c];
+        }
+        for (int c = 0; c < C; ++c) {
+            uint32_t v = cnt[c];
+#pragma unroll
+            for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0) r.seg_count[j][c] = v;
+        }
+    }
+    __syncwarp();
+    if (lane == 0) cpg_statistics(st, sp, order, criterion, r);
+    __syncwarp();
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&r);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(out + s);
+    for (int i = lane; i < (int)(sizeof(avt_cpg_stat) / 4); i += 32) dst[i] = src[i];
+}
+
 
 // ------------------------------------------------------------------------------------------------
 // (c) repartition

@@ -325,8 +325,11 @@ class Engine:
         self._check(self.lib.avt_grow_levels_ex(self.h, n_levels, criterion, _ptr(o), strategy, _ptr(m), npt, rec, max_records, C.byref(n)))
         return (rec, int(n.value)), list(npt)
 
-    def cpg_sweep(self, node: int, criterion: int, class_order: Optional[Sequence[int]] = None):
-        out = (CpgStat * max(self.n_splits, 1))()
+    def cpg_sweep(self, node: int, criterion: int, class_order: Optional[Sequence[int]] = None, out=None):
+        """avt_cpg_sweep; `out` = a (CpgStat * n_splits) array to reuse (e.g. CpgStat-array.from_address of page-locked memory:
+        a fresh 528-byte-per-split array costs more to allocate and fault in than the sweep takes)."""
+        if out is None:
+            out = (CpgStat * max(self.n_splits, 1))()
         o = None if class_order is None else np.ascontiguousarray(class_order, dtype=np.uint8)
         self._check(self.lib.avt_cpg_sweep(self.h, node, criterion, _ptr(o), out))
         return out
