@@ -1065,8 +1065,9 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
     int s_S = 0;
     {
         const size_t per_node = (size_t)e->C * max_bins * 128;
-        const bool usable = e->T == 1 && e->rowrot_ok && max_bins <= 256 && e->N < (1LL << 31) && per_node * 2 <= kMaxDynSmem && !e->signal_pending;
-        if (usable) s_S = (int)std::min<size_t>(std::min<size_t>(kMaxDynSmem / 2 / per_node, 8), (size_t)std::max(n_max, 1));
+        const bool usable = e->T == 1 && e->rowrot_ok && max_bins <= 256 && e->N < (1LL << 31) && per_node + 18 * 1024 <= kMaxDynSmem && !e->signal_pending;
+        // two blocks per SM: each has 17 KB of static shared memory (the warps' row tiles) beside its window of S nodes
+        if (usable) s_S = (int)std::min<size_t>(std::min<size_t>(std::max<size_t>((kMaxDynSmem / 2 - 18 * 1024) / per_node, 1), 8), (size_t)std::max(n_max, 1));
         if (s_S >= 1 && ((e->force_variant < 0 && f_G == 0 && (e->hist_sorted == 2 || (e->hist_sorted == 1 && variant == 1))) || e->force_variant == 4)) variant = 4;
         else s_S = 0;
     }
@@ -1381,7 +1382,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         sa.N = N; sa.A = e->A; sa.Bmax = max_bins; sa.S = s_S; sa.TB = e->TB; sa.C = e->C;
         const int achunks = (e->A + 31) / 32;
         const size_t smem = (size_t)s_S * e->C * max_bins * 128;
-        const int bpsm = (int)std::max<size_t>(1, std::min<size_t>(4, kMaxDynSmem / std::max<size_t>(smem, 1)));
+        const int bpsm = (int)std::max<size_t>(1, std::min<size_t>(4, (kMaxDynSmem + 1024) / (smem + 18 * 1024)));
         // spans: about four waves of blocks over all chunks, at least 2048 positions each
         long long spans = std::max<long long>(1, ((long long)e->sm_count * bpsm * 4 + achunks - 1) / achunks);
         sa.span = std::max<long long>(2048, (N + spans - 1) / spans);
@@ -1389,10 +1390,10 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         spans = (N + sa.span - 1) / sa.span;
         dim3 grid((unsigned)spans, (unsigned)achunks);
         if (e->any_w) {
-            CUDA_TRY(e, cudaFuncSetAttribute(hist_sorted_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+            CUDA_TRY(e, cudaFuncSetAttribute(hist_sorted_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kMaxDynSmem - 18 * 1024)));
             hist_sorted_kernel<true><<<grid, kSortedThreads, smem, e->stream>>>(sa);
         } else {
-            CUDA_TRY(e, cudaFuncSetAttribute(hist_sorted_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+            CUDA_TRY(e, cudaFuncSetAttribute(hist_sorted_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kMaxDynSmem - 18 * 1024)));
             hist_sorted_kernel<false><<<grid, kSortedThreads, smem, e->stream>>>(sa);
         }
         e->stats.last_hist_replicas = s_S;

@@ -48,15 +48,22 @@ __global__ void iota_kernel(uint32_t* out, long long N) {
 template <bool HAS_W>
 __global__ void __launch_bounds__(kSortedThreads) hist_sorted_kernel(const SortedArgs a) {
     extern __shared__ __align__(16) uint32_t ssh[];
+    constexpr int kWarps = kSortedThreads / 32;
+    __shared__ __align__(16) uint8_t s_tile[kWarps * 1024];   // per warp: the 32-byte code entries of the 32 rows it is working on
     __shared__ long long s_wend;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    constexpr int kWarps = kSortedThreads / 32;
     const int chunk = blockIdx.y;
     const long long p0 = (long long)blockIdx.x * a.span, p1 = min(a.N, p0 + a.span);
     const uint32_t slot_words = (uint32_t)a.C * a.Bmax * 32u;
     const uint32_t slot_bytes = slot_words * 4u, class_bytes = (uint32_t)a.Bmax * 128u;
     const uint32_t cnt_base = (uint32_t)__cvta_generic_to_shared(ssh);
+    const uint32_t tile_base = (uint32_t)__cvta_generic_to_shared(s_tile) + (uint32_t)warp * 1024u;
+    const uint32_t lane_base = cnt_base + (uint32_t)lane * 4u;
     const uint8_t* rr = a.rowrot + (long long)chunk * a.rowrot_rows * 32;
+    const int at = chunk * 32 + lane;
+    const int nbins = at < a.A ? a.bin_off[at + 1] - a.bin_off[at] : 0;
+    const int b0 = at < a.A ? a.bin_off[at] : 0;
+    for (uint32_t i = threadIdx.x; i < (uint32_t)a.S * slot_words; i += blockDim.x) ssh[i] = 0;   // flushed windows leave zeros behind
     long long cur = p0;
     while (cur < p1) {
         const uint32_t nb = a.keys[cur];              // first node of the window (the same value for every thread)
@@ -72,45 +79,60 @@ __global__ void __launch_bounds__(kSortedThreads) hist_sorted_kernel(const Sorte
             }
             s_wend = lo;
         }
-        for (uint32_t i = threadIdx.x; i < (uint32_t)a.S * slot_words; i += blockDim.x) ssh[i] = 0;
         __syncthreads();
         const long long wend = s_wend;
-        for (long long q = cur + (long long)warp * 32; q < wend; q += (long long)kWarps * 32) {
+        // Per warp 32 positions at a time.  A position's row entry (32 bytes of the rotated copy = one sector) is fetched by the
+        // lane that owns the position and parked in shared memory; the positions of the NEXT round are fetched before this
+        // round's updates are issued, so the two dependent loads (order -> row -> codes) are off the critical path.
+        uint32_t hb_l = 0xFFFFFFFFu, row_l = 0, w_l = 1;
+        uint4 c0 = make_uint4(0, 0, 0, 0), c1 = c0;
+        auto fetch = [&](long long q, uint32_t& hb, uint32_t& row, uint32_t& w, uint4& x0, uint4& x1) {
             const long long i = q + lane;
-            uint32_t hb_l = 0xFFFFFFFFu, row_l = 0, w_l = 1;
+            hb = 0xFFFFFFFFu;
+            row = 0;
+            w = 1;
             if (i < wend) {
                 const uint32_t node = a.keys[i];
-                row_l = a.perm[i];
-                if (!(a.skip && a.skip[node])) hb_l = cnt_base + (node - nb) * slot_bytes + (uint32_t)a.cls_s[i] * class_bytes;
-                if (HAS_W) w_l = a.w_s[i];
-            }
-            const int n_here = (int)min((long long)32, wend - q);
-            // 16 rows at a time: all their code bytes are requested before the first update is issued (one load -> one
-            // update per row in sequence leaves every warp waiting out a full memory latency per row: 13.6 clk per row and SM)
-            for (int j0 = 0; j0 < n_here; j0 += 16) {
-                uint32_t code[16];
-#pragma unroll
-                for (int k = 0; k < 16; ++k) {
-                    const uint32_t row = __shfl_sync(0xffffffffu, row_l, j0 + k);
-                    code[k] = __ldg(rr + (long long)row * 32 + ((lane - row) & 31u));   // lanes past the window hold row 0: a valid address
+                row = a.perm[i];
+                if (!(a.skip && a.skip[node])) hb = cnt_base + (node - nb) * slot_bytes + (uint32_t)a.cls_s[i] * class_bytes;
+                if (HAS_W) {
+                    w = a.w_s[i];
+                    if (w == 0u) hb = 0xFFFFFFFFu;
                 }
-#pragma unroll
-                for (int k = 0; k < 16; ++k) {
-                    const uint32_t hb = __shfl_sync(0xffffffffu, hb_l, j0 + k);
-                    const uint32_t w = HAS_W ? __shfl_sync(0xffffffffu, w_l, j0 + k) : 1u;
-                    if (hb != 0xFFFFFFFFu && (!HAS_W || w != 0u)) red_shared_add(hb + code[k] * 128u + (uint32_t)lane * 4u, w);   // warp-uniform
-                }
+                const uint4* src = reinterpret_cast<const uint4*>(rr + (long long)row * 32);
+                x0 = __ldg(src);
+                x1 = __ldg(src + 1);
             }
+        };
+        long long q = cur + (long long)warp * 32;
+        if (q < wend) fetch(q, hb_l, row_l, w_l, c0, c1);
+        for (; q < wend; q += (long long)kWarps * 32) {
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(tile_base + 32u * lane), "r"(c0.x), "r"(c0.y), "r"(c0.z), "r"(c0.w) : "memory");
+            asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(tile_base + 32u * lane + 16u), "r"(c1.x), "r"(c1.y), "r"(c1.z), "r"(c1.w) : "memory");
+            // one shuffle per row: counter block in 128-byte units (16 bits) and the row's rotation (5 bits) in one word
+            const uint32_t pk_c = hb_l == 0xFFFFFFFFu ? 0xFFFFFFFFu : ((hb_l - cnt_base) >> 7) | ((row_l & 31u) << 16);
+            const uint32_t w_c = w_l;
+            __syncwarp();
+            const long long qn = q + (long long)kWarps * 32;
+            if (qn < wend) fetch(qn, hb_l, row_l, w_l, c0, c1);
+#pragma unroll 8
+            for (int j = 0; j < 32; ++j) {
+                const uint32_t pk = __shfl_sync(0xffffffffu, pk_c, j);
+                const uint32_t w = HAS_W ? __shfl_sync(0xffffffffu, w_c, j) : 1u;
+                if (pk == 0xFFFFFFFFu) continue;   // warp-uniform: a skipped node, multiplicity 0, or past the window
+                uint32_t code;
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(code) : "r"(tile_base + 32u * j + ((lane - (pk >> 16)) & 31u)));
+                red_shared_add(lane_base + ((pk & 0xFFFFu) << 7) + code * 128u, w);
+            }
+            __syncwarp();
         }
         __syncthreads();
-        // flush the window: counter (node, class, bin, attribute) -> H[nb + node][bin_off[attr] + bin][class]
-        const int at = chunk * 32 + lane;
-        const int nbins = at < a.A ? a.bin_off[at + 1] - a.bin_off[at] : 0;
-        const int b0 = at < a.A ? a.bin_off[at] : 0;
+        // flush the window and leave zeros: counter (node, class, bin, attribute) -> H[nb + node][bin_off[attr] + bin][class]
         const uint32_t n_present = (uint32_t)min((long long)a.S, (long long)(a.keys[wend - 1] - nb) + 1);
         for (uint32_t i = threadIdx.x; i < n_present * slot_words; i += blockDim.x) {   // i & 31 == lane
             const uint32_t v = ssh[i];
             if (!v) continue;
+            ssh[i] = 0;
             const uint32_t rest = i >> 5;
             const int bin = (int)(rest % (uint32_t)a.Bmax);
             const uint32_t sc = rest / (uint32_t)a.Bmax;

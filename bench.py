@@ -584,7 +584,11 @@ def run_c3(args):
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                          "frac_of_spec_8000": achieved / 8000.0, "traffic": traffic, "traffic_source": traffic_src,
                          "alg_bytes_per_launch": alg_bytes_per_launch, "ms_per_launch": hist_ms_per_launch,
-                         "launch": {"grid": st.last_hist_grid, "block": st.last_hist_block, "smem": st.last_hist_smem, "replicas": st.last_hist_replicas}},
+                         "launch": {"grid": st.last_hist_grid, "block": st.last_hist_block, "smem": st.last_hist_smem, "replicas": st.last_hist_replicas},
+                         # the unit that actually bounds this pass: one shared-memory counter update per (row, tree, attribute)
+                         "shared_atomics": {"updates_per_launch": n_local * T * 32, "achieved_T_per_s": n_local * T * 32 / (hist_ms_per_launch * 1e-3) / 1e12 if hist_ms_per_launch > 0 else 0.0,
+                                            "peak_T_per_s": 6.2, "peak_source": "red.shared.add.u32, conflict-free, 32 warps per SM: tools/microbench/atoms_bench.cu, profiles/atoms_bench_r02.txt",
+                                            "frac": n_local * T * 32 / (hist_ms_per_launch * 1e-3) / 6.2e12 if hist_ms_per_launch > 0 else 0.0}},
             "clocks": sampler.summary(),
         }
         if not args.no_cpu_baseline and world == 1:
