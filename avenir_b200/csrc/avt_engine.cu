@@ -2239,25 +2239,35 @@ int avt_peer_export(avt_engine* e, void* handle64) {
 int avt_peer_import(avt_engine* e, int32_t n_ranks, int32_t rank, const void* handles) {
     if (!e || !handles || n_ranks < 1 || n_ranks > 16 || rank < 0 || rank >= n_ranks) return fail(e, AVT_E_INVALID, "avt_peer_import: bad argument (1..16 ranks)");
     if (!e->peer.arena) return fail(e, AVT_E_STATE, "avt_peer_import: call avt_peer_export first");
+    // one import per engine: the arena's flag words and tagged receive slots of an earlier session would pass for this one's
+    // (the epoch restarts at 0), and the earlier IPC mappings would leak
+    if (e->peer.n > 0) return fail(e, AVT_E_STATE, "avt_peer_import: this engine already imported its peers; create a new engine for a new set of ranks");
     if (int rc = use_device(e)) return rc;
     if (int rc = sync_and_resolve(e)) return rc;
-    e->peer.n = n_ranks;
-    e->peer.rank = rank;
     std::vector<const uint32_t*> h0((size_t)n_ranks), h1((size_t)n_ranks);
     std::vector<uint32_t*> rf((size_t)n_ranks);
+    std::vector<void*> bases((size_t)n_ranks, nullptr);
     for (int r = 0; r < n_ranks; ++r) {
         void* base = e->peer.arena;
         if (r != rank) {
             cudaIpcMemHandle_t h;
             memcpy(&h, (const char*)handles + (size_t)r * 64, 64);
-            CUDA_TRY(e, cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+            const cudaError_t st = cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess);
+            if (st != cudaSuccess) {
+                for (int q = 0; q < r; ++q)
+                    if (q != rank && bases[(size_t)q]) cudaIpcCloseMemHandle(bases[(size_t)q]);   // nothing of a failed import stays behind
+                return fail(e, AVT_E_CUDA, "avt_peer_import: cudaIpcOpenMemHandle of rank %d: %s", r, cudaGetErrorString(st));
+            }
         }
-        e->peer.base[r] = base;
+        bases[(size_t)r] = base;
         uint32_t* b = (uint32_t*)base;
         h0[(size_t)r] = b + 64;
         h1[(size_t)r] = b + 64 + e->peer.cap_words;
         rf[(size_t)r] = b + rank;  // this rank's flag word inside rank r's arena
     }
+    for (int r = 0; r < n_ranks; ++r) e->peer.base[r] = bases[(size_t)r];
+    e->peer.n = n_ranks;
+    e->peer.rank = rank;
     if (int rc = upload(e, e->d_peer_H[0], h0.data(), h0.size())) return rc;
     if (int rc = upload(e, e->d_peer_H[1], h1.data(), h1.size())) return rc;
     if (int rc = upload(e, e->d_remote_flags, rf.data(), rf.size())) return rc;

@@ -390,7 +390,9 @@ int avt_comm_init_rank(avt_engine* e, int32_t n_ranks, int32_t rank, const void*
  * into kernel (b).  avt_peer_export allocates the exchange buffers (2 x 8 MiB + flags) and returns their
  * 64-byte CUDA IPC handle; the host gathers all ranks' handles (rank order) and passes the n_ranks x 64 bytes
  * to avt_peer_import.  Levels whose histogram exceeds the buffers fall back to the NCCL path (which then
- * needs avt_comm_init_rank).  Same role as avt_comm_*: Hadoop's shuffle between mapper and reducer. */
+ * needs avt_comm_init_rank).  Same role as avt_comm_*: Hadoop's shuffle between mapper and reducer.
+ * One import per engine (a second one fails with AVT_E_STATE: the buffers still hold the first session's flags); an import
+ * that fails part-way closes the mappings it had opened and leaves the engine without peers. */
 int avt_peer_export(avt_engine* e, void* handle64);
 int avt_peer_import(avt_engine* e, int32_t n_ranks, int32_t rank, const void* handles);
 
