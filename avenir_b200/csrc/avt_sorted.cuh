@@ -99,9 +99,11 @@ __global__ void __launch_bounds__(kSortedThreads) hist_sorted_kernel(const Sorte
                     w = a.w_s[i];
                     if (w == 0u) hb = 0xFFFFFFFFu;
                 }
-                const uint4* src = reinterpret_cast<const uint4*>(rr + (long long)row * 32);
-                x0 = __ldg(src);
-                x1 = __ldg(src + 1);
+                if (hb != 0xFFFFFFFFu) {   // rows that are not counted (derived node, multiplicity 0) cost no code traffic either
+                    const uint4* src = reinterpret_cast<const uint4*>(rr + (long long)row * 32);
+                    x0 = __ldg(src);
+                    x1 = __ldg(src + 1);
+                }
             }
         };
         long long q = cur + (long long)warp * 32;
