@@ -30,6 +30,7 @@
  *   AVT_HIST_PACK=0   one byte per attribute instead of the bit-packed codes      AVT_HIST_JOINT=1 joint-code histogram kernel on packed schemas
  *   AVT_SUBTRACT=0|1  sibling subtraction off / on (default: on for >= 16 uint8 attributes)
  *   AVT_PDL=0         plain stream launches instead of programmatic dependent launch
+ *   AVT_HIST_BUDGET_KB=n  rows/smem kernel: shared memory an attribute group may take (default 100)
  *   AVT_ROT_PF=n      forest kernel: node ids / multiplicities prefetched into L2 n trees ahead (default 4, 0 = off)
  *   AVT_HIST_SORTED=0|1|2  sorted-rows kernel off / only in place of the global-atomics fallback / whenever the forest kernel does not fit (default 2)
  *   AVT_PEER_PUSH=0   pull form of the NVLink peer exchange                        AVT_PEER_OFF=1  avt_peer_import is ignored (NCCL only)
