@@ -1062,6 +1062,7 @@ static int launch_histogram(avt_engine* e, int n_max, const FusedRepart* fr, con
         const size_t fixed = (size_t)e->C * max_bins * 128 /* phantom slot */ + (fr ? (size_t)kForestWarps * 1024 : 0) + 64;
         if (e->rowrot_ok && max_bins <= 256 && per_tree + fixed <= kMaxDynSmem) {
             f_G = (int)std::min<size_t>((size_t)e->T, (kMaxDynSmem - fixed) / per_tree);
+            f_G = (int)std::min<long long>(f_G, std::max<long long>(1, 0xFFFFFFFFLL / std::max<long long>(e->Npad, 1)));   // 32-bit element offsets inside a tree group
             f_smem = fixed + per_tree * (size_t)f_G;
         }
         if (f_G >= 1 && e->force_variant < 0 && variant == 0) variant = 2;

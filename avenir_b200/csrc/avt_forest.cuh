@@ -176,7 +176,8 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
         nc1 = __ldg(src + 1);
         ncl = a.cls[row];
     };
-    const int pf_tiles = f.pf > 0 ? (f.pf + Gb - 1) / max(Gb, 1) : 0;
+    const uint32_t npad32 = (uint32_t)a.Npad;
+    const int pf_tiles = f.pf > 0 ? max(1, (f.pf + Gb - 1) / max(Gb, 1)) : 0;   // at least one tile, at least `pf` trees ahead
     long long tile = tile_lo + warp;
     if (tile < tile_hi) load_row(tile);
     for (; tile < tile_hi; tile += kForestWarps) {
@@ -205,21 +206,22 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
             n = AVT_NODE_NONE;
             w = 1u;
             if (g < Gb) {
-                n = nid_row[(long long)g * a.Npad];
-                if (HAS_W && lds_u8(has_w_base + g)) w = w_row[(long long)g * a.Npad];
+                n = nid_row[(uint32_t)g * npad32];   // 32-bit element index: the host keeps G * Npad below 2^32 (one IMAD.WIDE per address)
+                if (HAS_W && lds_u8(has_w_base + g)) w = w_row[(uint32_t)g * npad32];
             }
         };
-        // L2 prefetch of the 64 + 32 bytes a (tile, tree) pair reads: `pf` trees ahead inside this tile, and the first trees of
-        // the tile this warp visits `pf_tiles` rounds from now (the two-tree register prefetch covers one DRAM latency at best;
-        // measured on C3 at 20 M rows x 100 trees: 140.7 -> 125.0 ms per step with pf = 4, the same with 8 and 16)
-        if (f.pf > 0 && (lane & 15) == 0) {   // lanes 0 and 16: the two 32-byte sectors of a tile's node ids
+        // L2 prefetch of the 64 + 32 bytes a (tile, tree) pair reads, one whole tile ahead: when the warp starts a tile it requests,
+        // for every tree of the block, the node ids / multiplicities of the tile it will visit `pf_tiles` rounds from now (the
+        // two-tree register prefetch covers one DRAM latency at best; measured on C3 at 20 M rows x 100 trees: 140.7 -> 125.0 ms per
+        // step).  Lanes 0 and 16 only: the two 32-byte sectors of a tile's node ids.
+        if (f.pf > 0 && (lane & 15) == 0) {
             const long long ft = tile + (long long)pf_tiles * kForestWarps;
             if (ft < tile_hi) {
-                const long long frow = (ft << 5) + lane;
-                const int ng = min(f.pf, Gb);
-                for (int g = 0; g < ng; ++g) {
-                    prefetch_l2(a.nid + (long long)(t0 + g) * a.Npad + frow);
-                    if (HAS_W && lane == 0) prefetch_l2(a.wts + (long long)(t0 + g) * a.Npad + frow);
+                const uint16_t* pn = a.nid + (long long)t0 * a.Npad + (ft << 5) + lane;
+                const uint8_t* pw = HAS_W ? a.wts + (long long)t0 * a.Npad + (ft << 5) : nullptr;
+                for (int g = 0; g < Gb; ++g) {
+                    prefetch_l2(pn + (uint32_t)g * npad32);
+                    if (HAS_W && lane == 0) prefetch_l2(pw + (uint32_t)g * npad32);
                 }
             }
         }
@@ -232,10 +234,6 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
             n0 = n1;
             w0 = w1;
             fetch(g + 2, n1, w1);
-            if (f.pf > 0 && (lane & 15) == 0 && g + f.pf < Gb) {
-                prefetch_l2(nid_row + (long long)(g + f.pf) * a.Npad);
-                if (HAS_W && lane == 0) prefetch_l2(w_row + (long long)(g + f.pf) * a.Npad);
-            }
             uint32_t s = 0xFFFFu;
             if (REPART) {
                 uint32_t e = 0xFFFFFFFFu;
@@ -251,7 +249,7 @@ __global__ void __launch_bounds__(kForestThreads, 1) hist_rot_kernel(const HistA
                 }
                 node = e & 0xFFFFu;
                 s = e >> 16;
-                if (chunk == 0 && row < a.Npad) nid_out_row[(long long)g * a.Npad] = (uint16_t)node;
+                if (chunk == 0 && row < a.Npad) nid_out_row[(uint32_t)g * npad32] = (uint16_t)node;
             } else if (node != AVT_NODE_NONE) {
                 s = lds_u16(slot_of_base + 2u * (g * so_stride + min(node, (uint32_t)f.n_nodes_max)));
             }
