@@ -21,6 +21,9 @@ int run_cramer_correlation(const Props& conf, const std::string& in_path, const 
 // org.avenir.explore.HeterogeneityReductionCorrelation.run(args)  (explore/HeterogeneityReductionCorrelation.java:40-65)
 int run_heterogeneity_reduction_correlation(const Props& conf, const std::string& in_path, const std::string& out_path);
 
+// org.avenir.explore.CategoricalContinuousEncoding.run(args)  (explore/CategoricalContinuousEncoding.java:54-82)
+int run_categorical_continuous_encoding(const Props& conf, const std::string& in_path, const std::string& out_path);
+
 // org.avenir.tree.DataPartitioner.run(args)  (tree/DataPartitioner.java:59-105); takes no path arguments
 int run_data_partitioner(const Props& conf);
 

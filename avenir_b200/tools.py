@@ -62,6 +62,10 @@ class HeterogeneityReductionCorrelation(_Tool):
     java_class = "org.avenir.explore.HeterogeneityReductionCorrelation"
 
 
+class CategoricalContinuousEncoding(_Tool):
+    java_class = "org.avenir.explore.CategoricalContinuousEncoding"
+
+
 class DataPartitioner(_Tool):
     """tree/DataPartitioner.java:59-105; takes its paths from dap.project.base.path / dap.split.path, not from arguments."""
     java_class = "org.avenir.tree.DataPartitioner"
