@@ -3,6 +3,6 @@
 Only what the hot path needs lives here: csrc/ (sm_100a kernels, the C-ABI of include/avenir_tree.h and
 the C++ tool layer), a ctypes binding, the reference-named entry points, and synthetic-data helpers.
 """
-from .tools import CategoricalContinuousEncoding, ClassPartitionGenerator, CramerCorrelation, DataPartitioner, DecisionTreeBuilder, HeterogeneityReductionCorrelation, ModelPredictor, SplitGenerator, ToolFailure  # noqa: F401
+from .tools import CategoricalClassAffinity, CategoricalContinuousEncoding, ClassPartitionGenerator, CramerCorrelation, DataPartitioner, DecisionTreeBuilder, HeterogeneityReductionCorrelation, ModelPredictor, SplitGenerator, ToolFailure  # noqa: F401
 
-__all__ = ["DecisionTreeBuilder", "ClassPartitionGenerator", "ModelPredictor", "CramerCorrelation", "HeterogeneityReductionCorrelation", "SplitGenerator", "DataPartitioner", "CategoricalContinuousEncoding", "ToolFailure"]
+__all__ = ["DecisionTreeBuilder", "ClassPartitionGenerator", "ModelPredictor", "CramerCorrelation", "HeterogeneityReductionCorrelation", "SplitGenerator", "DataPartitioner", "CategoricalContinuousEncoding", "CategoricalClassAffinity", "ToolFailure"]

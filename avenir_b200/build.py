@@ -15,7 +15,7 @@ LIB = os.path.join(HERE, "libavenir_tree.so")
 CLI = os.path.join(HERE, "avenir-tree")
 
 CUDA_SOURCES = ["avt_engine.cu"]
-HOST_SOURCES = ["host/dtb.cpp", "host/cpg.cpp", "host/mop.cpp", "host/crc.cpp", "host/dap.cpp", "host/cce.cpp", "host/tool.cpp"]
+HOST_SOURCES = ["host/dtb.cpp", "host/cpg.cpp", "host/mop.cpp", "host/crc.cpp", "host/dap.cpp", "host/cce.cpp", "host/cca.cpp", "host/tool.cpp"]
 HEADERS = ["avt_kernels.cuh", "avt_scan.cuh", "avt_scan_fast.cuh", "avt_csv.cuh", "avt_predict.cuh", "avt_bagging.cuh", "avt_forest.cuh", "avt_joint.cuh", "avt_sorted.cuh", "avt_device.cuh", "fdlibm_log.cuh", "host/model.hpp", "host/javaemu.hpp", "host/json.hpp",
            "host/tool.hpp", "../../include/avenir_tree.h"]
 

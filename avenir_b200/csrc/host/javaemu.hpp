@@ -106,6 +106,11 @@ public:
         return put(k, V());
     }
     size_t size() const { return size_; }
+    // HashMap.clear() (JDK 8): every bucket emptied, the table keeps its length (later iteration orders depend on it)
+    void clear() {
+        for (auto& chain : tab_) chain.clear();
+        size_ = 0;
+    }
     template <class F>
     void for_each(F&& f) {
         for (auto& chain : tab_)

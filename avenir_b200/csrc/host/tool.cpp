@@ -61,8 +61,9 @@ extern "C" int avt_tool_run(const char* tool, int argc, const char* const* argv,
         if (ends_with(name, "ModelPredictor")) return run_model_predictor(conf, positional[0], positional[1]);
         if (ends_with(name, "CramerCorrelation")) return run_cramer_correlation(conf, positional[0], positional[1]);
         if (ends_with(name, "HeterogeneityReductionCorrelation")) return run_heterogeneity_reduction_correlation(conf, positional[0], positional[1]);
+        if (ends_with(name, "CategoricalClassAffinity")) return run_categorical_class_affinity(conf, positional[0], positional[1]);
         if (ends_with(name, "CategoricalContinuousEncoding")) return run_categorical_continuous_encoding(conf, positional[0], positional[1]);
-        throw std::runtime_error("unknown tool '" + name + "' (DecisionTreeBuilder | ClassPartitionGenerator | ModelPredictor | SplitGenerator | DataPartitioner | CramerCorrelation | HeterogeneityReductionCorrelation | CategoricalContinuousEncoding)");
+        throw std::runtime_error("unknown tool '" + name + "' (DecisionTreeBuilder | ClassPartitionGenerator | ModelPredictor | SplitGenerator | DataPartitioner | CramerCorrelation | HeterogeneityReductionCorrelation | CategoricalContinuousEncoding | CategoricalClassAffinity)");
     } catch (const ReferenceError& e) {
         set_err(errbuf, errlen, std::string("reference failure reproduced: ") + e.what());
     } catch (const Unsupported& e) {

@@ -24,6 +24,9 @@ int run_heterogeneity_reduction_correlation(const Props& conf, const std::string
 // org.avenir.explore.CategoricalContinuousEncoding.run(args)  (explore/CategoricalContinuousEncoding.java:54-82)
 int run_categorical_continuous_encoding(const Props& conf, const std::string& in_path, const std::string& out_path);
 
+// org.avenir.explore.CategoricalClassAffinity.run(args)  (explore/CategoricalClassAffinity.java:58-89); host code only
+int run_categorical_class_affinity(const Props& conf, const std::string& in_path, const std::string& out_path);
+
 // org.avenir.tree.DataPartitioner.run(args)  (tree/DataPartitioner.java:59-105); takes no path arguments
 int run_data_partitioner(const Props& conf);
 

@@ -62,6 +62,10 @@ class HeterogeneityReductionCorrelation(_Tool):
     java_class = "org.avenir.explore.HeterogeneityReductionCorrelation"
 
 
+class CategoricalClassAffinity(_Tool):
+    java_class = "org.avenir.explore.CategoricalClassAffinity"
+
+
 class CategoricalContinuousEncoding(_Tool):
     java_class = "org.avenir.explore.CategoricalContinuousEncoding"
 

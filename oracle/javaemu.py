@@ -151,6 +151,12 @@ class JavaHashMap:
 
     __setitem__ = put
 
+    def clear(self):
+        """HashMap.clear() (JDK 8): every bucket emptied, the table keeps its length."""
+        if self._tab is not None:
+            self._tab = [None] * self._cap
+        self._size = 0
+
     def __len__(self):
         return self._size
 

@@ -51,7 +51,7 @@ def hostmock_lib() -> C.CDLL:
     if _mock is None:
         os.makedirs(BUILD, exist_ok=True)
         so = os.path.join(BUILD, "libavt_hostmock.so")
-        host = [os.path.join(ROOT, "avenir_b200", "csrc", "host", f) for f in ("dtb.cpp", "cpg.cpp", "mop.cpp", "crc.cpp", "dap.cpp", "cce.cpp", "tool.cpp")]
+        host = [os.path.join(ROOT, "avenir_b200", "csrc", "host", f) for f in ("dtb.cpp", "cpg.cpp", "mop.cpp", "crc.cpp", "dap.cpp", "cce.cpp", "cca.cpp", "tool.cpp")]
         hdrs = [os.path.join(ROOT, "avenir_b200", "csrc", "host", f) for f in ("model.hpp", "javaemu.hpp", "json.hpp", "tool.hpp")]
         mock = os.path.join(ROOT, "tests", "mock", "mock_backend.cpp")
         ora = os.path.join(ROOT, "oracle", "hist_oracle.c")
