@@ -101,6 +101,31 @@ def test_histogram_sorted_rows_variant(n, nodes, weights):
     g.close()
 
 
+def test_pair_class_joint_counts_by_using_one_attributes_bins_as_nodes():
+    """The sufficient statistic of the pair-wise count consumers of explore/ (MutualInformation's feature-pair and
+    feature-pair-class distributions, explore/MutualInformation.java:181-214) from the existing entry points: repartition
+    the root by attribute i with the identity table (node = bin of i), then one level histogram is the joint count
+    (bin of i, bin of j, class) of i with EVERY other attribute j."""
+    n = 120_000
+    n_bins = [7, 300, 12, 5, 33]          # one uint16 column among them
+    cols, cls = synth.binned_dataset(n, n_bins, 3, seed=17, signal_attrs=3)
+    g = Engine(0)
+    g.load_dataset(cols, cls, n_bins, 3)
+    off = np.concatenate([[0], np.cumsum(n_bins)])
+    for i in (0, 2, 4):
+        g.forest_init(1)
+        g.histogram([1])                                    # the root frontier (the repartition applies to the last counted one)
+        lut = np.full((1, max(n_bins)), AVT_NODE_NONE, dtype=np.uint16)
+        lut[0, :n_bins[i]] = np.arange(n_bins[i])
+        g.repartition([i], lut)
+        h = g.histogram([n_bins[i]], fetch=True)            # [n_bins[i]][total bins][3]
+        for j in range(len(n_bins)):
+            want = np.zeros((n_bins[i], n_bins[j], 3), dtype=np.uint32)
+            np.add.at(want, (cols[i].astype(np.int64), cols[j].astype(np.int64), cls.astype(np.int64)), 1)
+            assert np.array_equal(h[:, off[j]:off[j + 1], :], want), (i, j)
+    g.close()
+
+
 def test_histogram_many_nodes_uses_fewer_replicas_then_global():
     n = 200000
     rng = np.random.default_rng(5)
