@@ -79,6 +79,7 @@ int run_categorical_continuous_encoding(const Props& conf, const std::string& in
     std::vector<int> attrs = ordinals;
     std::sort(attrs.begin(), attrs.end());
     attrs.erase(std::unique(attrs.begin(), attrs.end()), attrs.end());
+    if (attrs.empty()) throw ReferenceError("IllegalStateException: missing categorical attribute ordinals");
     for (int o : attrs)
         if (o < 0 || o >= 1024 || o == class_ord) throw Unsupported("attribute ordinal " + std::to_string(o) + ": outside 0..1023 or equal to the class ordinal");
     if (class_ord < 0 || class_ord >= 1024) throw Unsupported("class ordinal outside 0..1023");
@@ -139,17 +140,10 @@ int run_categorical_continuous_encoding(const Props& conf, const std::string& in
         eng.check(avt_level_fetch_hist(eng.raw(), 0, H.data()));
         const auto pc = classes.index.find(pos_value);
         const int pos_code = pc == classes.index.end() ? -1 : pc->second;
-        // totals over all rows: the (-1, "*") key of the weight-of-evidence form
+        // totals over all rows: the (-1, "*") key of the weight-of-evidence form (every row has exactly one value of the first attribute)
         long long all_pos = 0, all_neg = 0;
-        for (int b = 0; b < (attrs.empty() ? 0 : (int)values[0].names.size()); ++b)
+        for (int b = 0; b < (int)values[0].names.size(); ++b)
             for (int c = 0; c < C; ++c) (c == pos_code ? all_pos : all_neg) += H[(size_t)b * C + c];
-        if (attrs.empty()) {
-            for (auto& ln : lines) {
-                size_t b, e;
-                field_at(ln, d, class_ord, b, e);
-                (ln.compare(b, e - b, pos_value) == 0 ? all_pos : all_neg) += 1;
-            }
-        }
         for (size_t a = 0; a < attrs.size(); ++a) {
             std::vector<int> idx(values[a].names.size());
             for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
