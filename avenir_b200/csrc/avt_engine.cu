@@ -1704,7 +1704,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             e->d_lut.cap < (size_t)NF * lut_w || (!peer_level && (e->d_H.cap < (size_t)NF * e->TB * e->C || e->d_H2.cap < (size_t)NF * e->TB * e->C)) ||
             (peer_level && (e->d_hsum.cap < (size_t)NF * e->TB * e->C || e->d_hsum2.cap < (size_t)NF * e->TB * e->C)) ||
             (subtract && (e->d_skip.cap < (size_t)NF * g_max || e->d_drv_parent.cap < (size_t)NF * g_max || e->d_kids.cap < (size_t)NF * kMaxSeg)) || (want_records && e->d_records.cap < rec_off + (size_t)NF) ||
-            (fast_scan && e->d_nkids.cap < (size_t)NF)) {
+            e->d_nkids.cap < (size_t)NF + 1) {
             if (int rc = sync_and_resolve(e)) return rc;
             // flush records gathered so far: the record buffer may move
             if (want_records && rec_off) {
@@ -1731,7 +1731,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
             CUDA_TRY(e, e->d_best_eval.ensure(grow));
             CUDA_TRY(e, e->d_node_attr.ensure(grow));
             CUDA_TRY(e, e->d_lut.ensure(grow * lut_w));
-            if (fast_scan) CUDA_TRY(e, e->d_nkids.ensure(grow));
+            CUDA_TRY(e, e->d_nkids.ensure(grow + 1));   // child counts of the look-back scan / prefix scratch of plan_level
             // (a reallocation here drops the previous level's complete counts: no derivation on this level)
             const bool had_prev = level > 0;
             if (!peer_level) {
@@ -1828,6 +1828,7 @@ static int grow_device_loop(avt_engine* e, int32_t n_levels, int32_t criterion, 
         pa.node_attr = e->d_node_attr.p;
         pa.child_lut = e->d_lut.p;
         pa.next_count = e->d_next_count.p;
+        pa.prefix = e->d_nkids.p;
         pa.records = want_records ? e->d_records.p + rec_off : nullptr;
         pa.err = d_err_p;
         pa.next_node_base = nb_level(level + 1);

@@ -15,6 +15,7 @@ struct PlanArgs {
     int32_t* node_attr;        // [NF]
     uint16_t* child_lut;       // [NF][lut_w]
     int32_t* next_count;       // [T]
+    int32_t* prefix;           // [NF + 1] scratch of plan_level: exclusive prefix sum of the nodes' child counts
     avt_grow_record* records;  // [NF] (nullable)
     int32_t* err;              // set to 1 when a tree would exceed the node-id range
     int32_t* next_node_base;   // [T+1] (nullable)
@@ -112,23 +113,26 @@ __global__ void inherit_masks_kernel(const int32_t* nb_cur, const int32_t* nb_ne
     }
 }
 
-// Plans one tree with the whole block (blockDim.x = kScanThreads).
-__device__ void plan_tree(const PlanArgs& p, const SplitTable& st, int t, int next_base, int* warp_tot, int* running) {
-    const int nb = p.node_base[t], n = p.node_base[t + 1] - nb;
+// Whole-level planning by one block (blockDim.x = kScanThreads), flat over the nodes of ALL trees: a forest level of 100
+// trees x a few nodes used to be planned tree by tree, five block barriers each -- 0.6 ms of fixed cost per level of C3, the
+// part of the step that does not shrink with more GPUs.  Children are numbered per tree, so with E = exclusive prefix sum of
+// the child counts over all nodes (tree-major order), a node's first child is E[g] - E[first node of its tree], the next
+// frontier's base of tree t is E[first node of t], and its node count the difference of two such values.
+//   pass 1: child counts -> E (block scan, 256 nodes per round, carried in shared memory), kept in p.prefix[NF + 1]
+//   pass 2: one thread per node writes its tables, record and skip marks
+//   then next_count / next_node_base from E, then (optionally) the zeroing of the next level's histogram region.
+__device__ void plan_level(const PlanArgs& p, const SplitTable& st, int* warp_tot, int* running) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int NF = p.node_base[p.n_trees];
     if (threadIdx.x == 0) *running = 0;
     __syncthreads();
-    for (int i0 = 0; i0 < n; i0 += blockDim.x) {
-        const int i = i0 + threadIdx.x;
-        const int g = nb + i;
-        int nkids = 0, best_split = -1;
-        bool live = false;
-        avt_split sp{};
-        if (i < n) {
-            best_split = ldcg_i32(&p.best[g].best_split);
-            live = ldcg_i64(&p.best[g].population) > 0 && best_split >= 0;
-            if (live) {
-                sp = st.splits[best_split];
+    for (int g0 = 0; g0 < NF; g0 += blockDim.x) {
+        const int g = g0 + threadIdx.x;
+        int nkids = 0;
+        if (g < NF) {
+            const int best_split = ldcg_i32(&p.best[g].best_split);
+            if (ldcg_i64(&p.best[g].population) > 0 && best_split >= 0) {
+                const avt_split sp = st.splits[best_split];
                 for (int sg = 0; sg < sp.n_seg; ++sg) {
                     uint32_t pop = 0;
                     for (int c = 0; c < st.C; ++c) pop += ldcg_u32(&p.best_eval[g].seg_count[sg][c]);
@@ -136,7 +140,7 @@ __device__ void plan_tree(const PlanArgs& p, const SplitTable& st, int t, int ne
                 }
             }
         }
-        int v = nkids;  // block exclusive scan of nkids
+        int v = nkids;  // block inclusive scan of nkids
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             int u = __shfl_up_sync(0xffffffffu, v, d);
@@ -149,82 +153,81 @@ __device__ void plan_tree(const PlanArgs& p, const SplitTable& st, int t, int ne
             if (w < warp) woff += warp_tot[w];
             tot += warp_tot[w];
         }
-        const int first = *running + woff + v - nkids;
-        if (i < n) {
-            p.node_attr[g] = live ? sp.attr : -1;
-            uint16_t* lut = p.child_lut + (long long)g * p.lut_w;
-            for (int b = 0; b < p.lut_w; ++b) lut[b] = (uint16_t)AVT_NODE_NONE;
-            avt_grow_record rec;
-            rec.level = p.level; rec.tree = t; rec.node = i;
-            rec.split = live ? best_split : -1;
-            rec.n_ties = ldcg_i32(&p.best[g].n_ties);
-            rec.min_av = ldcg_f64(&p.best[g].min_av);
-            for (int sg = 0; sg < kMaxSeg; ++sg) { rec.child[sg] = -1; rec.child_pop[sg] = 0; rec.child_stat[sg] = 0.0; }
-            if (live) {
-                int k = 0;
-                for (int sg = 0; sg < sp.n_seg; ++sg) {
-                    long long pop = 0;
-                    for (int c = 0; c < st.C; ++c) pop += ldcg_u32(&p.best_eval[g].seg_count[sg][c]);
-                    rec.child_pop[sg] = pop;
-                    rec.child_stat[sg] = ldcg_f64(&p.best_eval[g].seg_stat[sg]);
-                    if (pop) rec.child[sg] = first + k++;
-                }
-                if (first + k > (int)AVT_NODE_NONE - 1) *p.err = 1;
-                const int B = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
-                for (int b = 0; b < B; ++b) {
-                    int sg;
-                    if (sp.kind == AVT_SPLIT_NUMERIC) {
-                        sg = 0;
-                        while (sg < sp.n_seg - 1 && b > st.bounds[sp.off + sg]) ++sg;
-                    } else {
-                        sg = st.seg_lut[sp.off + b];
-                        if (sg >= sp.n_seg) continue;
-                    }
-                    if (rec.child[sg] >= 0) lut[b] = (uint16_t)rec.child[sg];
-                }
-            }
-            if (p.kids) {
-                int32_t* kd = p.kids + (long long)g * kMaxSeg;
-                int derived = -1;
-                if (live && p.next_skip) {   // the most populous child (lowest segment on ties) is derived, not counted
-                    long long mx = -1;
-                    for (int sg = 0; sg < sp.n_seg; ++sg)
-                        if (rec.child[sg] >= 0 && rec.child_pop[sg] > mx) { mx = rec.child_pop[sg]; derived = sg; }
-                }
-                for (int sg = 0; sg < kMaxSeg; ++sg) {
-                    const int gi = rec.child[sg] >= 0 ? next_base + rec.child[sg] : -1;
-                    kd[sg] = gi;
-                    if (gi >= 0 && p.next_skip) {
-                        p.next_skip[gi] = sg == derived;
-                        p.next_parent[gi] = sg == derived ? g : -1;
-                    }
-                }
-            }
-            if (p.records) p.records[g] = rec;
-        }
+        if (g < NF) p.prefix[g] = *running + woff + v - nkids;
         __syncthreads();
         if (threadIdx.x == 0) *running += tot;
         __syncthreads();
     }
-    if (threadIdx.x == 0) p.next_count[t] = *running;
-    __syncthreads();
-}
-
-// Whole-level planning by one block: every tree, then the next frontier's node_base, then (optionally)
-// the zeroing of the next level's histogram region.
-__device__ void plan_level(const PlanArgs& p, const SplitTable& st, int* warp_tot, int* running) {
-    int next_base = 0;
-    for (int t = 0; t < p.n_trees; ++t) {
-        plan_tree(p, st, t, next_base, warp_tot, running);   // ends with a block barrier after next_count[t] is written
-        next_base += p.next_count[t];
-    }
-    if (threadIdx.x == 0 && p.next_node_base) {
-        int acc = 0;
-        for (int k = 0; k < p.n_trees; ++k) {
-            p.next_node_base[k] = acc;
-            acc += p.next_count[k];
+    if (threadIdx.x == 0) p.prefix[NF] = *running;
+    __syncthreads();   // (one block: its global writes are visible to its own threads behind the barrier)
+    for (int g = threadIdx.x; g < NF; g += blockDim.x) {
+        int lo = 0, hi = p.n_trees;   // last tree whose first node is <= g (empty trees share their successor's base and are skipped)
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (p.node_base[mid] <= g) lo = mid;
+            else hi = mid;
         }
-        p.next_node_base[p.n_trees] = acc;
+        const int t = lo, nb = p.node_base[t], i = g - nb;
+        const int next_base = p.prefix[nb], first = p.prefix[g] - next_base;
+        const int best_split = ldcg_i32(&p.best[g].best_split);
+        const bool live = ldcg_i64(&p.best[g].population) > 0 && best_split >= 0;
+        avt_split sp{};
+        if (live) sp = st.splits[best_split];
+        p.node_attr[g] = live ? sp.attr : -1;
+        uint16_t* lut = p.child_lut + (long long)g * p.lut_w;
+        for (int b = 0; b < p.lut_w; ++b) lut[b] = (uint16_t)AVT_NODE_NONE;
+        avt_grow_record rec;
+        rec.level = p.level; rec.tree = t; rec.node = i;
+        rec.split = live ? best_split : -1;
+        rec.n_ties = ldcg_i32(&p.best[g].n_ties);
+        rec.min_av = ldcg_f64(&p.best[g].min_av);
+        for (int sg = 0; sg < kMaxSeg; ++sg) { rec.child[sg] = -1; rec.child_pop[sg] = 0; rec.child_stat[sg] = 0.0; }
+        if (live) {
+            int k = 0;
+            for (int sg = 0; sg < sp.n_seg; ++sg) {
+                long long pop = 0;
+                for (int c = 0; c < st.C; ++c) pop += ldcg_u32(&p.best_eval[g].seg_count[sg][c]);
+                rec.child_pop[sg] = pop;
+                rec.child_stat[sg] = ldcg_f64(&p.best_eval[g].seg_stat[sg]);
+                if (pop) rec.child[sg] = first + k++;
+            }
+            if (first + k > (int)AVT_NODE_NONE - 1) *p.err = 1;
+            const int B = st.bin_off[sp.attr + 1] - st.bin_off[sp.attr];
+            for (int b = 0; b < B; ++b) {
+                int sg;
+                if (sp.kind == AVT_SPLIT_NUMERIC) {
+                    sg = 0;
+                    while (sg < sp.n_seg - 1 && b > st.bounds[sp.off + sg]) ++sg;
+                } else {
+                    sg = st.seg_lut[sp.off + b];
+                    if (sg >= sp.n_seg) continue;
+                }
+                if (rec.child[sg] >= 0) lut[b] = (uint16_t)rec.child[sg];
+            }
+        }
+        if (p.kids) {
+            int32_t* kd = p.kids + (long long)g * kMaxSeg;
+            int derived = -1;
+            if (live && p.next_skip) {   // the most populous child (lowest segment on ties) is derived, not counted
+                long long mx = -1;
+                for (int sg = 0; sg < sp.n_seg; ++sg)
+                    if (rec.child[sg] >= 0 && rec.child_pop[sg] > mx) { mx = rec.child_pop[sg]; derived = sg; }
+            }
+            for (int sg = 0; sg < kMaxSeg; ++sg) {
+                const int gi = rec.child[sg] >= 0 ? next_base + rec.child[sg] : -1;
+                kd[sg] = gi;
+                if (gi >= 0 && p.next_skip) {
+                    p.next_skip[gi] = sg == derived;
+                    p.next_parent[gi] = sg == derived ? g : -1;
+                }
+            }
+        }
+        if (p.records) p.records[g] = rec;
+    }
+    for (int t = threadIdx.x; t <= p.n_trees; t += blockDim.x) {
+        const int e0 = p.prefix[p.node_base[t]];
+        if (t < p.n_trees) p.next_count[t] = p.prefix[p.node_base[t + 1]] - e0;
+        if (p.next_node_base) p.next_node_base[t] = e0;
     }
     if (p.zero_ptr)
         for (long long i = threadIdx.x; i < p.zero_words; i += blockDim.x) p.zero_ptr[i] = 0;
